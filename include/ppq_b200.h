@@ -1,0 +1,136 @@
+/*
+ * ppq_b200.h -- C ABI of libppq_b200.so: the B200-native (sm_100a) replacement for the OpenFHE calls on the
+ * encrypted-aggregation hot path of CDACHPCIE25/PPQSFLHE.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to /root/reference).  The
+ * reference reaches all of them through OpenFHE's CryptoContext<DCRTPoly> (third-party, not vendored); the
+ * binding a maintainer would add on the reference side is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain C: opaque handles, pointers and sizes only; no C++/torch types.
+ *   - every function returns 0 on success, a negative PPQ_E* code on failure; ppq_last_error() returns a
+ *     thread-local message.  There is NO CPU fallback: without a usable sm_100a device every compute entry
+ *     point fails with PPQ_ECUDA.
+ *   - pointers named d_* are DEVICE pointers (cudaMalloc / torch CUDA storage); h_* are HOST pointers.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are asynchronous on
+ *     that stream; a context owns scratch memory, so use one stream at a time per context.
+ *   - residues are uint64 little-endian, canonical in [0, q_i); polynomials are limb-major ([limb][N]) in
+ *     EVALUATION format in OpenFHE's bit-reversed order unless stated otherwise, which is exactly the payload
+ *     of a serialized OpenFHE DCRTPoly.
+ *   - a ciphertext is [2][ell][N] (c0 limbs then c1 limbs); a batch is [n][2][ell][N].
+ *   - limb indices are "global": 0..L-1 = Q limbs, L..L+K-1 = auxiliary P limbs.
+ */
+#ifndef PPQ_B200_H
+#define PPQ_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PPQ_OK 0
+#define PPQ_EINVAL (-1)  /* bad argument */
+#define PPQ_ECUDA (-2)   /* CUDA error or no sm_100a device */
+#define PPQ_ENOMEM (-3)
+#define PPQ_EPARSE (-4)  /* CC.json could not be understood */
+
+typedef struct ppq_ctx ppq_ctx;
+typedef struct ppq_rekey ppq_rekey;
+
+const char* ppq_last_error(void);
+const char* ppq_version(void);
+
+/* ---- context: replaces Serial::DeserializeFromFile(cc_path, cc, SerType::JSON)
+ *      (server/src/changeCipherDomain.cpp:32-36, aggregateEncryptedWeights.cpp:46-50,
+ *       client/src/encryptModelWeights.cpp:32-36, decryptModelWeights.cpp:41-46) and the parameter side of
+ *      GenCryptoContext (server/src/genCC.cpp:46-79). */
+int ppq_ctx_create_from_ccjson(const char* json, size_t len, int device, ppq_ctx** out);
+/* explicit Q chain (q_0..q_{L-1}); P primes, roots and tables are derived by OpenFHE's HYBRID rules */
+int ppq_ctx_create(int logN, int L, const uint64_t* q_moduli, int dnum, int aux_bits, int extra_bits, int device,
+                   ppq_ctx** out);
+/* FLEXIBLEAUTOEXT chain for multiplicative depth `depth` (genCC.cpp:46-66 with a forced ring dimension) */
+int ppq_ctx_create_synthetic(int logN, int depth, int first_bits, int scale_bits, int extra_bits, int dnum,
+                             int device, ppq_ctx** out);
+void ppq_ctx_destroy(ppq_ctx*);
+
+typedef struct {
+    int32_t logN, L, K, dnum, alpha, device;
+} ppq_ctx_info_t;
+int ppq_ctx_info(const ppq_ctx*, ppq_ctx_info_t* info);
+int ppq_ctx_moduli(const ppq_ctx*, uint64_t* h_out /* L+K */);
+int ppq_ctx_roots(const ppq_ctx*, uint64_t* h_out /* L+K */);
+double ppq_ctx_scaling_factor(const ppq_ctx*, int level);     /* m_scalingFactorsReal[level]    */
+double ppq_ctx_scaling_factor_big(const ppq_ctx*, int level); /* m_scalingFactorsRealBig[level] */
+int ppq_ctx_num_parts(const ppq_ctx*, int ell);
+int ppq_sync(const ppq_ctx*, void* stream);
+/* ciphertexts of one internal wave (scratch is sized for it); 0 = automatic */
+int ppq_ctx_set_wave(ppq_ctx*, int n_ct);
+
+/* ---- RNS polynomial layer: replaces DCRTPoly::SetFormat(EVALUATION / COEFFICIENT), i.e. OpenFHE's
+ *      ChineseRemainderTransformFTT::ForwardTransformToBitReverseInPlace / InverseTransformFromBitReverseInPlace
+ *      (reached from every call below).  d_data: [n_polys][N] in place; h_limb_ids: global limb per poly. */
+int ppq_ntt_forward(ppq_ctx*, uint64_t* d_data, const int32_t* h_limb_ids, size_t n_polys, void* stream);
+int ppq_ntt_inverse(ppq_ctx*, uint64_t* d_data, const int32_t* h_limb_ids, size_t n_polys, void* stream);
+
+/* ---- re-encryption key: replaces Serial::DeserializeFromFile(rekey_path, reKey, SerType::JSON)
+ *      (server/src/changeCipherDomain.cpp:40-44).  b, a: [dnum][L+K][N] EVAL (EvalKey B-vector / A-vector). */
+int ppq_rekey_upload(ppq_ctx*, const uint64_t* h_b, const uint64_t* h_a, ppq_rekey** out);
+int ppq_rekey_from_device(ppq_ctx*, const uint64_t* d_b, const uint64_t* d_a, ppq_rekey** out); /* borrows */
+void ppq_rekey_destroy(ppq_rekey*);
+
+/* ---- cc->ReEncrypt(ct, reKey) with publicKey == nullptr (server/src/changeCipherDomain.cpp:74,89,105):
+ *      d_out[g] = ReEncrypt(d_in[g]) for g < n.  d_out may not alias d_in. */
+int ppq_reencrypt(ppq_ctx*, const ppq_rekey*, int ell, const uint64_t* d_in, uint64_t* d_out, size_t n,
+                  void* stream);
+/* fused cc->ReEncrypt + cc->EvalAdd (changeCipherDomain.cpp:105 followed by
+ * aggregateEncryptedWeights.cpp:106): d_acc[g] = d_acc[g] + ReEncrypt(d_in[g]) mod q, canonical. */
+int ppq_reencrypt_accumulate(ppq_ctx*, const ppq_rekey*, int ell, const uint64_t* d_in, uint64_t* d_acc, size_t n,
+                             void* stream);
+/* stage-by-stage views of the key switch (EvalKeySwitchPrecomputeCore / EvalFastKeySwitchCoreExt /
+ * ApproxModDown) for parity tests: digits [n][parts][ell+K][N] EVAL canonical, ext [n][2][ell+K][N]. */
+int ppq_ks_modup(ppq_ctx*, int ell, const uint64_t* d_c1 /* [n][ell][N] */, uint64_t* d_digits, size_t n,
+                 void* stream);
+
+/* ---- cc->EvalAdd(ct1, ct2) (server/src/aggregateEncryptedWeights.cpp:82,91,106) */
+int ppq_eval_add(ppq_ctx*, int ell, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, size_t n,
+                 void* stream);
+/* canonicalise lazily summed residues (after a cross-GPU uint64 sum of canonical partial sums) */
+int ppq_finalize_sum(ppq_ctx*, int ell, uint64_t* d_x, size_t n, void* stream);
+
+/* ---- cc->EvalMult(ct, c) (server/src/aggregateEncryptedWeights.cpp:83,92,107) under FLEXIBLEAUTOEXT.
+ *      rescale != 0 (noiseScaleDeg == 2): DropLastElementAndScale then multiply by the integer image of c at
+ *      scaling factor sf: d_in [n][2][ell][N] -> d_out [n][2][ell-1][N].
+ *      rescale == 0: multiply only, d_out [n][2][ell][N].  sf is the scaling factor of the level AFTER the
+ *      optional rescale (ppq_ctx_scaling_factor). */
+int ppq_eval_mult_const(ppq_ctx*, int ell, const uint64_t* d_in, uint64_t* d_out, size_t n, double c, double sf,
+                        int rescale, void* stream);
+
+/* ---- cc->MakeCKKSPackedPlaintext(values) (client/src/encryptModelWeights.cpp:82,90,109):
+ *      h/d_vals [n][n_vals] doubles (zero-padded to N/2 slots) -> d_pt [n][ell][N] EVAL, scale sf. */
+int ppq_encode(ppq_ctx*, int ell, const double* d_vals, size_t n_vals, double sf, uint64_t* d_pt, size_t n,
+               void* stream);
+/* ---- cc->Encrypt(publicKey, pt) (client/src/encryptModelWeights.cpp:83,91,110) with the sampled
+ *      polynomials supplied by the caller: d_small [n][3][N] int64 = (v, e0, e1) coefficients.
+ *      d_pkb / d_pka: [>=ell][N] EVAL (first ell limbs of the QP public key). */
+int ppq_encrypt(ppq_ctx*, int ell, const uint64_t* d_pkb, const uint64_t* d_pka, const uint64_t* d_pt,
+                const int64_t* d_small, uint64_t* d_ct, size_t n, void* stream);
+/* fills d_small [n][3][N] with (ternary, gauss, gauss) samples (counter-based generator, sigma = 3.19) */
+int ppq_sample_encrypt_noise(ppq_ctx*, uint64_t seed, int64_t* d_small, size_t n, void* stream);
+/* ---- cc->Decrypt(privateKey, ct, &pt) core (client/src/decryptModelWeights.cpp:81,90,108):
+ *      d_coeff [n][ell][N] = COEFF residues of c0 + c1*s.  d_sk: [>=ell][N] EVAL. */
+int ppq_decrypt_core(ppq_ctx*, int ell, const uint64_t* d_sk, const uint64_t* d_ct, uint64_t* d_coeff, size_t n,
+                     void* stream);
+/* ---- pt->GetRealPackedValue() (client/src/decryptModelWeights.cpp:83,92,109): CRT-compose, centre, divide
+ *      by sf, special FFT; d_vals [n][N/2].  OpenFHE's randomised decode noise is not added. */
+int ppq_decode(ppq_ctx*, int ell, const uint64_t* d_coeff, double sf, double* d_vals, size_t n, void* stream);
+
+/* ---- host-buffer convenience (the call a drop-in server makes): copies in, computes, copies out.
+ *      h_cts [n_clients][n_slots][2][ell][N]; rekeys[n_clients]; h_acc [n_slots][2][ell][N] =
+ *      sum over clients of ReEncrypt(ct, rekey[client]).  Synchronous. */
+int ppq_reencrypt_aggregate_host(ppq_ctx*, const ppq_rekey* const* rekeys, int ell, const uint64_t* h_cts,
+                                 size_t n_clients, size_t n_slots, uint64_t* h_acc);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

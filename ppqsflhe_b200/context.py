@@ -1,0 +1,297 @@
+"""Host-side mirror of the OpenFHE CryptoContext<DCRTPoly> surface that PPQSFLHE uses on its hot path, over the
+C ABI of libppq_b200.so.  Names, argument meaning and error behaviour follow the reference's call sites:
+
+    cc->ReEncrypt(ct, reKey)            server/src/changeCipherDomain.cpp:74,89,105
+    cc->EvalAdd(ct1, ct2)               server/src/aggregateEncryptedWeights.cpp:82,91,106
+    cc->EvalMult(ct, 0.5)               server/src/aggregateEncryptedWeights.cpp:83,92,107
+    cc->MakeCKKSPackedPlaintext(vals)   client/src/encryptModelWeights.cpp:82,90,109
+    cc->Encrypt(pk, pt)                 client/src/encryptModelWeights.cpp:83,91,110
+    cc->Decrypt(sk, ct, &pt)            client/src/decryptModelWeights.cpp:81,90,108
+    pt->SetLength / GetRealPackedValue  client/src/decryptModelWeights.cpp:82-83,91-92,109
+
+Every object here is a BATCH (the reference loops over ciphertexts one at a time; the B200 path processes all of
+them per launch).  torch is used only for device memory and streams.  No CPU fallback: constructing a context
+without a CUDA device raises.
+"""
+import ctypes as C
+from dataclasses import dataclass, replace
+
+import numpy as np
+import torch
+
+from . import _capi
+from ._capi import check, lib, vp
+
+
+def _ptr(t):
+    return vp(t.data_ptr())
+
+
+def _stream():
+    return vp(torch.cuda.current_stream().cuda_stream)
+
+
+def to_device_u64(a, device):
+    """numpy uint64 array -> torch int64 CUDA tensor with the same bits."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    return torch.from_numpy(a.view(np.int64)).to(device)
+
+
+def to_host_u64(t):
+    return t.detach().cpu().numpy().view(np.uint64)
+
+
+@dataclass
+class CtMeta:
+    """The scalar fields of an OpenFHE CiphertextImpl (d, l, h, e, s, sl)."""
+    noise_scale_deg: int = 2
+    level: int = 0
+    hops_level: int = 0
+    scaling_factor: float = 1.0
+    slots: int = 0
+
+
+class CiphertextBatch:
+    """n ciphertexts of ell limbs: data is a CUDA int64 tensor [n][2][ell][N] (uint64 bit patterns)."""
+
+    def __init__(self, data, meta):
+        assert data.dim() == 4 and data.shape[1] == 2 and data.dtype == torch.int64 and data.is_cuda
+        self.data = data.contiguous()
+        self.meta = meta
+
+    @property
+    def n(self):
+        return self.data.shape[0]
+
+    @property
+    def ell(self):
+        return self.data.shape[2]
+
+    def numpy(self):
+        return to_host_u64(self.data)
+
+
+class PlaintextBatch:
+    """CKKS packed plaintexts, either encoded (EVAL residues) or decoded (real values)."""
+
+    def __init__(self, data=None, meta=None, values=None):
+        self.data = data      # CUDA int64 [n][ell][N] or None
+        self.meta = meta
+        self.values = values  # CUDA float64 [n][N/2] or None
+        self.length = None
+
+    def SetLength(self, n):
+        self.length = int(n)
+
+    def GetRealPackedValue(self):
+        v = self.values.detach().cpu().numpy()
+        return v if self.length is None else v[:, : self.length]
+
+
+class EvalKey:
+    """Re-encryption key (EvalKeyRelin B/A vectors, [dnum][L+K][N] EVAL) resident on the device."""
+
+    def __init__(self, cc, b, a):
+        self.cc = cc
+        self.b = to_device_u64(b, cc.device) if isinstance(b, np.ndarray) else b
+        self.a = to_device_u64(a, cc.device) if isinstance(a, np.ndarray) else a
+        exp = (cc.dnum, cc.L + cc.K, cc.N)
+        if tuple(self.b.shape) != exp or tuple(self.a.shape) != exp:
+            raise ValueError(f"rekey must have shape {exp}")
+        h = vp()
+        check(lib().ppq_rekey_from_device(cc.h, _ptr(self.b), _ptr(self.a), C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().ppq_rekey_destroy(self.h)
+            self.h = None
+
+
+class CryptoContext:
+    def __init__(self, handle, device):
+        self.h = handle
+        self.device = torch.device("cuda", device)
+        info = _capi.CtxInfo()
+        check(lib().ppq_ctx_info(self.h, C.byref(info)))
+        self.logN, self.L, self.K, self.dnum, self.alpha = info.logN, info.L, info.K, info.dnum, info.alpha
+        self.N = 1 << self.logN
+        self.M = self.L + self.K
+        m = np.zeros(self.M, dtype=np.uint64)
+        check(lib().ppq_ctx_moduli(self.h, m.ctypes.data_as(_capi.u64p)))
+        self.moduli = m
+        r = np.zeros(self.M, dtype=np.uint64)
+        check(lib().ppq_ctx_roots(self.h, r.ctypes.data_as(_capi.u64p)))
+        self.roots = r
+
+    # ---- construction (Serial::DeserializeFromFile(cc_path, cc, SerType::JSON))
+    @classmethod
+    def from_ccjson(cls, text, device=0):
+        raw = text.encode() if isinstance(text, str) else text
+        h = vp()
+        check(lib().ppq_ctx_create_from_ccjson(raw, len(raw), device, C.byref(h)))
+        return cls(h, device)
+
+    @classmethod
+    def from_moduli(cls, logN, q_moduli, dnum, aux_bits=60, extra_bits=20, device=0):
+        q = np.ascontiguousarray(q_moduli, dtype=np.uint64)
+        h = vp()
+        check(lib().ppq_ctx_create(logN, len(q), q.ctypes.data_as(_capi.u64p), dnum, aux_bits, extra_bits, device,
+                                   C.byref(h)))
+        return cls(h, device)
+
+    @classmethod
+    def synthetic(cls, logN, depth, first_bits=60, scale_bits=59, extra_bits=20, dnum=3, device=0):
+        h = vp()
+        check(lib().ppq_ctx_create_synthetic(logN, depth, first_bits, scale_bits, extra_bits, dnum, device, C.byref(h)))
+        return cls(h, device)
+
+    def close(self):
+        if self.h:
+            lib().ppq_ctx_destroy(self.h)
+            self.h = None
+
+    def sf(self, level):
+        return lib().ppq_ctx_scaling_factor(self.h, level)
+
+    def sf_big(self, level):
+        return lib().ppq_ctx_scaling_factor_big(self.h, level)
+
+    def num_parts(self, ell):
+        return lib().ppq_ctx_num_parts(self.h, ell)
+
+    def GetBatchSize(self):
+        return self.N // 2
+
+    def set_wave(self, n):
+        check(lib().ppq_ctx_set_wave(self.h, int(n)))
+
+    def sync(self):
+        check(lib().ppq_sync(self.h, _stream()))
+
+    def empty_cts(self, n, ell):
+        return torch.empty((n, 2, ell, self.N), dtype=torch.int64, device=self.device)
+
+    # ---- RNS polynomial layer
+    def ntt(self, data, limb_ids, inverse=False):
+        """data: CUDA int64 [n_polys][N], in place."""
+        ids = np.ascontiguousarray(limb_ids, dtype=np.int32)
+        assert data.is_cuda and data.is_contiguous() and data.numel() == len(ids) * self.N
+        fn = lib().ppq_ntt_inverse if inverse else lib().ppq_ntt_forward
+        for s in range(0, len(ids), 32768):
+            chunk = ids[s:s + 32768]
+            check(fn(self.h, vp(data.data_ptr() + 8 * s * self.N), chunk.ctypes.data_as(_capi.i32p), len(chunk),
+                     _stream()))
+        return data
+
+    # ---- server side
+    def ReEncrypt(self, ct, rekey, out=None):
+        if out is None:
+            out = torch.empty_like(ct.data)
+        check(lib().ppq_reencrypt(self.h, rekey.h, ct.ell, _ptr(ct.data), _ptr(out), ct.n, _stream()))
+        return CiphertextBatch(out, replace(ct.meta))
+
+    def ReEncryptAccumulate(self, ct, rekey, acc):
+        """acc += ReEncrypt(ct) (fused ReEncrypt + EvalAdd); acc: CiphertextBatch of the same shape."""
+        check(lib().ppq_reencrypt_accumulate(self.h, rekey.h, ct.ell, _ptr(ct.data), _ptr(acc.data), ct.n, _stream()))
+        return acc
+
+    def KeySwitchModUp(self, c1):
+        """EvalKeySwitchPrecomputeCore: c1 [n][ell][N] -> digits [n][parts][ell+K][N] (for parity tests)."""
+        n, ell = c1.shape[0], c1.shape[1]
+        out = torch.zeros((n, self.num_parts(ell), ell + self.K, self.N), dtype=torch.int64, device=self.device)
+        check(lib().ppq_ks_modup(self.h, ell, _ptr(c1), _ptr(out), n, _stream()))
+        return out
+
+    def EvalAdd(self, a, b):
+        if a.ell != b.ell or a.n != b.n:
+            raise ValueError("EvalAdd: ciphertext batches differ in shape")
+        if (a.meta.level, a.meta.noise_scale_deg) != (b.meta.level, b.meta.noise_scale_deg):
+            raise ValueError("EvalAdd: operands at different level / noise scale degree (no automatic adjustment)")
+        out = torch.empty_like(a.data)
+        step = max(1, 65535 // (2 * a.ell))
+        for s in range(0, a.n, step):
+            e = min(a.n, s + step)
+            check(lib().ppq_eval_add(self.h, a.ell, _ptr(a.data[s:e]), _ptr(b.data[s:e]), _ptr(out[s:e]), e - s,
+                                     _stream()))
+        return CiphertextBatch(out, replace(a.meta))
+
+    def EvalMult(self, ct, c):
+        """cc->EvalMult(ct, double) under FLEXIBLEAUTOEXT: rescale first when noiseScaleDeg == 2."""
+        meta = replace(ct.meta)
+        ell = ct.ell
+        rescale = meta.noise_scale_deg == 2
+        if rescale:
+            meta.scaling_factor /= float(self.moduli[ell - 1])
+            meta.level += 1
+            meta.noise_scale_deg -= 1
+        sf = self.sf(meta.level)
+        lo = ell - 1 if rescale else ell
+        out = torch.empty((ct.n, 2, lo, self.N), dtype=torch.int64, device=self.device)
+        step = 8192
+        for s in range(0, ct.n, step):
+            e = min(ct.n, s + step)
+            check(lib().ppq_eval_mult_const(self.h, ell, _ptr(ct.data[s:e]), _ptr(out[s:e]), e - s, float(c), sf,
+                                            int(rescale), _stream()))
+        meta.noise_scale_deg += 1
+        meta.scaling_factor *= sf
+        return CiphertextBatch(out, meta)
+
+    def finalize_sum(self, acc):
+        step = max(1, 65535 // (2 * acc.ell))
+        for s in range(0, acc.n, step):
+            e = min(acc.n, s + step)
+            check(lib().ppq_finalize_sum(self.h, acc.ell, _ptr(acc.data[s:e]), e - s, _stream()))
+        return acc
+
+    # ---- client side
+    def MakeCKKSPackedPlaintext(self, values, ell=None):
+        """values: [n][<= N/2] real numbers (numpy or CUDA float64 tensor)."""
+        ell = self.L if ell is None else ell
+        v = values if torch.is_tensor(values) else torch.from_numpy(np.ascontiguousarray(values, dtype=np.float64))
+        v = v.to(self.device, dtype=torch.float64).contiguous()
+        if v.dim() == 1:
+            v = v[None, :]
+        n, nv = v.shape
+        sf = self.sf_big(0)
+        pt = torch.empty((n, ell, self.N), dtype=torch.int64, device=self.device)
+        step = max(1, 65535 // ell)
+        for s in range(0, n, step):
+            e = min(n, s + step)
+            check(lib().ppq_encode(self.h, ell, _ptr(v[s:e]), nv, sf, _ptr(pt[s:e]), e - s, _stream()))
+        meta = CtMeta(noise_scale_deg=2, level=0, scaling_factor=sf, slots=self.N // 2)
+        return PlaintextBatch(data=pt, meta=meta)
+
+    def Encrypt(self, pk, pt, small=None, seed=0):
+        """pk = (b, a) CUDA int64 [>=ell][N] each (QP public key; only the first ell limbs are used).
+        small: optional CUDA int64 [n][3][N] = injected (v, e0, e1) samples; sampled on the device otherwise."""
+        b, a = pk
+        n, ell = pt.data.shape[0], pt.data.shape[1]
+        if small is None:
+            small = torch.empty((n, 3, self.N), dtype=torch.int64, device=self.device)
+            check(lib().ppq_sample_encrypt_noise(self.h, int(seed), _ptr(small), n, _stream()))
+        ct = self.empty_cts(n, ell)
+        step = max(1, 65535 // (3 * ell))
+        for s in range(0, n, step):
+            e = min(n, s + step)
+            check(lib().ppq_encrypt(self.h, ell, _ptr(b), _ptr(a), _ptr(pt.data[s:e]), _ptr(small[s:e]), _ptr(ct[s:e]),
+                                    e - s, _stream()))
+        return CiphertextBatch(ct, replace(pt.meta))
+
+    def DecryptCore(self, sk, ct):
+        co = torch.empty((ct.n, ct.ell, self.N), dtype=torch.int64, device=self.device)
+        step = max(1, 65535 // ct.ell)
+        for s in range(0, ct.n, step):
+            e = min(ct.n, s + step)
+            check(lib().ppq_decrypt_core(self.h, ct.ell, _ptr(sk), _ptr(ct.data[s:e]), _ptr(co[s:e]), e - s, _stream()))
+        return co
+
+    def Decrypt(self, sk, ct):
+        co = self.DecryptCore(sk, ct)
+        vals = torch.empty((ct.n, self.N // 2), dtype=torch.float64, device=self.device)
+        step = 8192
+        for s in range(0, ct.n, step):
+            e = min(ct.n, s + step)
+            check(lib().ppq_decode(self.h, ct.ell, _ptr(co[s:e]), float(ct.meta.scaling_factor), _ptr(vals[s:e]), e - s,
+                                   _stream()))
+        return PlaintextBatch(values=vals, meta=replace(ct.meta))

@@ -1,0 +1,699 @@
+// capi.cu -- the C ABI of libppq_b200.so (include/ppq_b200.h): context/key/scratch management and the
+// orchestration of kernel launches for each reference-facing operation.  No CPU fallback: every compute entry
+// point needs a CUDA device and fails loudly otherwise.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/ppq_b200.h"
+#include "ckks.cuh"
+#include "kernels.cuh"
+#include "params.hpp"
+
+using namespace ppq;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CU(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess)                                                                        \
+            return fail(PPQ_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    cudaError_t upload(const std::vector<T>& h) {
+        release();
+        n = h.size();
+        if (!n) return cudaSuccess;
+        cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+        if (e != cudaSuccess) return e;
+        return cudaMemcpy(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice);
+    }
+    cudaError_t ensure(size_t want) {
+        if (want <= n) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) n = want;
+        return e;
+    }
+};
+
+static std::vector<BcJob> to_dev_jobs(const std::vector<host::Job>& j) {
+    std::vector<BcJob> o(j.size());
+    for (size_t i = 0; i < j.size(); ++i) o[i] = BcJob{j[i].src_first, j[i].ns, j[i].dst_slot, j[i].limb, j[i].chat_off, {0, 0, 0}};
+    return o;
+}
+
+struct KsPlanDev {
+    host::KsPlan h;
+    DevBuf<int> c1_limb, p_limb;
+    DevBuf<u64> c1_scale, c1_scale_sh, p_scale, p_scale_sh, up_chat, down_chat, pinv, pinv_sh;
+    DevBuf<BcJob> up_jobs, down_jobs;
+};
+struct RsPlanDev {
+    host::RsPlan h;
+    DevBuf<int> last_limb;
+    DevBuf<u64> last_scale, last_scale_sh, cst, cst_sh;
+    DevBuf<BcJob> jobs;
+};
+
+struct ppq_ctx {
+    host::Params hp;
+    int device = 0;
+    KCtx k{};
+    DevBuf<LimbC> limbs;
+    DevBuf<ulonglong2> twf, twi;
+    std::map<int, std::unique_ptr<KsPlanDev>> ks;
+    std::map<int, std::unique_ptr<RsPlanDev>> rs;
+    DevBuf<u64> scratch;   // key-switch wave scratch
+    DevBuf<u64> scratch2;  // rescale / encrypt / decrypt scratch
+    DevBuf<int> ids;       // limb ids of the plain NTT API
+    DevBuf<u64> ids_scale; // [2][n] N^-1 per poly (+ shoup)
+    DevBuf<u64> fac;       // [2][L] EvalMult factors
+    ckks::Tables fft;
+    int wave = 0;
+};
+struct ppq_rekey {
+    ppq_ctx* ctx = nullptr;
+    const u64* b = nullptr;
+    const u64* a = nullptr;
+    DevBuf<u64> own_b, own_a;
+};
+
+extern "C" const char* ppq_last_error(void) { return g_err.c_str(); }
+extern "C" const char* ppq_version(void) { return "ppq_b200 0.1 (sm_100a)"; }
+
+static int ctx_finish(std::unique_ptr<ppq_ctx>& c, int device, ppq_ctx** out) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(PPQ_ECUDA, "no CUDA device: libppq_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(PPQ_EINVAL, "bad device ordinal");
+    CU(cudaSetDevice(device));
+    c->device = device;
+    const host::Params& hp = c->hp;
+    const int M = hp.M();
+    const size_t N = hp.N;
+    std::vector<LimbC> lc(M);
+    for (int r = 0; r < M; ++r) {
+        const u64 q = hp.mod[r];
+        const int bl = 64 - __builtin_clzll(q);
+        lc[r].q = q;
+        lc[r].q2 = 2 * q;
+        lc[r].sh = (u32)(bl - 1);
+        lc[r].mu = (u64)((((unsigned __int128)1) << (64 + bl - 1)) / q);
+        lc[r].pad = 0;
+    }
+    CU(c->limbs.upload(lc));
+    {
+        std::vector<ulonglong2> f((size_t)M * N), i((size_t)M * N);
+#pragma omp parallel for
+        for (int r = 0; r < M; ++r)
+            host::build_twiddles(hp, r, reinterpret_cast<host::u64*>(f.data() + (size_t)r * N),
+                                 reinterpret_cast<host::u64*>(i.data() + (size_t)r * N));
+        CU(c->twf.upload(f));
+        CU(c->twi.upload(i));
+    }
+    c->k.limbs = c->limbs.p;
+    c->k.twf = c->twf.p;
+    c->k.twi = c->twi.p;
+    c->k.logN = hp.logN;
+    std::string err;
+    if (!ckks::build_tables(hp.logN, c->fft, err)) return fail(PPQ_ECUDA, err);
+    *out = c.release();
+    return PPQ_OK;
+}
+
+extern "C" int ppq_ctx_create(int logN, int L, const uint64_t* q, int dnum, int aux_bits, int extra_bits, int device,
+                              ppq_ctx** out) {
+    if (!q || !out || L < 1) return fail(PPQ_EINVAL, "ppq_ctx_create: bad arguments");
+    std::unique_ptr<ppq_ctx> c(new ppq_ctx);
+    c->hp.logN = logN;
+    c->hp.L = L;
+    c->hp.dnum = dnum;
+    c->hp.aux_bits = aux_bits;
+    c->hp.extra_bits = extra_bits;
+    c->hp.mod.assign(q, q + L);
+    std::string err;
+    if (!host::derive(c->hp, err)) return fail(PPQ_EINVAL, err);
+    return ctx_finish(c, device, out);
+}
+extern "C" int ppq_ctx_create_from_ccjson(const char* json, size_t len, int device, ppq_ctx** out) {
+    if (!json || !out) return fail(PPQ_EINVAL, "ppq_ctx_create_from_ccjson: bad arguments");
+    std::unique_ptr<ppq_ctx> c(new ppq_ctx);
+    std::string err;
+    if (!host::parse_ccjson(json, len, c->hp, err)) return fail(PPQ_EPARSE, err);
+    return ctx_finish(c, device, out);
+}
+extern "C" int ppq_ctx_create_synthetic(int logN, int depth, int first_bits, int scale_bits, int extra_bits, int dnum,
+                                        int device, ppq_ctx** out) {
+    if (!out || depth < 1 || logN < 12 || logN > 17) return fail(PPQ_EINVAL, "ppq_ctx_create_synthetic: bad arguments");
+    std::vector<host::u64> q = host::synthetic_chain(logN, depth, first_bits, scale_bits, extra_bits);
+    return ppq_ctx_create(logN, (int)q.size(), reinterpret_cast<const uint64_t*>(q.data()), dnum, 60, extra_bits, device, out);
+}
+extern "C" void ppq_ctx_destroy(ppq_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    delete c;
+}
+extern "C" int ppq_ctx_info(const ppq_ctx* c, ppq_ctx_info_t* o) {
+    if (!c || !o) return fail(PPQ_EINVAL, "ppq_ctx_info: null");
+    o->logN = c->hp.logN;
+    o->L = c->hp.L;
+    o->K = c->hp.K;
+    o->dnum = c->hp.dnum;
+    o->alpha = c->hp.alpha;
+    o->device = c->device;
+    return PPQ_OK;
+}
+extern "C" int ppq_ctx_moduli(const ppq_ctx* c, uint64_t* o) {
+    if (!c || !o) return fail(PPQ_EINVAL, "null");
+    std::memcpy(o, c->hp.mod.data(), sizeof(u64) * c->hp.M());
+    return PPQ_OK;
+}
+extern "C" int ppq_ctx_roots(const ppq_ctx* c, uint64_t* o) {
+    if (!c || !o) return fail(PPQ_EINVAL, "null");
+    std::memcpy(o, c->hp.root.data(), sizeof(u64) * c->hp.M());
+    return PPQ_OK;
+}
+extern "C" double ppq_ctx_scaling_factor(const ppq_ctx* c, int level) {
+    return (c && level >= 0 && level < c->hp.L) ? c->hp.sf[level] : 0.0;
+}
+extern "C" double ppq_ctx_scaling_factor_big(const ppq_ctx* c, int level) {
+    return (c && level >= 0 && level < c->hp.L) ? c->hp.sfbig[level] : 0.0;
+}
+extern "C" int ppq_ctx_num_parts(const ppq_ctx* c, int ell) {
+    if (!c || ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "bad ell");
+    int p = (ell + c->hp.alpha - 1) / c->hp.alpha;
+    return p > c->hp.dnum ? c->hp.dnum : p;
+}
+extern "C" int ppq_sync(const ppq_ctx* c, void* stream) {
+    if (!c) return fail(PPQ_EINVAL, "null");
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    return PPQ_OK;
+}
+extern "C" int ppq_ctx_set_wave(ppq_ctx* c, int n) {
+    if (!c || n < 0) return fail(PPQ_EINVAL, "bad wave");
+    c->wave = n;
+    return PPQ_OK;
+}
+
+// ------------------------------------------------------------------------------------------- plain NTT
+static int ntt_common(ppq_ctx* c, u64* d, const int32_t* ids, size_t n, void* stream, bool inverse) {
+    if (!c || !d || !ids) return fail(PPQ_EINVAL, "ppq_ntt: null argument");
+    if (n == 0) return PPQ_OK;
+    if (n > 65535) return fail(PPQ_EINVAL, "ppq_ntt: at most 65535 polynomials per call");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = c->hp.M();
+    std::vector<int> h(ids, ids + n);
+    std::vector<u64> sc(2 * n);
+    for (size_t i = 0; i < n; ++i) {
+        if (h[i] < 0 || h[i] >= M) return fail(PPQ_EINVAL, "ppq_ntt: limb id out of range");
+        sc[i] = c->hp.ninv[h[i]];
+        sc[n + i] = host::shoup(sc[i], c->hp.mod[h[i]]);
+    }
+    CU(c->ids.ensure(n));
+    CU(cudaMemcpyAsync(c->ids.p, h.data(), n * sizeof(int), cudaMemcpyHostToDevice, st));
+    if (inverse) {
+        CU(c->ids_scale.ensure(2 * n));
+        CU(cudaMemcpyAsync(c->ids_scale.p, sc.data(), 2 * n * sizeof(u64), cudaMemcpyHostToDevice, st));
+        launch_ntt_inverse(c->k, d, c->ids.p, c->ids_scale.p, c->ids_scale.p + n, (int)n, st);
+    } else {
+        launch_ntt_forward(c->k, d, c->ids.p, (int)n, st);
+    }
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));  // h / sc are stack-owned staging for the async copies
+    return PPQ_OK;
+}
+extern "C" int ppq_ntt_forward(ppq_ctx* c, uint64_t* d, const int32_t* ids, size_t n, void* stream) {
+    return ntt_common(c, (u64*)d, ids, n, stream, false);
+}
+extern "C" int ppq_ntt_inverse(ppq_ctx* c, uint64_t* d, const int32_t* ids, size_t n, void* stream) {
+    return ntt_common(c, (u64*)d, ids, n, stream, true);
+}
+
+// ------------------------------------------------------------------------------------------- rekeys
+extern "C" int ppq_rekey_upload(ppq_ctx* c, const uint64_t* hb, const uint64_t* ha, ppq_rekey** out) {
+    if (!c || !hb || !ha || !out) return fail(PPQ_EINVAL, "ppq_rekey_upload: null argument");
+    CU(cudaSetDevice(c->device));
+    std::unique_ptr<ppq_rekey> k(new ppq_rekey);
+    const size_t n = (size_t)c->hp.dnum * c->hp.M() * c->hp.N;
+    CU(k->own_b.ensure(n));
+    CU(k->own_a.ensure(n));
+    CU(cudaMemcpy(k->own_b.p, hb, n * sizeof(u64), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(k->own_a.p, ha, n * sizeof(u64), cudaMemcpyHostToDevice));
+    k->ctx = c;
+    k->b = k->own_b.p;
+    k->a = k->own_a.p;
+    *out = k.release();
+    return PPQ_OK;
+}
+extern "C" int ppq_rekey_from_device(ppq_ctx* c, const uint64_t* db, const uint64_t* da, ppq_rekey** out) {
+    if (!c || !db || !da || !out) return fail(PPQ_EINVAL, "ppq_rekey_from_device: null argument");
+    ppq_rekey* k = new ppq_rekey;
+    k->ctx = c;
+    k->b = (const u64*)db;
+    k->a = (const u64*)da;
+    *out = k;
+    return PPQ_OK;
+}
+extern "C" void ppq_rekey_destroy(ppq_rekey* k) {
+    if (!k) return;
+    if (k->ctx) cudaSetDevice(k->ctx->device);
+    delete k;
+}
+
+// ------------------------------------------------------------------------------------------- key switch
+static int get_ks_plan(ppq_ctx* c, int ell, KsPlanDev** out) {
+    auto it = c->ks.find(ell);
+    if (it == c->ks.end()) {
+        std::unique_ptr<KsPlanDev> p(new KsPlanDev);
+        host::build_ks_plan(c->hp, ell, p->h);
+        CU(p->c1_limb.upload(p->h.c1_limb));
+        CU(p->c1_scale.upload(p->h.c1_scale));
+        CU(p->c1_scale_sh.upload(p->h.c1_scale_sh));
+        CU(p->p_limb.upload(p->h.p_limb));
+        CU(p->p_scale.upload(p->h.p_scale));
+        CU(p->p_scale_sh.upload(p->h.p_scale_sh));
+        CU(p->up_chat.upload(p->h.up_chat));
+        CU(p->down_chat.upload(p->h.down_chat));
+        CU(p->pinv.upload(p->h.pinv));
+        CU(p->pinv_sh.upload(p->h.pinv_sh));
+        CU(p->up_jobs.upload(to_dev_jobs(p->h.up_jobs)));
+        CU(p->down_jobs.upload(to_dev_jobs(p->h.down_jobs)));
+        it = c->ks.emplace(ell, std::move(p)).first;
+    }
+    *out = it->second.get();
+    return PPQ_OK;
+}
+
+struct WaveLayout {
+    size_t y, dig, extq, extp, per_ct;  // sizes in u64 per ciphertext
+};
+static WaveLayout wave_layout(const ppq_ctx* c, int ell, int parts) {
+    const size_t N = c->hp.N, K = c->hp.K, M = ell + K;
+    WaveLayout w;
+    w.y = (size_t)ell * N;
+    w.dig = std::max((size_t)parts * M, (size_t)2 * ell) * N;  // digits, later reused for the ModDown conversion
+    w.extq = (size_t)2 * ell * N;
+    w.extp = (size_t)2 * K * N;
+    w.per_ct = w.y + w.dig + w.extq + w.extp;
+    return w;
+}
+static int pick_wave(const ppq_ctx* c, const WaveLayout& w, size_t n) {
+    size_t g;
+    if (c->wave > 0) {
+        g = (size_t)c->wave;
+    } else {
+        const char* e = std::getenv("PPQ_WAVE");
+        if (e && std::atoi(e) > 0) {
+            g = (size_t)std::atoi(e);
+        } else {
+            const size_t budget = (size_t)96 << 20;  // keep a wave's intermediates near the 126 MB L2
+            g = budget / (w.per_ct * sizeof(u64));
+            if (g < 1) g = 1;
+        }
+    }
+    if (g > n) g = n;
+    if (g > 32768) g = 32768;
+    return (int)g;
+}
+
+// shared driver: out[g] = (accumulate ? out[g] : 0) + ReEncrypt(in[g])
+static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64* in, u64* out, size_t n, void* stream,
+                            int accumulate) {
+    if (!c || !rk || !in || !out) return fail(PPQ_EINVAL, "ppq_reencrypt: null argument");
+    if (rk->ctx != c) return fail(PPQ_EINVAL, "ppq_reencrypt: rekey belongs to another context");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt: bad limb count");
+    if (n == 0) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    KsPlanDev* p;
+    int rc = get_ks_plan(c, ell, &p);
+    if (rc) return rc;
+    const size_t N = c->hp.N;
+    const int K = c->hp.K, L = c->hp.L, parts = p->h.parts;
+    const WaveLayout w = wave_layout(c, ell, parts);
+    const int G = pick_wave(c, w, n);
+    CU(c->scratch.ensure(w.per_ct * G));
+    u64* y = c->scratch.p;
+    u64* dig = y + w.y * G;
+    u64* extq = dig + w.dig * G;
+    u64* extp = extq + w.extq * G;
+    const size_t ct = (size_t)2 * ell * N;
+    for (size_t g0 = 0; g0 < n; g0 += G) {
+        const int ng = (int)std::min((size_t)G, n - g0);
+        const u64* in_g = in + g0 * ct;
+        u64* out_g = out + g0 * ct;
+        // 1-2. c1 -> COEFF, scaled by N^-1 (D_j/q_i)^-1
+        launch_inv_row(c->k, in_g + (size_t)ell * N, ct, y, w.y, p->c1_limb.p, ell, ng, st);
+        launch_inv_col(c->k, y, w.y, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, ng, st);
+        // 3. ModUp: approximate basis switch fused into the forward COL pass
+        launch_bc_fwd_col(c->k, y, w.y, dig, w.dig, p->up_jobs.p, (int)p->h.up_jobs.size(), p->up_chat.p, ng, 0, 0, st);
+        // 4. forward ROW pass + inner product with the rekey (+ inverse ROW pass on the P limbs)
+        IpArgs ia;
+        ia.c1 = in_g + (size_t)ell * N;
+        ia.c1_gs = ct;
+        ia.digits = dig;
+        ia.dig_gs = w.dig;
+        ia.key_b = rk->b;
+        ia.key_a = rk->a;
+        ia.extq = extq;
+        ia.extq_gs = w.extq;
+        ia.extp = extp;
+        ia.extp_gs = w.extp;
+        ia.ell = ell;
+        ia.K = K;
+        ia.L = L;
+        ia.parts = parts;
+        ia.alpha = c->hp.alpha;
+        launch_fwd_row_ip(c->k, ia, ng, st);
+        // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
+        launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, p->p_scale_sh.p, 2 * K, ng, st);
+        // 6. ModDown conversion P -> Q fused into the forward COL pass (digits buffer is dead: reuse it)
+        launch_bc_fwd_col(c->k, extp, w.extp, dig, w.dig, p->down_jobs.p, (int)p->h.down_jobs.size(), p->down_chat.p, ng, 0, 0, st);
+        // 7. forward ROW pass + (x - conv) P^-1 + c0 (+ running sum)
+        MdArgs ma;
+        ma.conv = dig;
+        ma.conv_gs = w.dig;
+        ma.extq = extq;
+        ma.extq_gs = w.extq;
+        ma.ct_in = in_g;
+        ma.in_gs = ct;
+        ma.out = out_g;
+        ma.out_gs = ct;
+        ma.pinv = p->pinv.p;
+        ma.pinv_sh = p->pinv_sh.p;
+        ma.ell = ell;
+        ma.accumulate = accumulate;
+        launch_fwd_row_moddown(c->k, ma, ng, st);
+    }
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+extern "C" int ppq_reencrypt(ppq_ctx* c, const ppq_rekey* rk, int ell, const uint64_t* in, uint64_t* out, size_t n,
+                             void* stream) {
+    if (in == out) return fail(PPQ_EINVAL, "ppq_reencrypt: d_out may not alias d_in");
+    return reencrypt_common(c, rk, ell, (const u64*)in, (u64*)out, n, stream, 0);
+}
+extern "C" int ppq_reencrypt_accumulate(ppq_ctx* c, const ppq_rekey* rk, int ell, const uint64_t* in, uint64_t* acc,
+                                        size_t n, void* stream) {
+    if (in == acc) return fail(PPQ_EINVAL, "ppq_reencrypt_accumulate: d_acc may not alias d_in");
+    return reencrypt_common(c, rk, ell, (const u64*)in, (u64*)acc, n, stream, 1);
+}
+
+extern "C" int ppq_ks_modup(ppq_ctx* c, int ell, const uint64_t* d_c1, uint64_t* d_digits, size_t n, void* stream) {
+    if (!c || !d_c1 || !d_digits) return fail(PPQ_EINVAL, "ppq_ks_modup: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_ks_modup: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n > 32768) return fail(PPQ_EINVAL, "ppq_ks_modup: batch too large");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    KsPlanDev* p;
+    int rc = get_ks_plan(c, ell, &p);
+    if (rc) return rc;
+    const size_t N = c->hp.N;
+    const int K = c->hp.K, M = ell + K, parts = p->h.parts;
+    const size_t ys = (size_t)ell * N, ds = (size_t)parts * M * N;
+    CU(c->scratch.ensure(ys * n));
+    u64* y = c->scratch.p;
+    launch_inv_row(c->k, (const u64*)d_c1, ys, y, ys, p->c1_limb.p, ell, (int)n, st);
+    launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, (int)n, st);
+    launch_bc_fwd_col(c->k, y, ys, (u64*)d_digits, ds, p->up_jobs.p, (int)p->h.up_jobs.size(), p->up_chat.p, (int)n, 0, 0, st);
+    // finish the converted limbs with a plain ROW pass; own-digit limbs are copies of c1
+    std::vector<int> ids((size_t)parts * M);
+    for (int j = 0; j < parts; ++j)
+        for (int r = 0; r < M; ++r) {
+            const bool own = r >= j * c->hp.alpha && r < std::min((j + 1) * c->hp.alpha, ell);
+            ids[(size_t)j * M + r] = own ? -1 : (r < ell ? r : c->hp.L + (r - ell));
+        }
+    CU(c->ids.ensure(ids.size()));
+    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    for (size_t g = 0; g < n; ++g) {
+        for (int j = 0; j < parts; ++j) {
+            const int s = j * c->hp.alpha, e = std::min(s + c->hp.alpha, ell);
+            CU(cudaMemcpyAsync((u64*)d_digits + g * ds + ((size_t)j * M + s) * N, (const u64*)d_c1 + g * ys + (size_t)s * N,
+                               (size_t)(e - s) * N * sizeof(u64), cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    launch_fwd_row_plain(c->k, (u64*)d_digits, ds, c->ids.p, parts * M, (int)n, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+// ------------------------------------------------------------------------------------------- EvalAdd / EvalMult
+extern "C" int ppq_eval_add(ppq_ctx* c, int ell, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n,
+                            void* stream) {
+    if (!c || !a || !b || !o) return fail(PPQ_EINVAL, "ppq_eval_add: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_eval_add: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n * 2 * ell > 65535) return fail(PPQ_EINVAL, "ppq_eval_add: batch too large for one call");
+    CU(cudaSetDevice(c->device));
+    launch_eval_add(c->k, (const u64*)a, (const u64*)b, (u64*)o, ell, n, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+extern "C" int ppq_finalize_sum(ppq_ctx* c, int ell, uint64_t* x, size_t n, void* stream) {
+    if (!c || !x) return fail(PPQ_EINVAL, "ppq_finalize_sum: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_finalize_sum: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n * 2 * ell > 65535) return fail(PPQ_EINVAL, "ppq_finalize_sum: batch too large for one call");
+    CU(cudaSetDevice(c->device));
+    launch_finalize_mod(c->k, (u64*)x, ell, n, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+
+extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint64_t* out, size_t n, double cst,
+                                   double sf, int rescale, void* stream) {
+    if (!c || !in || !out) return fail(PPQ_EINVAL, "ppq_eval_mult_const: null argument");
+    if (ell < (rescale ? 2 : 1) || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_eval_mult_const: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n > 16383) return fail(PPQ_EINVAL, "ppq_eval_mult_const: batch too large for one call");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    const int lo = rescale ? ell - 1 : ell;
+    std::vector<u64> f(2 * (size_t)lo);
+    host::mult_const_factors(c->hp, lo, sf, cst, f.data());
+    if (!rescale) {
+        for (int i = 0; i < lo; ++i) f[lo + i] = host::shoup(f[i], c->hp.mod[i]);
+        CU(c->fac.ensure(2 * (size_t)c->hp.L));
+        CU(cudaMemcpyAsync(c->fac.p, f.data(), f.size() * sizeof(u64), cudaMemcpyHostToDevice, st));
+        launch_mult_scalar(c->k, (const u64*)in, (u64*)out, c->fac.p, c->fac.p + lo, ell, n, st);
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(st));
+        return PPQ_OK;
+    }
+    auto it = c->rs.find(ell);
+    if (it == c->rs.end()) {
+        std::unique_ptr<RsPlanDev> p(new RsPlanDev);
+        host::build_rs_plan(c->hp, ell, p->h);
+        CU(p->last_limb.upload(p->h.last_limb));
+        CU(p->last_scale.upload(p->h.last_scale));
+        CU(p->last_scale_sh.upload(p->h.last_scale_sh));
+        CU(p->jobs.upload(to_dev_jobs(p->h.jobs)));
+        CU(p->cst.ensure(lo));
+        CU(p->cst_sh.ensure(lo));
+        it = c->rs.emplace(ell, std::move(p)).first;
+    }
+    RsPlanDev* p = it->second.get();
+    for (int i = 0; i < lo; ++i) {  // (x - t) * q_last^-1 * f  ==  (x - t) * (q_last^-1 f mod q)
+        f[i] = host::mulmod(f[i], p->h.qlinv[i], c->hp.mod[i]);
+        f[lo + i] = host::shoup(f[i], c->hp.mod[i]);
+    }
+    CU(cudaMemcpyAsync(p->cst.p, f.data(), lo * sizeof(u64), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->cst_sh.p, f.data() + lo, lo * sizeof(u64), cudaMemcpyHostToDevice, st));
+    // scratch: last limbs in COEFF [n][2][N] + converted limbs [n][2][ell-1][N]
+    const size_t rs_ = (size_t)2 * N, cs_ = (size_t)2 * lo * N, ct = (size_t)2 * ell * N;
+    CU(c->scratch2.ensure((rs_ + cs_) * n));
+    u64* r = c->scratch2.p;
+    u64* conv = r + rs_ * n;
+    // gather the two last limbs of every ciphertext (poly stride ell*N) via the strided inverse ROW pass
+    for (int poly = 0; poly < 2; ++poly)
+        launch_inv_row(c->k, (const u64*)in + ((size_t)poly * ell + lo) * N, ct, r + (size_t)poly * N, rs_,
+                       p->last_limb.p, 1, (int)n, st);
+    launch_inv_col(c->k, r, rs_, p->last_limb.p, p->last_scale.p, p->last_scale_sh.p, 2, (int)n, st);
+    launch_bc_fwd_col(c->k, r, rs_, conv, cs_, p->jobs.p, (int)p->h.jobs.size(), nullptr, (int)n, 1, c->hp.mod[lo], st);
+    RsArgs ra;
+    ra.conv = conv;
+    ra.conv_gs = cs_;
+    ra.ct_in = (const u64*)in;
+    ra.in_gs = ct;
+    ra.out = (u64*)out;
+    ra.out_gs = cs_;
+    ra.cst = p->cst.p;
+    ra.cst_sh = p->cst_sh.p;
+    ra.ell = ell;
+    launch_fwd_row_rescale(c->k, ra, (int)n, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+// ------------------------------------------------------------------------------------------- CKKS client side
+extern "C" int ppq_encode(ppq_ctx* c, int ell, const double* d_vals, size_t n_vals, double sf, uint64_t* d_pt, size_t n,
+                          void* stream) {
+    if (!c || !d_vals || !d_pt) return fail(PPQ_EINVAL, "ppq_encode: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_encode: bad limb count");
+    if (n_vals > c->hp.N / 2) return fail(PPQ_EINVAL, "ppq_encode: more values than slots");
+    if (n == 0) return PPQ_OK;
+    if (n * ell > 65535) return fail(PPQ_EINVAL, "ppq_encode: batch too large for one call");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    // scratch2: complex work [n][N/2] double2  (= n*N u64)  +  int64 coefficients [n][N]
+    CU(c->scratch2.ensure(2 * n * N));
+    double2* z = reinterpret_cast<double2*>(c->scratch2.p);
+    int64_t* co = reinterpret_cast<int64_t*>(c->scratch2.p + n * N);
+    ckks::launch_encode_fft(c->fft, d_vals, n_vals, sf, z, co, n, st);
+    launch_small_to_res(c->k, co, (u64*)d_pt, 1, ell, n, st);
+    std::vector<int> ids(n * ell);
+    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % ell);
+    CU(c->ids.ensure(ids.size()));
+    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    launch_ntt_forward(c->k, (u64*)d_pt, c->ids.p, (int)ids.size(), st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+extern "C" int ppq_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint64_t* pka, const uint64_t* pt,
+                           const int64_t* small, uint64_t* ct, size_t n, void* stream) {
+    if (!c || !pkb || !pka || !pt || !small || !ct) return fail(PPQ_EINVAL, "ppq_encrypt: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_encrypt: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n * 3 * ell > 65535) return fail(PPQ_EINVAL, "ppq_encrypt: batch too large for one call");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    CU(c->scratch2.ensure(n * 3 * ell * N));
+    u64* vee = c->scratch2.p;  // [n][3][ell][N]
+    launch_small_to_res(c->k, small, vee, 3, ell, n, st);
+    std::vector<int> ids(n * 3 * ell);
+    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % ell);
+    CU(c->ids.ensure(ids.size()));
+    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    launch_ntt_forward(c->k, vee, c->ids.p, (int)ids.size(), st);
+    launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, (const u64*)pt, (u64*)ct, ell, n, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+extern "C" int ppq_sample_encrypt_noise(ppq_ctx* c, uint64_t seed, int64_t* d_small, size_t n, void* stream) {
+    if (!c || !d_small) return fail(PPQ_EINVAL, "ppq_sample_encrypt_noise: null argument");
+    if (n == 0) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    ckks::launch_sample_noise(seed, d_small, c->hp.N, n, 3.19, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+
+extern "C" int ppq_decrypt_core(ppq_ctx* c, int ell, const uint64_t* sk, const uint64_t* ct, uint64_t* coeff, size_t n,
+                                void* stream) {
+    if (!c || !sk || !ct || !coeff) return fail(PPQ_EINVAL, "ppq_decrypt_core: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_decrypt_core: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n * ell > 65535) return fail(PPQ_EINVAL, "ppq_decrypt_core: batch too large for one call");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    launch_decrypt_pw(c->k, (const u64*)ct, (const u64*)sk, (u64*)coeff, ell, n, st);
+    std::vector<int32_t> ids(n * ell);
+    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int32_t)(i % ell);
+    return ntt_common(c, (u64*)coeff, ids.data(), ids.size(), stream, true);
+}
+
+extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf, double* d_vals, size_t n,
+                          void* stream) {
+    if (!c || !coeff || !d_vals) return fail(PPQ_EINVAL, "ppq_decode: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_decode: bad limb count");
+    if (n == 0) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    // Garner constants: ginv[i] = (q_0..q_{i-1})^-1 mod q_i ; wdbl[i] = double(q_0..q_{i-1})
+    std::vector<u64> gin(ell, 0);
+    std::vector<double> wd(ell, 1.0);
+    for (int i = 1; i < ell; ++i) {
+        u64 pr = 1;
+        for (int k = 0; k < i; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
+        gin[i] = host::invmod(pr, c->hp.mod[i]);
+        wd[i] = wd[i - 1] * (double)c->hp.mod[i - 1];
+    }
+    CU(c->fac.ensure(2 * (size_t)c->hp.L));
+    CU(cudaMemcpyAsync(c->fac.p, gin.data(), ell * sizeof(u64), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(c->fac.p + c->hp.L, wd.data(), ell * sizeof(double), cudaMemcpyHostToDevice, st));
+    CU(c->scratch2.ensure(n * N));
+    double2* z = reinterpret_cast<double2*>(c->scratch2.p);
+    ckks::launch_decode(c->fft, c->k, (const u64*)coeff, ell, c->fac.p, reinterpret_cast<const double*>(c->fac.p + c->hp.L),
+                        sf, z, d_vals, n, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+// ------------------------------------------------------------------------------------------- host-buffer path
+extern "C" int ppq_reencrypt_aggregate_host(ppq_ctx* c, const ppq_rekey* const* rekeys, int ell, const uint64_t* h_cts,
+                                            size_t n_clients, size_t n_slots, uint64_t* h_acc) {
+    if (!c || !rekeys || !h_cts || !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: bad limb count");
+    if (!n_clients || !n_slots) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    const size_t ct = (size_t)2 * ell * c->hp.N, blk = ct * n_slots;
+    // double-buffered upload: client c+1 is copied while client c is re-encrypted
+    DevBuf<u64> in[2], acc;
+    CU(in[0].ensure(blk));
+    CU(in[1].ensure(blk));
+    CU(acc.ensure(blk));
+    cudaStream_t sc, sx;
+    CU(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
+    cudaEvent_t up[2], done[2];
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaEventCreateWithFlags(&up[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+    }
+    int rc = PPQ_OK;
+    CU(cudaMemsetAsync(acc.p, 0, blk * sizeof(u64), sx));
+    for (size_t cl = 0; cl < n_clients && rc == PPQ_OK; ++cl) {
+        const int b = (int)(cl & 1);
+        if (cl >= 2) CU(cudaStreamWaitEvent(sc, done[b], 0));
+        CU(cudaMemcpyAsync(in[b].p, h_cts + cl * blk, blk * sizeof(u64), cudaMemcpyHostToDevice, sc));
+        CU(cudaEventRecord(up[b], sc));
+        CU(cudaStreamWaitEvent(sx, up[b], 0));
+        rc = reencrypt_common(c, rekeys[cl], ell, in[b].p, acc.p, n_slots, sx, 1);
+        CU(cudaEventRecord(done[b], sx));
+    }
+    if (rc == PPQ_OK) {
+        CU(cudaMemcpyAsync(h_acc, acc.p, blk * sizeof(u64), cudaMemcpyDeviceToHost, sx));
+        CU(cudaStreamSynchronize(sx));
+    }
+    cudaStreamSynchronize(sc);
+    cudaStreamSynchronize(sx);
+    for (int i = 0; i < 2; ++i) {
+        cudaEventDestroy(up[i]);
+        cudaEventDestroy(done[i]);
+    }
+    cudaStreamDestroy(sc);
+    cudaStreamDestroy(sx);
+    return rc;
+}

@@ -1,0 +1,208 @@
+// ckks.cu -- CKKS encode/decode kernels (FP64 special FFT) and the noise sampler.  See ckks.cuh.
+// Client-side path (encryptModelWeights / decryptModelWeights): one launch per FFT stage over the whole batch.
+#include "ckks.cuh"
+
+#include <cmath>
+#include <vector>
+
+namespace ppq {
+namespace ckks {
+
+Tables::~Tables() {
+    if (rot) cudaFree(rot);
+    if (ksi) cudaFree(ksi);
+}
+
+bool build_tables(int logN, Tables& t, std::string& err) {
+    const size_t N = (size_t)1 << logN, m = 2 * N, Nh = N / 2;
+    std::vector<unsigned> rot(Nh);
+    std::vector<double2> ksi(m + 1);
+    size_t five = 1;
+    for (size_t i = 0; i < Nh; ++i) {
+        rot[i] = (unsigned)five;
+        five = (five * 5) % m;
+    }
+    for (size_t j = 0; j < m; ++j) {
+        const double ang = 2.0 * M_PI * (double)j / (double)m;
+        ksi[j] = make_double2(std::cos(ang), std::sin(ang));
+    }
+    ksi[m] = ksi[0];
+    t.logN = logN;
+    cudaError_t e = cudaMalloc(&t.rot, Nh * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMalloc(&t.ksi, (m + 1) * sizeof(double2));
+    if (e == cudaSuccess) e = cudaMemcpy(t.rot, rot.data(), Nh * sizeof(unsigned), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(t.ksi, ksi.data(), (m + 1) * sizeof(double2), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        err = std::string("ckks tables: ") + cudaGetErrorString(e);
+        return false;
+    }
+    return true;
+}
+
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) {
+    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+
+// z[g][i] = (vals[g][i], 0) zero padded
+__global__ void k_load_vals(const double* __restrict__ vals, size_t n_vals, double2* __restrict__ z, unsigned Nh) {
+    const size_t g = blockIdx.y;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < Nh; i += gridDim.x * blockDim.x)
+        z[g * Nh + i] = make_double2(i < n_vals ? vals[g * n_vals + i] : 0.0, 0.0);
+}
+// one stage of FFTSpecialInv (decimation in frequency): len = current block length
+__global__ void k_fft_inv_stage(double2* __restrict__ z, unsigned Nh, unsigned len, const unsigned* __restrict__ rot,
+                                const double2* __restrict__ ksi, unsigned m) {
+    const size_t g = blockIdx.y;
+    const unsigned lenh = len >> 1, lenq = len << 2, gap = m / lenq;
+    double2* a = z + g * Nh;
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < Nh / 2; t += gridDim.x * blockDim.x) {
+        const unsigned j = t % lenh, i = (t / lenh) * len;
+        const unsigned idx = (lenq - (rot[j] % lenq)) * gap;
+        const double2 x = a[i + j], y = a[i + j + lenh];
+        a[i + j] = make_double2(x.x + y.x, x.y + y.y);
+        a[i + j + lenh] = cmul(make_double2(x.x - y.x, x.y - y.y), ksi[idx]);
+    }
+}
+// one stage of FFTSpecial (decimation in time)
+__global__ void k_fft_fwd_stage(double2* __restrict__ z, unsigned Nh, unsigned len, const unsigned* __restrict__ rot,
+                                const double2* __restrict__ ksi, unsigned m) {
+    const size_t g = blockIdx.y;
+    const unsigned lenh = len >> 1, lenq = len << 2, gap = m / lenq;
+    double2* a = z + g * Nh;
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < Nh / 2; t += gridDim.x * blockDim.x) {
+        const unsigned j = t % lenh, i = (t / lenh) * len;
+        const unsigned idx = (rot[j] % lenq) * gap;
+        const double2 u = a[i + j], v = cmul(a[i + j + lenh], ksi[idx]);
+        a[i + j] = make_double2(u.x + v.x, u.y + v.y);
+        a[i + j + lenh] = make_double2(u.x - v.x, u.y - v.y);
+    }
+}
+__global__ void k_bitrev(double2* __restrict__ z, unsigned Nh, int bits) {
+    const size_t g = blockIdx.y;
+    double2* a = z + g * Nh;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < Nh; i += gridDim.x * blockDim.x) {
+        const unsigned j = __brev(i) >> (32 - bits);
+        if (i < j) {
+            const double2 t = a[i];
+            a[i] = a[j];
+            a[j] = t;
+        }
+    }
+}
+// co[g][i] = llround(re(z[br(i)]) / Nh * sf), co[g][Nh + i] = same for the imaginary part
+__global__ void k_finish_encode(const double2* __restrict__ z, long long* __restrict__ co, unsigned Nh, int bits,
+                                double sf) {
+    const size_t g = blockIdx.y;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < Nh; i += gridDim.x * blockDim.x) {
+        const unsigned j = __brev(i) >> (32 - bits);
+        const double2 v = z[g * Nh + j];
+        co[g * 2 * Nh + i] = llround(v.x / (double)Nh * sf);
+        co[g * 2 * Nh + Nh + i] = llround(v.y / (double)Nh * sf);
+    }
+}
+
+static dim3 grid_for(size_t work, size_t n) {
+    unsigned gx = (unsigned)((work + 255) / 256);
+    if (gx > 1024) gx = 1024;
+    if (gx == 0) gx = 1;
+    return dim3(gx, (unsigned)n, 1);
+}
+
+void launch_encode_fft(const Tables& t, const double* d_vals, size_t n_vals, double sf, double2* z, int64_t* co,
+                       size_t n, cudaStream_t st) {
+    const unsigned N = 1u << t.logN, Nh = N / 2, m = 2 * N;
+    const int bits = t.logN - 1;
+    k_load_vals<<<grid_for(Nh, n), 256, 0, st>>>(d_vals, n_vals, z, Nh);
+    for (unsigned len = Nh; len >= 2; len >>= 1)
+        k_fft_inv_stage<<<grid_for(Nh / 2, n), 256, 0, st>>>(z, Nh, len, t.rot, t.ksi, m);
+    k_finish_encode<<<grid_for(Nh, n), 256, 0, st>>>(z, (long long*)co, Nh, bits, sf);
+}
+
+// CRT interpolation by Garner's mixed-radix digits, centred, as a double (Poly::CRTInterpolate + the
+// double conversion of CKKSPackedEncoding::Decode).  Digits v_i: X = sum v_i * prod_{k<i} q_k.
+// X > (Q-1)/2  <=>  digits compare above ((q_i-1)/2)_i from the top; then Q - X has digits q_i-1-v_i, plus 1.
+#define PPQ_MAX_DECODE_LIMBS 64
+__global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell, const u64* __restrict__ ginv,
+                                 double sf, double2* __restrict__ z) {
+    const u32 N = 1u << c.logN, Nh = N / 2;
+    const size_t g = blockIdx.y;
+    const u64* x = coeff + g * (size_t)ell * N;
+    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+        u64 v[PPQ_MAX_DECODE_LIMBS];
+        v[0] = x[n];
+        for (int i = 1; i < ell; ++i) {
+            const LimbC li = c.limbs[i];
+            u64 acc = 0;
+            for (int k = i - 1; k >= 0; --k) {
+                const u64 qk = reduce64(c.limbs[k].q, li);
+                acc = addmod(mulmod_barrett(acc, qk, li), reduce64(v[k], li), li.q);
+            }
+            v[i] = mulmod_barrett(submod(x[(size_t)i * N + n], acc, li.q), ginv[i], li);
+        }
+        bool neg = false;
+        for (int i = ell - 1; i >= 0; --i) {
+            const u64 h = (c.limbs[i].q - 1) >> 1;
+            if (v[i] != h) {
+                neg = v[i] > h;
+                break;
+            }
+        }
+        double d = 0.0;
+        for (int i = ell - 1; i >= 0; --i) {
+            const u64 q = c.limbs[i].q;
+            const u64 dig = neg ? q - 1 - v[i] : v[i];
+            d = d * (double)q + (double)dig;
+        }
+        if (neg) d = -(d + 1.0);
+        d /= sf;
+        if (n < Nh) z[g * Nh + n].x = d;
+        else z[g * Nh + (n - Nh)].y = d;
+    }
+}
+__global__ void k_take_real(const double2* __restrict__ z, double* __restrict__ out, unsigned Nh) {
+    const size_t g = blockIdx.y;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < Nh; i += gridDim.x * blockDim.x)
+        out[g * Nh + i] = z[g * Nh + i].x;
+}
+
+void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const double*,
+                   double sf, double2* z, double* d_vals, size_t n, cudaStream_t st) {
+    const unsigned N = 1u << t.logN, Nh = N / 2, m = 2 * N;
+    const int bits = t.logN - 1;
+    k_crt_to_complex<<<grid_for(N, n), 256, 0, st>>>(k, coeff, ell, d_ginv, sf, z);
+    k_bitrev<<<grid_for(Nh, n), 256, 0, st>>>(z, Nh, bits);
+    for (unsigned len = 2; len <= Nh; len <<= 1)
+        k_fft_fwd_stage<<<grid_for(Nh / 2, n), 256, 0, st>>>(z, Nh, len, t.rot, t.ksi, m);
+    k_take_real<<<grid_for(Nh, n), 256, 0, st>>>(z, d_vals, Nh);
+}
+
+// ---- counter-based sampler (splitmix64 of (seed, index)); ternary / rounded Gaussian (Box-Muller)
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+__global__ void k_sample_noise(unsigned long long seed, long long* __restrict__ out, size_t N, double sigma) {
+    const size_t g = blockIdx.y;
+    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * N; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t which = i / N;
+        const unsigned long long ctr = (g * 3 * N + i) * 2;
+        const unsigned long long r1 = mix64(seed ^ mix64(ctr)), r2 = mix64(seed ^ mix64(ctr + 1));
+        long long v;
+        if (which == 0) {
+            v = (long long)(r1 % 3) - 1;
+        } else {
+            const double u1 = ((double)(r1 >> 11) + 1.0) / 9007199254740993.0;
+            const double u2 = (double)(r2 >> 11) / 9007199254740992.0;
+            v = llround(sigma * sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
+        }
+        out[g * 3 * N + i] = v;
+    }
+}
+void launch_sample_noise(uint64_t seed, int64_t* d_small, size_t N, size_t n, double sigma, cudaStream_t st) {
+    k_sample_noise<<<grid_for(3 * N, n), 256, 0, st>>>(seed, (long long*)d_small, N, sigma);
+}
+
+}  // namespace ckks
+}  // namespace ppq

@@ -1,0 +1,566 @@
+// kernels.cu -- hand-written sm_100a kernels for the PPQSFLHE encrypted-aggregation hot path.
+//
+// Everything the reference does through OpenFHE on the CPU for
+//   cc->ReEncrypt   (server/src/changeCipherDomain.cpp:74,89,105)
+//   cc->EvalAdd / cc->EvalMult(.,0.5) (server/src/aggregateEncryptedWeights.cpp:82-83,91-92,106-107)
+//   cc->Encrypt / cc->Decrypt (client/src/encryptModelWeights.cpp:83,91,110; decryptModelWeights.cpp:81,90,108)
+// is expressed here as NTT passes (ntt_core.cuh) with the surrounding RNS arithmetic fused in as the
+// prologue or epilogue of a pass.  Integer modular arithmetic only: no tensor cores (nothing here is a dense
+// floating-point contraction).  Layouts are limb-major: a polynomial limb is N contiguous u64 residues.
+#include "kernels.cuh"
+#include "ckks.cuh"
+#include "ntt_core.cuh"
+
+namespace ppq {
+
+// ---------------------------------------------------------------------------------------------------------
+// streaming global accesses: data limbs are touched once per pass (evict-first), twiddles/keys stay cached
+__device__ __forceinline__ u64 ld_stream(const u64* p) { return __ldcs(p); }
+__device__ __forceinline__ void st_stream(u64* p, u64 v) { __stcs(p, v); }
+
+__device__ __forceinline__ void ld8(u64 (&a)[8], const u64* p) {  // 64 contiguous bytes, 16-byte aligned
+    const ulonglong2* v = reinterpret_cast<const ulonglong2*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        ulonglong2 t = v[i];
+        a[2 * i] = t.x;
+        a[2 * i + 1] = t.y;
+    }
+}
+__device__ __forceinline__ void ld8_ro(u64 (&a)[8], const u64* p) {
+    const ulonglong2* v = reinterpret_cast<const ulonglong2*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        ulonglong2 t = __ldg(v + i);
+        a[2 * i] = t.x;
+        a[2 * i + 1] = t.y;
+    }
+}
+__device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
+    ulonglong2* v = reinterpret_cast<ulonglong2*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = make_ulonglong2(a[2 * i], a[2 * i + 1]);
+}
+
+// =========================================================================================================
+// COL passes
+// =========================================================================================================
+// MODE 0: plain (src poly = blockIdx.y, limb from limb_ids)
+// MODE 1: approximate CRT basis switch prologue (ApproxSwitchCRTBasis: sum_i y_i * chat_i mod t, uncorrected)
+// MODE 2: centred SwitchModulus prologue (DropLastElementAndScale)
+template <int S, int W, int MODE>
+__global__ void __launch_bounds__(W << (S - 3))
+    k_fwd_col(KCtx c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs,
+              const BcJob* __restrict__ jobs, const u64* __restrict__ chat, const int* __restrict__ limb_ids,
+              u64 q_src) {
+    __shared__ u64 sm[W << S];
+    const u32 N = 1u << c.logN, n2 = N >> S;
+    const u32 w = threadIdx.x % W, u = threadIdx.x / W;
+    const u32 col = blockIdx.x * W + w;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+
+    int limb, ns = 1, chat_off = 0;
+    const u64* in;
+    u64* out;
+    if (MODE == 0) {
+        limb = limb_ids[y];
+        in = src + g * src_gs + (size_t)y * N;
+        out = dst + g * dst_gs + (size_t)y * N;
+    } else {
+        const BcJob jb = jobs[y];
+        limb = jb.limb;
+        ns = jb.ns;
+        chat_off = jb.chat_off;
+        in = src + g * src_gs + (size_t)jb.src_first * N;
+        out = dst + g * dst_gs + (size_t)jb.dst_slot * N;
+    }
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+
+    u64 a[8];
+    if (MODE == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + (size_t)point_of<S - 3>(u, k) * n2 + col);
+    } else if (MODE == 1) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = 0;
+        for (int i0 = 0; i0 < ns; i0 += 8) {
+            u64 hi[8], lo[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) hi[k] = lo[k] = 0;
+            const int i1 = min(ns, i0 + 8);
+            for (int i = i0; i < i1; ++i) {
+                const u64 ch = __ldg(chat + chat_off + i);
+                const u64* p = in + (size_t)i * N + col;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) mac128(hi[k], lo[k], p[(size_t)point_of<S - 3>(u, k) * n2], ch);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] += barrett128(hi[k], lo[k], lc);  // <= 4 chunks: stays < 4q
+        }
+    } else {
+        const u64 half = q_src >> 1;
+        const u64 qs_mod = reduce64(q_src, lc);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const u64 r = in[(size_t)point_of<S - 3>(u, k) * n2 + col];
+            const u64 v = reduce64(r, lc);
+            a[k] = r > half ? submod(v, qs_mod, lc.q) : v;
+        }
+    }
+    ColPos<W> pos{w};
+    fwd_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2, false);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy [0,4q): consumed by a ROW pass
+}
+
+template <int S, int W>
+__global__ void __launch_bounds__(W << (S - 3))
+    k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
+              const u64* __restrict__ scale, const u64* __restrict__ scale_sh) {
+    __shared__ u64 sm[W << S];
+    const u32 N = 1u << c.logN, n2 = N >> S;
+    const u32 w = threadIdx.x % W, u = threadIdx.x / W;
+    const u32 col = blockIdx.x * W + w;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const int limb = limb_map[y];
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twi + (size_t)limb * N;
+    u64* p = data + g * gs + (size_t)y * N + col;
+    u64 a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = p[(size_t)(8 * u + k) * n2];
+    ColPos<W> pos{w};
+    inv_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2, false);
+    const u64 sc = scale[y], scs = scale_sh[y];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) p[(size_t)point_of<S - 3>(u, k) * n2] = mul_shoup(a[k], sc, scs, lc.q);
+}
+
+// =========================================================================================================
+// ROW passes
+// =========================================================================================================
+template <int S>
+struct RowGeom {
+    static constexpr int R = 2048 >> S;       // rows per CTA: 2048 points, 256 threads
+    static constexpr int TPT = 1 << (S - 3);  // threads per transform
+    static constexpr int THREADS = R * TPT;
+    static constexpr int SMEM = R * RowPos<S>::PITCH;
+};
+
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS)
+    k_fwd_row_plain(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const int limb = limb_ids[y];
+    if (limb < 0) return;  // block-uniform: slot not to be transformed
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    u64* p = data + g * gs + (size_t)y * N + (size_t)row * n2;
+    u64 a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = p[point_of<S - 3>(u, k)];
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = csub(csub(a[k], lc.q2), lc.q);
+    st8(p + 8 * u, a);
+}
+
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS)
+    k_inv_row(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs,
+              const int* __restrict__ limb_map) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const int limb = limb_map[y];
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twi + (size_t)limb * N;
+    const size_t off = (size_t)y * N + (size_t)row * n2;
+    u64 a[8];
+    ld8(a, in + g * in_gs + off + 8 * u);
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    inv_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    u64* o = out + g * out_gs + off;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy [0,2q): consumed by k_inv_col
+}
+
+// Forward ROW pass + inner product with the re-encryption key (+ inverse ROW pass on the P limbs).
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_ip(KCtx c, IpArgs A) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const int r = blockIdx.y;
+    const u32 g = blockIdx.z;
+    const int M = A.ell + A.K;
+    const int limb = r < A.ell ? r : A.L + (r - A.ell);
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    const size_t off = (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+
+    u64 h0[8], l0[8], h1[8], l1[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) h0[k] = l0[k] = h1[k] = l1[k] = 0;
+
+    for (int j = 0; j < A.parts; ++j) {
+        const int s = j * A.alpha, e = min(s + A.alpha, A.ell);
+        u64 d[8];
+        if (r >= s && r < e) {  // own digit: the original EVAL limb of c1 (block-uniform branch)
+            ld8(d, A.c1 + g * A.c1_gs + (size_t)r * N + off + 8 * u);
+        } else {
+            const u64* in = A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) d[k] = ld_stream(in + point_of<S - 3>(u, k));
+            fwd_pass<S>(d, sm, pos, u, tw, n1 + row, lc.q, lc.q2, true);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) d[k] = csub(csub(d[k], lc.q2), lc.q);
+        }
+        u64 kb[8], ka[8];
+        const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off + 8 * u;
+        ld8_ro(kb, A.key_b + koff);
+        ld8_ro(ka, A.key_a + koff);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            mac128(h0[k], l0[k], d[k], kb[k]);
+            mac128(h1[k], l1[k], d[k], ka[k]);
+        }
+    }
+    u64 e0[8], e1[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        e0[k] = barrett128(h0[k], l0[k], lc);
+        e1[k] = barrett128(h1[k], l1[k], lc);
+    }
+    if (r < A.ell) {
+        u64* o = A.extq + g * A.extq_gs + (size_t)r * N + off + 8 * u;
+        st8(o, e0);
+        st8(o + (size_t)A.ell * N, e1);
+    } else {  // P limb: ModDown needs it in COEFF -> run the inverse ROW pass while the tile is in registers
+        const ulonglong2* twi = c.twi + (size_t)limb * N;
+        u64* o = A.extp + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
+        inv_pass<S>(e0, sm, pos, u, twi, n1 + row, lc.q, lc.q2, true);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e0[k];
+        o += (size_t)A.K * N;
+        inv_pass<S>(e1, sm, pos, u, twi, n1 + row, lc.q, lc.q2, true);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e1[k];
+    }
+}
+
+// Forward ROW pass + ModDown combine: out = (x - conv) * P^-1 (+ c0 on poly 0) (+ running sum).
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c, MdArgs A) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const int y = blockIdx.y;
+    const u32 g = blockIdx.z;
+    const int poly = y / A.ell, i = y % A.ell;
+    const LimbC lc = c.limbs[i];
+    const ulonglong2* tw = c.twf + (size_t)i * N;
+    const size_t off = (size_t)y * N + (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    u64 a[8];
+    const u64* in = A.conv + g * A.conv_gs + off;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
+    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    u64 x[8];
+    ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
+    const u64 pi = A.pinv[i], pis = A.pinv_sh[i];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const u64 v = csub(csub(a[k], lc.q2), lc.q);
+        a[k] = mul_shoup(x[k] + lc.q - v, pi, pis, lc.q);
+    }
+    if (poly == 0) {
+        ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], x[k], lc.q);
+    }
+    u64* o = A.out + g * A.out_gs + off + 8 * u;
+    if (A.accumulate) {
+        ld8(x, o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], x[k], lc.q);
+    }
+    st8(o, a);
+}
+
+// Forward ROW pass + rescale combine (DropLastElementAndScale, then the EvalMult constant folded in).
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_rescale(KCtx c, RsArgs A) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const int y = blockIdx.y;
+    const u32 g = blockIdx.z;
+    const int lm1 = A.ell - 1;
+    const int poly = y / lm1, i = y % lm1;
+    const LimbC lc = c.limbs[i];
+    const ulonglong2* tw = c.twf + (size_t)i * N;
+    const size_t roff = (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    u64 a[8];
+    const u64* in = A.conv + g * A.conv_gs + (size_t)y * N + roff;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
+    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    u64 x[8];
+    ld8(x, A.ct_in + g * A.in_gs + ((size_t)poly * A.ell + i) * N + roff + 8 * u);
+    const u64 cs = A.cst[i], css = A.cst_sh[i];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const u64 v = csub(csub(a[k], lc.q2), lc.q);
+        a[k] = mul_shoup(x[k] + lc.q - v, cs, css, lc.q);
+    }
+    st8(A.out + g * A.out_gs + (size_t)y * N + roff + 8 * u, a);
+}
+
+// =========================================================================================================
+// pointwise kernels: grid.x covers N/2 (two residues per thread), grid.y = flattened (ct, poly, limb)
+// =========================================================================================================
+__global__ void k_eval_add(KCtx c, const u64* __restrict__ a, const u64* __restrict__ b, u64* __restrict__ out,
+                           int ell) {
+    const u32 N = 1u << c.logN;
+    const u64 q = c.limbs[blockIdx.y % ell].q;
+    const size_t base = (size_t)blockIdx.y * N;
+    for (u32 n = (blockIdx.x * blockDim.x + threadIdx.x) * 2; n < N; n += gridDim.x * blockDim.x * 2) {
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(a + base + n);
+        const ulonglong2 z = *reinterpret_cast<const ulonglong2*>(b + base + n);
+        *reinterpret_cast<ulonglong2*>(out + base + n) = make_ulonglong2(addmod(x.x, z.x, q), addmod(x.y, z.y, q));
+    }
+}
+__global__ void k_finalize_mod(KCtx c, u64* __restrict__ x, int ell) {
+    const u32 N = 1u << c.logN;
+    const LimbC lc = c.limbs[blockIdx.y % ell];
+    const size_t base = (size_t)blockIdx.y * N;
+    for (u32 n = (blockIdx.x * blockDim.x + threadIdx.x) * 2; n < N; n += gridDim.x * blockDim.x * 2) {
+        ulonglong2 v = *reinterpret_cast<ulonglong2*>(x + base + n);
+        v.x = reduce64(v.x, lc);
+        v.y = reduce64(v.y, lc);
+        *reinterpret_cast<ulonglong2*>(x + base + n) = v;
+    }
+}
+__global__ void k_mult_scalar(KCtx c, const u64* __restrict__ in, u64* __restrict__ out, const u64* __restrict__ f,
+                              const u64* __restrict__ fs, int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const u64 q = c.limbs[i].q, w = f[i], ws = fs[i];
+    const size_t base = (size_t)blockIdx.y * N;
+    for (u32 n = (blockIdx.x * blockDim.x + threadIdx.x) * 2; n < N; n += gridDim.x * blockDim.x * 2) {
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(in + base + n);
+        *reinterpret_cast<ulonglong2*>(out + base + n) =
+            make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
+    }
+}
+// out[g][s][i][n] = small[g][s][n] mod q_i ; grid.y = g * n_small * ell + s * ell + i
+__global__ void k_small_to_res(KCtx c, const long long* __restrict__ small, u64* __restrict__ out, int n_small,
+                               int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const size_t sidx = blockIdx.y / ell;  // g * n_small + s
+    const LimbC lc = c.limbs[i];
+    const long long* sp = small + sidx * N;
+    u64* op = out + (size_t)blockIdx.y * N;
+    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+        const long long v = sp[n];
+        const u64 m = reduce64(v < 0 ? (u64)(-v) : (u64)v, lc);
+        op[n] = (v < 0 && m != 0) ? lc.q - m : m;
+    }
+    (void)n_small;
+}
+// grid.y = g * ell + i
+__global__ void k_encrypt_pw(KCtx c, const u64* __restrict__ pkb, const u64* __restrict__ pka,
+                             const u64* __restrict__ vee, const u64* __restrict__ pt, u64* __restrict__ ct, int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const size_t g = blockIdx.y / ell;
+    const LimbC lc = c.limbs[i];
+    const u64* v = vee + ((g * 3 + 0) * ell + i) * N;
+    const u64* e0 = vee + ((g * 3 + 1) * ell + i) * N;
+    const u64* e1 = vee + ((g * 3 + 2) * ell + i) * N;
+    const u64* m = pt + (g * ell + i) * N;
+    const u64* b = pkb + (size_t)i * N;
+    const u64* a = pka + (size_t)i * N;
+    u64* c0 = ct + ((g * 2 + 0) * ell + i) * N;
+    u64* c1 = ct + ((g * 2 + 1) * ell + i) * N;
+    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+        const u64 vv = v[n];
+        c0[n] = addmod(addmod(mulmod_barrett(vv, __ldg(b + n), lc), e0[n], lc.q), m[n], lc.q);
+        c1[n] = addmod(mulmod_barrett(vv, __ldg(a + n), lc), e1[n], lc.q);
+    }
+}
+__global__ void k_decrypt_pw(KCtx c, const u64* __restrict__ ct, const u64* __restrict__ sk, u64* __restrict__ out,
+                             int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const size_t g = blockIdx.y / ell;
+    const LimbC lc = c.limbs[i];
+    const u64* c0 = ct + ((g * 2 + 0) * ell + i) * N;
+    const u64* c1 = ct + ((g * 2 + 1) * ell + i) * N;
+    const u64* s = sk + (size_t)i * N;
+    u64* o = out + (g * ell + i) * N;
+    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x)
+        o[n] = addmod(c0[n], mulmod_barrett(c1[n], __ldg(s + n), lc), lc.q);
+}
+
+// =========================================================================================================
+// launchers
+// =========================================================================================================
+struct Split {
+    int S1, S2;
+};
+static Split split_of(int logN) {
+    switch (logN) {
+        case 12: return {6, 6};
+        case 13: return {7, 6};
+        case 14: return {7, 7};
+        case 15: return {8, 7};
+        case 16: return {8, 8};
+        case 17: return {9, 8};
+        default: return {0, 0};
+    }
+}
+template <int S>
+struct ColW {  // columns per CTA: 256 threads (512 for S = 9)
+    static constexpr int W = S == 6 ? 32 : S == 7 ? 16 : 8;
+};
+
+#define PPQ_COL_DISPATCH(S1, CALL)        \
+    switch (S1) {                         \
+        case 6: { constexpr int S = 6; CALL; } break; \
+        case 7: { constexpr int S = 7; CALL; } break; \
+        case 8: { constexpr int S = 8; CALL; } break; \
+        case 9: { constexpr int S = 9; CALL; } break; \
+        default: break;                   \
+    }
+#define PPQ_ROW_DISPATCH(S2, CALL)        \
+    switch (S2) {                         \
+        case 6: { constexpr int S = 6; CALL; } break; \
+        case 7: { constexpr int S = 7; CALL; } break; \
+        case 8: { constexpr int S = 8; CALL; } break; \
+        default: break;                   \
+    }
+
+template <int S, int MODE>
+static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* jobs,
+                           const u64* chat, const int* limb_ids, u64 q_src, int ny, int ng, cudaStream_t st) {
+    constexpr int W = ColW<S>::W;
+    const int n2 = (1 << c.logN) >> S;
+    dim3 grid(n2 / W, ny, ng), block(W << (S - 3));
+    k_fwd_col<S, W, MODE><<<grid, block, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, chat, limb_ids, q_src);
+}
+
+void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_polys, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 0>(c, data, 0, data, 0, nullptr, nullptr, d_limb_ids, 0, n_polys, 1, st)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, n_polys, 1), RowGeom<S>::THREADS, 0, st>>>(
+                                c, data, 0, d_limb_ids)));
+}
+
+void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
+                          cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, n_slots, n_g), RowGeom<S>::THREADS, 0, st>>>(
+                                c, data, gs, d_limb_ids)));
+}
+
+void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
+                    int n_slots, int n_g, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, n_slots, n_g), RowGeom<S>::THREADS, 0, st>>>(
+                                c, in, in_gs, out, out_gs, d_limb_map)));
+}
+void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
+                    const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n2 = 1 << sp.S2;
+    PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
+                                c, data, gs, d_limb_map, d_scale, d_scale_sh)));
+}
+void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale, const u64* d_scale_sh,
+                        int n_polys, cudaStream_t st) {
+    launch_inv_row(c, data, 0, data, 0, d_limb_ids, n_polys, 1, st);
+    launch_inv_col(c, data, 0, d_limb_ids, d_scale, d_scale_sh, n_polys, 1, st);
+}
+
+void launch_bc_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
+                       int n_jobs, const u64* d_chat, int n_g, int mode, u64 q_src, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    if (mode == 0) {
+        PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 1>(c, src, src_gs, dst, dst_gs, d_jobs, d_chat, nullptr, 0, n_jobs, n_g, st)));
+    } else {
+        PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 2>(c, src, src_gs, dst, dst_gs, d_jobs, d_chat, nullptr, q_src, n_jobs, n_g, st)));
+    }
+}
+
+void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_ip<S><<<dim3(n1 / RowGeom<S>::R, a.ell + a.K, n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+}
+void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, 2 * a.ell, n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+}
+void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_rescale<S><<<dim3(n1 / RowGeom<S>::R, 2 * (a.ell - 1), n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+}
+
+static dim3 pw_grid(const KCtx& c, size_t ny, int per_thread) {
+    const u32 N = 1u << c.logN;
+    u32 gx = N / (256u * per_thread);
+    if (gx == 0) gx = 1;
+    return dim3(gx, (unsigned)ny, 1);
+}
+void launch_eval_add(const KCtx& c, const u64* a, const u64* b, u64* out, int ell, size_t n_ct, cudaStream_t st) {
+    k_eval_add<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, a, b, out, ell);
+}
+void launch_finalize_mod(const KCtx& c, u64* x, int ell, size_t n_ct, cudaStream_t st) {
+    k_finalize_mod<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, x, ell);
+}
+void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
+                        size_t n_ct, cudaStream_t st) {
+    k_mult_scalar<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
+}
+void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
+                         cudaStream_t st) {
+    k_small_to_res<<<pw_grid(c, n_ct * n_small * ell, 1), 256, 0, st>>>(c, (const long long*)small, out, n_small, ell);
+}
+void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee, const u64* pt, u64* ct, int ell,
+                       size_t n_ct, cudaStream_t st) {
+    k_encrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, pkb, pka, vee, pt, ct, ell);
+}
+void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st) {
+    k_decrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, ct, sk, out, ell);
+}
+
+const char* kernels_build_info() { return "ppq_b200 kernels: sm_100a, radix-8 register groups, 2-pass (COL,ROW) NTT"; }
+
+}  // namespace ppq

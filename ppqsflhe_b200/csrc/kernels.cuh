@@ -1,0 +1,116 @@
+// kernels.cuh -- launcher interface between the C-ABI layer (capi.cu) and the sm_100a kernels (kernels.cu).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "modarith.cuh"
+
+namespace ppq {
+
+// Device-resident view of a context: per-limb constants and the twiddle tables (w, w_shoup) for every
+// modulus of Q u P, forward and inverse, each [M][N] ulonglong2.
+struct KCtx {
+    const LimbC* limbs;
+    const ulonglong2* twf;
+    const ulonglong2* twi;
+    int logN;
+};
+
+// One fused "base conversion -> forward COL pass" job (ModUp of a digit to one target limb, or ModDown of the
+// P part to one Q limb): out[dst_slot] = COLpass( sum_i src[src_first+i] * chat[chat_off+i]  mod q_limb ).
+struct BcJob {
+    int src_first;  // first source poly (index inside one ciphertext's source block)
+    int ns;         // number of source limbs
+    int dst_slot;   // destination poly inside one ciphertext's destination block
+    int limb;       // global limb index of the target modulus
+    int chat_off;   // offset into the chat[] constant array
+    int pad[3];
+};
+
+// ---- plain batched NTT (C-ABI ppq_ntt_forward / ppq_ntt_inverse).  data: [n_polys][N] in place,
+// d_limb_ids: device int[n_polys].  d_scale / d_scale_sh: per-POLY constant folded into the inverse (N^-1).
+void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_polys, cudaStream_t st);
+void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale, const u64* d_scale_sh,
+                        int n_polys, cudaStream_t st);
+
+// ---- generic strided inverse:  for g < n_g, y < n_slots:
+//   out[g*out_gs + y*N ..] = iNTT(in[g*in_gs + y*N ..]) * scale[y]   (limb = limb_map[y]), canonical.
+// row pass and column pass are separate launches; `tmp` may alias `out`.
+void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
+                    int n_slots, int n_g, cudaStream_t st);
+void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
+                    const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st);
+
+// ---- base conversion + forward COL pass.  src: [n_g] blocks of stride src_gs, dst likewise.
+// mode 0: approximate CRT basis switch (chat constants).  mode 1: centred SwitchModulus of ONE source limb
+// with modulus q_src (rescale, DropLastElementAndScale).
+void launch_bc_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
+                       int n_jobs, const u64* d_chat, int n_g, int mode, u64 q_src, cudaStream_t st);
+
+// ---- forward ROW pass fused with the key inner product (hybrid key switch, EvalFastKeySwitchCoreExt).
+struct IpArgs {
+    const u64* c1;       // EVAL c1 limbs of the batch: c1 + g*c1_gs + r*N (own-digit limbs are used as they are)
+    size_t c1_gs;
+    const u64* digits;   // COL-pass output of bc_fwd_col: digits + g*dig_gs + (j*(ell+K) + r)*N
+    size_t dig_gs;
+    const u64* key_b;    // [dnum][L+K][N]
+    const u64* key_a;
+    u64* extq;           // out, Q limbs:  extq + g*extq_gs + (poly*ell + r)*N, EVAL canonical
+    size_t extq_gs;
+    u64* extp;           // out, P limbs after the inverse ROW pass: extp + g*extp_gs + (poly*K + k)*N
+    size_t extp_gs;
+    int ell, K, L, parts, alpha;
+};
+void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
+
+// ---- forward ROW pass fused with the ModDown combine (+ c0, + optional accumulate = EvalAdd).
+struct MdArgs {
+    const u64* conv;   // COL-pass output: conv + g*conv_gs + (poly*ell + i)*N
+    size_t conv_gs;
+    const u64* extq;   // extq + g*extq_gs + (poly*ell + i)*N
+    size_t extq_gs;
+    const u64* ct_in;  // original ciphertexts [g][2][ell][N] (c0 is added to poly 0)
+    size_t in_gs;
+    u64* out;          // [g][2][ell][N]
+    size_t out_gs;
+    const u64* pinv;   // [ell]  P^-1 mod q_i
+    const u64* pinv_sh;
+    int ell;
+    int accumulate;    // 0: out = result ; 1: out = out + result mod q (EvalAdd into the running sum)
+};
+void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st);
+
+// ---- forward ROW pass fused with the rescale combine: out = (x - v) * cst[i] mod q_i
+struct RsArgs {
+    const u64* conv;   // conv + g*conv_gs + (poly*(ell-1) + i)*N
+    size_t conv_gs;
+    const u64* ct_in;  // [g][2][ell][N]
+    size_t in_gs;
+    u64* out;          // [g][2][ell-1][N]
+    size_t out_gs;
+    const u64* cst;    // [ell-1]
+    const u64* cst_sh;
+    int ell;
+};
+void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st);
+
+// ---- pointwise helpers
+// out = a + b mod q   (layout [n][2][ell][N], limb i -> modulus i)
+void launch_eval_add(const KCtx& c, const u64* a, const u64* b, u64* out, int ell, size_t n_ct, cudaStream_t st);
+// x = x mod q for lazily summed residues (after a cross-rank u64 sum)
+void launch_finalize_mod(const KCtx& c, u64* x, int ell, size_t n_ct, cudaStream_t st);
+// out = in * f[i] mod q_i
+void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
+                        size_t n_ct, cudaStream_t st);
+// small signed coefficients -> residues of limb i:  out[g][y][n] = small[g][y / ell][n] mod q_{y % ell}
+void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
+                         cudaStream_t st);
+// encrypt combine: ct[g][0][i] = pkb[i]*v + e0 + m ; ct[g][1][i] = pka[i]*v + e1   (all EVAL)
+void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee /*[g][3][ell][N]*/,
+                       const u64* pt /*[g][ell][N]*/, u64* ct, int ell, size_t n_ct, cudaStream_t st);
+// decrypt combine: out[g][i] = c0 + c1 * s   (EVAL)
+void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st);
+
+const char* kernels_build_info();
+
+}  // namespace ppq

@@ -1,0 +1,78 @@
+"""CPU-only checks of the drop-in boundary: the library loads, exports every symbol include/ppq_b200.h declares,
+binds through ctypes, and fails LOUDLY (no CPU fallback) when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "ppq_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ppq_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    import ppqsflhe_b200
+    ppqsflhe_b200.build()
+    names = _declared()
+    assert len(names) >= 30
+    out = subprocess.check_output(["nm", "-D", "--defined-only", ppqsflhe_b200.LIB_PATH]).decode()
+    exported = set(re.findall(r" T (ppq_[a-z0-9_]+)", out))
+    missing = [n for n in names if n not in exported]
+    assert not missing, f"declared in ppq_b200.h but not exported: {missing}"
+    from ppqsflhe_b200 import _capi
+    assert sorted(_capi._SIGS) == names, "ctypes binding table out of sync with the header"
+    assert ppqsflhe_b200.lib().ppq_version().startswith(b"ppq_b200")
+
+
+def test_sass_is_sm100a_only():
+    import ppqsflhe_b200
+    ppqsflhe_b200.build()
+    out = subprocess.check_output(["cuobjdump", "--list-elf", ppqsflhe_b200.LIB_PATH]).decode()
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_no_cpu_fallback_without_a_device(ccjson_text):
+    torch = pytest.importorskip("torch")
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from ppqsflhe_b200 import _capi
+    L = _capi.lib()
+    h = C.c_void_p()
+    raw = ccjson_text.encode()
+    rc = L.ppq_ctx_create_from_ccjson(raw, len(raw), 0, C.byref(h))
+    assert rc == -2 and b"no CPU fallback" in L.ppq_last_error()
+    with pytest.raises(_capi.PPQError):
+        _capi.check(rc)
+
+
+def test_bad_arguments_are_rejected_before_touching_the_device():
+    from ppqsflhe_b200 import _capi
+    L = _capi.lib()
+    h = C.c_void_p()
+    assert L.ppq_ctx_create_from_ccjson(b"{}", 2, 0, C.byref(h)) == -4          # PPQ_EPARSE
+    q = np.array([97], dtype=np.uint64)                                          # not 1 mod 2N
+    assert L.ppq_ctx_create(12, 1, q.ctypes.data_as(_capi.u64p), 1, 60, 0, 0, C.byref(h)) == -1
+    assert L.ppq_ctx_create_synthetic(11, 2, 60, 40, 20, 2, 0, C.byref(h)) == -1  # ring dimension out of range
+    assert L.ppq_reencrypt(None, None, 1, None, None, 0, None) == -1
+    assert L.ppq_ntt_forward(None, None, None, 0, None) == -1
+
+
+def test_product_never_imports_the_oracle():
+    """The oracle is test infrastructure: nothing under ppqsflhe_b200/ may reference it."""
+    pkg = os.path.join(ROOT, "ppqsflhe_b200")
+    for base, _, files in os.walk(pkg):
+        if os.sep + "build" in base:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h", "Makefile")):
+                text = open(os.path.join(base, f), errors="ignore").read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f
+                assert "ppq_oracle" not in text and "ppqo_" not in text, f

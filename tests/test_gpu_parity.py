@@ -1,0 +1,340 @@
+"""Parity tests proper: the sm_100a path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact for every integer stage; CKKS encode/decode within the stated tolerance.  Run with -m gpu on a B200."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+import oracle  # noqa: E402  (the checker)
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _cc_pair(kind):
+    from ppqsflhe_b200 import CryptoContext
+    if kind == "c1":
+        text = open(os.path.join(ROOT, "tests", "golden", "CC.json")).read()
+        return oracle.Oracle.from_ccjson(text), CryptoContext.from_ccjson(text, 0)
+    logN, depth, dnum, scale = kind
+    o = oracle.Oracle.synthetic(logN, depth, 60, scale, 20, dnum)
+    cc = CryptoContext.synthetic(logN, depth, 60, scale, 20, dnum, 0)
+    return o, cc
+
+
+def _rand_poly(rng, o, limbs):
+    return np.stack([rng.integers(0, int(o.moduli[r]), o.N, dtype=np.uint64) for r in limbs])
+
+
+def _rand_ct(rng, o, ell, n):
+    return np.stack([np.stack([_rand_poly(rng, o, range(ell)) for _ in range(2)]) for _ in range(n)])
+
+
+def _rand_key(rng, o):
+    kb = np.stack([_rand_poly(rng, o, range(o.M)) for _ in range(o.dnum)])
+    ka = np.stack([_rand_poly(rng, o, range(o.M)) for _ in range(o.dnum)])
+    return kb, ka
+
+
+def test_context_matches_oracle_and_ccjson():
+    o, cc = _cc_pair("c1")
+    assert (cc.logN, cc.L, cc.K, cc.dnum, cc.alpha) == (o.logN, o.L, o.K, o.dnum, o.alpha) == (14, 4, 2, 2, 2)
+    assert np.array_equal(cc.moduli, o.moduli) and np.array_equal(cc.roots, o.roots)
+    assert [cc.sf(i) for i in range(4)] == [o.sf(i) for i in range(4)]
+    assert cc.sf_big(0) == o.sf_big(0)
+    for kind in [(12, 3, 2, 40), (16, 18, 3, 59)]:
+        o2, cc2 = _cc_pair(kind)
+        assert np.array_equal(cc2.moduli, o2.moduli) and np.array_equal(cc2.roots, o2.roots)
+        assert (cc2.L, cc2.K, cc2.alpha) == (o2.L, o2.K, o2.alpha)
+
+
+@pytest.mark.parametrize("logN", [12, 13, 14, 15, 16, 17])
+def test_ntt_bit_exact(logN):
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    o, cc = _cc_pair((logN, 3, 2, 45))
+    rng = np.random.default_rng(100 + logN)
+    limbs = list(range(o.M)) + [0, o.M - 1]
+    x = _rand_poly(rng, o, limbs)
+    d = to_device_u64(x, cc.device)
+    cc.ntt(d, limbs)
+    got = to_host_u64(d)
+    for i, r in enumerate(limbs):
+        assert np.array_equal(got[i], o.ntt(r, x[i])), f"forward NTT differs, limb {r}"
+    cc.ntt(d, limbs, inverse=True)
+    assert np.array_equal(to_host_u64(d), x), "inverse(forward(x)) != x"
+    # inverse alone against the oracle
+    d = to_device_u64(x, cc.device)
+    cc.ntt(d, limbs, inverse=True)
+    got = to_host_u64(d)
+    for i, r in enumerate(limbs):
+        assert np.array_equal(got[i], o.ntt(r, x[i], inverse=True)), f"inverse NTT differs, limb {r}"
+
+
+def test_ntt_edge_values():
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    o, cc = _cc_pair("c1")
+    limbs = list(range(o.M))
+    for fill in ("zero", "max", "delta"):
+        x = np.zeros((o.M, o.N), dtype=np.uint64)
+        for r in limbs:
+            if fill == "max":
+                x[r, :] = o.moduli[r] - np.uint64(1)
+            elif fill == "delta":
+                x[r, 1] = 1
+        d = to_device_u64(x, cc.device)
+        cc.ntt(d, limbs)
+        got = to_host_u64(d)
+        for r in limbs:
+            assert np.array_equal(got[r], o.ntt(r, x[r]))
+
+
+def test_secret_key_golden_through_gpu():
+    """The real OpenFHE secret keys: NTT(ternary) on the GPU must hash to the digests of the serialized limbs."""
+    import hashlib
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    o, cc = _cc_pair("c1")
+    g = np.load(os.path.join(ROOT, "tests", "golden", "openfhe_sk_golden.npz"))
+    for c in (1, 2):
+        tern = g[f"c{c}_ternary"].astype(np.int64)
+        x = np.stack([np.where(tern < 0, tern + int(o.moduli[i]), tern).astype(np.uint64) for i in range(4)])
+        d = to_device_u64(x, cc.device)
+        cc.ntt(d, [0, 1, 2, 3])
+        got = to_host_u64(d)
+        for i in range(4):
+            assert hashlib.sha256(got[i].astype("<u8").tobytes()).hexdigest() == str(g[f"c{c}_sha256"][i])
+            assert np.array_equal(got[i][:8], g[f"c{c}_head"][i])
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 3), ("c1", 2), ("c1", 1), ((12, 5, 3, 45), 7), ((12, 5, 3, 45), 4),
+                                      ((13, 4, 2, 50), 6), ((15, 2, 2, 40), 4)])
+def test_modup_bit_exact(kind, ell):
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(7)
+    n = 3
+    c1 = np.stack([_rand_poly(rng, o, range(ell)) for _ in range(n)])
+    got = to_host_u64(cc.KeySwitchModUp(to_device_u64(c1, cc.device)))
+    for g in range(n):
+        assert np.array_equal(got[g], o.modup(ell, c1[g])), f"ModUp differs (ct {g})"
+
+
+@pytest.mark.parametrize("kind,ell,n", [("c1", 4, 5), ("c1", 3, 2), ("c1", 1, 1), ((12, 5, 3, 45), 7, 3),
+                                        ((12, 5, 3, 45), 5, 2), ((13, 4, 2, 50), 6, 2), ((15, 2, 2, 40), 4, 2),
+                                        ((16, 6, 3, 59), 8, 2), ((17, 2, 2, 40), 4, 1)])
+def test_reencrypt_bit_exact(kind, ell, n):
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(11)
+    ct = _rand_ct(rng, o, ell, n)
+    kb, ka = _rand_key(rng, o)
+    rk = EvalKey(cc, kb, ka)
+    out = cc.ReEncrypt(CiphertextBatch(to_device_u64(ct, cc.device), CtMeta()), rk).numpy()
+    for g in range(n):
+        want = o.reencrypt(ell, ct[g], kb, ka)
+        assert np.array_equal(out[g][1], want[1]), f"c1' differs (ct {g})"
+        assert np.array_equal(out[g][0], want[0]), f"c0' differs (ct {g})"
+
+
+def test_reencrypt_wave_size_independent():
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair((12, 3, 2, 45))
+    rng = np.random.default_rng(5)
+    ell, n = o.L, 7
+    ct = _rand_ct(rng, o, ell, n)
+    kb, ka = _rand_key(rng, o)
+    rk = EvalKey(cc, kb, ka)
+    b = CiphertextBatch(to_device_u64(ct, cc.device), CtMeta())
+    ref = cc.ReEncrypt(b, rk).numpy()
+    for wave in (1, 2, 3, 7):
+        cc.set_wave(wave)
+        assert np.array_equal(cc.ReEncrypt(b, rk).numpy(), ref)
+    cc.set_wave(0)
+
+
+def test_reencrypt_accumulate_matches_oracle_batch():
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair("c1")
+    rng = np.random.default_rng(13)
+    ell, n_clients, n_slots = 4, 3, 4
+    cts = np.stack([_rand_ct(rng, o, ell, n_slots) for _ in range(n_clients)])
+    keys = [_rand_key(rng, o) for _ in range(n_clients)]
+    acc = CiphertextBatch(torch.zeros((n_slots, 2, ell, cc.N), dtype=torch.int64, device=cc.device), CtMeta())
+    for c in range(n_clients):
+        rk = EvalKey(cc, *keys[c])
+        cc.ReEncryptAccumulate(CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()), rk, acc)
+    want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+    assert np.array_equal(acc.numpy(), want)
+
+
+def test_host_buffer_aggregate_entry_point():
+    import ctypes as C
+    from ppqsflhe_b200 import EvalKey
+    from ppqsflhe_b200._capi import check, lib, vp
+    o, cc = _cc_pair("c1")
+    rng = np.random.default_rng(17)
+    ell, n_clients, n_slots = 3, 4, 2
+    cts = np.ascontiguousarray(np.stack([_rand_ct(rng, o, ell, n_slots) for _ in range(n_clients)]))
+    keys = [_rand_key(rng, o) for _ in range(n_clients)]
+    rks = [EvalKey(cc, *k) for k in keys]
+    arr = (vp * n_clients)(*[r.h for r in rks])
+    out = np.zeros((n_slots, 2, ell, o.N), dtype=np.uint64)
+    check(lib().ppq_reencrypt_aggregate_host(cc.h, arr, ell, cts.ctypes.data_as(vp), n_clients, n_slots,
+                                             out.ctypes.data_as(vp)))
+    want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+    assert np.array_equal(out, want)
+
+
+def test_eval_add_and_finalize_bit_exact():
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, to_device_u64
+    o, cc = _cc_pair("c1")
+    rng = np.random.default_rng(19)
+    ell, n = 4, 3
+    a, b = _rand_ct(rng, o, ell, n), _rand_ct(rng, o, ell, n)
+    A = CiphertextBatch(to_device_u64(a, cc.device), CtMeta())
+    B = CiphertextBatch(to_device_u64(b, cc.device), CtMeta())
+    got = cc.EvalAdd(A, B).numpy()
+    for g in range(n):
+        assert np.array_equal(got[g], o.eval_add(ell, a[g], b[g]))
+    # lazy u64 sum of 8 canonical operands (what the NCCL reduce produces) then finalize
+    parts = [_rand_ct(rng, o, ell, n) for _ in range(8)]
+    lazy = np.zeros_like(parts[0])
+    want = np.zeros_like(parts[0])
+    for p in parts:
+        lazy = lazy + p
+        for g in range(n):
+            want[g] = o.eval_add(ell, want[g], p[g])
+    L = cc.finalize_sum(CiphertextBatch(to_device_u64(lazy, cc.device), CtMeta()))
+    assert np.array_equal(L.numpy(), want)
+
+
+@pytest.mark.parametrize("kind,ell,c", [("c1", 4, 0.5), ("c1", 3, 0.25), ((12, 5, 3, 45), 7, 1.0 / 3.0),
+                                        ((16, 6, 3, 59), 8, 1.0 / 64.0)])
+def test_eval_mult_rescale_bit_exact(kind, ell, c):
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, to_device_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(23)
+    n = 2
+    ct = _rand_ct(rng, o, ell, n)
+    level = o.L - ell
+    meta = CtMeta(noise_scale_deg=2, level=level, scaling_factor=o.sf_big(level) if level < o.L - 1 else 1.0)
+    got = cc.EvalMult(CiphertextBatch(to_device_u64(ct, cc.device), meta), c)
+    for g in range(n):
+        want, wmeta = o.eval_mult_const(ell, ct[g], dict(noise_scale_deg=2, level=level,
+                                                         scaling_factor=meta.scaling_factor), c)
+        assert np.array_equal(got.numpy()[g], want)
+    assert got.meta.level == wmeta["level"] and got.meta.noise_scale_deg == wmeta["noise_scale_deg"]
+    assert got.meta.scaling_factor == wmeta["scaling_factor"]
+    # multiply only (noiseScaleDeg 1)
+    meta1 = CtMeta(noise_scale_deg=1, level=level, scaling_factor=o.sf(level))
+    got1 = cc.EvalMult(CiphertextBatch(to_device_u64(ct, cc.device), meta1), c)
+    for g in range(n):
+        want1, _ = o.eval_mult_const(ell, ct[g], dict(noise_scale_deg=1, level=level, scaling_factor=o.sf(level)), c)
+        assert np.array_equal(got1.numpy()[g], want1)
+
+
+def test_encrypt_bit_exact_with_injected_samples_and_decrypt_core():
+    from ppqsflhe_b200 import PlaintextBatch, CtMeta, to_device_u64, to_host_u64
+    o, cc = _cc_pair("c1")
+    ell, n = 4, 3
+    s, sk, pkb, pka = o.keygen(31)
+    rng = np.random.default_rng(29)
+    pt = np.stack([_rand_poly(rng, o, range(ell)) for _ in range(n)])
+    small = np.stack([np.stack([oracle.sample_ternary(100 + g, o.N), oracle.sample_gauss(200 + g, o.N),
+                                oracle.sample_gauss(300 + g, o.N)]) for g in range(n)])
+    P = PlaintextBatch(data=to_device_u64(pt, cc.device), meta=CtMeta())
+    pk = (to_device_u64(pkb, cc.device), to_device_u64(pka, cc.device))
+    ct = cc.Encrypt(pk, P, small=torch.from_numpy(small).to(cc.device))
+    got = ct.numpy()
+    for g in range(n):
+        want = o.encrypt(ell, pkb, pka, pt[g], small[g][0], small[g][1], small[g][2])
+        assert np.array_equal(got[g], want)
+    co = to_host_u64(cc.DecryptCore(to_device_u64(sk, cc.device), ct))
+    for g in range(n):
+        assert np.array_equal(co[g], o.decrypt_core(ell, sk, got[g]))
+
+
+def test_encode_decode_tolerance():
+    """CKKS encode is not bit-reproducible: compare through decode.  Tolerance 2^-20 (north_star);
+    observed ~1e-9."""
+    from ppqsflhe_b200 import to_host_u64, to_device_u64
+    o, cc = _cc_pair("c1")
+    rng = np.random.default_rng(37)
+    n = 3
+    vals = np.clip(rng.normal(0, 0.05, (n, o.N // 2)), -0.3, 0.3)
+    vals[1, 5:] = 0.0  # a 5-value plaintext zero-padded to all slots, like `mean` / `std_dev`
+    P = cc.MakeCKKSPackedPlaintext(vals)
+    pt = to_host_u64(P.data)
+    sf = o.sf_big(0)
+    for g in range(n):
+        # (a) the GPU-encoded polynomial decodes (oracle decode) to the input
+        co = np.stack([o.ntt(i, pt[g][i], inverse=True) for i in range(o.L)])
+        back = o.decode(o.L, co, sf)
+        assert np.max(np.abs(back - vals[g])) < 2.0 ** -20
+        # (b) coefficients agree with the oracle's encoding up to FFT rounding (|diff| tiny relative to sf)
+        want = o.encode(o.L, vals[g], sf)
+        wco = o.ntt(0, want[0], inverse=True).astype(np.int64)
+        gco = co[0].astype(np.int64)
+        q0 = int(o.moduli[0])
+        diff = (gco - wco + q0 // 2) % q0 - q0 // 2
+        assert np.max(np.abs(diff)) <= 2 ** 12
+    # GPU decode of oracle-encoded data
+    enc = np.stack([o.encode(3, vals[g], o.sf(1) ** 2) for g in range(n)])
+    co = np.stack([[o.ntt(i, enc[g][i], inverse=True) for i in range(3)] for g in range(n)])
+    out = torch.empty((n, o.N // 2), dtype=torch.float64, device=cc.device)
+    from ppqsflhe_b200._capi import check, lib, vp
+    d = to_device_u64(co, cc.device)
+    check(lib().ppq_decode(cc.h, 3, vp(d.data_ptr()), o.sf(1) ** 2, vp(out.data_ptr()), n, None))
+    torch.cuda.synchronize()
+    assert np.max(np.abs(out.cpu().numpy() - vals)) < 2.0 ** -20
+    for g in range(n):
+        assert np.max(np.abs(out.cpu().numpy()[g] - o.decode(3, co[g], o.sf(1) ** 2))) < 1e-12
+
+
+def test_end_to_end_golden_round():
+    """The reference's recorded round: Enc(w1) under pk1 -> ReEncrypt to pk2 -> EvalAdd Enc(w2) -> EvalMult 0.5
+    -> Decrypt with sk2 must reproduce decrypted_weights_c2.json ((w1+w2)/2) within the CKKS tolerance 2^-20;
+    and the fan-out ReEncrypt(2->1) must decrypt under sk1 (decrypted_weights_c1.json)."""
+    from ppqsflhe_b200 import EvalKey, to_device_u64
+    o, cc = _cc_pair("c1")
+    g = np.load(os.path.join(ROOT, "tests", "golden", "weights_golden.npz"))
+    w1, w2 = g["c1_sample_values"].astype(np.float64), g["c2_sample_values"].astype(np.float64)
+    slots = o.N // 2
+    nct = (len(w1) + slots - 1) // slots
+
+    def chunks(w):
+        p = np.zeros(nct * slots)
+        p[: len(w)] = w
+        return p.reshape(nct, slots)
+
+    keys = {}
+    for c in (1, 2):
+        tern = np.load(os.path.join(ROOT, "tests", "golden", "openfhe_sk_golden.npz"))[f"c{c}_ternary"].astype(np.int64)
+        # scaffolding keygen from the oracle, but with the REAL OpenFHE secret of client c
+        s, sk, pkb, pka = o.keygen(40 + c)
+        sk = np.stack([o.small_to_eval(r, tern) for r in range(o.M)])
+        e = oracle.sample_gauss(900 + c, o.N)
+        pkb = np.stack([(o.small_to_eval(r, e).astype(object) - pka[r].astype(object) * sk[r].astype(object)) % int(o.moduli[r])
+                        for r in range(o.M)]).astype(np.uint64)
+        keys[c] = (sk, pkb, pka)
+    rk12 = EvalKey(cc, *o.rekeygen(51, keys[1][0], keys[2][1], keys[2][2]))
+    rk21 = EvalKey(cc, *o.rekeygen(52, keys[2][0], keys[1][1], keys[1][2]))
+    dev = cc.device
+    cts = {}
+    for c, w in ((1, w1), (2, w2)):
+        pt = cc.MakeCKKSPackedPlaintext(chunks(w))
+        cts[c] = cc.Encrypt((to_device_u64(keys[c][1], dev), to_device_u64(keys[c][2], dev)), pt, seed=1000 + c)
+    c12 = cc.ReEncrypt(cts[1], rk12)
+    agg = cc.EvalMult(cc.EvalAdd(cts[2], c12), 0.5)
+    assert agg.ell == 3 and agg.meta.level == 1 and agg.meta.noise_scale_deg == 2
+    assert abs(agg.meta.scaling_factor / 1.2089e24 - 1) < 1e-3
+    dec2 = cc.Decrypt(to_device_u64(keys[2][0], dev), agg).GetRealPackedValue().reshape(-1)[: len(w1)]
+    want = (w1 + w2) / 2
+    assert np.max(np.abs(dec2 - want)) < 2.0 ** -20
+    assert np.max(np.abs(dec2 - g["c2_decrypted_values"])) < 2.0 ** -20
+    back = cc.ReEncrypt(agg, rk21)
+    dec1 = cc.Decrypt(to_device_u64(keys[1][0], dev), back).GetRealPackedValue().reshape(-1)[: len(w1)]
+    assert np.max(np.abs(dec1 - g["c1_decrypted_values"])) < 2.0 ** -20
+    print("e2e max abs err:", np.max(np.abs(dec2 - want)), np.max(np.abs(dec1 - want)))
