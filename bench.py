@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py -- ReEncrypt+EvalAdd aggregation throughput (BASELINE.json metric) on N B200s of one node.
+
+One "step" = one full aggregation round of the workload: every client's ciphertexts are proxy re-encrypted with
+that client's re-encryption key (cc->ReEncrypt, server/src/changeCipherDomain.cpp:105) and summed into the
+per-slot running aggregate (cc->EvalAdd, server/src/aggregateEncryptedWeights.cpp:106); with N > 1 the clients are
+sharded across ranks and the per-rank partial sums are combined by ONE NCCL u64 sum-reduce + a final mod-q.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c3] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` = ciphertexts/s with inputs resident in HBM; `e2e` = the same metric
+through the host-buffer C-ABI call (H2D of every ciphertext and D2H of the aggregate inside the timed region).
+`--impl reference` times the reference's CPU algorithm (the oracle restatement of OpenFHE: the real OpenFHE is an
+un-vendored submodule absent from the reference tree) on the host cores with the same JSON shape.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# benchmark configurations.  slots = ciphertexts per client.
+CONFIGS = {
+    # name: logN, depth, first, scale, extra, dnum, clients, slots
+    "c1": dict(logN=14, depth=2, first=60, scale=40, extra=20, dnum=2, clients=2, slots=27,
+               desc="C1: 2-client GRU, CKKS N=2^14, 4 limbs (CC.json parameters)"),
+    "c2": dict(logN=15, depth=2, first=60, scale=40, extra=20, dnum=2, clients=8, slots=84,
+               desc="C2: 8-client LSTM (~1M params), CKKS N=2^15, 4 limbs"),
+    "c3": dict(logN=16, depth=18, first=60, scale=59, extra=20, dnum=3, clients=64, slots=54,
+               desc="C3: 64 clients x 54 cts, CKKS N=2^16, 20 limbs, dnum 3"),
+    "c4": dict(logN=17, depth=38, first=60, scale=59, extra=20, dnum=3, clients=16, slots=16,
+               desc="C4: 16 clients x 16 cts, CKKS N=2^17, 40 limbs, dnum 3"),
+}
+METRIC = "ciphertexts/s ReEncrypt+EvalAdd at N=2^16"
+UNIT = "ciphertexts/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def stage_alg_words(ell, K, parts, bk):
+    """Algorithmic (compulsory) u64 words per ciphertext, in units of N, for each of the 9 pipeline kernels
+    (DESIGN.md 'kernels').  bk = ciphertexts sharing one rekey inside a call (key traffic is amortised)."""
+    M = ell + K
+    conv = parts * M - ell
+    return [
+        2 * ell,                                   # k_inv_row(c1):        R ell + W ell
+        2 * ell,                                   # k_inv_col(c1):        R ell + W ell
+        ell + conv,                                # k_bconv(modup):       R ell (COEFF digits) + W converted limbs
+        2 * conv,                                  # k_fwd_col(modup):     R + W converted limbs
+        conv + ell + 2 * parts * M / bk + 2 * M,   # k_fwd_row_ip:         R digits + R own c1 + R keys/bk + W 2(ell+K)
+        4 * K,                                     # k_inv_col(P):         R 2K + W 2K
+        2 * K + 2 * ell,                           # k_bconv(moddown):     R 2K + W 2 ell
+        4 * ell,                                   # k_fwd_col(moddown):   R 2 ell + W 2 ell
+        9 * ell,                                   # k_fwd_row_moddown:    R conv 2l + R ext 2l + R c0 l + R acc 2l + W 2l
+    ]
+
+
+def path_alg_bytes(N, ell, K, dnum, bk):
+    """W_alg = 8 N (13 ell + 4 K + 2 dnum (ell+K) / B_k) bytes per ciphertext (ideal fusion)."""
+    return 8.0 * N * (13 * ell + 4 * K + 2.0 * dnum * (ell + K) / bk)
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+                pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_run(cfg, steps, warmup, sample_slots=None):
+    """The reference's CPU algorithm (oracle restatement of the OpenFHE path) on all host threads, on a bounded
+    sample of the workload: ONE client's rekey and `sample_slots` of its ciphertexts per step."""
+    import oracle
+    o = oracle.Oracle.synthetic(cfg["logN"], cfg["depth"], cfg["first"], cfg["scale"], cfg["extra"], cfg["dnum"])
+    T = oracle.max_threads()
+    ell = o.L
+    ct_bytes = 2 * ell * o.N * 8
+    if sample_slots is None:
+        sample_slots = max(2, min(4 * T, int((4 << 30) // ct_bytes), 256))
+    rng = np.random.default_rng(42)
+    q = o.moduli.astype(np.uint64)
+    cts = (rng.integers(0, 1 << 62, (1, sample_slots, 2, ell, o.N), dtype=np.uint64) % q[:ell].reshape(1, 1, 1, ell, 1))
+    kb = rng.integers(0, 1 << 62, (o.dnum, o.M, o.N), dtype=np.uint64) % q.reshape(1, o.M, 1)
+    ka = rng.integers(0, 1 << 62, (o.dnum, o.M, o.N), dtype=np.uint64) % q.reshape(1, o.M, 1)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        o.reencrypt_accumulate_batch(ell, cts, [kb], [ka], nthreads=T)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    t = float(np.median(times))
+    return {"value": sample_slots / t, "unit": UNIT, "cores": T, "kind": "port",
+            "sample": f"{sample_slots} ciphertexts of 1 client (ell={ell}, N=2^{o.logN}, K={o.K}, dnum={o.dnum}) per step, "
+                      f"{steps} steps after {warmup} warm-up, median; OpenFHE-algorithm CPU restatement (oracle/), "
+                      f"OpenMP over ciphertexts",
+            "ms_per_step": t * 1e3, "_ell": ell, "_K": o.K}
+
+
+def reference_arm(args, cfg):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
+    r = cpu_run(cfg, steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": cfg["desc"], "impl_note": "CPU, host cores only; each step is a bounded sample"},
+        "cpu_baseline": {k: v for k, v in r.items() if not k.startswith("_") and k != "ms_per_step"},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
+    ap.add_argument("--clients", type=int, default=0)
+    ap.add_argument("--slots", type=int, default=0)
+    ap.add_argument("--wave", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    cfg = dict(CONFIGS[args.config])
+    if args.clients:
+        cfg["clients"] = args.clients
+    if args.slots:
+        cfg["slots"] = args.slots
+    if args.impl == "reference":
+        return reference_arm(args, cfg)
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import torch
+    import torch.distributed as dist
+    from ppqsflhe_b200 import CiphertextBatch, CryptoContext, CtMeta, EvalKey
+    from ppqsflhe_b200._capi import check, lib, vp
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node N for --gpus N"
+
+    cc = CryptoContext.synthetic(cfg["logN"], cfg["depth"], cfg["first"], cfg["scale"], cfg["extra"], cfg["dnum"], local)
+    if args.wave:
+        cc.set_wave(args.wave)
+    ell, K, N, M = cc.L, cc.K, cc.N, cc.M
+    parts = cc.num_parts(ell)
+    n_slots = cfg["slots"]
+    my_clients = [c for c in range(cfg["clients"]) if c % world == rank]
+    qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
+
+    def rand_res(shape, q):  # uniform-ish residues, canonical
+        x = torch.randint(0, 1 << 62, shape, dtype=torch.int64, device=dev)
+        return x.remainder_(q)
+
+    torch.manual_seed(42 + rank)
+    cts = [CiphertextBatch(rand_res((n_slots, 2, ell, N), qv[:ell].view(1, 1, ell, 1)), CtMeta()) for _ in my_clients]
+    keys = [EvalKey(cc, rand_res((cc.dnum, M, N), qv.view(1, M, 1)), rand_res((cc.dnum, M, N), qv.view(1, M, 1)))
+            for _ in my_clients]
+    acc = CiphertextBatch(torch.zeros((n_slots, 2, ell, N), dtype=torch.int64, device=dev), CtMeta())
+    torch.cuda.synchronize()
+
+    def step():
+        acc.data.zero_()
+        for ct, rk in zip(cts, keys):
+            cc.ReEncryptAccumulate(ct, rk, acc)
+        if world > 1:
+            dist.reduce(acc.data, dst=0, op=dist.ReduceOp.SUM)  # residues < 2^60: an 8-way u64 sum cannot wrap
+            if rank == 0:
+                cc.finalize_sum(acc)
+
+    def timed(fn, k):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    check(lib().ppq_profile_enable(cc.h, 1))
+    sampler = ClockSampler(local)
+    sampler.start()
+    total_ms = timed(step, args.steps)
+    clocks = sampler.stop()
+    NST = 9  # PPQ_PROFILE_STAGES
+    pms = (C.c_double * NST)()
+    pl = (C.c_uint64 * NST)()
+    check(lib().ppq_profile_read(cc.h, pms, pl, 1))
+    check(lib().ppq_profile_enable(cc.h, 0))
+    stage_ms, stage_launches = list(pms), list(pl)
+    n_ct_step = cfg["clients"] * n_slots
+    ms_per_step = total_ms / args.steps
+    value = n_ct_step / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (CUDA events around every launch of it, inside the timed region)
+    peak, peak_src = peaks()
+    names = [lib().ppq_profile_stage_name(i).decode() for i in range(NST)]
+    dom = int(np.argmax(stage_ms))
+    words = stage_alg_words(ell, K, parts, n_slots)
+    local_ct = len(my_clients) * n_slots * args.steps
+    dom_bytes = words[dom] * 8.0 * N * local_ct
+    achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(args.config, {}).get(names[dom])
+        except Exception:
+            traffic = None
+    w_alg = path_alg_bytes(N, ell, K, cc.dnum, n_slots)
+    roofline = {
+        "bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+        "launch_avg_ms": stage_ms[dom] / max(1, stage_launches[dom]),
+        "alg_bytes_per_ct": words[dom] * 8.0 * N,
+        "stage_share": {n: (m / max(1e-9, sum(stage_ms))) for n, m in zip(names, stage_ms)},
+        "stage_gbs": {n: (w * 8.0 * N * local_ct / (m * 1e-3) / 1e9 if m > 0 else 0.0)
+                      for n, w, m in zip(names, words, stage_ms)},
+        "path": {"alg_bytes_per_ct": w_alg, "achieved": value / world * w_alg / 1e9, "frac": value / world * w_alg / 1e9 / peak,
+                 "note": "whole ReEncrypt+EvalAdd path per GPU against SURVEY 8(d) W_alg (ideal fusion)"},
+    }
+    gpu_launches = int(sum(stage_launches)) + (args.steps if (world > 1 and rank == 0) else 0)
+
+    # ---- e2e: host buffers in, aggregate out, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        blk = n_slots * 2 * ell * N
+        pool_n = max(1, min(len(my_clients), 4))
+        pool = [torch.empty(blk, dtype=torch.int64).pin_memory() for _ in range(pool_n)]
+        for i, p in enumerate(pool):
+            p.copy_(cts[i].data.view(-1))
+        h_acc = torch.empty(blk, dtype=torch.int64).pin_memory()
+        h2d = len(my_clients) * blk * 8
+        d2h = blk * 8 if rank == 0 else 0
+        if world == 1:
+            rks = (vp * len(keys))(*[k.h for k in keys])
+            ptrs = (vp * len(keys))(*[pool[i % pool_n].data_ptr() for i in range(len(keys))])
+
+            def e2e_step():
+                check(lib().ppq_reencrypt_aggregate_host(cc.h, rks, ell, ptrs, len(keys), n_slots, vp(h_acc.data_ptr())))
+        else:
+            side = torch.cuda.Stream()
+            dbuf = [torch.empty((n_slots, 2, ell, N), dtype=torch.int64, device=dev) for _ in range(2)]
+            up = [torch.cuda.Event() for _ in range(2)]
+            done = [torch.cuda.Event() for _ in range(2)]
+
+            def e2e_step():
+                main_s = torch.cuda.current_stream()
+                acc.data.zero_()
+                for i, rk in enumerate(keys):
+                    b = i & 1
+                    with torch.cuda.stream(side):
+                        if i >= 2:
+                            side.wait_event(done[b])
+                        dbuf[b].view(-1).copy_(pool[i % pool_n], non_blocking=True)
+                        up[b].record(side)
+                    main_s.wait_event(up[b])
+                    cc.ReEncryptAccumulate(CiphertextBatch(dbuf[b], CtMeta()), rk, acc)
+                    done[b].record(main_s)
+                dist.reduce(acc.data, dst=0, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    cc.finalize_sum(acc)
+                    h_acc.copy_(acc.data.view(-1), non_blocking=True)
+                torch.cuda.synchronize()
+
+        for _ in range(args.warmup):
+            e2e_step()
+        e_ms = timed(e2e_step, args.steps)
+        tot = torch.tensor([float(h2d), float(d2h)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tot)
+        e2e = {"value": n_ct_step / (e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(tot[0].item()),
+               "d2h_bytes_per_step": int(tot[1].item()), "ms_per_step": e_ms / args.steps,
+               "api": "ppq_reencrypt_aggregate_host (C ABI, pinned host buffers)" if world == 1 else
+                      "CryptoContext.ReEncryptAccumulate over pinned host buffers + NCCL reduce",
+               "note": f"every client's {blk * 8 >> 20} MiB upload is copied each step from a pool of {pool_n} pinned buffers"}
+        del pool, h_acc
+
+    # ---- CPU baseline on rank 0, N = 1 only
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        del cts, keys
+        torch.cuda.empty_cache()
+        r = cpu_run(cfg, 1, 1)
+        cpu = {k: v for k, v in r.items() if not k.startswith("_") and k != "ms_per_step"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": cfg["desc"], "clients": cfg["clients"], "cts_per_client": n_slots, "logN": cfg["logN"],
+                       "limbs": ell, "aux_limbs": K, "dnum": cc.dnum, "parallelism": f"clients sharded over {world} GPU(s)",
+                       "l2": "inputs per step (%.1f GiB per GPU) >> 126 MB L2; no flush needed" %
+                             (len(my_clients) * n_slots * 2 * ell * N * 8 / 2 ** 30),
+                       "residues": "uniform random canonical residues (timing is data independent)"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -124,11 +124,19 @@ int ppq_decrypt_core(ppq_ctx*, int ell, const uint64_t* d_sk, const uint64_t* d_
  *      by sf, special FFT; d_vals [n][N/2].  OpenFHE's randomised decode noise is not added. */
 int ppq_decode(ppq_ctx*, int ell, const uint64_t* d_coeff, double sf, double* d_vals, size_t n, void* stream);
 
-/* ---- host-buffer convenience (the call a drop-in server makes): copies in, computes, copies out.
- *      h_cts [n_clients][n_slots][2][ell][N]; rekeys[n_clients]; h_acc [n_slots][2][ell][N] =
- *      sum over clients of ReEncrypt(ct, rekey[client]).  Synchronous. */
-int ppq_reencrypt_aggregate_host(ppq_ctx*, const ppq_rekey* const* rekeys, int ell, const uint64_t* h_cts,
+/* ---- host-buffer convenience (the call a drop-in server makes once every client's upload has arrived):
+ *      h_cts[client] -> [n_slots][2][ell][N] in host memory (pinned for full PCIe rate); rekeys[n_clients];
+ *      h_acc [n_slots][2][ell][N] = sum over clients of ReEncrypt(ct, rekey[client]).  Uploads are double
+ *      buffered against the kernels.  Synchronous. */
+int ppq_reencrypt_aggregate_host(ppq_ctx*, const ppq_rekey* const* rekeys, int ell, const uint64_t* const* h_cts,
                                  size_t n_clients, size_t n_slots, uint64_t* h_acc);
+
+/* ---- per-stage device timing of the key-switch pipeline (CUDA events on the caller's stream).
+ *      stage s < PPQ_PROFILE_STAGES: see ppq_profile_stage_name.  ms / launches: arrays of that length. */
+#define PPQ_PROFILE_STAGES 9
+int ppq_profile_enable(ppq_ctx*, int on);
+int ppq_profile_read(ppq_ctx*, double* ms, uint64_t* launches, int reset);
+const char* ppq_profile_stage_name(int stage);
 
 #ifdef __cplusplus
 }

@@ -65,7 +65,10 @@ _SIGS = {
     "ppq_sample_encrypt_noise": (C.c_int, [vp, C.c_uint64, vp, C.c_size_t, vp]),
     "ppq_decrypt_core": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_size_t, vp]),
     "ppq_decode": (C.c_int, [vp, C.c_int, vp, C.c_double, vp, C.c_size_t, vp]),
-    "ppq_reencrypt_aggregate_host": (C.c_int, [vp, C.POINTER(vp), C.c_int, vp, C.c_size_t, C.c_size_t, vp]),
+    "ppq_reencrypt_aggregate_host": (C.c_int, [vp, C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
+    "ppq_profile_enable": (C.c_int, [vp, C.c_int]),
+    "ppq_profile_read": (C.c_int, [vp, f64p, u64p, C.c_int]),
+    "ppq_profile_stage_name": (C.c_char_p, [C.c_int]),
 }
 
 _lib = None

@@ -63,6 +63,10 @@ static std::vector<BcJob> to_dev_jobs(const std::vector<host::Job>& j) {
 
 struct KsPlanDev {
     host::KsPlan h;
+    struct Digit { int job_first, n_jobs, ns; };
+    std::vector<Digit> digits;  // ModUp jobs grouped by source digit
+    DevBuf<int> dig_ids;        // [parts*(ell+K)] limb of every digit slot, -1 for the digit's own limbs
+    DevBuf<int> conv_ids;       // [2*ell] limb of every ModDown slot
     DevBuf<int> c1_limb, p_limb;
     DevBuf<u64> c1_scale, c1_scale_sh, p_scale, p_scale_sh, up_chat, down_chat, pinv, pinv_sh;
     DevBuf<BcJob> up_jobs, down_jobs;
@@ -89,6 +93,19 @@ struct ppq_ctx {
     DevBuf<u64> fac;       // [2][L] EvalMult factors
     ckks::Tables fft;
     int wave = 0;
+    // per-stage CUDA-event profiling of the key-switch pipeline (ppq_profile_*)
+    static const int NSTAGE = 9, RING = 64;
+    bool prof = false;
+    cudaEvent_t ev[RING][NSTAGE + 1] = {};
+    bool ev_made = false, ev_used[RING] = {};
+    unsigned long long prof_wave = 0;
+    double prof_ms[NSTAGE] = {};
+    unsigned long long prof_launches[NSTAGE] = {};
+    ~ppq_ctx() {
+        if (ev_made)
+            for (int i = 0; i < RING; ++i)
+                for (int j = 0; j <= NSTAGE; ++j) cudaEventDestroy(ev[i][j]);
+    }
 };
 struct ppq_rekey {
     ppq_ctx* ctx = nullptr;
@@ -298,6 +315,20 @@ static int get_ks_plan(ppq_ctx* c, int ell, KsPlanDev** out) {
         CU(p->pinv_sh.upload(p->h.pinv_sh));
         CU(p->up_jobs.upload(to_dev_jobs(p->h.up_jobs)));
         CU(p->down_jobs.upload(to_dev_jobs(p->h.down_jobs)));
+        {
+            const int M = ell + c->hp.K;
+            std::vector<int> ids((size_t)p->h.parts * M, -1), cids(2 * (size_t)ell);
+            for (size_t i = 0; i < p->h.up_jobs.size(); ++i) {
+                const host::Job& jb = p->h.up_jobs[i];
+                ids[jb.dst_slot] = jb.limb;
+                if (p->digits.empty() || p->h.up_jobs[p->digits.back().job_first].src_first != jb.src_first)
+                    p->digits.push_back({(int)i, 0, jb.ns});
+                p->digits.back().n_jobs++;
+            }
+            for (int i = 0; i < 2 * ell; ++i) cids[i] = i % ell;
+            CU(p->dig_ids.upload(ids));
+            CU(p->conv_ids.upload(cids));
+        }
         it = c->ks.emplace(ell, std::move(p)).first;
     }
     *out = it->second.get();
@@ -336,6 +367,53 @@ static int pick_wave(const ppq_ctx* c, const WaveLayout& w, size_t n) {
     return (int)g;
 }
 
+static void prof_collect(ppq_ctx* c, int slot) {
+    if (!c->ev_used[slot]) return;
+    cudaEventSynchronize(c->ev[slot][ppq_ctx::NSTAGE]);
+    for (int s = 0; s < ppq_ctx::NSTAGE; ++s) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c->ev[slot][s], c->ev[slot][s + 1]) == cudaSuccess) {
+            c->prof_ms[s] += ms;
+            c->prof_launches[s] += 1;
+        }
+    }
+    c->ev_used[slot] = false;
+}
+extern "C" int ppq_profile_enable(ppq_ctx* c, int on) {
+    if (!c) return fail(PPQ_EINVAL, "null");
+    CU(cudaSetDevice(c->device));
+    if (on && !c->ev_made) {
+        for (int i = 0; i < ppq_ctx::RING; ++i)
+            for (int j = 0; j <= ppq_ctx::NSTAGE; ++j) CU(cudaEventCreate(&c->ev[i][j]));
+        c->ev_made = true;
+    }
+    if (c->ev_made)
+        for (int i = 0; i < ppq_ctx::RING; ++i) prof_collect(c, i);
+    c->prof = on != 0;
+    return PPQ_OK;
+}
+extern "C" int ppq_profile_read(ppq_ctx* c, double* ms, uint64_t* launches, int reset) {
+    if (!c || !ms || !launches) return fail(PPQ_EINVAL, "null");
+    CU(cudaSetDevice(c->device));
+    if (c->ev_made)
+        for (int i = 0; i < ppq_ctx::RING; ++i) prof_collect(c, i);
+    for (int s = 0; s < ppq_ctx::NSTAGE; ++s) {
+        ms[s] = c->prof_ms[s];
+        launches[s] = c->prof_launches[s];
+        if (reset) {
+            c->prof_ms[s] = 0;
+            c->prof_launches[s] = 0;
+        }
+    }
+    return PPQ_OK;
+}
+extern "C" const char* ppq_profile_stage_name(int s) {
+    static const char* names[ppq_ctx::NSTAGE] = {"k_inv_row(c1)",     "k_inv_col(c1,scale)", "k_bconv(modup)",
+                                                 "k_fwd_col(modup)",  "k_fwd_row_ip",        "k_inv_col(P,scale)",
+                                                 "k_bconv(moddown)",  "k_fwd_col(moddown)",  "k_fwd_row_moddown"};
+    return (s >= 0 && s < ppq_ctx::NSTAGE) ? names[s] : "";
+}
+
 // shared driver: out[g] = (accumulate ? out[g] : 0) + ReEncrypt(in[g])
 static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64* in, u64* out, size_t n, void* stream,
                             int accumulate) {
@@ -362,11 +440,26 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         const int ng = (int)std::min((size_t)G, n - g0);
         const u64* in_g = in + g0 * ct;
         u64* out_g = out + g0 * ct;
+        const int slot = (int)(c->prof_wave % ppq_ctx::RING);
+        cudaEvent_t* ev = c->ev[slot];
+        const bool prof = c->prof;
+        if (prof) {
+            prof_collect(c, slot);
+            cudaEventRecord(ev[0], st);
+        }
         // 1-2. c1 -> COEFF, scaled by N^-1 (D_j/q_i)^-1
         launch_inv_row(c->k, in_g + (size_t)ell * N, ct, y, w.y, p->c1_limb.p, ell, ng, st);
+        if (prof) cudaEventRecord(ev[1], st);
         launch_inv_col(c->k, y, w.y, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, ng, st);
-        // 3. ModUp: approximate basis switch fused into the forward COL pass
-        launch_bc_fwd_col(c->k, y, w.y, dig, w.dig, p->up_jobs.p, (int)p->h.up_jobs.size(), p->up_chat.p, ng, 0, 0, st);
+        if (prof) cudaEventRecord(ev[2], st);
+        // 3. ModUp: approximate basis switch of every digit to its complementary limbs (pointwise)
+        for (const auto& d : p->digits)
+            if (!launch_bconv(c->k, y, w.y, dig, w.dig, p->up_jobs.p + d.job_first, d.n_jobs, p->up_chat.p, d.ns, ng, st))
+                return fail(PPQ_EINVAL, "digit wider than 32 limbs");
+        if (prof) cudaEventRecord(ev[3], st);
+        // 3b. forward COL pass of the converted limbs (the digit's own limbs stay as they are in c1)
+        launch_fwd_col_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
+        if (prof) cudaEventRecord(ev[4], st);
         // 4. forward ROW pass + inner product with the rekey (+ inverse ROW pass on the P limbs)
         IpArgs ia;
         ia.c1 = in_g + (size_t)ell * N;
@@ -385,10 +478,18 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ia.parts = parts;
         ia.alpha = c->hp.alpha;
         launch_fwd_row_ip(c->k, ia, ng, st);
+        if (prof) cudaEventRecord(ev[5], st);
         // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
         launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, p->p_scale_sh.p, 2 * K, ng, st);
-        // 6. ModDown conversion P -> Q fused into the forward COL pass (digits buffer is dead: reuse it)
-        launch_bc_fwd_col(c->k, extp, w.extp, dig, w.dig, p->down_jobs.p, (int)p->h.down_jobs.size(), p->down_chat.p, ng, 0, 0, st);
+        if (prof) cudaEventRecord(ev[6], st);
+        // 6. ModDown conversion P -> Q (pointwise; the digits buffer is dead: reuse it), then its COL pass
+        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.p, ell, p->down_chat.p, K, ng, st))
+            return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
+        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.p + ell, ell, p->down_chat.p, K, ng, st))
+            return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
+        if (prof) cudaEventRecord(ev[7], st);
+        launch_fwd_col_plain(c->k, dig, w.dig, p->conv_ids.p, 2 * ell, ng, st);
+        if (prof) cudaEventRecord(ev[8], st);
         // 7. forward ROW pass + (x - conv) P^-1 + c0 (+ running sum)
         MdArgs ma;
         ma.conv = dig;
@@ -404,6 +505,11 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ma.ell = ell;
         ma.accumulate = accumulate;
         launch_fwd_row_moddown(c->k, ma, ng, st);
+        if (prof) {
+            cudaEventRecord(ev[9], st);
+            c->ev_used[slot] = true;
+            c->prof_wave++;
+        }
     }
     CU(cudaGetLastError());
     return PPQ_OK;
@@ -436,7 +542,10 @@ extern "C" int ppq_ks_modup(ppq_ctx* c, int ell, const uint64_t* d_c1, uint64_t*
     u64* y = c->scratch.p;
     launch_inv_row(c->k, (const u64*)d_c1, ys, y, ys, p->c1_limb.p, ell, (int)n, st);
     launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, (int)n, st);
-    launch_bc_fwd_col(c->k, y, ys, (u64*)d_digits, ds, p->up_jobs.p, (int)p->h.up_jobs.size(), p->up_chat.p, (int)n, 0, 0, st);
+    for (const auto& d : p->digits)
+        if (!launch_bconv(c->k, y, ys, (u64*)d_digits, ds, p->up_jobs.p + d.job_first, d.n_jobs, p->up_chat.p, d.ns, (int)n, st))
+            return fail(PPQ_EINVAL, "digit wider than 32 limbs");
+    launch_fwd_col_plain(c->k, (u64*)d_digits, ds, p->dig_ids.p, parts * M, (int)n, st);
     // finish the converted limbs with a plain ROW pass; own-digit limbs are copies of c1
     std::vector<int> ids((size_t)parts * M);
     for (int j = 0; j < parts; ++j)
@@ -532,7 +641,7 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
         launch_inv_row(c->k, (const u64*)in + ((size_t)poly * ell + lo) * N, ct, r + (size_t)poly * N, rs_,
                        p->last_limb.p, 1, (int)n, st);
     launch_inv_col(c->k, r, rs_, p->last_limb.p, p->last_scale.p, p->last_scale_sh.p, 2, (int)n, st);
-    launch_bc_fwd_col(c->k, r, rs_, conv, cs_, p->jobs.p, (int)p->h.jobs.size(), nullptr, (int)n, 1, c->hp.mod[lo], st);
+    launch_sw_fwd_col(c->k, r, rs_, conv, cs_, p->jobs.p, (int)p->h.jobs.size(), (int)n, c->hp.mod[lo], st);
     RsArgs ra;
     ra.conv = conv;
     ra.conv_gs = cs_;
@@ -652,8 +761,9 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
 }
 
 // ------------------------------------------------------------------------------------------- host-buffer path
-extern "C" int ppq_reencrypt_aggregate_host(ppq_ctx* c, const ppq_rekey* const* rekeys, int ell, const uint64_t* h_cts,
-                                            size_t n_clients, size_t n_slots, uint64_t* h_acc) {
+extern "C" int ppq_reencrypt_aggregate_host(ppq_ctx* c, const ppq_rekey* const* rekeys, int ell,
+                                            const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                            uint64_t* h_acc) {
     if (!c || !rekeys || !h_cts || !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null argument");
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: bad limb count");
     if (!n_clients || !n_slots) return PPQ_OK;
@@ -677,7 +787,8 @@ extern "C" int ppq_reencrypt_aggregate_host(ppq_ctx* c, const ppq_rekey* const* 
     for (size_t cl = 0; cl < n_clients && rc == PPQ_OK; ++cl) {
         const int b = (int)(cl & 1);
         if (cl >= 2) CU(cudaStreamWaitEvent(sc, done[b], 0));
-        CU(cudaMemcpyAsync(in[b].p, h_cts + cl * blk, blk * sizeof(u64), cudaMemcpyHostToDevice, sc));
+        if (!h_cts[cl] || !rekeys[cl]) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null client entry");
+        CU(cudaMemcpyAsync(in[b].p, h_cts[cl], blk * sizeof(u64), cudaMemcpyHostToDevice, sc));
         CU(cudaEventRecord(up[b], sc));
         CU(cudaStreamWaitEvent(sx, up[b], 0));
         rc = reencrypt_common(c, rekeys[cl], ell, in[b].p, acc.p, n_slots, sx, 1);

@@ -45,8 +45,7 @@ __device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
 // =========================================================================================================
 // COL passes
 // =========================================================================================================
-// MODE 0: plain (src poly = blockIdx.y, limb from limb_ids)
-// MODE 1: approximate CRT basis switch prologue (ApproxSwitchCRTBasis: sum_i y_i * chat_i mod t, uncorrected)
+// MODE 0: plain (src poly = blockIdx.y, limb from limb_ids; a negative limb id skips the slot)
 // MODE 2: centred SwitchModulus prologue (DropLastElementAndScale)
 template <int S, int W, int MODE>
 __global__ void __launch_bounds__(W << (S - 3))
@@ -64,6 +63,7 @@ __global__ void __launch_bounds__(W << (S - 3))
     u64* out;
     if (MODE == 0) {
         limb = limb_ids[y];
+        if (limb < 0) return;  // block-uniform
         in = src + g * src_gs + (size_t)y * N;
         out = dst + g * dst_gs + (size_t)y * N;
     } else {
@@ -81,23 +81,6 @@ __global__ void __launch_bounds__(W << (S - 3))
     if (MODE == 0) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + (size_t)point_of<S - 3>(u, k) * n2 + col);
-    } else if (MODE == 1) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) a[k] = 0;
-        for (int i0 = 0; i0 < ns; i0 += 8) {
-            u64 hi[8], lo[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) hi[k] = lo[k] = 0;
-            const int i1 = min(ns, i0 + 8);
-            for (int i = i0; i < i1; ++i) {
-                const u64 ch = __ldg(chat + chat_off + i);
-                const u64* p = in + (size_t)i * N + col;
-#pragma unroll
-                for (int k = 0; k < 8; ++k) mac128(hi[k], lo[k], p[(size_t)point_of<S - 3>(u, k) * n2], ch);
-            }
-#pragma unroll
-            for (int k = 0; k < 8; ++k) a[k] += barrett128(hi[k], lo[k], lc);  // <= 4 chunks: stays < 4q
-        }
     } else {
         const u64 half = q_src >> 1;
         const u64 qs_mod = reduce64(q_src, lc);
@@ -109,9 +92,9 @@ __global__ void __launch_bounds__(W << (S - 3))
         }
     }
     ColPos<W> pos{w};
-    fwd_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2, false);
+    fwd_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy [0,4q): consumed by a ROW pass
+    for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy [0,8q): consumed by a ROW pass
 }
 
 template <int S, int W>
@@ -131,10 +114,52 @@ __global__ void __launch_bounds__(W << (S - 3))
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = p[(size_t)(8 * u + k) * n2];
     ColPos<W> pos{w};
-    inv_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2, false);
+    inv_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false);
     const u64 sc = scale[y], scs = scale_sh[y];
 #pragma unroll
     for (int k = 0; k < 8; ++k) p[(size_t)point_of<S - 3>(u, k) * n2] = mul_shoup(a[k], sc, scs, lc.q);
+}
+
+// =========================================================================================================
+// Approximate CRT basis switch (DCRTPolyImpl::ApproxSwitchCRTBasis), pointwise over coefficients:
+//   dst[job.dst_slot][n] = ( sum_{i<NS} src[src_first+i][n] * chat[job.chat_off+i] ) mod q_{job.limb}
+// WITHOUT the overflow correction (bit-exactness with OpenFHE needs the approximate form).  One thread owns
+// one coefficient: its NS source residues are loaded once (coalesced) and reused for the TPB targets of this
+// block; products accumulate in 128 bits and are Barrett-reduced once per 8 terms.  All jobs of a launch
+// share (src_first, NS).  Sources are canonical COEFF residues already scaled by (D/q_i)^-1 (k_inv_col).
+// =========================================================================================================
+template <int NS, int TPB>
+__global__ void __launch_bounds__(256)
+    k_bconv(KCtx c, const u64* __restrict__ src, size_t src_gs, u64* __restrict__ dst, size_t dst_gs,
+            const BcJob* __restrict__ jobs, int n_jobs, const u64* __restrict__ chat) {
+    const u32 N = 1u << c.logN;
+    const u32 n = blockIdx.x * 256 + threadIdx.x;
+    const u32 g = blockIdx.z;
+    const int j0 = blockIdx.y * TPB;
+    const BcJob first = jobs[j0];
+    const u64* in = src + g * src_gs + (size_t)first.src_first * N + n;
+    u64 y[NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) y[i] = in[(size_t)i * N];
+    u64* out = dst + g * dst_gs + n;
+#pragma unroll
+    for (int t = 0; t < TPB; ++t) {
+        if (j0 + t < n_jobs) {  // block-uniform
+            const BcJob jb = jobs[j0 + t];
+            const LimbC lc = c.limbs[jb.limb];
+            const u64* ch = chat + jb.chat_off;
+            u64 r = 0;
+#pragma unroll
+            for (int i0 = 0; i0 < NS; i0 += 8) {
+                u64 hi = 0, lo = 0;
+#pragma unroll
+                for (int i = i0; i < (i0 + 8 < NS ? i0 + 8 : NS); ++i) mac128(hi, lo, y[i], __ldg(ch + i));
+                r += barrett128(hi, lo, lc);
+            }
+            if (NS > 8) r = canon4(r, lc);  // at most 4 chunks
+            out[(size_t)jb.dst_slot * N] = r;
+        }
+    }
 }
 
 // =========================================================================================================
@@ -166,9 +191,9 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS)
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = p[point_of<S - 3>(u, k)];
     RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = csub(csub(a[k], lc.q2), lc.q);
+    for (int k = 0; k < 8; ++k) a[k] = canon8(a[k], lc);
     st8(p + 8 * u, a);
 }
 
@@ -189,10 +214,10 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS)
     u64 a[8];
     ld8(a, in + g * in_gs + off + 8 * u);
     RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-    inv_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    inv_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
     u64* o = out + g * out_gs + off;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy [0,2q): consumed by k_inv_col
+    for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy [0,4q): consumed by k_inv_col
 }
 
 // Forward ROW pass + inner product with the re-encryption key (+ inverse ROW pass on the P limbs).
@@ -225,9 +250,9 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_ip(KCtx c, IpAr
             const u64* in = A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
 #pragma unroll
             for (int k = 0; k < 8; ++k) d[k] = ld_stream(in + point_of<S - 3>(u, k));
-            fwd_pass<S>(d, sm, pos, u, tw, n1 + row, lc.q, lc.q2, true);
+            fwd_pass<S>(d, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) d[k] = csub(csub(d[k], lc.q2), lc.q);
+            for (int k = 0; k < 8; ++k) d[k] = canon8(d[k], lc);
         }
         u64 kb[8], ka[8];
         const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off + 8 * u;
@@ -252,11 +277,11 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_ip(KCtx c, IpAr
     } else {  // P limb: ModDown needs it in COEFF -> run the inverse ROW pass while the tile is in registers
         const ulonglong2* twi = c.twi + (size_t)limb * N;
         u64* o = A.extp + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
-        inv_pass<S>(e0, sm, pos, u, twi, n1 + row, lc.q, lc.q2, true);
+        inv_pass<S>(e0, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e0[k];
         o += (size_t)A.K * N;
-        inv_pass<S>(e1, sm, pos, u, twi, n1 + row, lc.q, lc.q2, true);
+        inv_pass<S>(e1, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e1[k];
     }
@@ -281,13 +306,13 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c,
     const u64* in = A.conv + g * A.conv_gs + off;
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
-    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
     u64 x[8];
     ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
     const u64 pi = A.pinv[i], pis = A.pinv_sh[i];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const u64 v = csub(csub(a[k], lc.q2), lc.q);
+        const u64 v = canon8(a[k], lc);
         a[k] = mul_shoup(x[k] + lc.q - v, pi, pis, lc.q);
     }
     if (poly == 0) {
@@ -324,13 +349,13 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_rescale(KCtx c,
     const u64* in = A.conv + g * A.conv_gs + (size_t)y * N + roff;
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
-    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2, false);
+    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
     u64 x[8];
     ld8(x, A.ct_in + g * A.in_gs + ((size_t)poly * A.ell + i) * N + roff + 8 * u);
     const u64 cs = A.cst[i], css = A.cst_sh[i];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const u64 v = csub(csub(a[k], lc.q2), lc.q);
+        const u64 v = canon8(a[k], lc);
         a[k] = mul_shoup(x[k] + lc.q - v, cs, css, lc.q);
     }
     st8(A.out + g * A.out_gs + (size_t)y * N + roff + 8 * u, a);
@@ -507,14 +532,36 @@ void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u
     launch_inv_col(c, data, 0, d_limb_ids, d_scale, d_scale_sh, n_polys, 1, st);
 }
 
-void launch_bc_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
-                       int n_jobs, const u64* d_chat, int n_g, int mode, u64 q_src, cudaStream_t st) {
+void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
+                          cudaStream_t st) {
     const Split sp = split_of(c.logN);
-    if (mode == 0) {
-        PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 1>(c, src, src_gs, dst, dst_gs, d_jobs, d_chat, nullptr, 0, n_jobs, n_g, st)));
-    } else {
-        PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 2>(c, src, src_gs, dst, dst_gs, d_jobs, d_chat, nullptr, q_src, n_jobs, n_g, st)));
+    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 0>(c, data, gs, data, gs, nullptr, nullptr, d_limb_ids, 0, n_slots, n_g, st)));
+}
+
+void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
+                       int n_jobs, int n_g, u64 q_src, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 2>(c, src, src_gs, dst, dst_gs, d_jobs, nullptr, nullptr, q_src, n_jobs, n_g, st)));
+}
+
+template <int NS>
+static void bconv_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* jobs,
+                         int n_jobs, const u64* chat, int n_g, cudaStream_t st) {
+    constexpr int TPB = 4;
+    dim3 grid((1u << c.logN) / 256, (n_jobs + TPB - 1) / TPB, n_g);
+    k_bconv<NS, TPB><<<grid, 256, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, n_jobs, chat);
+}
+bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
+                  int n_jobs, const u64* d_chat, int ns, int n_g, cudaStream_t st) {
+#define PPQ_BC(NSV) case NSV: bconv_launch<NSV>(c, src, src_gs, dst, dst_gs, d_jobs, n_jobs, d_chat, n_g, st); return true;
+    switch (ns) {
+        PPQ_BC(1) PPQ_BC(2) PPQ_BC(3) PPQ_BC(4) PPQ_BC(5) PPQ_BC(6) PPQ_BC(7) PPQ_BC(8)
+        PPQ_BC(9) PPQ_BC(10) PPQ_BC(11) PPQ_BC(12) PPQ_BC(13) PPQ_BC(14) PPQ_BC(15) PPQ_BC(16)
+        PPQ_BC(17) PPQ_BC(18) PPQ_BC(19) PPQ_BC(20) PPQ_BC(21) PPQ_BC(22) PPQ_BC(23) PPQ_BC(24)
+        PPQ_BC(25) PPQ_BC(26) PPQ_BC(27) PPQ_BC(28) PPQ_BC(29) PPQ_BC(30) PPQ_BC(31) PPQ_BC(32)
+        default: return false;
     }
+#undef PPQ_BC
 }
 
 void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {

@@ -41,11 +41,19 @@ void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t
 void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
                     const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st);
 
-// ---- base conversion + forward COL pass.  src: [n_g] blocks of stride src_gs, dst likewise.
-// mode 0: approximate CRT basis switch (chat constants).  mode 1: centred SwitchModulus of ONE source limb
-// with modulus q_src (rescale, DropLastElementAndScale).
-void launch_bc_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
-                       int n_jobs, const u64* d_chat, int n_g, int mode, u64 q_src, cudaStream_t st);
+// ---- approximate CRT basis switch, pointwise (ApproxSwitchCRTBasis).  All `n_jobs` jobs share src_first and
+// ns (= `ns`); dst[g][job.dst_slot] = sum_i src[g][src_first+i] * chat[job.chat_off+i] mod q_{job.limb}.
+// Returns false if ns is outside 1..32.
+bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
+                  int n_jobs, const u64* d_chat, int ns, int n_g, cudaStream_t st);
+// ---- plain forward COL pass in place over [n_g] blocks of n_slots polys (negative limb id = skip the slot);
+// output is lazy [0,8q) and must be consumed by a forward ROW pass.
+void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
+                          cudaStream_t st);
+// ---- centred SwitchModulus of ONE source limb with modulus q_src (rescale, DropLastElementAndScale) fused
+// into the forward COL pass.
+void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
+                       int n_jobs, int n_g, u64 q_src, cudaStream_t st);
 
 // ---- forward ROW pass fused with the key inner product (hybrid key switch, EvalFastKeySwitchCoreExt).
 struct IpArgs {

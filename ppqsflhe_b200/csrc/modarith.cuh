@@ -4,7 +4,8 @@
 // FMA pipe, so the multiply count per butterfly is THE cost driver ("integer-pipe co-bound").
 // Conventions:
 //   * q < 2^60 for every limb (OpenFHE 60-bit NATIVEINT limbs), so 4q and even 8q fit in a u64.
-//   * "lazy" values live in [0,2q) or [0,4q); every value written to HBM that crosses the C-ABI is canonical.
+//   * "lazy" values live in [0,4q) (inverse passes) or [0,8q) (forward passes); 8q < 2^63.  Every value that
+//     crosses the C-ABI is canonical.
 //   * Shoup multiplication by a precomputed constant w needs ws = floor(w * 2^64 / q) and accepts ANY 64-bit x.
 //   * Barrett reduction of a 128-bit accumulator needs mu = floor(2^(64+sh) / q), sh = bitlen(q) - 1,
 //     and is valid for x < 2^(63 + bitlen(q)) (e.g. a sum of up to 8 products y*c with y < 2^60, c < q).
@@ -38,11 +39,24 @@ __device__ __forceinline__ u64 mul_shoup_lazy(u64 x, u64 w, u64 ws, u64 q) {
 }
 __device__ __forceinline__ u64 mul_shoup(u64 x, u64 w, u64 ws, u64 q) { return csub(mul_shoup_lazy(x, w, ws, q), q); }
 
-// 128-bit accumulator: (hi,lo) += a * b
+// x * w mod q in [0, 4q) for any x < 2^64, with a 3-multiply approximation of the high product:
+// h' = x1*w1 + hi32(x0*w1) + hi32(x1*w0) underestimates floor(x*ws / 2^64) by at most 2 (the dropped terms are
+// lo32(x0*w1) + lo32(x1*w0) < 2^33 units of 2^32 and x0*w0 < 2^64), so the remainder grows by at most 2q.
+// 3 IMAD.WIDE + 2 adds instead of 4 IMAD.WIDE + a 4-deep carry chain: the butterflies use this one.
+__device__ __forceinline__ u64 mul_shoup_lazy4(u64 x, u64 w, u64 ws, u64 q) {
+    const u32 x0 = (u32)x, x1 = (u32)(x >> 32), s0 = (u32)ws, s1 = (u32)(ws >> 32);
+    const u64 p01 = (u64)x0 * s1, p10 = (u64)x1 * s0;
+    const u64 mid = (p01 >> 32) + (p10 >> 32);
+    const u64 h = (u64)x1 * s1 + mid;
+    return x * w - h * q;
+}
+
+// 128-bit accumulator: (hi,lo) += a * b   (4 IMAD.WIDE + carry adds; nvcc's __int128 lowering is the tightest)
 __device__ __forceinline__ void mac128(u64& hi, u64& lo, u64 a, u64 b) {
-    u64 pl = a * b;
-    u64 ph = __umul64hi(a, b);
-    asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, %3;" : "+l"(lo), "+l"(hi) : "l"(pl), "l"(ph));
+    unsigned __int128 acc = ((unsigned __int128)hi << 64) | lo;
+    acc += (unsigned __int128)a * b;
+    hi = (u64)(acc >> 64);
+    lo = (u64)acc;
 }
 
 // (hi,lo) mod q, canonical.  Requires (hi,lo) < 2^(63 + bitlen(q)).
@@ -58,6 +72,11 @@ __device__ __forceinline__ u64 barrett128(u64 hi, u64 lo, const LimbC& c) {
 __device__ __forceinline__ u64 mulmod_barrett(u64 a, u64 b, const LimbC& c) {
     return barrett128(__umul64hi(a, b), a * b, c);
 }
+
+// [0, 8q) -> [0, q)
+__device__ __forceinline__ u64 canon8(u64 x, const LimbC& c) { return csub(csub(csub(x, c.q2 << 1), c.q2), c.q); }
+// [0, 4q) -> [0, q)
+__device__ __forceinline__ u64 canon4(u64 x, const LimbC& c) { return csub(csub(x, c.q2), c.q); }
 
 __device__ __forceinline__ u64 addmod(u64 a, u64 b, u64 q) { return csub(a + b, q); }
 __device__ __forceinline__ u64 submod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }

@@ -29,18 +29,19 @@
 
 namespace ppq {
 
-// ---- lazy butterflies (Harvey).  Forward keeps values in [0,4q); inverse keeps them in [0,2q).
-__device__ __forceinline__ void ct_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q2) {
-    u64 x = csub(X, q2);
-    u64 t = mul_shoup_lazy(Y, tw.x, tw.y, q);
+// ---- lazy butterflies (Harvey, with the 3-multiply Shoup product whose result lies in [0,4q)).
+// Forward keeps values in [0,8q); inverse keeps them in [0,4q).  q4 = 4q.
+__device__ __forceinline__ void ct_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4) {
+    u64 x = csub(X, q4);
+    u64 t = mul_shoup_lazy4(Y, tw.x, tw.y, q);
     X = x + t;
-    Y = x - t + q2;
+    Y = x - t + q4;
 }
-__device__ __forceinline__ void gs_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q2) {
+__device__ __forceinline__ void gs_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4) {
     u64 s = X + Y;
-    u64 d = X - Y + q2;
-    X = csub(s, q2);
-    Y = mul_shoup_lazy(d, tw.x, tw.y, q);
+    u64 d = X - Y + q4;
+    X = csub(s, q4);
+    Y = mul_shoup_lazy4(d, tw.x, tw.y, q);
 }
 
 template <int LO>
@@ -51,7 +52,7 @@ __device__ __forceinline__ u32 point_of(u32 u, int k) {
 // Forward stages on point bits BHI-1 .. LO (register bits BHI-1-LO .. 0).
 template <int S, int LO, int BHI>
 __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u, u64 q,
-                                          u64 q2) {
+                                          u64 q4) {
     const u32 uhi = u >> LO;
 #pragma unroll
     for (int rb = BHI - 1 - LO; rb >= 0; --rb) {
@@ -62,7 +63,7 @@ __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restr
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
-                ct_bfly(a[k], a[k + (1 << rb)], t, q, q2);
+                ct_bfly(a[k], a[k + (1 << rb)], t, q, q4);
             }
         }
     }
@@ -71,7 +72,7 @@ __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restr
 // Inverse stages on point bits BLO .. LO+2 (register bits BLO-LO .. 2), ascending.
 template <int S, int LO, int BLO>
 __device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u, u64 q,
-                                          u64 q2) {
+                                          u64 q4) {
     const u32 uhi = u >> LO;
 #pragma unroll
     for (int rb = BLO - LO; rb <= 2; ++rb) {
@@ -82,7 +83,7 @@ __device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restr
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
-                gs_bfly(a[k], a[k + (1 << rb)], t, q, q2);
+                gs_bfly(a[k], a[k + (1 << rb)], t, q, q4);
             }
         }
     }
@@ -116,45 +117,45 @@ __device__ __forceinline__ void sm_load(u64 (&a)[8], const u64* sm, const Pos& p
 __host__ __device__ constexpr int cmax(int a, int b) { return a > b ? a : b; }
 __host__ __device__ constexpr int cmin(int a, int b) { return a < b ? a : b; }
 
-// Forward pass over one size-2^S transform.  In: a[k] = point point_of<S-3>(u,k), values in [0,4q).
-// Out: a[k] = point point_of<0>(u,k) = 8u + k, values in [0,4q).  `guard` inserts a leading barrier so the
+// Forward pass over one size-2^S transform.  In: a[k] = point point_of<S-3>(u,k), values in [0,8q).
+// Out: a[k] = point point_of<0>(u,k) = 8u + k, values in [0,8q).  `guard` inserts a leading barrier so the
 // shared buffer can be reused across loop iterations (write-after-read protection).
 template <int S, class Pos>
 __device__ __forceinline__ void fwd_pass(u64 (&a)[8], u64* sm, const Pos& pos, u32 u, const ulonglong2* __restrict__ tw,
-                                         u32 rowfac, u64 q, u64 q2, bool guard) {
+                                         u32 rowfac, u64 q, u64 q4, bool guard) {
     constexpr int LO0 = S - 3;
     constexpr int LO1 = cmax(S - 6, 0);
-    fwd_group<S, LO0, S>(a, tw, rowfac, u, q, q2);
+    fwd_group<S, LO0, S>(a, tw, rowfac, u, q, q4);
     if (guard) __syncthreads();
     sm_store<LO0>(a, sm, pos, u);
     __syncthreads();
     sm_load<LO1>(a, sm, pos, u);
-    fwd_group<S, LO1, LO0>(a, tw, rowfac, u, q, q2);
+    fwd_group<S, LO1, LO0>(a, tw, rowfac, u, q, q4);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);  // same words this thread just read: no barrier needed before
         __syncthreads();
         sm_load<0>(a, sm, pos, u);
-        fwd_group<S, 0, LO1>(a, tw, rowfac, u, q, q2);
+        fwd_group<S, 0, LO1>(a, tw, rowfac, u, q, q4);
     }
 }
 
-// Inverse pass.  In: a[k] = point 8u + k, values in [0,2q).  Out: a[k] = point_of<S-3>(u,k), in [0,2q).
+// Inverse pass.  In: a[k] = point 8u + k, values in [0,4q).  Out: a[k] = point_of<S-3>(u,k), in [0,4q).
 template <int S, class Pos>
 __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u32 u, const ulonglong2* __restrict__ tw,
-                                         u32 rowfac, u64 q, u64 q2, bool guard) {
+                                         u32 rowfac, u64 q, u64 q4, bool guard) {
     constexpr int LOL = S - 3;           // last group
     constexpr int LO1 = cmin(3, S - 3);  // second group
-    inv_group<S, 0, 0>(a, tw, rowfac, u, q, q2);
+    inv_group<S, 0, 0>(a, tw, rowfac, u, q, q4);
     if (guard) __syncthreads();
     sm_store<0>(a, sm, pos, u);
     __syncthreads();
     sm_load<LO1>(a, sm, pos, u);
-    inv_group<S, LO1, 3>(a, tw, rowfac, u, q, q2);
+    inv_group<S, LO1, 3>(a, tw, rowfac, u, q, q4);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);
         __syncthreads();
         sm_load<LOL>(a, sm, pos, u);
-        inv_group<S, LOL, 6>(a, tw, rowfac, u, q, q2);
+        inv_group<S, LOL, 6>(a, tw, rowfac, u, q, q4);
     }
 }
 

@@ -180,9 +180,9 @@ def test_host_buffer_aggregate_entry_point():
     keys = [_rand_key(rng, o) for _ in range(n_clients)]
     rks = [EvalKey(cc, *k) for k in keys]
     arr = (vp * n_clients)(*[r.h for r in rks])
+    ptrs = (vp * n_clients)(*[cts[c].ctypes.data for c in range(n_clients)])
     out = np.zeros((n_slots, 2, ell, o.N), dtype=np.uint64)
-    check(lib().ppq_reencrypt_aggregate_host(cc.h, arr, ell, cts.ctypes.data_as(vp), n_clients, n_slots,
-                                             out.ctypes.data_as(vp)))
+    check(lib().ppq_reencrypt_aggregate_host(cc.h, arr, ell, ptrs, n_clients, n_slots, out.ctypes.data_as(vp)))
     want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
     assert np.array_equal(out, want)
 
@@ -280,17 +280,18 @@ def test_encode_decode_tolerance():
         q0 = int(o.moduli[0])
         diff = (gco - wco + q0 // 2) % q0 - q0 // 2
         assert np.max(np.abs(diff)) <= 2 ** 12
-    # GPU decode of oracle-encoded data
-    enc = np.stack([o.encode(3, vals[g], o.sf(1) ** 2) for g in range(n)])
-    co = np.stack([[o.ntt(i, enc[g][i], inverse=True) for i in range(3)] for g in range(n)])
+    # GPU decode of oracle-encoded data (4 limbs, scale sfBig[0] ~ 2^59; a 2^80 scale would overflow the
+    # int64 coefficients of Encode, in OpenFHE as in the oracle)
+    enc = np.stack([o.encode(4, vals[g], sf) for g in range(n)])
+    co = np.stack([[o.ntt(i, enc[g][i], inverse=True) for i in range(4)] for g in range(n)])
     out = torch.empty((n, o.N // 2), dtype=torch.float64, device=cc.device)
     from ppqsflhe_b200._capi import check, lib, vp
     d = to_device_u64(co, cc.device)
-    check(lib().ppq_decode(cc.h, 3, vp(d.data_ptr()), o.sf(1) ** 2, vp(out.data_ptr()), n, None))
+    check(lib().ppq_decode(cc.h, 4, vp(d.data_ptr()), sf, vp(out.data_ptr()), n, None))
     torch.cuda.synchronize()
     assert np.max(np.abs(out.cpu().numpy() - vals)) < 2.0 ** -20
     for g in range(n):
-        assert np.max(np.abs(out.cpu().numpy()[g] - o.decode(3, co[g], o.sf(1) ** 2))) < 1e-12
+        assert np.max(np.abs(out.cpu().numpy()[g] - o.decode(4, co[g], sf))) < 1e-12
 
 
 def test_end_to_end_golden_round():
