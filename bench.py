@@ -198,6 +198,7 @@ def main():
     import torch.distributed as dist
     from ppqsflhe_b200 import CiphertextBatch, CryptoContext, CtMeta, EvalKey
     from ppqsflhe_b200._capi import check, lib, vp
+    from ppqsflhe_b200.aggregate import clients_of_rank, reduce_partial_sums
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -215,7 +216,7 @@ def main():
     ell, K, N, M = cc.L, cc.K, cc.N, cc.M
     parts = cc.num_parts(ell)
     n_slots = cfg["slots"]
-    my_clients = [c for c in range(cfg["clients"]) if c % world == rank]
+    my_clients = clients_of_rank(cfg["clients"], world, rank)
     qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
 
     def rand_res(shape, q):  # uniform-ish residues, canonical
@@ -234,7 +235,7 @@ def main():
         for ct, rk in zip(cts, keys):
             cc.ReEncryptAccumulate(ct, rk, acc)
         if world > 1:
-            dist.reduce(acc.data, dst=0, op=dist.ReduceOp.SUM)  # residues < 2^60: an 8-way u64 sum cannot wrap
+            reduce_partial_sums(acc.data, world, dst=0)  # residues < 2^60: an 8-way u64 sum cannot wrap
             if rank == 0:
                 cc.finalize_sum(acc)
 
@@ -338,7 +339,7 @@ def main():
                     main_s.wait_event(up[b])
                     cc.ReEncryptAccumulate(CiphertextBatch(dbuf[b], CtMeta()), rk, acc)
                     done[b].record(main_s)
-                dist.reduce(acc.data, dst=0, op=dist.ReduceOp.SUM)
+                reduce_partial_sums(acc.data, world, dst=0)
                 if rank == 0:
                     cc.finalize_sum(acc)
                     h_acc.copy_(acc.data.view(-1), non_blocking=True)

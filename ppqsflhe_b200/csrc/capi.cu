@@ -357,7 +357,9 @@ static int pick_wave(const ppq_ctx* c, const WaveLayout& w, size_t n) {
         if (e && std::atoi(e) > 0) {
             g = (size_t)std::atoi(e);
         } else {
-            const size_t budget = (size_t)96 << 20;  // keep a wave's intermediates near the 126 MB L2
+            // Measured on B200 (profiles/): the pipeline is integer-issue bound, not HBM bound, so large waves
+            // (fewer, fuller launches: no tail effect) beat L2-resident small waves.  2 GiB of scratch.
+            const size_t budget = (size_t)2 << 30;
             g = budget / (w.per_ct * sizeof(u64));
             if (g < 1) g = 1;
         }
