@@ -1,0 +1,88 @@
+#!/usr/bin/env python
+"""Summarise ncu outputs into small committed text files under profiles/.
+
+    python tools/ncu_summarize.py launches gpurun_out/X_launches.csv  > profiles/rNN_launches.md
+    python tools/ncu_summarize.py full     gpurun_out/X.ncu-rep       > profiles/rNN_ncu_full.md
+"""
+import collections
+import csv
+import io
+import re
+import subprocess
+import sys
+
+KEYS = [
+    ("gpu__time_duration.sum", "time"),
+    ("launch__grid_size", "grid"),
+    ("launch__registers_per_thread", "regs"),
+    ("dram__bytes_read.sum", "dram_rd"),
+    ("dram__bytes_write.sum", "dram_wr"),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram%"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm%"),
+    ("sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed", "fmaheavy%"),
+    ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "alu%"),
+    ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue%"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps%"),
+    ("smsp__inst_executed.sum", "warp_inst"),
+    ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem_conf"),
+    ("lts__t_sector_hit_rate.pct", "l2hit%"),
+]
+STALLS = ["math_pipe_throttle", "not_selected", "wait", "dispatch_stall", "long_scoreboard", "short_scoreboard", "barrier",
+          "mio_throttle", "lg_throttle", "selected"]
+
+
+def short(name):
+    name = re.sub(r"\(.*", "", name).replace("void ", "").replace("ppq::", "")
+    return name.strip()
+
+
+def launches(path):
+    rows = [r for r in csv.reader(l for l in open(path) if l.startswith('"'))]
+    hdr = rows[0]
+    ki, vi, gi = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        k = short(r[ki])
+        a = agg.setdefault(k, [0, 0.0, r[gi]])
+        a[0] += 1
+        a[1] += float(r[vi].replace(",", "")) / 1e3
+    tot = sum(a[1] for a in agg.values())
+    print("| kernel | launches | total us | avg us | share | grid of first |")
+    print("|---|---:|---:|---:|---:|---|")
+    for k, (n, us, g) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print(f"| `{k}` | {n} | {us:.1f} | {us / n:.1f} | {us / tot:.3f} | {g} |")
+    print(f"\n{sum(a[0] for a in agg.values())} launches, {tot / 1e3:.2f} ms (ncu-serialised, cold cache: compare SHARES, not absolutes)")
+
+
+def full(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    print("| kernel | " + " | ".join(s for _, s in KEYS) + " | top stalls (pc samples) |")
+    print("|---|" + "---:|" * len(KEYS) + "---|")
+    for r in data:
+        cells = []
+        for k, _ in KEYS:
+            if k in idx:
+                v = r[idx[k]].replace(",", "")
+                try:
+                    f = float(v)
+                    v = f"{f:.4g}" if abs(f) < 1e6 else f"{f:.4e}"
+                except ValueError:
+                    pass
+                cells.append(f"{v} {units[idx[k]]}".strip())
+            else:
+                cells.append("-")
+        st = []
+        for s in STALLS:
+            k = f"smsp__pcsamp_warps_issue_stalled_{s}"
+            if k in idx:
+                st.append((float(r[idx[k]].replace(",", "") or 0), s))
+        tot = sum(v for v, _ in st) or 1
+        st = ", ".join(f"{s} {v / tot:.0%}" for v, s in sorted(st, reverse=True)[:4])
+        print(f"| `{short(r[idx['Kernel Name']])}` | " + " | ".join(cells) + f" | {st} |")
+
+
+if __name__ == "__main__":
+    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
