@@ -68,8 +68,8 @@ struct KsPlanDev {
     DevBuf<int> dig_ids;        // [parts*(ell+K)] limb of every digit slot, -1 for the digit's own limbs
     DevBuf<int> conv_ids;       // [2*ell] limb of every ModDown slot
     DevBuf<int> c1_limb, p_limb;
-    DevBuf<u64> c1_scale, c1_scale_sh, p_scale, p_scale_sh, up_chat, down_chat, pinv, pinv_sh;
-    DevBuf<BcJob> up_jobs, down_jobs;
+    DevBuf<u64> c1_scale, c1_scale_sh, p_scale, p_scale_sh, pinv, pinv_sh;
+    std::vector<BcJob> up_jobs, down_jobs;  // host: packed into kernel parameters per launch (launch_bconv)
 };
 struct RsPlanDev {
     host::RsPlan h;
@@ -83,6 +83,7 @@ struct ppq_ctx {
     int device = 0;
     KCtx k{};
     DevBuf<LimbC> limbs;
+    std::vector<LimbC> h_limbs;
     DevBuf<ulonglong2> twf, twi;
     std::map<int, std::unique_ptr<KsPlanDev>> ks;
     std::map<int, std::unique_ptr<RsPlanDev>> rs;
@@ -138,6 +139,7 @@ static int ctx_finish(std::unique_ptr<ppq_ctx>& c, int device, ppq_ctx** out) {
         lc[r].pad = 0;
     }
     CU(c->limbs.upload(lc));
+    c->h_limbs = lc;
     {
         std::vector<ulonglong2> f((size_t)M * N), i((size_t)M * N);
 #pragma omp parallel for
@@ -309,12 +311,10 @@ static int get_ks_plan(ppq_ctx* c, int ell, KsPlanDev** out) {
         CU(p->p_limb.upload(p->h.p_limb));
         CU(p->p_scale.upload(p->h.p_scale));
         CU(p->p_scale_sh.upload(p->h.p_scale_sh));
-        CU(p->up_chat.upload(p->h.up_chat));
-        CU(p->down_chat.upload(p->h.down_chat));
         CU(p->pinv.upload(p->h.pinv));
         CU(p->pinv_sh.upload(p->h.pinv_sh));
-        CU(p->up_jobs.upload(to_dev_jobs(p->h.up_jobs)));
-        CU(p->down_jobs.upload(to_dev_jobs(p->h.down_jobs)));
+        p->up_jobs = to_dev_jobs(p->h.up_jobs);
+        p->down_jobs = to_dev_jobs(p->h.down_jobs);
         {
             const int M = ell + c->hp.K;
             std::vector<int> ids((size_t)p->h.parts * M, -1), cids(2 * (size_t)ell);
@@ -456,7 +456,7 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         if (prof) cudaEventRecord(ev[2], st);
         // 3. ModUp: approximate basis switch of every digit to its complementary limbs (pointwise)
         for (const auto& d : p->digits)
-            if (!launch_bconv(c->k, y, w.y, dig, w.dig, p->up_jobs.p + d.job_first, d.n_jobs, p->up_chat.p, d.ns, ng, st))
+            if (!launch_bconv(c->k, y, w.y, dig, w.dig, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, ng, st))
                 return fail(PPQ_EINVAL, "digit wider than 32 limbs");
         if (prof) cudaEventRecord(ev[3], st);
         // 3b. forward COL pass of the converted limbs (the digit's own limbs stay as they are in c1)
@@ -485,9 +485,9 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, p->p_scale_sh.p, 2 * K, ng, st);
         if (prof) cudaEventRecord(ev[6], st);
         // 6. ModDown conversion P -> Q (pointwise; the digits buffer is dead: reuse it), then its COL pass
-        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.p, ell, p->down_chat.p, K, ng, st))
+        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data(), ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
-        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.p + ell, ell, p->down_chat.p, K, ng, st))
+        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data() + ell, ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
         if (prof) cudaEventRecord(ev[7], st);
         launch_fwd_col_plain(c->k, dig, w.dig, p->conv_ids.p, 2 * ell, ng, st);
@@ -545,7 +545,7 @@ extern "C" int ppq_ks_modup(ppq_ctx* c, int ell, const uint64_t* d_c1, uint64_t*
     launch_inv_row(c->k, (const u64*)d_c1, ys, y, ys, p->c1_limb.p, ell, (int)n, st);
     launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, (int)n, st);
     for (const auto& d : p->digits)
-        if (!launch_bconv(c->k, y, ys, (u64*)d_digits, ds, p->up_jobs.p + d.job_first, d.n_jobs, p->up_chat.p, d.ns, (int)n, st))
+        if (!launch_bconv(c->k, y, ys, (u64*)d_digits, ds, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, (int)n, st))
             return fail(PPQ_EINVAL, "digit wider than 32 limbs");
     launch_fwd_col_plain(c->k, (u64*)d_digits, ds, p->dig_ids.p, parts * M, (int)n, st);
     // finish the converted limbs with a plain ROW pass; own-digit limbs are copies of c1

@@ -125,40 +125,81 @@ __global__ void __launch_bounds__(W << (S - 3))
 //   dst[job.dst_slot][n] = ( sum_{i<NS} src[src_first+i][n] * chat[job.chat_off+i] ) mod q_{job.limb}
 // WITHOUT the overflow correction (bit-exactness with OpenFHE needs the approximate form).  One thread owns
 // one coefficient: its NS source residues are loaded once (coalesced) and reused for the TPB targets of this
-// block; products accumulate in 128 bits and are Barrett-reduced once per 8 terms.  All jobs of a launch
-// share (src_first, NS).  Sources are canonical COEFF residues already scaled by (D/q_i)^-1 (k_inv_col).
+// block.  All jobs of a launch share (src_first, NS).  Sources are canonical COEFF residues (< 2^60) already
+// scaled by (D/q_i)^-1 (k_inv_col).
+//
+// The exact integer sum is formed with a 30-bit Karatsuba split, y = y1 2^30 + y0, c = c1 2^30 + c0:
+//   sum y c = A0 + (A1 - A0 - A2) 2^30 + A2 2^60,  A0 = sum y0 c0, A2 = sum y1 c1, A1 = sum (y0+y1)(c0+c1)
+// i.e. THREE multiply-adds per term, each a single IMAD.WIDE with a 64-bit addend (no carry chain), instead of
+// the four IMAD.WIDE + carries of a 64x64->128 MAC: wide multiplies are the scarce resource on B200 (~5 clk
+// per warp and SMSP on the fmaheavy pipe, tools/ubench/int_pipes.cu).  Up to 8 terms per accumulator set
+// (A0, A2 < 8 2^60; A1 may wrap: only A1 - A0 - A2 = sum (y1 c0 + y0 c1) < 2^64 is used, and that is exact modulo
+// 2^64), one Barrett reduction per 8 terms.  Unsigned products only: a signed IMAD.WIDE costs two passes on B200
+// (measured, profiles/r01_notes.md).  chat3[.] = (c0, c1, c0 + c1, 0).
 // =========================================================================================================
-template <int NS, int TPB>
+__device__ __forceinline__ u64 kara_reduce(u64 A0, u64 A2, u64 A1, const LimbC& lc) {
+    const u64 mid = A1 - A0 - A2;  // = sum (y1 c0 + y0 c1) < 2^64: exact modulo 2^64
+    unsigned __int128 t = (unsigned __int128)A0 + ((unsigned __int128)mid << 30) + ((unsigned __int128)A2 << 60);
+    return barrett128((u64)(t >> 64), (u64)t, lc);
+}
+
+// Constants of one launch travel as a kernel parameter (constant bank, read with LDC/ULDC by a block-uniform index):
+// per-thread LDG of conversion constants saturated L1TEX (74 % in profiles/r01_notes.md) without doing useful work.
+template <int NS>
+struct BcPack {
+    struct J {
+        u64 q, mu;
+        u32 sh;
+        int dst_slot;
+        u32 pad[2];
+        uint4 c[NS];  // (c0, c1, c0 + c1, 0) per source limb
+    };
+    static constexpr int MAXJ = (12288 / (int)sizeof(J)) < 48 ? (12288 / (int)sizeof(J)) : 48;
+    int n_jobs, src_first;
+    int pad[2];
+    J j[MAXJ];
+};
+
+template <int NS>
 __global__ void __launch_bounds__(256)
-    k_bconv(KCtx c, const u64* __restrict__ src, size_t src_gs, u64* __restrict__ dst, size_t dst_gs,
-            const BcJob* __restrict__ jobs, int n_jobs, const u64* __restrict__ chat) {
-    const u32 N = 1u << c.logN;
+    k_bconv(int logN, const u64* __restrict__ src, size_t src_gs, u64* __restrict__ dst, size_t dst_gs,
+            const __grid_constant__ BcPack<NS> P) {
+    const u32 N = 1u << logN;
     const u32 n = blockIdx.x * 256 + threadIdx.x;
     const u32 g = blockIdx.z;
-    const int j0 = blockIdx.y * TPB;
-    const BcJob first = jobs[j0];
-    const u64* in = src + g * src_gs + (size_t)first.src_first * N + n;
-    u64 y[NS];
+    const u64* in = src + g * src_gs + (size_t)P.src_first * N + n;
+    u32 y0[NS], y1[NS], ys[NS];
 #pragma unroll
-    for (int i = 0; i < NS; ++i) y[i] = in[(size_t)i * N];
+    for (int i = 0; i < NS; ++i) {
+        const u64 y = ld_stream(in + (size_t)i * N);
+        y0[i] = (u32)y & 0x3fffffffu;
+        y1[i] = (u32)(y >> 30);
+        ys[i] = y0[i] + y1[i];
+    }
     u64* out = dst + g * dst_gs + n;
+#pragma unroll 2
+    for (int t = 0; t < P.n_jobs; ++t) {
+        const typename BcPack<NS>::J& J = P.j[t];
+        LimbC lc;
+        lc.q = J.q;
+        lc.q2 = J.q << 1;
+        lc.mu = J.mu;
+        lc.sh = J.sh;
+        u64 r = 0;
 #pragma unroll
-    for (int t = 0; t < TPB; ++t) {
-        if (j0 + t < n_jobs) {  // block-uniform
-            const BcJob jb = jobs[j0 + t];
-            const LimbC lc = c.limbs[jb.limb];
-            const u64* ch = chat + jb.chat_off;
-            u64 r = 0;
+        for (int i0 = 0; i0 < NS; i0 += 8) {
+            u64 A0 = 0, A2 = 0, A1 = 0;
 #pragma unroll
-            for (int i0 = 0; i0 < NS; i0 += 8) {
-                u64 hi = 0, lo = 0;
-#pragma unroll
-                for (int i = i0; i < (i0 + 8 < NS ? i0 + 8 : NS); ++i) mac128(hi, lo, y[i], __ldg(ch + i));
-                r += barrett128(hi, lo, lc);
+            for (int i = i0; i < (i0 + 8 < NS ? i0 + 8 : NS); ++i) {
+                const uint4 cc = J.c[i];
+                A0 += (u64)y0[i] * cc.x;
+                A2 += (u64)y1[i] * cc.y;
+                A1 += (u64)ys[i] * cc.z;
             }
-            if (NS > 8) r = canon4(r, lc);  // at most 4 chunks
-            out[(size_t)jb.dst_slot * N] = r;
+            r += kara_reduce(A0, A2, A1, lc);
         }
+        if (NS > 8) r = canon4(r, lc);  // at most 4 chunks
+        out[(size_t)J.dst_slot * N] = r;
     }
 }
 
@@ -546,14 +587,31 @@ void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, s
 
 template <int NS>
 static void bconv_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* jobs,
-                         int n_jobs, const u64* chat, int n_g, cudaStream_t st) {
-    constexpr int TPB = 4;
-    dim3 grid((1u << c.logN) / 256, (n_jobs + TPB - 1) / TPB, n_g);
-    k_bconv<NS, TPB><<<grid, 256, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, n_jobs, chat);
+                         int n_jobs, const u64* chat, const LimbC* limbs, int n_g, cudaStream_t st) {
+    typedef BcPack<NS> P;
+    for (int j0 = 0; j0 < n_jobs; j0 += P::MAXJ) {
+        P pk;
+        pk.n_jobs = n_jobs - j0 < P::MAXJ ? n_jobs - j0 : P::MAXJ;
+        pk.src_first = jobs[j0].src_first;
+        pk.pad[0] = pk.pad[1] = 0;
+        for (int t = 0; t < pk.n_jobs; ++t) {
+            const BcJob& jb = jobs[j0 + t];
+            const LimbC& lc = limbs[jb.limb];
+            typename P::J& J = pk.j[t];
+            J.q = lc.q;
+            J.mu = lc.mu;
+            J.sh = lc.sh;
+            J.dst_slot = jb.dst_slot;
+            J.pad[0] = J.pad[1] = 0;
+            for (int i = 0; i < NS; ++i) J.c[i] = chat_split(chat[jb.chat_off + i]);
+        }
+        dim3 grid((1u << c.logN) / 256, 1, n_g);
+        k_bconv<NS><<<grid, 256, 0, st>>>(c.logN, src, src_gs, dst, dst_gs, pk);
+    }
 }
-bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
-                  int n_jobs, const u64* d_chat, int ns, int n_g, cudaStream_t st) {
-#define PPQ_BC(NSV) case NSV: bconv_launch<NSV>(c, src, src_gs, dst, dst_gs, d_jobs, n_jobs, d_chat, n_g, st); return true;
+bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* h_jobs,
+                  int n_jobs, const u64* h_chat, const LimbC* h_limbs, int ns, int n_g, cudaStream_t st) {
+#define PPQ_BC(NSV) case NSV: bconv_launch<NSV>(c, src, src_gs, dst, dst_gs, h_jobs, n_jobs, h_chat, h_limbs, n_g, st); return true;
     switch (ns) {
         PPQ_BC(1) PPQ_BC(2) PPQ_BC(3) PPQ_BC(4) PPQ_BC(5) PPQ_BC(6) PPQ_BC(7) PPQ_BC(8)
         PPQ_BC(9) PPQ_BC(10) PPQ_BC(11) PPQ_BC(12) PPQ_BC(13) PPQ_BC(14) PPQ_BC(15) PPQ_BC(16)

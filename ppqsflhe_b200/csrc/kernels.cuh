@@ -43,9 +43,15 @@ void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, 
 
 // ---- approximate CRT basis switch, pointwise (ApproxSwitchCRTBasis).  All `n_jobs` jobs share src_first and
 // ns (= `ns`); dst[g][job.dst_slot] = sum_i src[g][src_first+i] * chat[job.chat_off+i] mod q_{job.limb}.
-// Returns false if ns is outside 1..32.
-bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
-                  int n_jobs, const u64* d_chat, int ns, int n_g, cudaStream_t st);
+// h_jobs / h_chat / h_limbs are HOST arrays: the constants of a launch are packed into the kernel parameter
+// (constant bank) by the launcher.  Returns false if ns is outside 1..32.
+bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* h_jobs,
+                  int n_jobs, const u64* h_chat, const LimbC* h_limbs, int ns, int n_g, cudaStream_t st);
+// (c0, c1, c0 + c1, 0) of a conversion constant c < 2^60 (30-bit Karatsuba split, see k_bconv)
+inline uint4 chat_split(u64 c) {
+    const u32 c0 = (u32)(c & 0x3fffffffull), c1 = (u32)(c >> 30);
+    return make_uint4(c0, c1, c0 + c1, 0u);
+}
 // ---- plain forward COL pass in place over [n_g] blocks of n_slots polys (negative limb id = skip the slot);
 // output is lazy [0,8q) and must be consumed by a forward ROW pass.
 void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,

@@ -43,12 +43,47 @@ __device__ __forceinline__ u64 mul_shoup(u64 x, u64 w, u64 ws, u64 q) { return c
 // h' = x1*w1 + hi32(x0*w1) + hi32(x1*w0) underestimates floor(x*ws / 2^64) by at most 2 (the dropped terms are
 // lo32(x0*w1) + lo32(x1*w0) < 2^33 units of 2^32 and x0*w0 < 2^64), so the remainder grows by at most 2q.
 // 3 IMAD.WIDE + 2 adds instead of 4 IMAD.WIDE + a 4-deep carry chain: the butterflies use this one.
+// Written as PTX so that the instruction selection is the minimal one measured on B200 (tools/ubench/int_pipes.cu:
+// IMAD 2 clk, IMAD.WIDE / IMAD.HI ~5 clk per warp and SMSP, all on the fmaheavy pipe, which is the binding pipe of
+// every NTT kernel): 5 wide/hi multiplies + 4 low multiplies + 2 adds, x*w - h*q evaluated as x*w + h*(2^64 - q) so
+// that the products chain through the multiply-add addend instead of separate negate/add instructions.
 __device__ __forceinline__ u64 mul_shoup_lazy4(u64 x, u64 w, u64 ws, u64 q) {
+#ifdef PPQ_PLAIN_SHOUP
     const u32 x0 = (u32)x, x1 = (u32)(x >> 32), s0 = (u32)ws, s1 = (u32)(ws >> 32);
     const u64 p01 = (u64)x0 * s1, p10 = (u64)x1 * s0;
     const u64 mid = (p01 >> 32) + (p10 >> 32);
     const u64 h = (u64)x1 * s1 + mid;
     return x * w - h * q;
+#else
+    const u64 nq = 0ull - q;
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 x0, x1, w0, w1, s0, s1, n0, n1, a, b, m0, m1, h0, h1, r0, r1;\n\t"
+        ".reg .u64 h, t;\n\t"
+        "mov.b64 {x0, x1}, %1;\n\t"
+        "mov.b64 {w0, w1}, %2;\n\t"
+        "mov.b64 {s0, s1}, %3;\n\t"
+        "mov.b64 {n0, n1}, %4;\n\t"
+        "mul.hi.u32 a, x0, s1;\n\t"
+        "mul.hi.u32 b, x1, s0;\n\t"
+        "add.cc.u32 m0, a, b;\n\t"
+        "addc.u32 m1, 0, 0;\n\t"
+        "mov.b64 h, {m0, m1};\n\t"
+        "mad.wide.u32 h, x1, s1, h;\n\t"
+        "mov.b64 {h0, h1}, h;\n\t"
+        "mul.wide.u32 t, x0, w0;\n\t"
+        "mad.wide.u32 t, h0, n0, t;\n\t"
+        "mov.b64 {r0, r1}, t;\n\t"
+        "mad.lo.u32 r1, x0, w1, r1;\n\t"
+        "mad.lo.u32 r1, x1, w0, r1;\n\t"
+        "mad.lo.u32 r1, h0, n1, r1;\n\t"
+        "mad.lo.u32 r1, h1, n0, r1;\n\t"
+        "mov.b64 %0, {r0, r1};\n\t"
+        "}"
+        : "=l"(r)
+        : "l"(x), "l"(w), "l"(ws), "l"(nq));
+    return r;
+#endif
 }
 
 // 128-bit accumulator: (hi,lo) += a * b   (4 IMAD.WIDE + carry adds; nvcc's __int128 lowering is the tightest)

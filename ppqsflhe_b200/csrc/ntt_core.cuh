@@ -32,10 +32,13 @@ namespace ppq {
 // ---- lazy butterflies (Harvey, with the 3-multiply Shoup product whose result lies in [0,4q)).
 // Forward keeps values in [0,8q); inverse keeps them in [0,4q).  q4 = 4q.
 __device__ __forceinline__ void ct_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4) {
-    u64 x = csub(X, q4);
-    u64 t = mul_shoup_lazy4(Y, tw.x, tw.y, q);
-    X = x + t;
-    Y = x - t + q4;
+    // conditional subtraction folded into three-input adds (IADD3 on the ALU pipe; a two-input 64-bit add is
+    // otherwise placed on the fmaheavy pipe as IMAD.X, which is the binding pipe)
+    const bool ge = X >= q4;
+    const u64 s1 = ge ? q4 : 0ull, s2 = ge ? 0ull : q4;
+    const u64 t = mul_shoup_lazy4(Y, tw.x, tw.y, q);
+    Y = X + s2 - t;
+    X = X - s1 + t;
 }
 __device__ __forceinline__ void gs_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4) {
     u64 s = X + Y;
