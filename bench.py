@@ -52,8 +52,8 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def stage_alg_words(ell, K, parts, bk):
-    """Algorithmic (compulsory) u64 words per ciphertext, in units of N, for each of the 9 pipeline kernels
+def stage_alg_words(ell, K, parts, bk, split=True):
+    """Algorithmic (compulsory) u64 words per ciphertext, in units of N, for each of the 11 pipeline stages
     (DESIGN.md 'kernels').  bk = ciphertexts sharing one rekey inside a call (key traffic is amortised)."""
     M = ell + K
     conv = parts * M - ell
@@ -62,7 +62,9 @@ def stage_alg_words(ell, K, parts, bk):
         2 * ell,                                   # k_inv_col(c1):        R ell + W ell
         ell + conv,                                # k_bconv(modup):       R ell (COEFF digits) + W converted limbs
         2 * conv,                                  # k_fwd_col(modup):     R + W converted limbs
-        conv + ell + 2 * parts * M / bk + 2 * M,   # k_fwd_row_ip:         R digits + R own c1 + R keys/bk + W 2(ell+K)
+        (2 * conv) if split else 0,                # k_fwd_row(modup):     R + W converted limbs (split form only)
+        conv + ell + 2 * parts * M / bk + 2 * M,   # k_ip_tma / k_fwd_row_ip: R digits + R own c1 + R keys/bk + W 2(ell+K)
+        (4 * K) if split else 0,                   # k_inv_row(P):         R 2K + W 2K (split form only)
         4 * K,                                     # k_inv_col(P):         R 2K + W 2K
         2 * K + 2 * ell,                           # k_bconv(moddown):     R 2K + W 2 ell
         4 * ell,                                   # k_fwd_col(moddown):   R 2 ell + W 2 ell
@@ -264,7 +266,7 @@ def main():
     sampler.start()
     total_ms = timed(step, args.steps)
     clocks = sampler.stop()
-    NST = 9  # PPQ_PROFILE_STAGES
+    NST = 11  # PPQ_PROFILE_STAGES
     pms = (C.c_double * NST)()
     pl = (C.c_uint64 * NST)()
     check(lib().ppq_profile_read(cc.h, pms, pl, 1))
@@ -278,7 +280,7 @@ def main():
     peak, peak_src = peaks()
     names = [lib().ppq_profile_stage_name(i).decode() for i in range(NST)]
     dom = int(np.argmax(stage_ms))
-    words = stage_alg_words(ell, K, parts, n_slots)
+    words = stage_alg_words(ell, K, parts, n_slots, split=os.environ.get("PPQ_IP_FUSED", "0") in ("", "0"))
     local_ct = len(my_clients) * n_slots * args.steps
     dom_bytes = words[dom] * 8.0 * N * local_ct
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0

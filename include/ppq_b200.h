@@ -133,7 +133,7 @@ int ppq_reencrypt_aggregate_host(ppq_ctx*, const ppq_rekey* const* rekeys, int e
 
 /* ---- per-stage device timing of the key-switch pipeline (CUDA events on the caller's stream).
  *      stage s < PPQ_PROFILE_STAGES: see ppq_profile_stage_name.  ms / launches: arrays of that length. */
-#define PPQ_PROFILE_STAGES 9
+#define PPQ_PROFILE_STAGES 11
 int ppq_profile_enable(ppq_ctx*, int on);
 int ppq_profile_read(ppq_ctx*, double* ms, uint64_t* launches, int reset);
 const char* ppq_profile_stage_name(int stage);

@@ -94,8 +94,9 @@ struct ppq_ctx {
     DevBuf<u64> fac;       // [2][L] EvalMult factors
     ckks::Tables fft;
     int wave = 0;
+    bool ip_split = true;  // inner product as k_fwd_row_plain + k_ip_tma + k_inv_row (PPQ_IP_FUSED=1: one fused kernel)
     // per-stage CUDA-event profiling of the key-switch pipeline (ppq_profile_*)
-    static const int NSTAGE = 9, RING = 64;
+    static const int NSTAGE = 11, RING = 64;
     bool prof = false;
     cudaEvent_t ev[RING][NSTAGE + 1] = {};
     bool ev_made = false, ev_used[RING] = {};
@@ -153,6 +154,10 @@ static int ctx_finish(std::unique_ptr<ppq_ctx>& c, int device, ppq_ctx** out) {
     c->k.twf = c->twf.p;
     c->k.twi = c->twi.p;
     c->k.logN = hp.logN;
+    {
+        const char* e = std::getenv("PPQ_IP_FUSED");
+        c->ip_split = !(e && std::atoi(e) != 0) && hp.N >= 2048 && hp.dnum <= 6;
+    }
     std::string err;
     if (!ckks::build_tables(hp.logN, c->fft, err)) return fail(PPQ_ECUDA, err);
     *out = c.release();
@@ -410,9 +415,10 @@ extern "C" int ppq_profile_read(ppq_ctx* c, double* ms, uint64_t* launches, int 
     return PPQ_OK;
 }
 extern "C" const char* ppq_profile_stage_name(int s) {
-    static const char* names[ppq_ctx::NSTAGE] = {"k_inv_row(c1)",     "k_inv_col(c1,scale)", "k_bconv(modup)",
-                                                 "k_fwd_col(modup)",  "k_fwd_row_ip",        "k_inv_col(P,scale)",
-                                                 "k_bconv(moddown)",  "k_fwd_col(moddown)",  "k_fwd_row_moddown"};
+    static const char* names[ppq_ctx::NSTAGE] = {"k_inv_row(c1)",      "k_inv_col(c1,scale)", "k_bconv(modup)",
+                                                 "k_fwd_col(modup)",   "k_fwd_row(modup)",    "k_ip_tma|k_fwd_row_ip",
+                                                 "k_inv_row(P)",       "k_inv_col(P,scale)",  "k_bconv(moddown)",
+                                                 "k_fwd_col(moddown)", "k_fwd_row_moddown"};
     return (s >= 0 && s < ppq_ctx::NSTAGE) ? names[s] : "";
 }
 
@@ -479,19 +485,32 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ia.L = L;
         ia.parts = parts;
         ia.alpha = c->hp.alpha;
-        launch_fwd_row_ip(c->k, ia, ng, st);
-        if (prof) cudaEventRecord(ev[5], st);
+        if (c->ip_split) {
+            launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
+            if (prof) cudaEventRecord(ev[5], st);
+            if (!launch_ip_tma(c->k, ia, ng, st)) return fail(PPQ_EINVAL, "ppq_reencrypt: split inner product needs N >= 2048 and <= 6 digits");
+            if (prof) cudaEventRecord(ev[6], st);
+            launch_inv_row(c->k, extp, w.extp, extp, w.extp, p->p_limb.p, 2 * K, ng, st);
+            if (prof) cudaEventRecord(ev[7], st);
+        } else {
+            if (prof) cudaEventRecord(ev[5], st);
+            launch_fwd_row_ip(c->k, ia, ng, st);
+            if (prof) {
+                cudaEventRecord(ev[6], st);
+                cudaEventRecord(ev[7], st);
+            }
+        }
         // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
         launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, p->p_scale_sh.p, 2 * K, ng, st);
-        if (prof) cudaEventRecord(ev[6], st);
+        if (prof) cudaEventRecord(ev[8], st);
         // 6. ModDown conversion P -> Q (pointwise; the digits buffer is dead: reuse it), then its COL pass
         if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data(), ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
         if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data() + ell, ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
-        if (prof) cudaEventRecord(ev[7], st);
+        if (prof) cudaEventRecord(ev[9], st);
         launch_fwd_col_plain(c->k, dig, w.dig, p->conv_ids.p, 2 * ell, ng, st);
-        if (prof) cudaEventRecord(ev[8], st);
+        if (prof) cudaEventRecord(ev[10], st);
         // 7. forward ROW pass + (x - conv) P^-1 + c0 (+ running sum)
         MdArgs ma;
         ma.conv = dig;
@@ -508,7 +527,7 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ma.accumulate = accumulate;
         launch_fwd_row_moddown(c->k, ma, ng, st);
         if (prof) {
-            cudaEventRecord(ev[9], st);
+            cudaEventRecord(ev[11], st);
             c->ev_used[slot] = true;
             c->prof_wave++;
         }

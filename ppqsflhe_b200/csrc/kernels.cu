@@ -328,6 +328,133 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_ip(KCtx c, IpAr
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Pointwise inner product with the re-encryption key (EvalFastKeySwitchCoreExt), keys staged by TMA.
+// One CTA owns (limb r, tile of IPT points).  Its key tile -- parts x {b,a} x IPT residues -- is brought into
+// shared memory ONCE by cp.async.bulk (TMA bulk copies completing on an mbarrier) and then reused for every
+// ciphertext of the wave: the rekey is read from L2/HBM once per wave instead of once per ciphertext.
+// Digits arrive in EVAL form (converted limbs from k_fwd_row_plain, own-digit limbs straight from c1).
+// Products use the 30-bit Karatsuba split of k_bconv (3 IMAD.WIDE per term, no carry chains).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int IPT = 2048;  // points per tile: 8 per thread, 256 threads
+
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, u32 bytes, u64* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+struct Kara3 {  // 30-bit split of a residue < 2^60
+    u32 lo, hi, sum;
+    __device__ __forceinline__ explicit Kara3(u64 v) : lo((u32)v & 0x3fffffffu), hi((u32)(v >> 30)), sum(lo + hi) {}
+};
+struct KaraAcc {
+    u64 A0 = 0, A1 = 0, A2 = 0;
+    __device__ __forceinline__ void mac(const Kara3& x, const Kara3& y) {
+        A0 += (u64)x.lo * y.lo;
+        A2 += (u64)x.hi * y.hi;
+        A1 += (u64)x.sum * y.sum;
+    }
+    __device__ __forceinline__ u64 reduce(const LimbC& lc) const { return kara_reduce(A0, A2, A1, lc); }
+};
+
+template <int PARTS>
+__global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
+    extern __shared__ __align__(128) unsigned char ip_smem[];
+    u64* keys = reinterpret_cast<u64*>(ip_smem);              // [PARTS][2][IPT]
+    u64* bar = keys + (size_t)PARTS * 2 * IPT;
+    const u32 N = 1u << c.logN;
+    const int r = blockIdx.y;
+    const int M = A.ell + A.K;
+    const int limb = r < A.ell ? r : A.L + (r - A.ell);
+    const size_t off = (size_t)blockIdx.x * IPT;
+    const LimbC lc = c.limbs[limb];
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, (u32)(PARTS * 2 * IPT * sizeof(u64)));
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) {
+            const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off;
+            tma_bulk_g2s(keys + (size_t)(2 * j) * IPT, A.key_b + koff, IPT * sizeof(u64), bar);
+            tma_bulk_g2s(keys + (size_t)(2 * j + 1) * IPT, A.key_a + koff, IPT * sizeof(u64), bar);
+        }
+    }
+    const int own = r < A.ell ? r / A.alpha : -1;  // the digit whose own limb r is (taken from c1 as it is)
+    const int g0 = blockIdx.z * g_per_cta;
+    const int g1 = min(n_g, g0 + g_per_cta);
+    // digits of the next (ciphertext, chunk) are fetched while the current one is multiplied: with two CTAs per
+    // SM the loads in flight would otherwise not cover the HBM latency
+    auto fetch = [&](int it, ulonglong2 (&d)[PARTS]) {
+        const int g = g0 + (it >> 2);
+        const u32 pt = (u32)(it & 3) * 512 + threadIdx.x * 2;
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) {
+            const u64* dp = (j == own) ? A.c1 + g * A.c1_gs + (size_t)r * N + off
+                                       : A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
+            d[j] = __ldcs(reinterpret_cast<const ulonglong2*>(dp + pt));
+        }
+    };
+    const int n_it = (g1 - g0) * 4;
+    ulonglong2 dn[PARTS];
+    if (n_it > 0) fetch(0, dn);
+    mbar_wait(bar, 0);
+    for (int it = 0; it < n_it; ++it) {
+        ulonglong2 d[PARTS];
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) d[j] = dn[j];
+        if (it + 1 < n_it) fetch(it + 1, dn);
+        const int g = g0 + (it >> 2);
+        const u32 pt = (u32)(it & 3) * 512 + threadIdx.x * 2;  // two adjacent points per 16-byte access
+        u64* o0;
+        u64* o1;
+        if (r < A.ell) {
+            o0 = A.extq + g * A.extq_gs + (size_t)r * N + off;
+            o1 = o0 + (size_t)A.ell * N;
+        } else {
+            o0 = A.extp + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
+            o1 = o0 + (size_t)A.K * N;
+        }
+        KaraAcc b0, b1, a0, a1;
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) {
+            const ulonglong2 kb = *reinterpret_cast<const ulonglong2*>(keys + (size_t)(2 * j) * IPT + pt);
+            const ulonglong2 ka = *reinterpret_cast<const ulonglong2*>(keys + (size_t)(2 * j + 1) * IPT + pt);
+            const Kara3 dx(d[j].x), dy(d[j].y);
+            b0.mac(dx, Kara3(kb.x));
+            b1.mac(dy, Kara3(kb.y));
+            a0.mac(dx, Kara3(ka.x));
+            a1.mac(dy, Kara3(ka.y));
+        }
+        *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
+        *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
+    }
+}
+
 // Forward ROW pass + ModDown combine: out = (x - conv) * P^-1 (+ c0 on poly 0) (+ running sum).
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c, MdArgs A) {
@@ -626,6 +753,29 @@ void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st)
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_ip<S><<<dim3(n1 / RowGeom<S>::R, a.ell + a.K, n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+}
+bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
+    const int N = 1 << c.logN;
+    if (N % IPT) return false;
+    const int tiles = N / IPT, M = a.ell + a.K;
+    // enough CTAs for >= 2 waves of 2 CTAs per SM, but as few key-tile reloads as possible
+    int gz = 1;
+    while (tiles * M * gz < 148 * 4 && gz < n_g) gz *= 2;
+    const int g_per = (n_g + gz - 1) / gz;
+    gz = (n_g + g_per - 1) / g_per;
+    dim3 grid(tiles, M, gz);
+#define PPQ_IP(P)                                                                                          \
+    case P: {                                                                                              \
+        const size_t sm = (size_t)P * 2 * IPT * sizeof(u64) + 16;                                          \
+        cudaFuncSetAttribute(k_ip_tma<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);           \
+        k_ip_tma<P><<<grid, 256, sm, st>>>(c, a, n_g, g_per);                                             \
+        return true;                                                                                       \
+    }
+    switch (a.parts) {
+        PPQ_IP(1) PPQ_IP(2) PPQ_IP(3) PPQ_IP(4) PPQ_IP(5) PPQ_IP(6)
+        default: return false;
+    }
+#undef PPQ_IP
 }
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);

@@ -76,6 +76,10 @@ struct IpArgs {
     int ell, K, L, parts, alpha;
 };
 void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
+// ---- split form: digits already in EVAL (k_fwd_row_plain on a.digits); pointwise inner product with the key tile
+// staged in shared memory by TMA bulk copies and reused across the wave.  extp receives EVAL P limbs (run
+// launch_inv_row on it afterwards).  Returns false if the shape is unsupported (parts > 6 or N < 2048).
+bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
 
 // ---- forward ROW pass fused with the ModDown combine (+ c0, + optional accumulate = EvalAdd).
 struct MdArgs {

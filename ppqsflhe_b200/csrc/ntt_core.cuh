@@ -62,7 +62,11 @@ __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restr
         const u32 base = rowfac << (S - 1 - LO - rb);
 #pragma unroll
         for (int g = 0; g < (4 >> rb); ++g) {
+#ifdef PPQ_EXP_NOTW
+            const ulonglong2 t = make_ulonglong2(q ^ (u64)(base + uhi + g), q4 ^ (u64)(uhi * 77 + g));
+#else
             const ulonglong2 t = __ldg(tw + (base + ((uhi << (2 - rb)) | (u32)g)));
+#endif
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
@@ -82,7 +86,11 @@ __device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restr
         const u32 base = rowfac << (S - 1 - LO - rb);
 #pragma unroll
         for (int g = 0; g < (4 >> rb); ++g) {
+#ifdef PPQ_EXP_NOTW
+            const ulonglong2 t = make_ulonglong2(q ^ (u64)(base + uhi + g), q4 ^ (u64)(uhi * 77 + g));
+#else
             const ulonglong2 t = __ldg(tw + (base + ((uhi << (2 - rb)) | (u32)g)));
+#endif
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
