@@ -1,0 +1,80 @@
+// changeCipherDomain -- drop-in for the reference's server/src/changeCipherDomain.cpp (same argv, exit codes,
+// progress lines and file schema), with cc->ReEncrypt (:74,89,105) replaced by ONE batched ppq_reencrypt call
+// through the C ABI of libppq_b200.so.  No CPU fallback: without a B200 the context load fails and the tool exits 1.
+#include "ppq_session.hpp"
+
+using namespace ppqhost;
+
+int main(int argc, char* argv[]) {
+    if (argc != 5) {
+        std::cerr << "Usage: " << argv[0] << " <cc_path> <rekey_path> <input_encfile> <output_encfile>" << std::endl;
+        return 1;
+    }
+    const std::string cc_path = argv[1], rekey_path = argv[2], input_encfile = argv[3], output_encfile = argv[4];
+    try {
+        // Step 1: CryptoContext (reference :32-36)
+        std::unique_ptr<Session> s;
+        try {
+            s.reset(new Session(cc_path));
+        } catch (const std::exception& e) {
+            std::cerr << "[recrypt] ERROR: Failed to load CryptoContext: " << cc_path << " (" << e.what() << ")" << std::endl;
+            return 1;
+        }
+        std::cout << "[recrypt] CryptoContext loaded\n";
+
+        // Step 2: re-encryption key (reference :40-44) -> device-resident [dnum][L+K][N] B and A vectors
+        ppq_rekey* rk = nullptr;
+        try {
+            const wire::EvalKeyPolys ek = wire::read_eval_key(wire::slurp(rekey_path));
+            if ((int)ek.a.size() != s->dnum) throw std::runtime_error("key has " + std::to_string(ek.a.size()) + " digits, context dnum is " + std::to_string(s->dnum));
+            const size_t M = (size_t)s->L + s->K, per = M * s->N;
+            std::vector<uint64_t> b(per * s->dnum), a(per * s->dnum);
+            for (int j = 0; j < s->dnum; ++j) {
+                const std::vector<uint64_t> bj = s->flatten(ek.b[j], M, "rekey B"), aj = s->flatten(ek.a[j], M, "rekey A");
+                std::copy(bj.begin(), bj.end(), b.begin() + j * per);
+                std::copy(aj.begin(), aj.end(), a.begin() + j * per);
+            }
+            ck(ppq_rekey_upload(s->cc, b.data(), a.data(), &rk), "ppq_rekey_upload");
+        } catch (const std::exception& e) {
+            std::cerr << "[recrypt] ERROR: Failed to load ReKey from " << rekey_path << " (" << e.what() << ")" << std::endl;
+            return 1;
+        }
+        std::cout << "[recrypt] ReKey loaded\n";
+
+        // Step 3: encrypted weights (reference :48-55)
+        std::vector<wire::Layer> layers;
+        try {
+            layers = wire::read_container(input_encfile);
+        } catch (const std::exception& e) {
+            std::cerr << "[recrypt] ERROR: Could not open input encrypted weights file (" << e.what() << ")\n";
+            return 1;
+        }
+
+        // Step 4: ReEncrypt every field (reference :61-115), all ciphertexts of the file in one call per limb count
+        std::vector<BlobRef> refs = blob_refs(layers);
+        std::map<uint32_t, Batch> groups = decode_all(*s, refs);
+        for (auto& kv : groups) {
+            Batch& b = kv.second;
+            Dev<uint64_t> d_in(b.data.size()), d_out(b.data.size());
+            d_in.upload(b.data.data(), b.data.size());
+            ck(ppq_reencrypt(s->cc, rk, (int)b.ell, d_in.p, d_out.p, b.n(), nullptr), "ppq_reencrypt");
+            ck(ppq_sync(s->cc, nullptr), "ppq_sync");
+            d_out.download(b.data.data(), b.data.size());
+            encode_back(*s, b, b.ell, b.meta, b.data, refs);  // level / scale / slots unchanged by a key switch
+        }
+        ppq_rekey_destroy(rk);
+
+        // Step 5: output (reference :118-124)
+        try {
+            wire::write_container(output_encfile, layers);
+        } catch (const std::exception&) {
+            std::cerr << "[recrypt] ERROR: Failed to open output file\n";
+            return 1;
+        }
+        std::cout << "[recrypt] Re-encryption completed successfully. Output: " << output_encfile << std::endl;
+        return 0;
+    } catch (const std::exception& e) {
+        std::cerr << "[recrypt] ERROR: " << e.what() << std::endl;
+        return 1;
+    }
+}

@@ -1,0 +1,130 @@
+// ppq_session.hpp -- what the four tools share: the context loaded from CC.json through the C ABI, device/pinned
+// buffers, and the batching of every ciphertext blob of a container file into ONE device batch (the reference loops
+// ciphertext by ciphertext, e.g. server/src/changeCipherDomain.cpp:61-115; the B200 path takes them all per call).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <iostream>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../include/ppq_b200.h"
+#include "ppq_wire.hpp"
+
+namespace ppqhost {
+
+inline void cu(cudaError_t e, const char* what) {
+    if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e));
+}
+inline void ck(int rc, const char* what) {
+    if (rc != PPQ_OK) throw std::runtime_error(std::string(what) + ": " + ppq_last_error());
+}
+
+template <class T>
+struct Dev {
+    T* p = nullptr;
+    size_t n = 0;
+    Dev() {}
+    explicit Dev(size_t count) { alloc(count); }
+    Dev(const Dev&) = delete;
+    Dev& operator=(const Dev&) = delete;
+    ~Dev() { if (p) cudaFree(p); }
+    void alloc(size_t count) {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = count;
+        if (count) cu(cudaMalloc(&p, count * sizeof(T)), "cudaMalloc");
+    }
+    void upload(const T* h, size_t count) { cu(cudaMemcpy(p, h, count * sizeof(T), cudaMemcpyHostToDevice), "H2D copy"); }
+    void download(T* h, size_t count) const { cu(cudaMemcpy(h, p, count * sizeof(T), cudaMemcpyDeviceToHost), "D2H copy"); }
+};
+
+struct Session {
+    ppq_ctx* cc = nullptr;
+    ppq_ctx_info_t info{};
+    size_t N = 0;
+    int L = 0, K = 0, dnum = 0;
+    std::vector<uint64_t> moduli;  // L + K
+
+    explicit Session(const std::string& cc_path) {
+        const std::string text = wire::slurp(cc_path);
+        int device = 0;
+        if (const char* e = std::getenv("PPQ_DEVICE")) device = std::atoi(e);
+        ck(ppq_ctx_create_from_ccjson(text.data(), text.size(), device, &cc), "ppq_ctx_create_from_ccjson");
+        ck(ppq_ctx_info(cc, &info), "ppq_ctx_info");
+        N = (size_t)1 << info.logN;
+        L = info.L;
+        K = info.K;
+        dnum = info.dnum;
+        moduli.resize((size_t)L + K);
+        ck(ppq_ctx_moduli(cc, moduli.data()), "ppq_ctx_moduli");
+    }
+    Session(const Session&) = delete;
+    ~Session() { if (cc) ppq_ctx_destroy(cc); }
+
+    // a DCRTPoly read from a key file -> [limbs][N] contiguous, checked against this context's basis
+    std::vector<uint64_t> flatten(const wire::Poly& p, size_t want_limbs, const char* what) const {
+        if (p.limbs.size() != want_limbs)
+            throw std::runtime_error(std::string(what) + ": expected " + std::to_string(want_limbs) + " limbs, file has " +
+                                     std::to_string(p.limbs.size()));
+        if (p.format != 0) throw std::runtime_error(std::string(what) + ": element is not in EVALUATION format");
+        std::vector<uint64_t> out(want_limbs * N);
+        for (size_t i = 0; i < want_limbs; ++i) {
+            if (p.moduli[i] != moduli[i]) throw std::runtime_error(std::string(what) + ": limb modulus does not match CC.json's basis");
+            if (p.limbs[i].size() != N) throw std::runtime_error(std::string(what) + ": limb length is not the ring dimension");
+            std::copy(p.limbs[i].begin(), p.limbs[i].end(), out.begin() + i * N);
+        }
+        return out;
+    }
+};
+
+// every blob of a container, in file order, with a pointer back to where its replacement goes
+struct BlobRef {
+    std::string* slot;
+};
+inline std::vector<BlobRef> blob_refs(std::vector<wire::Layer>& layers) {
+    std::vector<BlobRef> r;
+    for (auto& l : layers) {
+        r.push_back({&l.mean});
+        r.push_back({&l.std_dev});
+        for (auto& v : l.values) r.push_back({&v});
+    }
+    return r;
+}
+
+// A batch of ciphertexts with the same limb count, resident on the host as [n][2][ell][N].
+struct Batch {
+    uint32_t ell = 0;
+    std::vector<size_t> index;         // position in the file-order blob list
+    std::vector<wire::CtMeta> meta;
+    std::vector<uint64_t> data;
+    size_t n() const { return index.size(); }
+};
+// decode all blobs, grouped by limb count (one group in every file the reference flow produces)
+inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<BlobRef>& refs) {
+    std::map<uint32_t, Batch> groups;
+    for (size_t i = 0; i < refs.size(); ++i) {
+        wire::Ct c = wire::decode_ct(*refs[i].slot);
+        if (c.N != s.N) throw std::runtime_error("ciphertext ring dimension differs from CC.json");
+        if ((int)c.ell > s.L) throw std::runtime_error("ciphertext has more limbs than the context");
+        for (uint32_t k = 0; k < c.ell; ++k)
+            if (c.moduli[k] != s.moduli[k]) throw std::runtime_error("ciphertext limb modulus does not match CC.json's basis");
+        Batch& b = groups[c.ell];
+        b.ell = c.ell;
+        b.index.push_back(i);
+        b.meta.push_back(c.meta);
+        b.data.insert(b.data.end(), c.data.begin(), c.data.end());
+    }
+    return groups;
+}
+inline void encode_back(const Session& s, const Batch& b, uint32_t ell_out, const std::vector<wire::CtMeta>& meta,
+                        const std::vector<uint64_t>& data, const std::vector<BlobRef>& refs) {
+    const size_t ct = (size_t)2 * ell_out * s.N;
+    for (size_t k = 0; k < b.n(); ++k)
+        *refs[b.index[k]].slot = wire::encode_ct(meta[k], ell_out, (uint32_t)s.N, s.moduli.data(), data.data() + k * ct);
+}
+
+}  // namespace ppqhost

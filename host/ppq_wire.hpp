@@ -1,0 +1,344 @@
+// ppq_wire.hpp -- file formats of the four PPQSFLHE tools, host side (C++17, header only).
+//
+//   * container:  {"weights_summary":[{"layer","shape","mean","std_dev","values":[...]}]}  -- the schema written
+//     by client/src/encryptModelWeights.cpp:64-129 and rewritten by server/src/changeCipherDomain.cpp:57-124,
+//     server/src/aggregateEncryptedWeights.cpp:64-120; read by client/src/decryptModelWeights.cpp:68-121.
+//   * base64:     standard alphabet, padding, NO newlines (lib/base64_utils.h:10-49, OpenSSL BIO_FLAGS_BASE64_NO_NL).
+//   * keys / CC:  cereal JSON archives as OpenFHE writes them (client/src/keyGen.cpp:41-48, REkeyGen.cpp:60,
+//     server/src/genCC.cpp:89).  The DCRTPoly element layout is taken from a REAL file in the reference tree,
+//     client/storage/client_1/private/client_1-private.key:  {"v":[{"v":{"ptr_wrapper":{"data":{"v":[residues],
+//     "m":{"v":modulus}}}},"f":format,"p":...}, ...],"f":format,"p":...}.
+//   * ciphertext blob: the reference stores base64(cereal PortableBinary(Ciphertext<DCRTPoly>)), which embeds the
+//     whole crypto context per blob.  No sample blob exists in the reference tree, cereal and
+//     OpenFHE are absent, so that byte layout cannot be verified here; instead of shipping an unverifiable
+//     imitation this codec writes a self-describing blob ("PPQCT1\0\0" magic, the ciphertext scalars of
+//     CiphertextImpl -- noiseScaleDeg, level, hopslevel, encoding, slots, scalingFactor, scalingFactorInt -- then
+//     per polynomial and limb: modulus, length, raw little-endian residues, i.e. the same payload order as a
+//     serialized DCRTPoly).  decode_ct() rejects anything else loudly.  The codec is isolated in this header so a
+//     cereal-exact one can replace it when a real blob is available.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "json_min.hpp"
+
+namespace wire {
+
+// ------------------------------------------------------------------------------------------------ files
+inline std::string slurp(const std::string& path) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f.is_open()) throw std::runtime_error("cannot open " + path);
+    std::ostringstream ss;
+    ss << f.rdbuf();
+    return ss.str();
+}
+inline void spit(const std::string& path, const std::string& data) {
+    std::ofstream f(path, std::ios::binary);
+    if (!f.is_open()) throw std::runtime_error("cannot write " + path);
+    f.write(data.data(), (std::streamsize)data.size());
+    if (!f.good()) throw std::runtime_error("short write to " + path);
+}
+
+// ------------------------------------------------------------------------------------------------ base64
+inline std::string base64_encode(const unsigned char* p, size_t n) {
+    static const char T[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+    std::string out;
+    out.resize((n + 2) / 3 * 4);
+    size_t o = 0, i = 0;
+    for (; i + 2 < n; i += 3) {
+        const uint32_t v = ((uint32_t)p[i] << 16) | ((uint32_t)p[i + 1] << 8) | p[i + 2];
+        out[o++] = T[v >> 18];
+        out[o++] = T[(v >> 12) & 63];
+        out[o++] = T[(v >> 6) & 63];
+        out[o++] = T[v & 63];
+    }
+    if (i < n) {
+        uint32_t v = (uint32_t)p[i] << 16;
+        if (i + 1 < n) v |= (uint32_t)p[i + 1] << 8;
+        out[o++] = T[v >> 18];
+        out[o++] = T[(v >> 12) & 63];
+        out[o++] = (i + 1 < n) ? T[(v >> 6) & 63] : '=';
+        out[o++] = '=';
+    }
+    return out;
+}
+inline std::vector<unsigned char> base64_decode(const std::string& s) {
+    static int8_t D[256];
+    static bool init = false;
+    if (!init) {
+        std::memset(D, -1, sizeof D);
+        const char* T = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+        for (int i = 0; i < 64; ++i) D[(unsigned char)T[i]] = (int8_t)i;
+        init = true;
+    }
+    std::vector<unsigned char> out;
+    out.reserve(s.size() / 4 * 3);
+    uint32_t acc = 0;
+    int bits = 0;
+    for (unsigned char c : s) {
+        if (c == '=') break;
+        const int8_t d = D[c];
+        if (d < 0) {
+            if (c == '\n' || c == '\r') continue;
+            throw std::runtime_error("base64: invalid character");
+        }
+        acc = (acc << 6) | (uint32_t)d;
+        bits += 6;
+        if (bits >= 8) {
+            bits -= 8;
+            out.push_back((unsigned char)(acc >> bits));
+        }
+    }
+    return out;
+}
+
+// ------------------------------------------------------------------------------------------------ ciphertext blob
+struct CtMeta {  // the scalar members of lbcrypto::CiphertextImpl ("d","l","h","e","s","si","sl")
+    uint32_t noise_scale_deg = 2, level = 0, hops_level = 0, encoding = 3 /* CKKS_PACKED_ENCODING */, slots = 0;
+    double scaling_factor = 1.0;
+    uint64_t scaling_factor_int = 1;
+};
+struct Ct {
+    CtMeta meta;
+    uint32_t ell = 0, N = 0;
+    std::vector<uint64_t> moduli;  // [ell]
+    std::vector<uint64_t> data;    // [2][ell][N] EVAL, bit-reversed order
+};
+static const char CT_MAGIC[8] = {'P', 'P', 'Q', 'C', 'T', '1', 0, 0};
+
+template <class T>
+inline void put(std::string& o, T v) { o.append(reinterpret_cast<const char*>(&v), sizeof v); }
+template <class T>
+inline T get(const unsigned char*& p, const unsigned char* e) {
+    if ((size_t)(e - p) < sizeof(T)) throw std::runtime_error("ciphertext blob truncated");
+    T v;
+    std::memcpy(&v, p, sizeof v);
+    p += sizeof v;
+    return v;
+}
+
+// data: [2][ell][N]
+inline std::string encode_ct(const CtMeta& m, uint32_t ell, uint32_t N, const uint64_t* moduli, const uint64_t* data) {
+    std::string o;
+    o.reserve(96 + (size_t)2 * ell * (16 + (size_t)N * 8));
+    o.append(CT_MAGIC, 8);
+    put<uint32_t>(o, m.noise_scale_deg);
+    put<uint32_t>(o, m.level);
+    put<uint32_t>(o, m.hops_level);
+    put<uint32_t>(o, m.encoding);
+    put<double>(o, m.scaling_factor);
+    put<uint64_t>(o, m.scaling_factor_int);
+    put<uint32_t>(o, m.slots);
+    put<uint32_t>(o, 0u);               // format: 0 = EVALUATION
+    put<uint64_t>(o, 2);                // number of polynomials
+    for (int poly = 0; poly < 2; ++poly) {
+        put<uint64_t>(o, ell);
+        for (uint32_t i = 0; i < ell; ++i) {
+            put<uint64_t>(o, moduli[i]);
+            put<uint64_t>(o, N);
+            o.append(reinterpret_cast<const char*>(data + ((size_t)poly * ell + i) * N), (size_t)N * 8);
+        }
+    }
+    return base64_encode(reinterpret_cast<const unsigned char*>(o.data()), o.size());
+}
+inline Ct decode_ct(const std::string& b64) {
+    const std::vector<unsigned char> raw = base64_decode(b64);
+    const unsigned char* p = raw.data();
+    const unsigned char* e = p + raw.size();
+    if (raw.size() < 8 || std::memcmp(p, CT_MAGIC, 8) != 0)
+        throw std::runtime_error(
+            "ciphertext blob is not in PPQCT1 format (an OpenFHE cereal-binary blob cannot be read: its layout is "
+            "unverifiable without OpenFHE, see host/ppq_wire.hpp)");
+    p += 8;
+    Ct c;
+    c.meta.noise_scale_deg = get<uint32_t>(p, e);
+    c.meta.level = get<uint32_t>(p, e);
+    c.meta.hops_level = get<uint32_t>(p, e);
+    c.meta.encoding = get<uint32_t>(p, e);
+    c.meta.scaling_factor = get<double>(p, e);
+    c.meta.scaling_factor_int = get<uint64_t>(p, e);
+    c.meta.slots = get<uint32_t>(p, e);
+    if (get<uint32_t>(p, e) != 0) throw std::runtime_error("ciphertext blob: not in EVALUATION format");
+    if (get<uint64_t>(p, e) != 2) throw std::runtime_error("ciphertext blob: expected 2 polynomials");
+    for (int poly = 0; poly < 2; ++poly) {
+        const uint64_t ell = get<uint64_t>(p, e);
+        if (ell == 0 || ell > 4096) throw std::runtime_error("ciphertext blob: bad limb count");
+        if (poly == 0) {
+            c.ell = (uint32_t)ell;
+            c.moduli.resize(ell);
+        } else if (ell != c.ell) {
+            throw std::runtime_error("ciphertext blob: polynomials differ in limb count");
+        }
+        for (uint32_t i = 0; i < c.ell; ++i) {
+            const uint64_t q = get<uint64_t>(p, e), n = get<uint64_t>(p, e);
+            if (poly == 0 && i == 0) {
+                if (n == 0 || (n & (n - 1)) || n > (1u << 20)) throw std::runtime_error("ciphertext blob: bad ring dimension");
+                c.N = (uint32_t)n;
+                c.data.resize((size_t)2 * c.ell * c.N);
+            }
+            if (n != c.N) throw std::runtime_error("ciphertext blob: limbs differ in length");
+            if (poly == 0) c.moduli[i] = q;
+            else if (c.moduli[i] != q) throw std::runtime_error("ciphertext blob: polynomials differ in moduli");
+            if ((size_t)(e - p) < (size_t)n * 8) throw std::runtime_error("ciphertext blob truncated");
+            std::memcpy(c.data.data() + ((size_t)poly * c.ell + i) * c.N, p, (size_t)n * 8);
+            p += (size_t)n * 8;
+        }
+    }
+    if (p != e) throw std::runtime_error("ciphertext blob: trailing bytes");
+    return c;
+}
+
+// ------------------------------------------------------------------------------------------------ cereal JSON keys
+struct Poly {  // one DCRTPoly: limbs[i] has N residues mod moduli[i]
+    std::vector<uint64_t> moduli;
+    std::vector<std::vector<uint64_t>> limbs;
+    int format = 0;
+};
+inline bool looks_like_dcrtpoly(const jmin::Value& v) {
+    if (!v.is_object()) return false;
+    const jmin::Value* a = v.find("v");
+    if (!a || !a->is_array() || a->size() == 0) return false;
+    const jmin::Value& first = a->at(0);
+    return first.is_object() && first.find("v") && first.at("v").is_object() && first.at("v").find("ptr_wrapper");
+}
+inline Poly read_dcrtpoly(const jmin::Value& v) {
+    if (!looks_like_dcrtpoly(v)) throw std::runtime_error("key file: element is not a serialized DCRTPoly");
+    Poly p;
+    if (const jmin::Value* f = v.find("f")) p.format = (int)f->as_i64();
+    for (const auto& np : v.at("v").arr) {
+        const jmin::Value& d = np->at("v").at("ptr_wrapper").at("data");
+        const jmin::Value& vals = d.at("v");
+        std::vector<uint64_t> limb(vals.size());
+        for (size_t i = 0; i < limb.size(); ++i) limb[i] = vals.arr[i]->as_u64();
+        p.moduli.push_back(d.at("m").at("v").as_u64());
+        p.limbs.push_back(std::move(limb));
+    }
+    return p;
+}
+// depth-first search for the first member called `key` anywhere below v
+inline const jmin::Value* find_member(const jmin::Value& v, const std::string& key) {
+    if (v.is_object()) {
+        for (const auto& kv : v.obj) {
+            if (kv.first == key) return kv.second.get();
+        }
+        for (const auto& kv : v.obj) {
+            if (kv.first == "cc") continue;  // the embedded crypto context never holds key material
+            if (const jmin::Value* r = find_member(*kv.second, key)) return r;
+        }
+    } else if (v.is_array()) {
+        for (const auto& x : v.arr)
+            if (const jmin::Value* r = find_member(*x, key)) return r;
+    }
+    return nullptr;
+}
+// PrivateKeyImpl: member "s" (client/src/keyGen.cpp:46 writes it; decryptModelWeights.cpp:49-54 reads it)
+inline Poly read_private_key(const std::string& text) {
+    jmin::Ptr root = jmin::parse(text);
+    const jmin::Value* s = find_member(*root, "s");
+    if (!s) throw std::runtime_error("private key file: no member \"s\"");
+    return read_dcrtpoly(*s);
+}
+// PublicKeyImpl: member "h" = [b, a] (keyGen.cpp:41; encryptModelWeights.cpp:44-48)
+inline std::vector<Poly> read_public_key(const std::string& text) {
+    jmin::Ptr root = jmin::parse(text);
+    const jmin::Value* h = find_member(*root, "h");
+    if (!h || !h->is_array() || h->size() != 2) throw std::runtime_error("public key file: no member \"h\" with two elements");
+    return {read_dcrtpoly(h->at(0)), read_dcrtpoly(h->at(1))};
+}
+// EvalKeyRelinImpl: member "k" = [A-vector, B-vector], each a list of dnum DCRTPolys (REkeyGen.cpp:60;
+// changeCipherDomain.cpp:40-44)
+struct EvalKeyPolys {
+    std::vector<Poly> a, b;
+};
+inline EvalKeyPolys read_eval_key(const std::string& text) {
+    jmin::Ptr root = jmin::parse(text);
+    const jmin::Value* k = find_member(*root, "k");
+    if (!k || !k->is_array() || k->size() != 2) throw std::runtime_error("re-encryption key file: no member \"k\" with two vectors");
+    EvalKeyPolys out;
+    for (const auto& x : k->at(0).arr) out.a.push_back(read_dcrtpoly(*x));
+    for (const auto& x : k->at(1).arr) out.b.push_back(read_dcrtpoly(*x));
+    if (out.a.empty() || out.a.size() != out.b.size()) throw std::runtime_error("re-encryption key file: A and B vectors differ in length");
+    return out;
+}
+
+// writers of the same element layout (used by the test scaffolding that fabricates key files)
+inline jmin::Ptr dcrtpoly_to_json(const Poly& p) {
+    jmin::Ptr o = jmin::make(jmin::Value::Object);
+    jmin::Ptr arr = jmin::make(jmin::Value::Array);
+    for (size_t i = 0; i < p.limbs.size(); ++i) {
+        jmin::Ptr vals = jmin::make(jmin::Value::Array);
+        for (uint64_t x : p.limbs[i]) vals->arr.push_back(jmin::make_u64(x));
+        jmin::Ptr m = jmin::make(jmin::Value::Object);
+        jmin::set(m, "v", jmin::make_u64(p.moduli[i]));
+        jmin::Ptr data = jmin::make(jmin::Value::Object);
+        jmin::set(data, "cereal_class_version", jmin::make_u64(1));
+        jmin::set(data, "v", vals);
+        jmin::set(data, "m", m);
+        jmin::Ptr pw = jmin::make(jmin::Value::Object);
+        jmin::set(pw, "valid", jmin::make_u64(1));
+        jmin::set(pw, "data", data);
+        jmin::Ptr vv = jmin::make(jmin::Value::Object);
+        jmin::set(vv, "polymorphic_id", jmin::make_u64(1073741824));
+        jmin::set(vv, "ptr_wrapper", pw);
+        jmin::Ptr np = jmin::make(jmin::Value::Object);
+        jmin::set(np, "cereal_class_version", jmin::make_u64(1));
+        jmin::set(np, "v", vv);
+        jmin::set(np, "f", jmin::make_u64((uint64_t)p.format));
+        arr->arr.push_back(np);
+    }
+    jmin::set(o, "cereal_class_version", jmin::make_u64(1));
+    jmin::set(o, "v", arr);
+    jmin::set(o, "f", jmin::make_u64((uint64_t)p.format));
+    return o;
+}
+
+// ------------------------------------------------------------------------------------------------ container
+struct Layer {
+    jmin::Ptr layer, shape;          // copied through verbatim
+    std::string mean, std_dev;       // base64 blobs (encrypted files)
+    std::vector<std::string> values;
+};
+inline std::vector<Layer> read_container(const std::string& path) {
+    jmin::Ptr root = jmin::parse(slurp(path));
+    const jmin::Value* ws = root->find("weights_summary");
+    if (!ws || !ws->is_array()) throw std::runtime_error(path + ": no \"weights_summary\" array");
+    std::vector<Layer> out;
+    for (const auto& e : ws->arr) {
+        Layer l;
+        for (const auto& kv : e->obj) {
+            if (kv.first == "layer") l.layer = kv.second;
+            else if (kv.first == "shape") l.shape = kv.second;
+        }
+        if (!l.layer || !l.shape) throw std::runtime_error(path + ": entry without layer/shape");
+        l.mean = e->at("mean").as_string();
+        l.std_dev = e->at("std_dev").as_string();
+        for (const auto& v : e->at("values").arr) l.values.push_back(v->as_string());
+        out.push_back(std::move(l));
+    }
+    return out;
+}
+inline void write_container(const std::string& path, const std::vector<Layer>& layers) {
+    jmin::Ptr root = jmin::make(jmin::Value::Object);
+    jmin::Ptr arr = jmin::make(jmin::Value::Array);
+    for (const Layer& l : layers) {
+        jmin::Ptr o = jmin::make(jmin::Value::Object);
+        jmin::set(o, "layer", l.layer);
+        jmin::set(o, "shape", l.shape);
+        jmin::set(o, "mean", jmin::make_string(l.mean));
+        jmin::set(o, "std_dev", jmin::make_string(l.std_dev));
+        jmin::Ptr vals = jmin::make(jmin::Value::Array);
+        for (const std::string& v : l.values) vals->arr.push_back(jmin::make_string(v));
+        jmin::set(o, "values", vals);
+        arr->arr.push_back(o);
+    }
+    jmin::set(root, "weights_summary", arr);
+    spit(path, jmin::dump(*root, 2) + "\n");
+}
+inline bool same_json(const jmin::Value& a, const jmin::Value& b) { return jmin::dump(a, 0) == jmin::dump(b, 0); }
+
+}  // namespace wire

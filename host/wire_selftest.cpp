@@ -1,0 +1,168 @@
+// wire_selftest -- host-only checks of the file-format code (no GPU, no libppq_b200): driven by tests/test_host_wire.py
+//   wire_selftest base64                 RFC 4648 known answers + random round trips
+//   wire_selftest blob                   ciphertext blob round trip, rejection of foreign / truncated blobs
+//   wire_selftest json                   parser / printer round trip, nlohmann-style key ordering and indent
+//   wire_selftest privkey <file>         parse a cereal-JSON PrivateKey: prints limb count, N, moduli, FNV-1a of limbs
+//   wire_selftest mkkeys <in.json> <dir> fabricate key files in OpenFHE's cereal JSON element layout from residues
+#include <iostream>
+#include <random>
+
+#include "ppq_wire.hpp"
+
+static int fails = 0;
+#define CHECK(c)                                                          \
+    do {                                                                  \
+        if (!(c)) {                                                       \
+            std::cerr << "FAILED: " #c " at line " << __LINE__ << "\n"; \
+            ++fails;                                                      \
+        }                                                                 \
+    } while (0)
+
+static uint64_t fnv(const std::vector<uint64_t>& v) {
+    uint64_t h = 1469598103934665603ull;
+    for (uint64_t x : v)
+        for (int b = 0; b < 8; ++b) {
+            h ^= (x >> (8 * b)) & 0xff;
+            h *= 1099511628211ull;
+        }
+    return h;
+}
+
+static int t_base64() {
+    const char* kat[][2] = {{"", ""}, {"f", "Zg=="}, {"fo", "Zm8="}, {"foo", "Zm9v"}, {"foob", "Zm9vYg=="}, {"fooba", "Zm9vYmE="}, {"foobar", "Zm9vYmFy"}};
+    for (auto& k : kat) {
+        CHECK(wire::base64_encode((const unsigned char*)k[0], std::strlen(k[0])) == k[1]);
+        auto d = wire::base64_decode(k[1]);
+        CHECK(std::string(d.begin(), d.end()) == k[0]);
+    }
+    std::mt19937_64 rng(7);
+    for (int n : {1, 2, 3, 57, 1000, 65537}) {
+        std::vector<unsigned char> v(n);
+        for (auto& c : v) c = (unsigned char)rng();
+        std::string e = wire::base64_encode(v.data(), v.size());
+        CHECK(e.find('\n') == std::string::npos);
+        CHECK(e.size() == (size_t)(n + 2) / 3 * 4);
+        CHECK(wire::base64_decode(e) == v);
+    }
+    bool threw = false;
+    try { wire::base64_decode("ab$d"); } catch (const std::exception&) { threw = true; }
+    CHECK(threw);
+    return fails;
+}
+
+static int t_blob() {
+    const uint32_t ell = 3, N = 64;
+    std::vector<uint64_t> mod = {1152921504606748673ull, 1099510054913ull, 1099511922689ull}, data((size_t)2 * ell * N);
+    std::mt19937_64 rng(11);
+    for (size_t i = 0; i < data.size(); ++i) data[i] = rng() % mod[(i / N) % ell];
+    wire::CtMeta m;
+    m.noise_scale_deg = 2; m.level = 1; m.hops_level = 0; m.slots = 32; m.scaling_factor = 1.2089e24; m.scaling_factor_int = 1;
+    const std::string b = wire::encode_ct(m, ell, N, mod.data(), data.data());
+    wire::Ct c = wire::decode_ct(b);
+    CHECK(c.ell == ell && c.N == N && c.moduli == mod && c.data == data);
+    CHECK(c.meta.level == 1 && c.meta.noise_scale_deg == 2 && c.meta.slots == 32 && c.meta.scaling_factor == 1.2089e24);
+    for (const std::string& bad : {std::string("QUJD"), b.substr(0, b.size() / 2), std::string()}) {
+        bool threw = false;
+        try { wire::decode_ct(bad); } catch (const std::exception&) { threw = true; }
+        CHECK(threw);
+    }
+    return fails;
+}
+
+static int t_json() {
+    const std::string src = "{\"weights_summary\":[{\"values\":[\"QQ==\"],\"shape\":[2,3],\"layer\":\"gru/kernel\",\"mean\":\"TQ==\",\"std_dev\":\"Uw==\"}],\"x\":18446744073709551615,\"y\":-1.5e-3,\"z\":\"a\\\"b\\n\"}";
+    jmin::Ptr v = jmin::parse(src);
+    CHECK(v->at("x").as_u64() == 18446744073709551615ull);
+    CHECK(v->at("y").as_double() == -1.5e-3);
+    CHECK(v->at("z").as_string() == "a\"b\n");
+    const std::string out = jmin::dump(*v, 2);
+    // nlohmann setw(2): sorted keys, 2-space indent, one element per line
+    const std::string want =
+        "{\n  \"weights_summary\": [\n    {\n      \"layer\": \"gru/kernel\",\n      \"mean\": \"TQ==\",\n      \"shape\": [\n        2,\n        3\n      ],\n"
+        "      \"std_dev\": \"Uw==\",\n      \"values\": [\n        \"QQ==\"\n      ]\n    }\n  ],\n  \"x\": 18446744073709551615,\n  \"y\": -1.5e-3,\n  \"z\": \"a\\\"b\\n\"\n}";
+    CHECK(out == want);
+    CHECK(jmin::dump(*jmin::parse(out), 2) == out);
+    bool threw = false;
+    try { jmin::parse("{\"a\": [1, 2}"); } catch (const std::exception&) { threw = true; }
+    CHECK(threw);
+    // DCRTPoly element layout round trip
+    wire::Poly p;
+    p.moduli = {97, 193};
+    p.limbs = {{1, 2, 3, 4}, {5, 6, 7, 8}};
+    jmin::Ptr key = jmin::make(jmin::Value::Object);
+    jmin::set(key, "s", wire::dcrtpoly_to_json(p));
+    wire::Poly q = wire::read_private_key(jmin::dump(*key, 4, false));
+    CHECK(q.moduli == p.moduli && q.limbs == p.limbs && q.format == 0);
+    return fails;
+}
+
+static int t_privkey(const char* path) {
+    wire::Poly p = wire::read_private_key(wire::slurp(path));
+    std::cout << "limbs " << p.limbs.size() << " N " << p.limbs[0].size() << " format " << p.format << "\n";
+    for (size_t i = 0; i < p.limbs.size(); ++i) std::cout << "limb " << i << " q " << p.moduli[i] << " fnv " << fnv(p.limbs[i]) << "\n";
+    return 0;
+}
+
+// in.json: {"N":..,"moduli":[..],"sk":[[..]..],"pk_b":[[..]..],"pk_a":[[..]..],"rk_b":[[[..]..]..],"rk_a":[[[..]..]..]} (any subset)
+static wire::Poly poly_from(const jmin::Value& limbs, const std::vector<uint64_t>& mod) {
+    wire::Poly p;
+    for (size_t i = 0; i < limbs.size(); ++i) {
+        std::vector<uint64_t> l(limbs.at(i).size());
+        for (size_t k = 0; k < l.size(); ++k) l[k] = limbs.at(i).arr[k]->as_u64();
+        p.limbs.push_back(std::move(l));
+        p.moduli.push_back(mod[i]);
+    }
+    return p;
+}
+static jmin::Ptr wrap(const char* member, jmin::Ptr payload) {  // value0 -> ptr_wrapper -> data -> {member}
+    jmin::Ptr data = jmin::make(jmin::Value::Object);
+    jmin::set(data, "cereal_class_version", jmin::make_u64(0));
+    jmin::set(data, member, payload);
+    jmin::Ptr pw = jmin::make(jmin::Value::Object);
+    jmin::set(pw, "id", jmin::make_u64(2147483649ull));
+    jmin::set(pw, "data", data);
+    jmin::Ptr v0 = jmin::make(jmin::Value::Object);
+    jmin::set(v0, "polymorphic_id", jmin::make_u64(1073741824));
+    jmin::set(v0, "ptr_wrapper", pw);
+    jmin::Ptr root = jmin::make(jmin::Value::Object);
+    jmin::set(root, "value0", v0);
+    return root;
+}
+static int t_mkkeys(const char* in, const std::string& dir) {
+    jmin::Ptr r = jmin::parse(wire::slurp(in));
+    std::vector<uint64_t> mod;
+    for (const auto& m : r->at("moduli").arr) mod.push_back(m->as_u64());
+    if (const jmin::Value* sk = r->find("sk"))
+        wire::spit(dir + "/private.key", jmin::dump(*wrap("s", wire::dcrtpoly_to_json(poly_from(*sk, mod))), 4, false));
+    if (r->find("pk_b")) {
+        jmin::Ptr h = jmin::make(jmin::Value::Array);
+        h->arr.push_back(wire::dcrtpoly_to_json(poly_from(r->at("pk_b"), mod)));
+        h->arr.push_back(wire::dcrtpoly_to_json(poly_from(r->at("pk_a"), mod)));
+        wire::spit(dir + "/public.key", jmin::dump(*wrap("h", h), 4, false));
+    }
+    if (r->find("rk_b")) {
+        jmin::Ptr k = jmin::make(jmin::Value::Array), av = jmin::make(jmin::Value::Array), bv = jmin::make(jmin::Value::Array);
+        for (const auto& d : r->at("rk_a").arr) av->arr.push_back(wire::dcrtpoly_to_json(poly_from(*d, mod)));
+        for (const auto& d : r->at("rk_b").arr) bv->arr.push_back(wire::dcrtpoly_to_json(poly_from(*d, mod)));
+        k->arr.push_back(av);
+        k->arr.push_back(bv);
+        wire::spit(dir + "/rekey.key", jmin::dump(*wrap("k", k), 4, false));
+    }
+    return 0;
+}
+
+int main(int argc, char** argv) {
+    try {
+        const std::string mode = argc > 1 ? argv[1] : "";
+        if (mode == "base64") return t_base64() ? 1 : 0;
+        if (mode == "blob") return t_blob() ? 1 : 0;
+        if (mode == "json") return t_json() ? 1 : 0;
+        if (mode == "privkey" && argc == 3) return t_privkey(argv[2]);
+        if (mode == "mkkeys" && argc == 4) return t_mkkeys(argv[2], argv[3]);
+        std::cerr << "usage: wire_selftest base64|blob|json|privkey <file>|mkkeys <in.json> <dir>\n";
+        return 2;
+    } catch (const std::exception& e) {
+        std::cerr << "wire_selftest: " << e.what() << "\n";
+        return 1;
+    }
+}
