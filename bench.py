@@ -305,6 +305,32 @@ def main():
     }
     gpu_launches = int(sum(stage_launches)) + (args.steps if (world > 1 and rank == 0) else 0)
 
+    # ---- standalone batched NTT / iNTT (second half of BASELINE.json's metric: "NTT HBM GB/s"), rank 0 only.
+    # Algorithmic bytes per limb transform = 16 N (read N u64 + write N u64; a transform is two HBM passes here).
+    ntt = None
+    if rank == 0:
+        reps = 20
+        ids = np.tile(np.arange(M, dtype=np.int32), reps)          # every limb of Q u P, `reps` polys each
+        buf = rand_res((len(ids), N), qv.repeat(reps).view(-1, 1))  # 27 x 20 x 512 KiB = 270 MiB > L2
+        res = {}
+        for name, inv in (("fwd", False), ("inv", True)):
+            cc.ntt(buf, ids, inverse=inv)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                cc.ntt(buf, ids, inverse=inv)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 5
+            res[name] = {"ms": ms, "gbs": 16.0 * N * len(ids) / (ms * 1e-3) / 1e9, "limb_ntt_per_s": len(ids) / (ms * 1e-3)}
+        ntt = {"logN": cfg["logN"], "polys": int(len(ids)), "bytes": int(buf.numel() * 8), "alg_bytes_per_transform": 16 * N,
+               "fwd_gbs": res["fwd"]["gbs"], "inv_gbs": res["inv"]["gbs"], "fwd_frac": res["fwd"]["gbs"] / peak,
+               "inv_frac": res["inv"]["gbs"] / peak, "fwd_limb_ntt_per_s": res["fwd"]["limb_ntt_per_s"],
+               "inv_limb_ntt_per_s": res["inv"]["limb_ntt_per_s"], "api": "ppq_ntt_forward / ppq_ntt_inverse (C ABI)"}
+        del buf
+        torch.cuda.empty_cache()
+
     # ---- e2e: host buffers in, aggregate out, copies inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -378,7 +404,7 @@ def main():
                        "l2": "inputs per step (%.1f GiB per GPU) >> 126 MB L2; no flush needed" %
                              (len(my_clients) * n_slots * 2 * ell * N * 8 / 2 ** 30),
                        "residues": "uniform random canonical residues (timing is data independent)"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
+            "roofline": roofline, "ntt": ntt, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

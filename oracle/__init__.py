@@ -289,7 +289,14 @@ def sample_uniform(seed, q, n):
 
 
 def max_threads():
-    return lib().ppqo_max_threads()
+    """Host threads the CPU baseline may use: the cores this process may run on.  (torchrun exports
+    OMP_NUM_THREADS=1, so omp_get_max_threads() alone would silently time a single thread.)"""
+    import os
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    return max(n, lib().ppqo_max_threads())
 
 
 def parse_ccjson(text):
