@@ -1,6 +1,7 @@
 // capi.cu -- the C ABI of libppq_b200.so (include/ppq_b200.h): context/key/scratch management and the
 // orchestration of kernel launches for each reference-facing operation.  No CPU fallback: every compute entry
 // point needs a CUDA device and fails loudly otherwise.
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -694,8 +695,30 @@ extern "C" int ppq_encode(ppq_ctx* c, int ell, const double* d_vals, size_t n_va
     CU(c->scratch2.ensure(2 * n * N));
     double2* z = reinterpret_cast<double2*>(c->scratch2.p);
     int64_t* co = reinterpret_cast<int64_t*>(c->scratch2.p + n * N);
-    ckks::launch_encode_fft(c->fft, d_vals, n_vals, sf, z, co, n, st);
+    // Scaling factors beyond what an int64 coefficient can hold (FLEXIBLEAUTOEXT at level 0 with 59-bit scaling
+    // primes: sfBig = 2^79) are applied in two steps, as OpenFHE's CKKSPackedEncoding::Encode does with its
+    // approxFactor: round at sf / 2^a, then multiply the residues by 2^a mod q_i.  a keeps |coefficient| < 2^62 for
+    // slot values up to 16 in magnitude; encode is tolerance-checked only.
+    int sf_exp = 0;
+    std::frexp(sf, &sf_exp);
+    const int approx = sf_exp > 58 ? sf_exp - 58 : 0;
+    ckks::launch_encode_fft(c->fft, d_vals, n_vals, std::ldexp(sf, -approx), z, co, n, st);
     launch_small_to_res(c->k, co, (u64*)d_pt, 1, ell, n, st);
+    if (approx > 0) {
+        std::vector<u64> f(2 * (size_t)ell);
+        for (int i = 0; i < ell; ++i) {
+            const u64 q = c->hp.mod[i];
+            u64 t = 1, b = 2 % q;
+            for (int e = approx; e; e >>= 1, b = host::mulmod(b, b, q))
+                if (e & 1) t = host::mulmod(t, b, q);
+            f[i] = t;
+            f[ell + i] = host::shoup(t, q);
+        }
+        CU(c->fac.ensure(2 * (size_t)c->hp.L));
+        CU(cudaMemcpyAsync(c->fac.p, f.data(), f.size() * sizeof(u64), cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));  // f is stack-owned staging
+        launch_mult_scalar_polys(c->k, (const u64*)d_pt, (u64*)d_pt, c->fac.p, c->fac.p + ell, ell, n * ell, st);
+    }
     std::vector<int> ids(n * ell);
     for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % ell);
     CU(c->ids.ensure(ids.size()));

@@ -804,6 +804,10 @@ void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, 
                         size_t n_ct, cudaStream_t st) {
     k_mult_scalar<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
 }
+void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
+                              size_t n_polys, cudaStream_t st) {
+    k_mult_scalar<<<pw_grid(c, n_polys, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
+}
 void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
                          cudaStream_t st) {
     k_small_to_res<<<pw_grid(c, n_ct * n_small * ell, 1), 256, 0, st>>>(c, (const long long*)small, out, n_small, ell);

@@ -120,6 +120,9 @@ void launch_finalize_mod(const KCtx& c, u64* x, int ell, size_t n_ct, cudaStream
 // out = in * f[i] mod q_i
 void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                         size_t n_ct, cudaStream_t st);
+// same over a flat list of n_polys polynomials whose limb index is (poly index % ell)
+void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
+                              size_t n_polys, cudaStream_t st);
 // small signed coefficients -> residues of limb i:  out[g][y][n] = small[g][y / ell][n] mod q_{y % ell}
 void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
                          cudaStream_t st);

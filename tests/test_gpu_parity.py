@@ -123,7 +123,10 @@ def test_modup_bit_exact(kind, ell):
 
 @pytest.mark.parametrize("kind,ell,n", [("c1", 4, 5), ("c1", 3, 2), ("c1", 1, 1), ((12, 5, 3, 45), 7, 3),
                                         ((12, 5, 3, 45), 5, 2), ((13, 4, 2, 50), 6, 2), ((15, 2, 2, 40), 4, 2),
-                                        ((16, 6, 3, 59), 8, 2), ((17, 2, 2, 40), 4, 1)])
+                                        ((16, 6, 3, 59), 8, 2), ((17, 2, 2, 40), 4, 1),
+                                        # BASELINE.json full sizes: C3 (N=2^16, 20 limbs, K=7, digits 7/7/6), its fan-out
+                                        # level ell-1 (digits 7/7/5), C4 (N=2^17, 40 limbs, K=14, digits 14/14/12)
+                                        ((16, 18, 3, 59), 20, 2), ((16, 18, 3, 59), 19, 1), ((17, 38, 3, 59), 40, 1)])
 def test_reencrypt_bit_exact(kind, ell, n):
     from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
     o, cc = _cc_pair(kind)
@@ -136,6 +139,47 @@ def test_reencrypt_bit_exact(kind, ell, n):
         want = o.reencrypt(ell, ct[g], kb, ka)
         assert np.array_equal(out[g][1], want[1]), f"c1' differs (ct {g})"
         assert np.array_equal(out[g][0], want[0]), f"c0' differs (ct {g})"
+
+
+def test_fused_and_split_inner_product_agree(monkeypatch):
+    """The two forms of the key inner product (one fused ROW-pass kernel / forward ROW pass + TMA-staged pointwise
+    kernel + inverse ROW pass) must give identical ciphertexts."""
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    outs = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("PPQ_IP_FUSED", fused)
+        o, cc = _cc_pair((14, 5, 3, 50))
+        rng = np.random.default_rng(21)
+        ct = _rand_ct(rng, o, o.L, 3)
+        kb, ka = _rand_key(rng, o)
+        outs.append(cc.ReEncrypt(CiphertextBatch(to_device_u64(ct, cc.device), CtMeta()), EvalKey(cc, kb, ka)).numpy())
+        cc.close()
+    assert np.array_equal(outs[0], outs[1])
+    assert np.array_equal(outs[0][0], o.reencrypt(o.L, ct[0], kb, ka))
+
+
+def test_full_size_round_trip_c3():
+    """Size-independent property at BASELINE.json's C3 size (N=2^16, 20 limbs, dnum 3): Decrypt_{sk2}(ReEncrypt_{1->2}(
+    Enc_{pk1}(m))) = m within the CKKS tolerance, and ReEncrypt+EvalAdd of two clients decrypts to the sum."""
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair((16, 18, 3, 59))
+    dev = cc.device
+    rng = np.random.default_rng(3)
+    keys = {c: o.keygen(70 + c) for c in (1, 2, 3)}          # (s, sk_eval, pk_b, pk_a)
+    rk = {c: EvalKey(cc, *o.rekeygen(80 + c, keys[c][1], keys[3][2], keys[3][3])) for c in (1, 2)}
+    m = {c: np.clip(rng.normal(0, 0.05, (2, o.N // 2)), -0.3, 0.3) for c in (1, 2)}
+    acc = CiphertextBatch(torch.zeros((2, 2, o.L, o.N), dtype=torch.int64, device=dev), CtMeta())
+    for c in (1, 2):
+        pt = cc.MakeCKKSPackedPlaintext(m[c])
+        ct = cc.Encrypt((to_device_u64(keys[c][2], dev), to_device_u64(keys[c][3], dev)), pt, seed=5 + c)
+        if c == 1:
+            one = cc.ReEncrypt(ct, rk[1])
+            dec = cc.Decrypt(to_device_u64(keys[3][1], dev), one).GetRealPackedValue()
+            assert np.max(np.abs(dec - m[1])) < 2.0 ** -20
+            acc.meta = ct.meta
+        cc.ReEncryptAccumulate(ct, rk[c], acc)
+    dec = cc.Decrypt(to_device_u64(keys[3][1], dev), acc).GetRealPackedValue()
+    assert np.max(np.abs(dec - (m[1] + m[2]))) < 2.0 ** -19
 
 
 def test_reencrypt_wave_size_independent():
