@@ -284,11 +284,15 @@ def main():
     local_ct = len(my_clients) * n_slots * args.steps
     dom_bytes = words[dom] * 8.0 * N * local_ct
     achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
+    # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/ncu_traffic.json holds
+    # dram__bytes_read.sum + dram__bytes_write.sum per ciphertext), scaled to this run's ciphertexts per launch
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    cts_per_launch = local_ct / max(1, stage_launches[dom])
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(args.config, {}).get(names[dom])
+            per_ct = json.load(open(tpath)).get(args.config, {}).get("dram_bytes_per_ct", {}).get(names[dom])
+            traffic = per_ct * cts_per_launch if per_ct is not None else None
         except Exception:
             traffic = None
     w_alg = path_alg_bytes(N, ell, K, cc.dnum, n_slots)
@@ -296,14 +300,20 @@ def main():
         "bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
         "launch_avg_ms": stage_ms[dom] / max(1, stage_launches[dom]),
-        "alg_bytes_per_ct": words[dom] * 8.0 * N,
+        "alg_bytes_per_ct": words[dom] * 8.0 * N, "alg_bytes_per_launch": words[dom] * 8.0 * N * cts_per_launch,
+        "cts_per_launch": cts_per_launch,
         "stage_share": {n: (m / max(1e-9, sum(stage_ms))) for n, m in zip(names, stage_ms)},
         "stage_gbs": {n: (w * 8.0 * N * local_ct / (m * 1e-3) / 1e9 if m > 0 else 0.0)
                       for n, w, m in zip(names, words, stage_ms)},
         "path": {"alg_bytes_per_ct": w_alg, "achieved": value / world * w_alg / 1e9, "frac": value / world * w_alg / 1e9 / peak,
                  "note": "whole ReEncrypt+EvalAdd path per GPU against SURVEY 8(d) W_alg (ideal fusion)"},
     }
-    gpu_launches = int(sum(stage_launches)) + (args.steps if (world > 1 and rank == 0) else 0)
+    # kernels of ours launched inside the timed region: per wave 2 (c1 inverse) + `parts` ModUp conversions + COL pass
+    # + inner product (3 kernels in the split form, 1 fused) + P inverse COL + 2 ModDown conversions + COL + ROW pass,
+    # plus the final mod-q kernel on the root after the cross-GPU reduce
+    split = os.environ.get("PPQ_IP_FUSED", "0") in ("", "0")
+    per_wave = 2 + parts + 1 + (3 if split else 1) + 1 + 2 + 1 + 1
+    gpu_launches = int(stage_launches[0]) * per_wave + (args.steps if (world > 1 and rank == 0) else 0)
 
     # ---- standalone batched NTT / iNTT (second half of BASELINE.json's metric: "NTT HBM GB/s"), rank 0 only.
     # Algorithmic bytes per limb transform = 16 N (read N u64 + write N u64; a transform is two HBM passes here).

@@ -11,12 +11,18 @@
 #include "ckks.cuh"
 #include "ntt_core.cuh"
 
+#ifndef PPQ_ROW_MINB
+#define PPQ_ROW_MINB 5
+#endif
 namespace ppq {
 
 // ---------------------------------------------------------------------------------------------------------
 // streaming global accesses: data limbs are touched once per pass (evict-first), twiddles/keys stay cached
 __device__ __forceinline__ u64 ld_stream(const u64* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(u64* p, u64 v) { __stcs(p, v); }
+
+// bring a line that the epilogue will read into L2 while the NTT pass runs (costs no register)
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __device__ __forceinline__ void ld8(u64 (&a)[8], const u64* p) {  // 64 contiguous bytes, 16-byte aligned
     const ulonglong2* v = reinterpret_cast<const ulonglong2*>(p);
@@ -215,14 +221,14 @@ struct RowGeom {
 };
 
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS)
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
     k_fwd_row_plain(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const u32 y = blockIdx.y, g = blockIdx.z;
+    const u32 y = blockIdx.z, g = blockIdx.y;  // g fastest: CTAs sharing a limb's twiddles are co-resident
     const int limb = limb_ids[y];
     if (limb < 0) return;  // block-uniform: slot not to be transformed
     const LimbC lc = c.limbs[limb];
@@ -239,7 +245,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS)
 }
 
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS)
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
     k_inv_row(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs,
               const int* __restrict__ limb_map) {
     typedef RowGeom<S> G;
@@ -247,7 +253,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS)
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const u32 y = blockIdx.y, g = blockIdx.z;
+    const u32 y = blockIdx.z, g = blockIdx.y;  // g fastest: CTAs sharing a limb's twiddles are co-resident
     const int limb = limb_map[y];
     const LimbC lc = c.limbs[limb];
     const ulonglong2* tw = c.twi + (size_t)limb * N;
@@ -263,14 +269,14 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS)
 
 // Forward ROW pass + inner product with the re-encryption key (+ inverse ROW pass on the P limbs).
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_ip(KCtx c, IpArgs A) {
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_ip(KCtx c, IpArgs A) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const int r = blockIdx.y;
-    const u32 g = blockIdx.z;
+    const int r = blockIdx.z;
+    const u32 g = blockIdx.y;
     const int M = A.ell + A.K;
     const int limb = r < A.ell ? r : A.L + (r - A.ell);
     const LimbC lc = c.limbs[limb];
@@ -457,14 +463,14 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
 
 // Forward ROW pass + ModDown combine: out = (x - conv) * P^-1 (+ c0 on poly 0) (+ running sum).
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c, MdArgs A) {
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_moddown(KCtx c, MdArgs A) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const int y = blockIdx.y;
-    const u32 g = blockIdx.z;
+    const int y = blockIdx.z;
+    const u32 g = blockIdx.y;
     const int poly = y / A.ell, i = y % A.ell;
     const LimbC lc = c.limbs[i];
     const ulonglong2* tw = c.twf + (size_t)i * N;
@@ -474,6 +480,10 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c,
     const u64* in = A.conv + g * A.conv_gs + off;
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
+    u64* o = A.out + g * A.out_gs + off + 8 * u;
+    prefetch_l2(A.extq + g * A.extq_gs + off + 8 * u);
+    if (poly == 0) prefetch_l2(A.ct_in + g * A.in_gs + off + 8 * u);
+    if (A.accumulate) prefetch_l2(o);
     fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
     u64 x[8];
     ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
@@ -488,7 +498,6 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c,
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], x[k], lc.q);
     }
-    u64* o = A.out + g * A.out_gs + off + 8 * u;
     if (A.accumulate) {
         ld8(x, o);
 #pragma unroll
@@ -499,14 +508,14 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_moddown(KCtx c,
 
 // Forward ROW pass + rescale combine (DropLastElementAndScale, then the EvalMult constant folded in).
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS) k_fwd_row_rescale(KCtx c, RsArgs A) {
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_rescale(KCtx c, RsArgs A) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const int y = blockIdx.y;
-    const u32 g = blockIdx.z;
+    const int y = blockIdx.z;
+    const u32 g = blockIdx.y;
     const int lm1 = A.ell - 1;
     const int poly = y / lm1, i = y % lm1;
     const LimbC lc = c.limbs[i];
@@ -668,7 +677,7 @@ void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_p
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
     PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 0>(c, data, 0, data, 0, nullptr, nullptr, d_limb_ids, 0, n_polys, 1, st)));
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, n_polys, 1), RowGeom<S>::THREADS, 0, st>>>(
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, 1, n_polys), RowGeom<S>::THREADS, 0, st>>>(
                                 c, data, 0, d_limb_ids)));
 }
 
@@ -676,7 +685,7 @@ void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
                           cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, n_slots, n_g), RowGeom<S>::THREADS, 0, st>>>(
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, n_g, n_slots), RowGeom<S>::THREADS, 0, st>>>(
                                 c, data, gs, d_limb_ids)));
 }
 
@@ -684,7 +693,7 @@ void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t
                     int n_slots, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, n_slots, n_g), RowGeom<S>::THREADS, 0, st>>>(
+    PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, n_g, n_slots), RowGeom<S>::THREADS, 0, st>>>(
                                 c, in, in_gs, out, out_gs, d_limb_map)));
 }
 void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
@@ -752,7 +761,7 @@ bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t
 void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_ip<S><<<dim3(n1 / RowGeom<S>::R, a.ell + a.K, n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_ip<S><<<dim3(n1 / RowGeom<S>::R, n_g, a.ell + a.K), RowGeom<S>::THREADS, 0, st>>>(c, a)));
 }
 bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
     const int N = 1 << c.logN;
@@ -780,12 +789,12 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, 2 * a.ell, n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, n_g, 2 * a.ell), RowGeom<S>::THREADS, 0, st>>>(c, a)));
 }
 void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_rescale<S><<<dim3(n1 / RowGeom<S>::R, 2 * (a.ell - 1), n_g), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_rescale<S><<<dim3(n1 / RowGeom<S>::R, n_g, 2 * (a.ell - 1)), RowGeom<S>::THREADS, 0, st>>>(c, a)));
 }
 
 static dim3 pw_grid(const KCtx& c, size_t ny, int per_thread) {
