@@ -363,9 +363,10 @@ static int pick_wave(const ppq_ctx* c, const WaveLayout& w, size_t n) {
         if (e && std::atoi(e) > 0) {
             g = (size_t)std::atoi(e);
         } else {
-            // Measured on B200 (profiles/): the pipeline is integer-issue bound, not HBM bound, so large waves
-            // (fewer, fuller launches: no tail effect) beat L2-resident small waves.  2 GiB of scratch.
-            const size_t budget = (size_t)2 << 30;
+            // Measured on B200 (profiles/r01_notes.md): the pipeline is integer-issue bound, not HBM bound, so large
+            // waves (fewer, fuller launches, key tiles reused over more ciphertexts) beat L2-resident small ones:
+            // C3 13 / 26 / 54 ciphertexts per wave = 5676 / 5862 / 6038 ct/s.  6 GiB of scratch (of 180 GB).
+            const size_t budget = (size_t)6 << 30;
             g = budget / (w.per_ct * sizeof(u64));
             if (g < 1) g = 1;
         }

@@ -174,16 +174,15 @@ __global__ void __launch_bounds__(256)
     const u32 n = blockIdx.x * 256 + threadIdx.x;
     const u32 g = blockIdx.z;
     const u64* in = src + g * src_gs + (size_t)P.src_first * N + n;
-    u32 y0[NS], y1[NS], ys[NS];
+    u32 y0[NS], y1[NS];  // y0 + y1 is re-formed per term (one ALU add; the ALU pipe has slack, registers do not)
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
         const u64 y = ld_stream(in + (size_t)i * N);
         y0[i] = (u32)y & 0x3fffffffu;
         y1[i] = (u32)(y >> 30);
-        ys[i] = y0[i] + y1[i];
     }
     u64* out = dst + g * dst_gs + n;
-#pragma unroll 2
+#pragma unroll(NS <= 8 ? 2 : 1)
     for (int t = 0; t < P.n_jobs; ++t) {
         const typename BcPack<NS>::J& J = P.j[t];
         LimbC lc;
@@ -200,7 +199,7 @@ __global__ void __launch_bounds__(256)
                 const uint4 cc = J.c[i];
                 A0 += (u64)y0[i] * cc.x;
                 A2 += (u64)y1[i] * cc.y;
-                A1 += (u64)ys[i] * cc.z;
+                A1 += (u64)(y0[i] + y1[i]) * cc.z;
             }
             r += kara_reduce(A0, A2, A1, lc);
         }
