@@ -8,7 +8,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libppq_b200.so")
+# PPQ_B200_LIB lets tools/stage_times.py A/B-test differently compiled builds of the same library (still sm_100a CUDA).
+LIB_PATH = os.environ.get("PPQ_B200_LIB") or os.path.join(_HERE, "lib", "libppq_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 HEADER = os.path.join(_HERE, "..", "include", "ppq_b200.h")
 

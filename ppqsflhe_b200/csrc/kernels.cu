@@ -14,7 +14,16 @@
 #ifndef PPQ_ROW_MINB
 #define PPQ_ROW_MINB 5
 #endif
+#ifndef PPQ_COL_MINB
+#define PPQ_COL_MINB 5  // 51 registers: 8.4 -> 7.7 us/ct on the inverse COL passes, forward unchanged (profiles/r03_notes.md)
+#endif
 namespace ppq {
+
+#ifndef PPQ_NO_ZADD
+#define PPQ_Z(lc) ((u64)(lc).pad)  // run-time zero, see ct_bfly_lazy
+#else
+#define PPQ_Z(lc) 0ull
+#endif
 
 // ---------------------------------------------------------------------------------------------------------
 // streaming global accesses: data limbs are touched once per pass (evict-first), twiddles/keys stay cached
@@ -54,7 +63,7 @@ __device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
 // MODE 0: plain (src poly = blockIdx.y, limb from limb_ids; a negative limb id skips the slot)
 // MODE 2: centred SwitchModulus prologue (DropLastElementAndScale)
 template <int S, int W, int MODE>
-__global__ void __launch_bounds__(W << (S - 3))
+__global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     k_fwd_col(KCtx c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs,
               const BcJob* __restrict__ jobs, const u64* __restrict__ chat, const int* __restrict__ limb_ids,
               u64 q_src) {
@@ -98,13 +107,13 @@ __global__ void __launch_bounds__(W << (S - 3))
         }
     }
     ColPos<W> pos{w};
-    fwd_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false);
+    fwd_pass<S, ColPos<W>, FWD_COL_IN>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
 #pragma unroll
-    for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy [0,8q): consumed by a ROW pass
+    for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy (< 16q): consumed by a ROW pass
 }
 
 template <int S, int W>
-__global__ void __launch_bounds__(W << (S - 3))
+__global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
               const u64* __restrict__ scale, const u64* __restrict__ scale_sh) {
     __shared__ u64 sm[W << S];
@@ -120,7 +129,7 @@ __global__ void __launch_bounds__(W << (S - 3))
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = p[(size_t)(8 * u + k) * n2];
     ColPos<W> pos{w};
-    inv_pass<S>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false);
+    inv_pass<S, ColPos<W>, INV_COL_IN>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false);
     const u64 sc = scale[y], scs = scale_sh[y];
 #pragma unroll
     for (int k = 0; k < 8; ++k) p[(size_t)point_of<S - 3>(u, k) * n2] = mul_shoup(a[k], sc, scs, lc.q);
@@ -237,9 +246,9 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = p[point_of<S - 3>(u, k)];
     RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = canon8(a[k], lc);
+    for (int k = 0; k < 8; ++k) a[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
     st8(p + 8 * u, a);
 }
 
@@ -260,7 +269,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
     u64 a[8];
     ld8(a, in + g * in_gs + off + 8 * u);
     RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-    inv_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    inv_pass<S, RowPos<S>, INV_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
     u64* o = out + g * out_gs + off;
 #pragma unroll
     for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy [0,4q): consumed by k_inv_col
@@ -296,9 +305,9 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_i
             const u64* in = A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
 #pragma unroll
             for (int k = 0; k < 8; ++k) d[k] = ld_stream(in + point_of<S - 3>(u, k));
-            fwd_pass<S>(d, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true);
+            fwd_pass<S, RowPos<S>, FWD_ROW_IN>(d, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true, PPQ_Z(lc));
 #pragma unroll
-            for (int k = 0; k < 8; ++k) d[k] = canon8(d[k], lc);
+            for (int k = 0; k < 8; ++k) d[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(d[k], lc);
         }
         u64 kb[8], ka[8];
         const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off + 8 * u;
@@ -323,11 +332,11 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_i
     } else {  // P limb: ModDown needs it in COEFF -> run the inverse ROW pass while the tile is in registers
         const ulonglong2* twi = c.twi + (size_t)limb * N;
         u64* o = A.extp + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
-        inv_pass<S>(e0, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
+        inv_pass<S, RowPos<S>, INV_ROW_IN>(e0, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e0[k];
         o += (size_t)A.K * N;
-        inv_pass<S>(e1, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
+        inv_pass<S, RowPos<S>, INV_ROW_IN>(e1, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
 #pragma unroll
         for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e1[k];
     }
@@ -483,14 +492,15 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     prefetch_l2(A.extq + g * A.extq_gs + off + 8 * u);
     if (poly == 0) prefetch_l2(A.ct_in + g * A.in_gs + off + 8 * u);
     if (A.accumulate) prefetch_l2(o);
-    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
     u64 x[8];
     ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
     const u64 pi = A.pinv[i], pis = A.pinv_sh[i];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const u64 v = canon8(a[k], lc);
-        a[k] = mul_shoup(x[k] + lc.q - v, pi, pis, lc.q);
+        // the exact Shoup product takes any 64-bit input: fold to < 8q only, x + 8q - v < 9q
+        const u64 v = fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+        a[k] = mul_shoup(x[k] + (lc.q2 << 2) - v, pi, pis, lc.q);
     }
     if (poly == 0) {
         ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
@@ -525,14 +535,15 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_r
     const u64* in = A.conv + g * A.conv_gs + (size_t)y * N + roff;
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
-    fwd_pass<S>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
     u64 x[8];
     ld8(x, A.ct_in + g * A.in_gs + ((size_t)poly * A.ell + i) * N + roff + 8 * u);
     const u64 cs = A.cst[i], css = A.cst_sh[i];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const u64 v = canon8(a[k], lc);
-        a[k] = mul_shoup(x[k] + lc.q - v, cs, css, lc.q);
+        // the exact Shoup product takes any 64-bit input: fold to < 8q only, x + 8q - v < 9q
+        const u64 v = fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+        a[k] = mul_shoup(x[k] + (lc.q2 << 2) - v, cs, css, lc.q);
     }
     st8(A.out + g * A.out_gs + (size_t)y * N + roff + 8 * u, a);
 }

@@ -27,10 +27,14 @@
 #pragma once
 #include "modarith.cuh"
 
+#ifndef PPQ_BFLY_V
+#define PPQ_BFLY_V 2  // 2 = statically tracked lazy bounds (default); 0 = fold on every butterfly (round-1 form)
+#endif
+
 namespace ppq {
 
-// ---- lazy butterflies (Harvey, with the 3-multiply Shoup product whose result lies in [0,4q)).
-// Forward keeps values in [0,8q); inverse keeps them in [0,4q).  q4 = 4q.
+// ---- lazy butterflies (Harvey, with the 3-multiply Shoup product whose result lies in [0,4q)), round-1 form
+// (PPQ_BFLY_V == 0): one fold per butterfly, forward values in [0,8q), inverse in [0,4q).  q4 = 4q.
 __device__ __forceinline__ void ct_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4) {
     // conditional subtraction folded into three-input adds (IADD3 on the ALU pipe; a two-input 64-bit add is
     // otherwise placed on the fmaheavy pipe as IMAD.X, which is the binding pipe)
@@ -47,19 +51,81 @@ __device__ __forceinline__ void gs_bfly(u64& X, u64& Y, ulonglong2 tw, u64 q, u6
     Y = mul_shoup_lazy4(d, tw.x, tw.y, q);
 }
 
+// ---- forward butterflies with statically tracked bounds (PPQ_BFLY_V == 2).  q < 2^60, so 16q <= 2^64: a value may
+// grow to < 16q before it has to be folded.  One CT stage maps a uniform bound b (units of q) to b + 4
+// (X' = X + t, Y' = X - t + 4q with t < 4q; Y itself is only ever multiplied, and the Shoup product accepts any
+// 64-bit input), so a conditional subtraction of 8q is needed only on stages entered with b > 12: about every
+// second stage instead of every stage.
+__host__ __device__ constexpr int fwd_bound_after(int b, int stages) {
+    for (int i = 0; i < stages; ++i) {
+        if (b + 4 > 16) b = 8;
+        b += 4;
+    }
+    return b;
+}
+template <bool FOLD>
+__device__ __forceinline__ void ct_bfly_lazy(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4, u64 z) {
+    const u64 t = mul_shoup_lazy4(Y, tw.x, tw.y, q);
+    if (FOLD) {
+        const u64 q8 = q4 << 1;
+        if (X >= q8) X -= q8;
+    }
+    Y = X + q4 - t;
+    // z is a run-time zero (LimbC::pad): a THREE-input add cannot be turned into IMAD.X, which ptxas otherwise
+    // places on the fmaheavy pipe -- the binding pipe of every NTT kernel (tools/sass_cost.py)
+    X = X + t + z;
+}
+
+// ---- inverse (Gentleman-Sande) butterflies with statically tracked per-register bounds.  Invariant: every
+// register is < 8q when a butterfly reads it, so X + Y and X - Y + 8q stay below 16q <= 2^64.  The difference goes
+// through the Shoup product (< 4q); the sum is folded by 8q only if its bound exceeds 8q.  Registers that hold
+// products (bound 4) pair with each other in the next stage (the two inputs of a GS butterfly always have the same
+// history), so about a third of the folds of a radix-8 group disappear, and nearly all of them in the first group
+// of a pass that reads canonical data.
+struct InvPlan {
+    unsigned fold;  // bit (8*stage + k): fold the sum written to register k in that stage
+    int out;        // bound (units of q) of every register after the group
+};
+__host__ __device__ constexpr InvPlan inv_plan(int bin, int first_rb) {
+    int b[8] = {bin, bin, bin, bin, bin, bin, bin, bin};
+    unsigned fold = 0;
+    int st = 0;
+    for (int rb = first_rb; rb <= 2; ++rb, ++st)
+        for (int k = 0; k < 8; ++k)
+            if (!(k & (1 << rb))) {
+                const int j = k | (1 << rb);
+                const int sum = b[k] + b[j];
+                if (sum > 8) fold |= 1u << (8 * st + k);
+                b[k] = sum > 8 ? 8 : sum;
+                b[j] = 4;
+            }
+    int out = 0;
+    for (int k = 0; k < 8; ++k) out = b[k] > out ? b[k] : out;
+    return InvPlan{fold, out};
+}
+template <bool FOLD>
+__device__ __forceinline__ void gs_bfly_lazy(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q8) {
+    u64 s = X + Y;
+    const u64 d = X - Y + q8;
+    if (FOLD) s = csub(s, q8);
+    X = s;
+    Y = mul_shoup_lazy4(d, tw.x, tw.y, q);
+}
+
 template <int LO>
 __device__ __forceinline__ u32 point_of(u32 u, int k) {
     return ((u >> LO) << (LO + 3)) | ((u32)k << LO) | (u & ((1u << LO) - 1u));
 }
 
 // Forward stages on point bits BHI-1 .. LO (register bits BHI-1-LO .. 0).
-template <int S, int LO, int BHI>
+template <int S, int LO, int BHI, int B = 8>
 __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u, u64 q,
-                                          u64 q4) {
+                                          u64 q4, u64 z = 0) {
     const u32 uhi = u >> LO;
 #pragma unroll
     for (int rb = BHI - 1 - LO; rb >= 0; --rb) {
         const u32 base = rowfac << (S - 1 - LO - rb);
+        const bool fold = fwd_bound_after(B, BHI - 1 - LO - rb) + 4 > 16;  // folds at compile time (unrolled)
 #pragma unroll
         for (int g = 0; g < (4 >> rb); ++g) {
 #ifdef PPQ_EXP_NOTW
@@ -70,17 +136,25 @@ __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restr
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
+#if PPQ_BFLY_V == 2
+                if (fold) ct_bfly_lazy<true>(a[k], a[k + (1 << rb)], t, q, q4, z);
+                else ct_bfly_lazy<false>(a[k], a[k + (1 << rb)], t, q, q4, z);
+#else
+                (void)fold;
                 ct_bfly(a[k], a[k + (1 << rb)], t, q, q4);
+#endif
             }
         }
     }
 }
 
 // Inverse stages on point bits BLO .. LO+2 (register bits BLO-LO .. 2), ascending.
-template <int S, int LO, int BLO>
+template <int S, int LO, int BLO, int B = 4>
 __device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u, u64 q,
                                           u64 q4) {
     const u32 uhi = u >> LO;
+    constexpr InvPlan plan = inv_plan(B, BLO - LO);
+    (void)plan;
 #pragma unroll
     for (int rb = BLO - LO; rb <= 2; ++rb) {
         const u32 base = rowfac << (S - 1 - LO - rb);
@@ -94,7 +168,14 @@ __device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restr
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
+#if PPQ_BFLY_V == 2
+                if ((plan.fold >> (8 * (rb - (BLO - LO)) + k)) & 1u)
+                    gs_bfly_lazy<true>(a[k], a[k + (1 << rb)], t, q, q4 << 1);
+                else
+                    gs_bfly_lazy<false>(a[k], a[k + (1 << rb)], t, q, q4 << 1);
+#else
                 gs_bfly(a[k], a[k + (1 << rb)], t, q, q4);
+#endif
             }
         }
     }
@@ -131,42 +212,77 @@ __host__ __device__ constexpr int cmin(int a, int b) { return a < b ? a : b; }
 // Forward pass over one size-2^S transform.  In: a[k] = point point_of<S-3>(u,k), values in [0,8q).
 // Out: a[k] = point point_of<0>(u,k) = 8u + k, values in [0,8q).  `guard` inserts a leading barrier so the
 // shared buffer can be reused across loop iterations (write-after-read protection).
-template <int S, class Pos>
+#if PPQ_BFLY_V == 2
+constexpr int FWD_COL_IN = 4, FWD_ROW_IN = 16;  // COL passes read canonical (or < 4q) data, ROW passes a COL pass's output
+template <int S, int BIN>
+struct FwdOut {
+    static constexpr int B = fwd_bound_after(BIN, S);
+};
+#else
+constexpr int FWD_COL_IN = 8, FWD_ROW_IN = 8;
+template <int S, int BIN>
+struct FwdOut {
+    static constexpr int B = 8;
+};
+#endif
+// [0, B q) -> [0, q) for B <= 16
+template <int B>
+__device__ __forceinline__ u64 canon_b(u64 x, const LimbC& c) {
+    if (B > 8) x = csub(x, c.q2 << 2);
+    if (B > 4) x = csub(x, c.q2 << 1);
+    if (B > 2) x = csub(x, c.q2);
+    return csub(x, c.q);
+}
+// [0, B q) -> [0, 8q)
+template <int B>
+__device__ __forceinline__ u64 fold8_b(u64 x, const LimbC& c) {
+    return B > 8 ? csub(x, c.q2 << 2) : x;
+}
+
+template <int S, class Pos, int BIN = 8>
 __device__ __forceinline__ void fwd_pass(u64 (&a)[8], u64* sm, const Pos& pos, u32 u, const ulonglong2* __restrict__ tw,
-                                         u32 rowfac, u64 q, u64 q4, bool guard) {
+                                         u32 rowfac, u64 q, u64 q4, bool guard, u64 z = 0) {
     constexpr int LO0 = S - 3;
     constexpr int LO1 = cmax(S - 6, 0);
-    fwd_group<S, LO0, S>(a, tw, rowfac, u, q, q4);
+    fwd_group<S, LO0, S, BIN>(a, tw, rowfac, u, q, q4, z);
     if (guard) __syncthreads();
     sm_store<LO0>(a, sm, pos, u);
     __syncthreads();
     sm_load<LO1>(a, sm, pos, u);
-    fwd_group<S, LO1, LO0>(a, tw, rowfac, u, q, q4);
+    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(a, tw, rowfac, u, q, q4, z);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);  // same words this thread just read: no barrier needed before
         __syncthreads();
         sm_load<0>(a, sm, pos, u);
-        fwd_group<S, 0, LO1>(a, tw, rowfac, u, q, q4);
+        fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(a, tw, rowfac, u, q, q4, z);
     }
 }
 
-// Inverse pass.  In: a[k] = point 8u + k, values in [0,4q).  Out: a[k] = point_of<S-3>(u,k), in [0,4q).
-template <int S, class Pos>
+// Inverse pass.  In: a[k] = point 8u + k, values < BIN q.  Out: a[k] = point_of<S-3>(u,k), < 8q (< 4q for
+// PPQ_BFLY_V == 0).
+#if PPQ_BFLY_V == 2
+constexpr int INV_ROW_IN = 1, INV_COL_IN = 8;  // ROW passes read canonical data, COL passes a ROW pass's output (< 8q)
+#else
+constexpr int INV_ROW_IN = 4, INV_COL_IN = 4;
+#endif
+template <int S, class Pos, int BIN = 4>
 __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u32 u, const ulonglong2* __restrict__ tw,
                                          u32 rowfac, u64 q, u64 q4, bool guard) {
     constexpr int LOL = S - 3;           // last group
     constexpr int LO1 = cmin(3, S - 3);  // second group
-    inv_group<S, 0, 0>(a, tw, rowfac, u, q, q4);
+    constexpr int B1 = inv_plan(BIN, 0).out;
+    constexpr int B2 = inv_plan(B1, 3 - LO1).out;
+    inv_group<S, 0, 0, BIN>(a, tw, rowfac, u, q, q4);
     if (guard) __syncthreads();
     sm_store<0>(a, sm, pos, u);
     __syncthreads();
     sm_load<LO1>(a, sm, pos, u);
-    inv_group<S, LO1, 3>(a, tw, rowfac, u, q, q4);
+    inv_group<S, LO1, 3, B1>(a, tw, rowfac, u, q, q4);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);
         __syncthreads();
         sm_load<LOL>(a, sm, pos, u);
-        inv_group<S, LOL, 6>(a, tw, rowfac, u, q, q4);
+        inv_group<S, LOL, 6, B2>(a, tw, rowfac, u, q, q4);
     }
 }
 
