@@ -12,7 +12,13 @@
 #include "ntt_core.cuh"
 
 #ifndef PPQ_ROW_MINB
-#define PPQ_ROW_MINB 5
+#define PPQ_ROW_MINB 8  // 128-thread CTAs (PPQ_ROW_PTS 1024), 64 registers: best of 5..20 on B200 (profiles/r01_notes.md)
+#endif
+#ifndef PPQ_ROW_PTS
+#define PPQ_ROW_PTS 1024
+#endif
+#ifndef PPQ_COL_WDIV
+#define PPQ_COL_WDIV 1
 #endif
 #ifndef PPQ_COL_MINB
 #define PPQ_COL_MINB 5  // 51 registers: 8.4 -> 7.7 us/ct on the inverse COL passes, forward unchanged (profiles/r03_notes.md)
@@ -222,7 +228,7 @@ __global__ void __launch_bounds__(256)
 // =========================================================================================================
 template <int S>
 struct RowGeom {
-    static constexpr int R = 2048 >> S;       // rows per CTA: 2048 points, 256 threads
+    static constexpr int R = PPQ_ROW_PTS >> S;  // rows per CTA: PPQ_ROW_PTS points, 8 per thread
     static constexpr int TPT = 1 << (S - 3);  // threads per transform
     static constexpr int THREADS = R * TPT;
     static constexpr int SMEM = R * RowPos<S>::PITCH;
@@ -655,7 +661,7 @@ static Split split_of(int logN) {
 }
 template <int S>
 struct ColW {  // columns per CTA: 256 threads (512 for S = 9)
-    static constexpr int W = S == 6 ? 32 : S == 7 ? 16 : 8;
+    static constexpr int W = (S == 6 ? 32 : S == 7 ? 16 : 8) / PPQ_COL_WDIV;
 };
 
 #define PPQ_COL_DISPATCH(S1, CALL)        \

@@ -185,12 +185,16 @@ __device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restr
 // (stride-8 and stride-32 register patterns both become conflict free).  COL tiles: [point][column].
 template <int S>
 struct RowPos {
+    // the 2^(S-3) threads of one row transform are consecutive lanes of ONE warp for S <= 8: the exchanges between
+    // radix-8 groups then need __syncwarp only, and the warps of a CTA never wait for each other
+    static constexpr bool WARP_LOCAL = (S - 3) <= 5;
     static constexpr int PITCH = (1 << S) + (1 << (S - 3));
     u32 base;  // w * PITCH
     __device__ __forceinline__ u32 operator()(u32 p) const { return base + p + (p >> 3); }
 };
 template <int W>
 struct ColPos {
+    static constexpr bool WARP_LOCAL = false;  // a column transform spans every warp of the CTA
     u32 w;
     __device__ __forceinline__ u32 operator()(u32 p) const { return p * W + w; }
 };
@@ -204,6 +208,15 @@ template <int LO, class Pos>
 __device__ __forceinline__ void sm_load(u64 (&a)[8], const u64* sm, const Pos& pos, u32 u) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = sm[pos(point_of<LO>(u, k))];
+}
+
+template <class Pos>
+__device__ __forceinline__ void pass_sync() {
+#ifndef PPQ_NO_WARPSYNC
+    if (Pos::WARP_LOCAL) __syncwarp();
+    else
+#endif
+        __syncthreads();
 }
 
 __host__ __device__ constexpr int cmax(int a, int b) { return a > b ? a : b; }
@@ -245,14 +258,14 @@ __device__ __forceinline__ void fwd_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
     constexpr int LO0 = S - 3;
     constexpr int LO1 = cmax(S - 6, 0);
     fwd_group<S, LO0, S, BIN>(a, tw, rowfac, u, q, q4, z);
-    if (guard) __syncthreads();
+    if (guard) pass_sync<Pos>();
     sm_store<LO0>(a, sm, pos, u);
-    __syncthreads();
+    pass_sync<Pos>();
     sm_load<LO1>(a, sm, pos, u);
     fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(a, tw, rowfac, u, q, q4, z);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);  // same words this thread just read: no barrier needed before
-        __syncthreads();
+        pass_sync<Pos>();
         sm_load<0>(a, sm, pos, u);
         fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(a, tw, rowfac, u, q, q4, z);
     }
@@ -273,14 +286,14 @@ __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
     constexpr int B1 = inv_plan(BIN, 0).out;
     constexpr int B2 = inv_plan(B1, 3 - LO1).out;
     inv_group<S, 0, 0, BIN>(a, tw, rowfac, u, q, q4);
-    if (guard) __syncthreads();
+    if (guard) pass_sync<Pos>();
     sm_store<0>(a, sm, pos, u);
-    __syncthreads();
+    pass_sync<Pos>();
     sm_load<LO1>(a, sm, pos, u);
     inv_group<S, LO1, 3, B1>(a, tw, rowfac, u, q, q4);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);
-        __syncthreads();
+        pass_sync<Pos>();
         sm_load<LOL>(a, sm, pos, u);
         inv_group<S, LOL, 6, B2>(a, tw, rowfac, u, q, q4);
     }

@@ -24,11 +24,14 @@ def main():
     ap.add_argument("--config", default="c3")
     ap.add_argument("--clients", type=int, default=2)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--wave", type=int, default=0)
     ap.add_argument("--tag", default=os.environ.get("PPQ_B200_LIB", "default"))
     a = ap.parse_args()
     cfg = CONFIGS[a.config]
     dev = torch.device("cuda", 0)
     cc = CryptoContext.synthetic(cfg["logN"], cfg["depth"], cfg["first"], cfg["scale"], cfg["extra"], cfg["dnum"], 0)
+    if a.wave:
+        cc.set_wave(a.wave)
     ell, M, N, n = cc.L, cc.M, cc.N, cfg["slots"]
     qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
     torch.manual_seed(1)
