@@ -68,13 +68,15 @@ __device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
 // =========================================================================================================
 // MODE 0: plain (src poly = blockIdx.y, limb from limb_ids; a negative limb id skips the slot)
 // MODE 2: centred SwitchModulus prologue (DropLastElementAndScale)
-template <int S, int W, int MODE>
+// SAME: the ROW size equals the COL size (n2 = 2^S), else n2 = 2^(S-1) (split_of): with n2 known at compile time the
+// eight strided accesses of a thread share one base register and use immediate offsets.
+template <int S, int W, int MODE, bool SAME>
 __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     k_fwd_col(KCtx c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs,
               const BcJob* __restrict__ jobs, const u64* __restrict__ chat, const int* __restrict__ limb_ids,
               u64 q_src) {
     __shared__ u64 sm[W << S];
-    const u32 N = 1u << c.logN, n2 = N >> S;
+    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
     const u32 w = threadIdx.x % W, u = threadIdx.x / W;
     const u32 col = blockIdx.x * W + w;
     const u32 y = blockIdx.y, g = blockIdx.z;
@@ -118,12 +120,12 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy (< 16q): consumed by a ROW pass
 }
 
-template <int S, int W>
+template <int S, int W, bool SAME>
 __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
               const u64* __restrict__ scale, const u64* __restrict__ scale_sh) {
     __shared__ u64 sm[W << S];
-    const u32 N = 1u << c.logN, n2 = N >> S;
+    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
     const u32 w = threadIdx.x % W, u = threadIdx.x / W;
     const u32 col = blockIdx.x * W + w;
     const u32 y = blockIdx.y, g = blockIdx.z;
@@ -253,8 +255,13 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
     for (int k = 0; k < 8; ++k) a[k] = p[point_of<S - 3>(u, k)];
     RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
     fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
+    if (FwdOut<S, FWD_ROW_IN>::B > 8 && lc.sh >= 28u) {  // block-uniform
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+        for (int k = 0; k < 8; ++k) a[k] = canon16_q(a[k], lc);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+    }
     st8(p + 8 * u, a);
 }
 
@@ -506,18 +513,21 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     for (int k = 0; k < 8; ++k) {
         // the exact Shoup product takes any 64-bit input: fold to < 8q only, x + 8q - v < 9q
         const u64 v = fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
-        a[k] = mul_shoup(x[k] + (lc.q2 << 2) - v, pi, pis, lc.q);
+        a[k] = mul_shoup_lazy(x[k] + (lc.q2 << 2) - v, pi, pis, lc.q);  // < 2q
     }
+    // + c0 (< q) + running sum (< q) stays below 4q: one canonicalisation at the end instead of one per addition
     if (poly == 0) {
         ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], x[k], lc.q);
+        for (int k = 0; k < 8; ++k) a[k] += x[k];
     }
     if (A.accumulate) {
         ld8(x, o);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], x[k], lc.q);
+        for (int k = 0; k < 8; ++k) a[k] += x[k];
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = canon4(a[k], lc);
     st8(o, a);
 }
 
@@ -686,7 +696,10 @@ static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* ds
     constexpr int W = ColW<S>::W;
     const int n2 = (1 << c.logN) >> S;
     dim3 grid(n2 / W, ny, ng), block(W << (S - 3));
-    k_fwd_col<S, W, MODE><<<grid, block, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, chat, limb_ids, q_src);
+    if (n2 == (1 << S))
+        k_fwd_col<S, W, MODE, true><<<grid, block, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, chat, limb_ids, q_src);
+    else
+        k_fwd_col<S, W, MODE, false><<<grid, block, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, chat, limb_ids, q_src);
 }
 
 void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_polys, cudaStream_t st) {
@@ -716,8 +729,13 @@ void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, 
                     const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n2 = 1 << sp.S2;
-    PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
-                                c, data, gs, d_limb_map, d_scale, d_scale_sh)));
+    if (sp.S1 == sp.S2) {
+        PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W, true><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
+                                    c, data, gs, d_limb_map, d_scale, d_scale_sh)));
+    } else {
+        PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W, false><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
+                                    c, data, gs, d_limb_map, d_scale, d_scale_sh)));
+    }
 }
 void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale, const u64* d_scale_sh,
                         int n_polys, cudaStream_t st) {

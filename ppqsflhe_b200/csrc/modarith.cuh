@@ -30,7 +30,17 @@ struct LimbC {
     u32 pad;
 };
 
-__device__ __forceinline__ u64 csub(u64 x, u64 q) { return x >= q ? x - q : x; }
+// Conditional subtraction for q <= 2^63 and x < 2^63 + q (every caller: x < 16q, q < 2^60): the SIGN of x - q decides,
+// so the compare is one 32-bit ISETP on the high word instead of a two-instruction 64-bit compare
+// (5 instructions instead of 6; the NTT kernels' time follows their instruction count, profiles/r01_notes.md).
+__device__ __forceinline__ u64 csub(u64 x, u64 q) {
+#ifdef PPQ_PLAIN_CSUB
+    return x >= q ? x - q : x;
+#else
+    const u64 d = x - q;
+    return (int)(d >> 32) < 0 ? x : d;
+#endif
+}
 
 // x * w mod q in [0, 2q) for any x < 2^64 (Shoup / Harvey).
 __device__ __forceinline__ u64 mul_shoup_lazy(u64 x, u64 w, u64 ws, u64 q) {
@@ -112,6 +122,16 @@ __device__ __forceinline__ u64 mulmod_barrett(u64 a, u64 b, const LimbC& c) {
 __device__ __forceinline__ u64 canon8(u64 x, const LimbC& c) { return csub(csub(csub(x, c.q2 << 1), c.q2), c.q); }
 // [0, 4q) -> [0, q)
 __device__ __forceinline__ u64 canon4(u64 x, const LimbC& c) { return csub(csub(x, c.q2), c.q); }
+
+// [0, 16q) -> [0, q) with ONE quotient estimate instead of a chain of four conditional subtractions (12 instructions
+// instead of 20).  Needs bitlen(q) >= 29.  x / q = (x >> (sh-27)) * floor(2^(32+sh)/q) / 2^59; the estimate is exact or
+// one short (both truncations together lose < 2^-26), so the remainder lies in [0, 2q).  floor(2^(32+sh)/q) is the high
+// word of the Barrett constant mu.
+__device__ __forceinline__ u64 canon16_q(u64 x, const LimbC& c) {
+    const u32 xs = (u32)(x >> (c.sh - 27u));
+    const u32 k = __umulhi(xs, (u32)(c.mu >> 32)) >> 27;
+    return csub(x - (u64)k * c.q, c.q);
+}
 
 __device__ __forceinline__ u64 addmod(u64 a, u64 b, u64 q) { return csub(a + b, q); }
 __device__ __forceinline__ u64 submod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }

@@ -66,10 +66,7 @@ __host__ __device__ constexpr int fwd_bound_after(int b, int stages) {
 template <bool FOLD>
 __device__ __forceinline__ void ct_bfly_lazy(u64& X, u64& Y, ulonglong2 tw, u64 q, u64 q4, u64 z) {
     const u64 t = mul_shoup_lazy4(Y, tw.x, tw.y, q);
-    if (FOLD) {
-        const u64 q8 = q4 << 1;
-        if (X >= q8) X -= q8;
-    }
+    if (FOLD) X = csub(X, q4 << 1);
     Y = X + q4 - t;
     // z is a run-time zero (LimbC::pad): a THREE-input add cannot be turned into IMAD.X, which ptxas otherwise
     // places on the fmaheavy pipe -- the binding pipe of every NTT kernel (tools/sass_cost.py)
