@@ -160,6 +160,12 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
 // 2^64), one Barrett reduction per 8 terms.  Unsigned products only: a signed IMAD.WIDE costs two passes on B200
 // (measured, profiles/r01_notes.md).  chat3[.] = (c0, c1, c0 + c1, 0).
 // =========================================================================================================
+// 32 x 32 + 64 -> 64 multiply-add spelled in PTX (k_ip_tma: 17.1 -> 15.9 us/ct together with the pre-split keys)
+__device__ __forceinline__ u64 madw(u32 a, u32 b, u64 c) {
+    u64 r;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
+    return r;
+}
 __device__ __forceinline__ u64 kara_reduce(u64 A0, u64 A2, u64 A1, const LimbC& lc) {
     const u64 mid = A1 - A0 - A2;  // = sum (y1 c0 + y0 c1) < 2^64: exact modulo 2^64
     unsigned __int128 t = (unsigned __int128)A0 + ((unsigned __int128)mid << 30) + ((unsigned __int128)A2 << 60);
@@ -191,12 +197,16 @@ __global__ void __launch_bounds__(256)
     const u32 n = blockIdx.x * 256 + threadIdx.x;
     const u32 g = blockIdx.z;
     const u64* in = src + g * src_gs + (size_t)P.src_first * N + n;
-    u32 y0[NS], y1[NS];  // y0 + y1 is re-formed per term (one ALU add; the ALU pipe has slack, registers do not)
+    // narrow digits (NS <= 8) keep y0 + y1 in a register; wide ones re-form it per term (registers are the scarcer
+    // resource there)
+    constexpr bool KEEP = NS <= 8;
+    u32 y0[NS], y1[NS], ys[KEEP ? NS : 1];
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
         const u64 y = ld_stream(in + (size_t)i * N);
         y0[i] = (u32)y & 0x3fffffffu;
         y1[i] = (u32)(y >> 30);
+        if (KEEP) ys[i] = y0[i] + y1[i];
     }
     u64* out = dst + g * dst_gs + n;
 #pragma unroll(NS <= 8 ? 2 : 1)
@@ -210,13 +220,19 @@ __global__ void __launch_bounds__(256)
         u64 r = 0;
 #pragma unroll
         for (int i0 = 0; i0 < NS; i0 += 8) {
-            u64 A0 = 0, A2 = 0, A1 = 0;
+            u64 A0, A2, A1;
+            {
+                const uint4 cc = J.c[i0];
+                A0 = (u64)y0[i0] * cc.x;  // C products here: the PTX form measured 3 % slower in this kernel
+                A2 = (u64)y1[i0] * cc.y;
+                A1 = (u64)(KEEP ? ys[i0] : y0[i0] + y1[i0]) * cc.z;
+            }
 #pragma unroll
-            for (int i = i0; i < (i0 + 8 < NS ? i0 + 8 : NS); ++i) {
+            for (int i = i0 + 1; i < (i0 + 8 < NS ? i0 + 8 : NS); ++i) {
                 const uint4 cc = J.c[i];
                 A0 += (u64)y0[i] * cc.x;
                 A2 += (u64)y1[i] * cc.y;
-                A1 += (u64)(y0[i] + y1[i]) * cc.z;
+                A1 += (u64)(KEEP ? ys[i] : y0[i] + y1[i]) * cc.z;
             }
             r += kara_reduce(A0, A2, A1, lc);
         }
@@ -395,13 +411,16 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 struct Kara3 {  // 30-bit split of a residue < 2^60
     u32 lo, hi, sum;
     __device__ __forceinline__ explicit Kara3(u64 v) : lo((u32)v & 0x3fffffffu), hi((u32)(v >> 30)), sum(lo + hi) {}
+    struct Packed {};  // v = lo | hi << 32 (kara_pack): the halves are the two registers of v
+    __device__ __forceinline__ Kara3(u64 v, Packed) : lo((u32)v), hi((u32)(v >> 32)), sum(lo + hi) {}
 };
+__device__ __forceinline__ u64 kara_pack(u64 v) { return (v & 0x3fffffffull) | ((v >> 30) << 32); }
 struct KaraAcc {
     u64 A0 = 0, A1 = 0, A2 = 0;
     __device__ __forceinline__ void mac(const Kara3& x, const Kara3& y) {
-        A0 += (u64)x.lo * y.lo;
-        A2 += (u64)x.hi * y.hi;
-        A1 += (u64)x.sum * y.sum;
+        A0 = madw(x.lo, y.lo, A0);
+        A2 = madw(x.hi, y.hi, A2);
+        A1 = madw(x.sum, y.sum, A1);
     }
     __device__ __forceinline__ u64 reduce(const LimbC& lc) const { return kara_reduce(A0, A2, A1, lc); }
 };
@@ -450,6 +469,13 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
     ulonglong2 dn[PARTS];
     if (n_it > 0) fetch(0, dn);
     mbar_wait(bar, 0);
+    // the key tile is reused for every ciphertext of the wave: split it into Karatsuba halves ONCE, in place
+    for (int i = threadIdx.x; i < PARTS * 2 * IPT / 2; i += 256) {
+        ulonglong2* kp = reinterpret_cast<ulonglong2*>(keys) + i;
+        const ulonglong2 v = *kp;
+        *kp = make_ulonglong2(kara_pack(v.x), kara_pack(v.y));
+    }
+    __syncthreads();
     for (int it = 0; it < n_it; ++it) {
         ulonglong2 d[PARTS];
 #pragma unroll
@@ -472,10 +498,10 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
             const ulonglong2 kb = *reinterpret_cast<const ulonglong2*>(keys + (size_t)(2 * j) * IPT + pt);
             const ulonglong2 ka = *reinterpret_cast<const ulonglong2*>(keys + (size_t)(2 * j + 1) * IPT + pt);
             const Kara3 dx(d[j].x), dy(d[j].y);
-            b0.mac(dx, Kara3(kb.x));
-            b1.mac(dy, Kara3(kb.y));
-            a0.mac(dx, Kara3(ka.x));
-            a1.mac(dy, Kara3(ka.y));
+            b0.mac(dx, Kara3(kb.x, Kara3::Packed{}));
+            b1.mac(dy, Kara3(kb.y, Kara3::Packed{}));
+            a0.mac(dx, Kara3(ka.x, Kara3::Packed{}));
+            a1.mac(dy, Kara3(ka.y, Kara3::Packed{}));
         }
         *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
         *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
