@@ -88,6 +88,7 @@ struct ppq_ctx {
     DevBuf<ulonglong2> twf, twi;
     std::map<int, std::unique_ptr<KsPlanDev>> ks;
     std::map<int, std::unique_ptr<RsPlanDev>> rs;
+    DevBuf<u64> key_pinv, key_pinv_sh;  // [L] P^-1 mod q_i (+ Shoup), used once per re-encryption key
     DevBuf<u64> scratch;   // key-switch wave scratch
     DevBuf<u64> scratch2;  // rescale / encrypt / decrypt scratch
     DevBuf<int> ids;       // limb ids of the plain NTT API
@@ -114,7 +115,12 @@ struct ppq_rekey {
     ppq_ctx* ctx = nullptr;
     const u64* b = nullptr;
     const u64* a = nullptr;
-    DevBuf<u64> own_b, own_a;
+    // Q limbs multiplied by P^-1 mod q_i (see launch_scale_key): in place for an uploaded key (stride L+K), a private
+    // [dnum][L][N] copy for a borrowed one (the caller's buffers are never written)
+    const u64* qb = nullptr;
+    const u64* qa = nullptr;
+    int q_stride = 0;
+    DevBuf<u64> own_b, own_a, own_qb, own_qa;
 };
 
 extern "C" const char* ppq_last_error(void) { return g_err.c_str(); }
@@ -275,6 +281,39 @@ extern "C" int ppq_ntt_inverse(ppq_ctx* c, uint64_t* d, const int32_t* ids, size
 }
 
 // ------------------------------------------------------------------------------------------- rekeys
+// P^-1 mod q_i for every Q limb, and the scaled Q part of a key (ModDown without a multiplication, kernels.cuh)
+static int rekey_scale_q(ppq_ctx* c, ppq_rekey* k, bool in_place) {
+    const host::Params& hp = c->hp;
+    const int L = hp.L, M = hp.M();
+    if (!c->key_pinv.p) {
+        host::KsPlan plan;
+        host::build_ks_plan(hp, L, plan);
+        CU(c->key_pinv.upload(plan.pinv));
+        CU(c->key_pinv_sh.upload(plan.pinv_sh));
+    }
+    u64 *qb, *qa;
+    if (in_place) {
+        qb = k->own_b.p;
+        qa = k->own_a.p;
+        k->q_stride = M;
+    } else {
+        const size_t n = (size_t)hp.dnum * L * hp.N;
+        CU(k->own_qb.ensure(n));
+        CU(k->own_qa.ensure(n));
+        qb = k->own_qb.p;
+        qa = k->own_qa.p;
+        k->q_stride = L;
+    }
+    // legacy default stream: ordered after whatever produced a borrowed key on a blocking stream
+    launch_scale_key(c->k, k->b, M, qb, k->q_stride, c->key_pinv.p, c->key_pinv_sh.p, L, hp.dnum, 0);
+    launch_scale_key(c->k, k->a, M, qa, k->q_stride, c->key_pinv.p, c->key_pinv_sh.p, L, hp.dnum, 0);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(0));
+    k->qb = qb;
+    k->qa = qa;
+    return PPQ_OK;
+}
+
 extern "C" int ppq_rekey_upload(ppq_ctx* c, const uint64_t* hb, const uint64_t* ha, ppq_rekey** out) {
     if (!c || !hb || !ha || !out) return fail(PPQ_EINVAL, "ppq_rekey_upload: null argument");
     CU(cudaSetDevice(c->device));
@@ -287,16 +326,21 @@ extern "C" int ppq_rekey_upload(ppq_ctx* c, const uint64_t* hb, const uint64_t* 
     k->ctx = c;
     k->b = k->own_b.p;
     k->a = k->own_a.p;
+    int rc = rekey_scale_q(c, k.get(), true);
+    if (rc != PPQ_OK) return rc;
     *out = k.release();
     return PPQ_OK;
 }
 extern "C" int ppq_rekey_from_device(ppq_ctx* c, const uint64_t* db, const uint64_t* da, ppq_rekey** out) {
     if (!c || !db || !da || !out) return fail(PPQ_EINVAL, "ppq_rekey_from_device: null argument");
-    ppq_rekey* k = new ppq_rekey;
+    CU(cudaSetDevice(c->device));
+    std::unique_ptr<ppq_rekey> k(new ppq_rekey);
     k->ctx = c;
     k->b = (const u64*)db;
     k->a = (const u64*)da;
-    *out = k;
+    int rc = rekey_scale_q(c, k.get(), false);
+    if (rc != PPQ_OK) return rc;
+    *out = k.release();
     return PPQ_OK;
 }
 extern "C" void ppq_rekey_destroy(ppq_rekey* k) {
@@ -478,6 +522,9 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ia.dig_gs = w.dig;
         ia.key_b = rk->b;
         ia.key_a = rk->a;
+        ia.key_qb = rk->qb;
+        ia.key_qa = rk->qa;
+        ia.key_q_stride = rk->q_stride;
         ia.extq = extq;
         ia.extq_gs = w.extq;
         ia.extp = extp;
@@ -523,8 +570,6 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ma.in_gs = ct;
         ma.out = out_g;
         ma.out_gs = ct;
-        ma.pinv = p->pinv.p;
-        ma.pinv_sh = p->pinv_sh.p;
         ma.ell = ell;
         ma.accumulate = accumulate;
         launch_fwd_row_moddown(c->k, ma, ng, st);

@@ -339,9 +339,15 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_i
             for (int k = 0; k < 8; ++k) d[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(d[k], lc);
         }
         u64 kb[8], ka[8];
-        const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off + 8 * u;
-        ld8_ro(kb, A.key_b + koff);
-        ld8_ro(ka, A.key_a + koff);
+        if (r < A.ell) {
+            const size_t koff = ((size_t)j * A.key_q_stride + limb) * N + off + 8 * u;
+            ld8_ro(kb, A.key_qb + koff);
+            ld8_ro(ka, A.key_qa + koff);
+        } else {
+            const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off + 8 * u;
+            ld8_ro(kb, A.key_b + koff);
+            ld8_ro(ka, A.key_a + koff);
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             mac128(h0[k], l0[k], d[k], kb[k]);
@@ -445,9 +451,10 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
         mbar_expect_tx(bar, (u32)(PARTS * 2 * IPT * sizeof(u64)));
 #pragma unroll
         for (int j = 0; j < PARTS; ++j) {
-            const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off;
-            tma_bulk_g2s(keys + (size_t)(2 * j) * IPT, A.key_b + koff, IPT * sizeof(u64), bar);
-            tma_bulk_g2s(keys + (size_t)(2 * j + 1) * IPT, A.key_a + koff, IPT * sizeof(u64), bar);
+            const bool isq = r < A.ell;  // Q limbs come from the P^-1-scaled copy
+            const size_t koff = ((size_t)j * (isq ? A.key_q_stride : A.L + A.K) + limb) * N + off;
+            tma_bulk_g2s(keys + (size_t)(2 * j) * IPT, (isq ? A.key_qb : A.key_b) + koff, IPT * sizeof(u64), bar);
+            tma_bulk_g2s(keys + (size_t)(2 * j + 1) * IPT, (isq ? A.key_qa : A.key_a) + koff, IPT * sizeof(u64), bar);
         }
     }
     const int own = r < A.ell ? r / A.alpha : -1;  // the digit whose own limb r is (taken from c1 as it is)
@@ -534,14 +541,10 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
     u64 x[8];
     ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
-    const u64 pi = A.pinv[i], pis = A.pinv_sh[i];
+    // keys and conversion constants carry P^-1 already (launch_scale_key, build_ks_plan): (x - conv) P^-1 = x' - conv'.
+    // x' + 8q - conv' (+ c0) (+ running sum) < 11q, canonicalised once.
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        // the exact Shoup product takes any 64-bit input: fold to < 8q only, x + 8q - v < 9q
-        const u64 v = fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
-        a[k] = mul_shoup_lazy(x[k] + (lc.q2 << 2) - v, pi, pis, lc.q);  // < 2q
-    }
-    // + c0 (< q) + running sum (< q) stays below 4q: one canonicalisation at the end instead of one per addition
+    for (int k = 0; k < 8; ++k) a[k] = x[k] + (lc.q2 << 2) - fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
     if (poly == 0) {
         ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
 #pragma unroll
@@ -552,8 +555,13 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] += x[k];
     }
+    if (lc.sh >= 28u) {  // block-uniform
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = canon4(a[k], lc);
+        for (int k = 0; k < 8; ++k) a[k] = canon16_q(a[k], lc);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = canon_b<16>(a[k], lc);
+    }
     st8(o, a);
 }
 
@@ -626,6 +634,18 @@ __global__ void k_mult_scalar(KCtx c, const u64* __restrict__ in, u64* __restric
         *reinterpret_cast<ulonglong2*>(out + base + n) =
             make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
     }
+}
+// out[(j*out_stride + i)*N + n] = in[(j*in_stride + i)*N + n] * f[i] mod q_i ; grid (N/512, L, dnum)
+__global__ void k_scale_key(KCtx c, const u64* in, int in_stride, u64* out, int out_stride,  // in may alias out
+                            const u64* __restrict__ f, const u64* __restrict__ fs) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y, j = blockIdx.z;
+    const u64 q = c.limbs[i].q, w = f[i], ws = fs[i];
+    const u32 n = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (n >= N) return;
+    const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(in + ((size_t)j * in_stride + i) * N + n);
+    *reinterpret_cast<ulonglong2*>(out + ((size_t)j * out_stride + i) * N + n) =
+        make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
 }
 // out[g][s][i][n] = small[g][s][n] mod q_i ; grid.y = g * n_small * ell + s * ell + i
 __global__ void k_small_to_res(KCtx c, const long long* __restrict__ small, u64* __restrict__ out, int n_small,
@@ -876,6 +896,11 @@ void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, 
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st) {
     k_mult_scalar<<<pw_grid(c, n_polys, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
+}
+void launch_scale_key(const KCtx& c, const u64* in, int in_stride, u64* out, int out_stride, const u64* d_pinv,
+                      const u64* d_pinv_sh, int L, int dnum, cudaStream_t st) {
+    const u32 N = 1u << c.logN;
+    k_scale_key<<<dim3((N / 2 + 255) / 256, L, dnum), 256, 0, st>>>(c, in, in_stride, out, out_stride, d_pinv, d_pinv_sh);
 }
 void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
                          cudaStream_t st) {

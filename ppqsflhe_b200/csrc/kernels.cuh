@@ -67,8 +67,11 @@ struct IpArgs {
     size_t c1_gs;
     const u64* digits;   // COL-pass output of bc_fwd_col: digits + g*dig_gs + (j*(ell+K) + r)*N
     size_t dig_gs;
-    const u64* key_b;    // [dnum][L+K][N]
+    const u64* key_b;    // [dnum][L+K][N]  (P limbs are read from here)
     const u64* key_a;
+    const u64* key_qb;   // Q limbs pre-multiplied by P^-1 mod q_i: key_qb + (j*key_q_stride + i)*N  (ppq_rekey)
+    const u64* key_qa;
+    int key_q_stride;
     u64* extq;           // out, Q limbs:  extq + g*extq_gs + (poly*ell + r)*N, EVAL canonical
     size_t extq_gs;
     u64* extp;           // out, P limbs after the inverse ROW pass: extp + g*extp_gs + (poly*K + k)*N
@@ -91,11 +94,13 @@ struct MdArgs {
     size_t in_gs;
     u64* out;          // [g][2][ell][N]
     size_t out_gs;
-    const u64* pinv;   // [ell]  P^-1 mod q_i
-    const u64* pinv_sh;
     int ell;
     int accumulate;    // 0: out = result ; 1: out = out + result mod q (EvalAdd into the running sum)
 };
+// ---- key_q = key * P^-1 mod q_i on the Q limbs of a re-encryption key (once per key): with the ModDown conversion
+// constants scaled the same way, (x - conv) * P^-1 becomes x' - conv' and the ModDown epilogue has no multiplication
+void launch_scale_key(const KCtx& c, const u64* in, int in_stride, u64* out, int out_stride, const u64* d_pinv,
+                      const u64* d_pinv_sh, int L, int dnum, cudaStream_t st);
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st);
 
 // ---- forward ROW pass fused with the rescale combine: out = (x - v) * cst[i] mod q_i

@@ -324,7 +324,10 @@ void build_ks_plan(const Params& p, int ell, KsPlan& o) {
     for (int poly = 0; poly < 2; ++poly)
         for (int i = 0; i < ell; ++i) {
             Job jb{poly * K, K, poly * ell + i, i, (int)o.down_chat.size()};
-            for (int k = 0; k < K; ++k) o.down_chat.push_back(hat_mod(p.mod, L, L + K, L + k, p.mod[i]));
+            // [P/p_k]_{q_i} * P^-1 mod q_i: the ModDown multiplication by P^-1 is folded into the conversion (and, on
+            // the other operand, into the key: launch_scale_key), both exact modulo q_i
+            for (int k = 0; k < K; ++k)
+                o.down_chat.push_back(mulmod(hat_mod(p.mod, L, L + K, L + k, p.mod[i]), o.pinv[i], p.mod[i]));
             o.down_jobs.push_back(jb);
         }
 }
