@@ -241,6 +241,62 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// Two adjacent coefficients per thread (narrow digits, NS <= 8): the per-target work that does not depend on the
+// coefficient -- loading the conversion constants from the constant bank, loop control, address arithmetic -- is
+// paid once per pair, and the residues travel as 16-byte accesses.  PPQ_BCONV_PAIR=0 selects the one-coefficient form.
+#ifndef PPQ_BCONV_PAIR
+#define PPQ_BCONV_PAIR 1
+#endif
+template <int NS>
+__global__ void __launch_bounds__(256)
+    k_bconv2(int logN, const u64* __restrict__ src, size_t src_gs, u64* __restrict__ dst, size_t dst_gs,
+             const __grid_constant__ BcPack<NS> P) {
+    const u32 N = 1u << logN;
+    const u32 n = (blockIdx.x * 256 + threadIdx.x) * 2;
+    const u32 g = blockIdx.z;
+    const u64* in = src + g * src_gs + (size_t)P.src_first * N + n;
+    u32 y0[2][NS], y1[2][NS], ys[2][NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+        const ulonglong2 y = __ldcs(reinterpret_cast<const ulonglong2*>(in + (size_t)i * N));
+        y0[0][i] = (u32)y.x & 0x3fffffffu;
+        y1[0][i] = (u32)(y.x >> 30);
+        ys[0][i] = y0[0][i] + y1[0][i];
+        y0[1][i] = (u32)y.y & 0x3fffffffu;
+        y1[1][i] = (u32)(y.y >> 30);
+        ys[1][i] = y0[1][i] + y1[1][i];
+    }
+    u64* out = dst + g * dst_gs + n;
+#pragma unroll 1
+    for (int t = 0; t < P.n_jobs; ++t) {
+        const typename BcPack<NS>::J& J = P.j[t];
+        LimbC lc;
+        lc.q = J.q;
+        lc.q2 = J.q << 1;
+        lc.mu = J.mu;
+        lc.sh = J.sh;
+        u64 A0[2], A2[2], A1[2];
+#pragma unroll
+        for (int i = 0; i < NS; ++i) {
+            const uint4 cc = J.c[i];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                if (i == 0) {
+                    A0[e] = (u64)y0[e][i] * cc.x;
+                    A2[e] = (u64)y1[e][i] * cc.y;
+                    A1[e] = (u64)ys[e][i] * cc.z;
+                } else {
+                    A0[e] += (u64)y0[e][i] * cc.x;
+                    A2[e] += (u64)y1[e][i] * cc.y;
+                    A1[e] += (u64)ys[e][i] * cc.z;
+                }
+            }
+        }
+        *reinterpret_cast<ulonglong2*>(out + (size_t)J.dst_slot * N) =
+            make_ulonglong2(kara_reduce(A0[0], A2[0], A1[0], lc), kara_reduce(A0[1], A2[1], A1[1], lc));
+    }
+}
+
 // =========================================================================================================
 // ROW passes
 // =========================================================================================================
@@ -821,8 +877,14 @@ static void bconv_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst,
             J.pad[0] = J.pad[1] = 0;
             for (int i = 0; i < NS; ++i) J.c[i] = chat_split(chat[jb.chat_off + i]);
         }
-        dim3 grid((1u << c.logN) / 256, 1, n_g);
-        k_bconv<NS><<<grid, 256, 0, st>>>(c.logN, src, src_gs, dst, dst_gs, pk);
+        if (PPQ_BCONV_PAIR && NS <= 8 && c.logN >= 9) {
+            dim3 grid((1u << c.logN) / 512, 1, n_g);
+            k_bconv2<(NS <= 8 ? NS : 1)><<<grid, 256, 0, st>>>(c.logN, src, src_gs, dst, dst_gs,
+                                                               reinterpret_cast<const BcPack<(NS <= 8 ? NS : 1)>&>(pk));
+        } else {
+            dim3 grid((1u << c.logN) / 256, 1, n_g);
+            k_bconv<NS><<<grid, 256, 0, st>>>(c.logN, src, src_gs, dst, dst_gs, pk);
+        }
     }
 }
 bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* h_jobs,
