@@ -160,6 +160,14 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
 // 2^64), one Barrett reduction per 8 terms.  Unsigned products only: a signed IMAD.WIDE costs two passes on B200
 // (measured, profiles/r01_notes.md).  chat3[.] = (c0, c1, c0 + c1, 0).
 // =========================================================================================================
+// 32 x 32 -> 64 product spelled in PTX: the C form (u64)a * b with b read from the kernel parameter goes through a
+// zero-extended uniform register pair and leaves additions of zero behind in the SASS; ptxas fuses this product with
+// the C addition that follows into one IMAD.WIDE
+__device__ __forceinline__ u64 mulw(u32 a, u32 b) {
+    u64 r;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(r) : "r"(a), "r"(b));
+    return r;
+}
 // 32 x 32 + 64 -> 64 multiply-add spelled in PTX (k_ip_tma: 17.1 -> 15.9 us/ct together with the pre-split keys)
 __device__ __forceinline__ u64 madw(u32 a, u32 b, u64 c) {
     u64 r;
@@ -223,16 +231,16 @@ __global__ void __launch_bounds__(256)
             u64 A0, A2, A1;
             {
                 const uint4 cc = J.c[i0];
-                A0 = (u64)y0[i0] * cc.x;  // C products here: the PTX form measured 3 % slower in this kernel
-                A2 = (u64)y1[i0] * cc.y;
-                A1 = (u64)(KEEP ? ys[i0] : y0[i0] + y1[i0]) * cc.z;
+                A0 = mulw(y0[i0], cc.x);
+                A2 = mulw(y1[i0], cc.y);
+                A1 = mulw(KEEP ? ys[i0] : y0[i0] + y1[i0], cc.z);
             }
 #pragma unroll
             for (int i = i0 + 1; i < (i0 + 8 < NS ? i0 + 8 : NS); ++i) {
                 const uint4 cc = J.c[i];
-                A0 += (u64)y0[i] * cc.x;
-                A2 += (u64)y1[i] * cc.y;
-                A1 += (u64)(KEEP ? ys[i] : y0[i] + y1[i]) * cc.z;
+                A0 += mulw(y0[i], cc.x);  // mul.wide + C add: one IMAD.WIDE (a PTX mad.wide is split by ptxas, 3 % slower)
+                A2 += mulw(y1[i], cc.y);
+                A1 += mulw(KEEP ? ys[i] : y0[i] + y1[i], cc.z);
             }
             r += kara_reduce(A0, A2, A1, lc);
         }
@@ -282,13 +290,13 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 if (i == 0) {
-                    A0[e] = (u64)y0[e][i] * cc.x;
-                    A2[e] = (u64)y1[e][i] * cc.y;
-                    A1[e] = (u64)ys[e][i] * cc.z;
+                    A0[e] = mulw(y0[e][i], cc.x);
+                    A2[e] = mulw(y1[e][i], cc.y);
+                    A1[e] = mulw(ys[e][i], cc.z);
                 } else {
-                    A0[e] += (u64)y0[e][i] * cc.x;
-                    A2[e] += (u64)y1[e][i] * cc.y;
-                    A1[e] += (u64)ys[e][i] * cc.z;
+                    A0[e] += mulw(y0[e][i], cc.x);
+                    A2[e] += mulw(y1[e][i], cc.y);
+                    A1[e] += mulw(ys[e][i], cc.z);
                 }
             }
         }
