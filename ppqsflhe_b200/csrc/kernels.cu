@@ -488,9 +488,9 @@ __device__ __forceinline__ u64 kara_pack(u64 v) { return (v & 0x3fffffffull) | (
 struct KaraAcc {
     u64 A0 = 0, A1 = 0, A2 = 0;
     __device__ __forceinline__ void mac(const Kara3& x, const Kara3& y) {
-        A0 = madw(x.lo, y.lo, A0);
-        A2 = madw(x.hi, y.hi, A2);
-        A1 = madw(x.sum, y.sum, A1);
+        A0 += mulw(x.lo, y.lo);
+        A2 += mulw(x.hi, y.hi);
+        A1 += mulw(x.sum, y.sum);
     }
     __device__ __forceinline__ u64 reduce(const LimbC& lc) const { return kara_reduce(A0, A2, A1, lc); }
 };
