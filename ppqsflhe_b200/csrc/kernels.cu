@@ -449,7 +449,11 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_i
 // Digits arrive in EVAL form (converted limbs from k_fwd_row_plain, own-digit limbs straight from c1).
 // Products use the 30-bit Karatsuba split of k_bconv (3 IMAD.WIDE per term, no carry chains).
 // ---------------------------------------------------------------------------------------------------------
-constexpr int IPT = 2048;  // points per tile: 8 per thread, 256 threads
+#ifndef PPQ_IPT
+#define PPQ_IPT 512  // 24 KiB key tile (3 digits): 4 CTAs/SM; 2048 (2 CTAs/SM) left the kernel latency-bound: 14.9 -> 13.1 us/ct
+#endif
+constexpr int IPT = PPQ_IPT;     // points per key tile; 256 threads take 512 points (two each) per step
+constexpr int IPC = IPT / 512;   // steps per ciphertext
 
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
@@ -495,8 +499,11 @@ struct KaraAcc {
     __device__ __forceinline__ u64 reduce(const LimbC& lc) const { return kara_reduce(A0, A2, A1, lc); }
 };
 
+#ifndef PPQ_IP_MINB
+#define PPQ_IP_MINB 4  // 64 registers, 4 CTAs/SM (5: 14.3, 6: 15.0 us/ct)
+#endif
 template <int PARTS>
-__global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
+__global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
     extern __shared__ __align__(128) unsigned char ip_smem[];
     u64* keys = reinterpret_cast<u64*>(ip_smem);              // [PARTS][2][IPT]
     u64* bar = keys + (size_t)PARTS * 2 * IPT;
@@ -527,8 +534,8 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
     // digits of the next (ciphertext, chunk) are fetched while the current one is multiplied: with two CTAs per
     // SM the loads in flight would otherwise not cover the HBM latency
     auto fetch = [&](int it, ulonglong2 (&d)[PARTS]) {
-        const int g = g0 + (it >> 2);
-        const u32 pt = (u32)(it & 3) * 512 + threadIdx.x * 2;
+        const int g = g0 + it / IPC;
+        const u32 pt = (u32)(it % IPC) * 512 + threadIdx.x * 2;
 #pragma unroll
         for (int j = 0; j < PARTS; ++j) {
             const u64* dp = (j == own) ? A.c1 + g * A.c1_gs + (size_t)r * N + off
@@ -536,7 +543,7 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
             d[j] = __ldcs(reinterpret_cast<const ulonglong2*>(dp + pt));
         }
     };
-    const int n_it = (g1 - g0) * 4;
+    const int n_it = (g1 - g0) * IPC;
     ulonglong2 dn[PARTS];
     if (n_it > 0) fetch(0, dn);
     mbar_wait(bar, 0);
@@ -552,8 +559,8 @@ __global__ void __launch_bounds__(256) k_ip_tma(KCtx c, IpArgs A, int n_g, int g
 #pragma unroll
         for (int j = 0; j < PARTS; ++j) d[j] = dn[j];
         if (it + 1 < n_it) fetch(it + 1, dn);
-        const int g = g0 + (it >> 2);
-        const u32 pt = (u32)(it & 3) * 512 + threadIdx.x * 2;  // two adjacent points per 16-byte access
+        const int g = g0 + it / IPC;
+        const u32 pt = (u32)(it % IPC) * 512 + threadIdx.x * 2;  // two adjacent points per 16-byte access
         u64* o0;
         u64* o1;
         if (r < A.ell) {
@@ -919,7 +926,7 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
     const int tiles = N / IPT, M = a.ell + a.K;
     // enough CTAs for >= 2 waves of 2 CTAs per SM, but as few key-tile reloads as possible
     int gz = 1;
-    while (tiles * M * gz < 148 * 4 && gz < n_g) gz *= 2;
+    while (tiles * M * gz < 148 * 4 * (2048 / IPT) && gz < n_g) gz *= 2;
     const int g_per = (n_g + gz - 1) / gz;
     gz = (n_g + g_per - 1) / g_per;
     dim3 grid(tiles, M, gz);
