@@ -115,21 +115,38 @@ __device__ __forceinline__ u32 point_of(u32 u, int k) {
 }
 
 // Forward stages on point bits BHI-1 .. LO (register bits BHI-1-LO .. 0).
-template <int S, int LO, int BHI, int B = 8>
-__device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u, u64 q,
-                                          u64 q4, u64 z = 0) {
+// The (up to) seven twiddles of a radix-8 group, slot (4 >> rb) - 1 + g.  Loading them is separate from using them so
+// that a pass can request the NEXT group's twiddles before the shared-memory exchange: their L2 latency (the top
+// stall of the ROW passes, profiles/r04_ncu_full.md) then overlaps the exchange instead of following it.
+template <int S, int LO, int BHI>
+__device__ __forceinline__ void fwd_group_tw(ulonglong2 (&t)[7], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u) {
     const u32 uhi = u >> LO;
 #pragma unroll
     for (int rb = BHI - 1 - LO; rb >= 0; --rb) {
         const u32 base = rowfac << (S - 1 - LO - rb);
+#pragma unroll
+        for (int g = 0; g < (4 >> rb); ++g) t[(4 >> rb) - 1 + g] = __ldg(tw + (base + ((uhi << (2 - rb)) | (u32)g)));
+    }
+}
+template <int S, int LO, int BLO>
+__device__ __forceinline__ void inv_group_tw(ulonglong2 (&t)[7], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u) {
+    const u32 uhi = u >> LO;
+#pragma unroll
+    for (int rb = BLO - LO; rb <= 2; ++rb) {
+        const u32 base = rowfac << (S - 1 - LO - rb);
+#pragma unroll
+        for (int g = 0; g < (4 >> rb); ++g) t[(4 >> rb) - 1 + g] = __ldg(tw + (base + ((uhi << (2 - rb)) | (u32)g)));
+    }
+}
+
+template <int S, int LO, int BHI, int B = 8>
+__device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2 (&tws)[7], u64 q, u64 q4, u64 z = 0) {
+#pragma unroll
+    for (int rb = BHI - 1 - LO; rb >= 0; --rb) {
         const bool fold = fwd_bound_after(B, BHI - 1 - LO - rb) + 4 > 16;  // folds at compile time (unrolled)
 #pragma unroll
         for (int g = 0; g < (4 >> rb); ++g) {
-#ifdef PPQ_EXP_NOTW
-            const ulonglong2 t = make_ulonglong2(q ^ (u64)(base + uhi + g), q4 ^ (u64)(uhi * 77 + g));
-#else
-            const ulonglong2 t = __ldg(tw + (base + ((uhi << (2 - rb)) | (u32)g)));
-#endif
+            const ulonglong2 t = tws[(4 >> rb) - 1 + g];
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
@@ -147,21 +164,14 @@ __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2* __restr
 
 // Inverse stages on point bits BLO .. LO+2 (register bits BLO-LO .. 2), ascending.
 template <int S, int LO, int BLO, int B = 4>
-__device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2* __restrict__ tw, u32 rowfac, u32 u, u64 q,
-                                          u64 q4) {
-    const u32 uhi = u >> LO;
+__device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2 (&tws)[7], u64 q, u64 q4) {
     constexpr InvPlan plan = inv_plan(B, BLO - LO);
     (void)plan;
 #pragma unroll
     for (int rb = BLO - LO; rb <= 2; ++rb) {
-        const u32 base = rowfac << (S - 1 - LO - rb);
 #pragma unroll
         for (int g = 0; g < (4 >> rb); ++g) {
-#ifdef PPQ_EXP_NOTW
-            const ulonglong2 t = make_ulonglong2(q ^ (u64)(base + uhi + g), q4 ^ (u64)(uhi * 77 + g));
-#else
-            const ulonglong2 t = __ldg(tw + (base + ((uhi << (2 - rb)) | (u32)g)));
-#endif
+            const ulonglong2 t = tws[(4 >> rb) - 1 + g];
 #pragma unroll
             for (int lk = 0; lk < (1 << rb); ++lk) {
                 const int k = (g << (rb + 1)) | lk;
@@ -254,17 +264,21 @@ __device__ __forceinline__ void fwd_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
                                          u32 rowfac, u64 q, u64 q4, bool guard, u64 z = 0) {
     constexpr int LO0 = S - 3;
     constexpr int LO1 = cmax(S - 6, 0);
-    fwd_group<S, LO0, S, BIN>(a, tw, rowfac, u, q, q4, z);
+    ulonglong2 t[7];
+    fwd_group_tw<S, LO0, S>(t, tw, rowfac, u);
+    fwd_group<S, LO0, S, BIN>(a, t, q, q4, z);
+    fwd_group_tw<S, LO1, LO0>(t, tw, rowfac, u);  // in flight during the exchange
     if (guard) pass_sync<Pos>();
     sm_store<LO0>(a, sm, pos, u);
     pass_sync<Pos>();
     sm_load<LO1>(a, sm, pos, u);
-    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(a, tw, rowfac, u, q, q4, z);
+    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(a, t, q, q4, z);
     if constexpr (S > 6) {
+        fwd_group_tw<S, 0, LO1>(t, tw, rowfac, u);
         sm_store<LO1>(a, sm, pos, u);  // same words this thread just read: no barrier needed before
         pass_sync<Pos>();
         sm_load<0>(a, sm, pos, u);
-        fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(a, tw, rowfac, u, q, q4, z);
+        fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(a, t, q, q4, z);
     }
 }
 
@@ -282,17 +296,23 @@ __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
     constexpr int LO1 = cmin(3, S - 3);  // second group
     constexpr int B1 = inv_plan(BIN, 0).out;
     constexpr int B2 = inv_plan(B1, 3 - LO1).out;
-    inv_group<S, 0, 0, BIN>(a, tw, rowfac, u, q, q4);
+    ulonglong2 t[7];
+    inv_group_tw<S, 0, 0>(t, tw, rowfac, u);
+    inv_group<S, 0, 0, BIN>(a, t, q, q4);
+    // (unlike the forward passes, requesting the next group's twiddles before the exchange does not pay here:
+    // the inverse kernels are register-tighter and measured 2-3 % slower with it)
     if (guard) pass_sync<Pos>();
     sm_store<0>(a, sm, pos, u);
     pass_sync<Pos>();
     sm_load<LO1>(a, sm, pos, u);
-    inv_group<S, LO1, 3, B1>(a, tw, rowfac, u, q, q4);
+    inv_group_tw<S, LO1, 3>(t, tw, rowfac, u);
+    inv_group<S, LO1, 3, B1>(a, t, q, q4);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);
         pass_sync<Pos>();
         sm_load<LOL>(a, sm, pos, u);
-        inv_group<S, LOL, 6, B2>(a, tw, rowfac, u, q, q4);
+        inv_group_tw<S, LOL, 6>(t, tw, rowfac, u);
+        inv_group<S, LOL, 6, B2>(a, t, q, q4);
     }
 }
 
