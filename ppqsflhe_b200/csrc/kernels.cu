@@ -14,6 +14,9 @@
 #ifndef PPQ_ROW_MINB
 #define PPQ_ROW_MINB 8  // 128-thread CTAs (PPQ_ROW_PTS 1024), 64 registers: best of 5..20 on B200 (profiles/r01_notes.md)
 #endif
+#ifndef PPQ_ROW_GPC
+#define PPQ_ROW_GPC 3  // ciphertexts per ROW CTA (same rows, same twiddles: the later ones find the twiddles in L1); 1: 134.4, 2: 133.6, 3: 133.2, 6-18: 133.1-134.0 us/ct
+#endif
 #ifndef PPQ_ROW_PTS
 #define PPQ_ROW_PTS 1024
 #endif
@@ -318,23 +321,25 @@ struct RowGeom {
 
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
-    k_fwd_row_plain(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids) {
+    k_fwd_row_plain(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const u32 y = blockIdx.z, g = blockIdx.y;  // g fastest: CTAs sharing a limb's twiddles are co-resident
+    const u32 y = blockIdx.z;
     const int limb = limb_ids[y];
     if (limb < 0) return;  // block-uniform: slot not to be transformed
     const LimbC lc = c.limbs[limb];
     const ulonglong2* tw = c.twf + (size_t)limb * N;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const u32 gend = min((u32)n_g, (blockIdx.y + 1) * PPQ_ROW_GPC);
+    for (u32 g = blockIdx.y * PPQ_ROW_GPC; g < gend; ++g) {
     u64* p = data + g * gs + (size_t)y * N + (size_t)row * n2;
     u64 a[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = p[point_of<S - 3>(u, k)];
-    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
+    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, PPQ_ROW_GPC > 1, PPQ_Z(lc));
     if (FwdOut<S, FWD_ROW_IN>::B > 8 && lc.sh >= 28u) {  // block-uniform
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] = canon16_q(a[k], lc);
@@ -343,29 +348,33 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
         for (int k = 0; k < 8; ++k) a[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
     }
     st8(p + 8 * u, a);
+    }
 }
 
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
     k_inv_row(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs,
-              const int* __restrict__ limb_map) {
+              const int* __restrict__ limb_map, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
-    const u32 y = blockIdx.z, g = blockIdx.y;  // g fastest: CTAs sharing a limb's twiddles are co-resident
+    const u32 y = blockIdx.z;
     const int limb = limb_map[y];
     const LimbC lc = c.limbs[limb];
     const ulonglong2* tw = c.twi + (size_t)limb * N;
     const size_t off = (size_t)y * N + (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const u32 gend = min((u32)n_g, (blockIdx.y + 1) * PPQ_ROW_GPC);
+    for (u32 g = blockIdx.y * PPQ_ROW_GPC; g < gend; ++g) {
     u64 a[8];
     ld8(a, in + g * in_gs + off + 8 * u);
-    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-    inv_pass<S, RowPos<S>, INV_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    inv_pass<S, RowPos<S>, INV_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, PPQ_ROW_GPC > 1);
     u64* o = out + g * out_gs + off;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy [0,4q): consumed by k_inv_col
+    for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy (< 8q): consumed by k_inv_col
+    }
 }
 
 // Forward ROW pass + inner product with the re-encryption key (+ inverse ROW pass on the P limbs).
@@ -588,19 +597,20 @@ __global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, i
 
 // Forward ROW pass + ModDown combine: out = (x - conv) * P^-1 (+ c0 on poly 0) (+ running sum).
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_moddown(KCtx c, MdArgs A) {
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_moddown(KCtx c, MdArgs A, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
     const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
     const u32 row = blockIdx.x * G::R + w;
     const int y = blockIdx.z;
-    const u32 g = blockIdx.y;
     const int poly = y / A.ell, i = y % A.ell;
     const LimbC lc = c.limbs[i];
     const ulonglong2* tw = c.twf + (size_t)i * N;
     const size_t off = (size_t)y * N + (size_t)row * n2;
     RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const u32 gend = min((u32)n_g, (blockIdx.y + 1) * PPQ_ROW_GPC);
+    for (u32 g = blockIdx.y * PPQ_ROW_GPC; g < gend; ++g) {
     u64 a[8];
     const u64* in = A.conv + g * A.conv_gs + off;
 #pragma unroll
@@ -609,7 +619,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     prefetch_l2(A.extq + g * A.extq_gs + off + 8 * u);
     if (poly == 0) prefetch_l2(A.ct_in + g * A.in_gs + off + 8 * u);
     if (A.accumulate) prefetch_l2(o);
-    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
+    fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, PPQ_ROW_GPC > 1, PPQ_Z(lc));
     u64 x[8];
     ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
     // keys and conversion constants carry P^-1 already (launch_scale_key, build_ks_plan): (x - conv) P^-1 = x' - conv'.
@@ -634,6 +644,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
         for (int k = 0; k < 8; ++k) a[k] = canon_b<16>(a[k], lc);
     }
     st8(o, a);
+    }
 }
 
 // Forward ROW pass + rescale combine (DropLastElementAndScale, then the EvalMult constant folded in).
@@ -807,6 +818,7 @@ struct ColW {  // columns per CTA: 256 threads (512 for S = 9)
         default: break;                   \
     }
 
+static inline int gpc_blocks(int n_g) { return (n_g + PPQ_ROW_GPC - 1) / PPQ_ROW_GPC; }
 template <int S, int MODE>
 static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* jobs,
                            const u64* chat, const int* limb_ids, u64 q_src, int ny, int ng, cudaStream_t st) {
@@ -824,23 +836,23 @@ void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_p
     const int n1 = 1 << sp.S1;
     PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 0>(c, data, 0, data, 0, nullptr, nullptr, d_limb_ids, 0, n_polys, 1, st)));
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, 1, n_polys), RowGeom<S>::THREADS, 0, st>>>(
-                                c, data, 0, d_limb_ids)));
+                                c, data, 0, d_limb_ids, 1)));
 }
 
 void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
                           cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, n_g, n_slots), RowGeom<S>::THREADS, 0, st>>>(
-                                c, data, gs, d_limb_ids)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
+                                c, data, gs, d_limb_ids, n_g)));
 }
 
 void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
                     int n_slots, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, n_g, n_slots), RowGeom<S>::THREADS, 0, st>>>(
-                                c, in, in_gs, out, out_gs, d_limb_map)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
+                                c, in, in_gs, out, out_gs, d_limb_map, n_g)));
 }
 void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
                     const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st) {
@@ -946,7 +958,7 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, n_g, 2 * a.ell), RowGeom<S>::THREADS, 0, st>>>(c, a)));
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), 2 * a.ell), RowGeom<S>::THREADS, 0, st>>>(c, a, n_g)));
 }
 void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
