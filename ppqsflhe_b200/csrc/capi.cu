@@ -92,7 +92,7 @@ struct ppq_ctx {
     DevBuf<u64> scratch;   // key-switch wave scratch
     DevBuf<u64> scratch2;  // rescale / encrypt / decrypt scratch
     DevBuf<int> ids;       // limb ids of the plain NTT API
-    DevBuf<u64> ids_scale; // [2][n] N^-1 per poly (+ shoup)
+    DevBuf<u64> ids_scale; // [n][4] output factor N^-1 per poly (host::scale4)
     DevBuf<u64> fac;       // [2][L] EvalMult factors
     ckks::Tables fft;
     int wave = 0;
@@ -254,18 +254,18 @@ static int ntt_common(ppq_ctx* c, u64* d, const int32_t* ids, size_t n, void* st
     cudaStream_t st = (cudaStream_t)stream;
     const int M = c->hp.M();
     std::vector<int> h(ids, ids + n);
-    std::vector<u64> sc(2 * n);
+    std::vector<u64> f(n);
     for (size_t i = 0; i < n; ++i) {
         if (h[i] < 0 || h[i] >= M) return fail(PPQ_EINVAL, "ppq_ntt: limb id out of range");
-        sc[i] = c->hp.ninv[h[i]];
-        sc[n + i] = host::shoup(sc[i], c->hp.mod[h[i]]);
+        f[i] = c->hp.ninv[h[i]];
     }
+    const std::vector<u64> sc = inverse ? host::scale4(c->hp, h, f) : std::vector<u64>();
     CU(c->ids.ensure(n));
     CU(cudaMemcpyAsync(c->ids.p, h.data(), n * sizeof(int), cudaMemcpyHostToDevice, st));
     if (inverse) {
-        CU(c->ids_scale.ensure(2 * n));
-        CU(cudaMemcpyAsync(c->ids_scale.p, sc.data(), 2 * n * sizeof(u64), cudaMemcpyHostToDevice, st));
-        launch_ntt_inverse(c->k, d, c->ids.p, c->ids_scale.p, c->ids_scale.p + n, (int)n, st);
+        CU(c->ids_scale.ensure(4 * n));
+        CU(cudaMemcpyAsync(c->ids_scale.p, sc.data(), 4 * n * sizeof(u64), cudaMemcpyHostToDevice, st));
+        launch_ntt_inverse(c->k, d, c->ids.p, c->ids_scale.p, (int)n, st);
     } else {
         launch_ntt_forward(c->k, d, c->ids.p, (int)n, st);
     }
@@ -356,11 +356,9 @@ static int get_ks_plan(ppq_ctx* c, int ell, KsPlanDev** out) {
         std::unique_ptr<KsPlanDev> p(new KsPlanDev);
         host::build_ks_plan(c->hp, ell, p->h);
         CU(p->c1_limb.upload(p->h.c1_limb));
-        CU(p->c1_scale.upload(p->h.c1_scale));
-        CU(p->c1_scale_sh.upload(p->h.c1_scale_sh));
+        CU(p->c1_scale.upload(host::scale4(c->hp, p->h.c1_limb, p->h.c1_scale)));
         CU(p->p_limb.upload(p->h.p_limb));
-        CU(p->p_scale.upload(p->h.p_scale));
-        CU(p->p_scale_sh.upload(p->h.p_scale_sh));
+        CU(p->p_scale.upload(host::scale4(c->hp, p->h.p_limb, p->h.p_scale)));
         CU(p->pinv.upload(p->h.pinv));
         CU(p->pinv_sh.upload(p->h.pinv_sh));
         p->up_jobs = to_dev_jobs(p->h.up_jobs);
@@ -504,7 +502,7 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         // 1-2. c1 -> COEFF, scaled by N^-1 (D_j/q_i)^-1
         launch_inv_row(c->k, in_g + (size_t)ell * N, ct, y, w.y, p->c1_limb.p, ell, ng, st);
         if (prof) cudaEventRecord(ev[1], st);
-        launch_inv_col(c->k, y, w.y, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, ng, st);
+        launch_inv_col(c->k, y, w.y, p->c1_limb.p, p->c1_scale.p, ell, ng, st);
         if (prof) cudaEventRecord(ev[2], st);
         // 3. ModUp: approximate basis switch of every digit to its complementary limbs (pointwise)
         for (const auto& d : p->digits)
@@ -550,7 +548,7 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
             }
         }
         // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
-        launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, p->p_scale_sh.p, 2 * K, ng, st);
+        launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, 2 * K, ng, st);
         if (prof) cudaEventRecord(ev[8], st);
         // 6. ModDown conversion P -> Q (pointwise; the digits buffer is dead: reuse it), then its COL pass
         if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data(), ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
@@ -609,7 +607,7 @@ extern "C" int ppq_ks_modup(ppq_ctx* c, int ell, const uint64_t* d_c1, uint64_t*
     CU(c->scratch.ensure(ys * n));
     u64* y = c->scratch.p;
     launch_inv_row(c->k, (const u64*)d_c1, ys, y, ys, p->c1_limb.p, ell, (int)n, st);
-    launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, p->c1_scale_sh.p, ell, (int)n, st);
+    launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, ell, (int)n, st);
     for (const auto& d : p->digits)
         if (!launch_bconv(c->k, y, ys, (u64*)d_digits, ds, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, (int)n, st))
             return fail(PPQ_EINVAL, "digit wider than 32 limbs");
@@ -685,8 +683,7 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
         std::unique_ptr<RsPlanDev> p(new RsPlanDev);
         host::build_rs_plan(c->hp, ell, p->h);
         CU(p->last_limb.upload(p->h.last_limb));
-        CU(p->last_scale.upload(p->h.last_scale));
-        CU(p->last_scale_sh.upload(p->h.last_scale_sh));
+        CU(p->last_scale.upload(host::scale4(c->hp, p->h.last_limb, p->h.last_scale)));
         CU(p->jobs.upload(to_dev_jobs(p->h.jobs)));
         CU(p->cst.ensure(lo));
         CU(p->cst_sh.ensure(lo));
@@ -708,7 +705,7 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
     for (int poly = 0; poly < 2; ++poly)
         launch_inv_row(c->k, (const u64*)in + ((size_t)poly * ell + lo) * N, ct, r + (size_t)poly * N, rs_,
                        p->last_limb.p, 1, (int)n, st);
-    launch_inv_col(c->k, r, rs_, p->last_limb.p, p->last_scale.p, p->last_scale_sh.p, 2, (int)n, st);
+    launch_inv_col(c->k, r, rs_, p->last_limb.p, p->last_scale.p, 2, (int)n, st);
     launch_sw_fwd_col(c->k, r, rs_, conv, cs_, p->jobs.p, (int)p->h.jobs.size(), (int)n, c->hp.mod[lo], st);
     RsArgs ra;
     ra.conv = conv;

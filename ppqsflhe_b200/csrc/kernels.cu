@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
 template <int S, int W, bool SAME>
 __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
-              const u64* __restrict__ scale, const u64* __restrict__ scale_sh) {
+              const u64* __restrict__ scale) {
     __shared__ u64 sm[W << S];
     constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
     const u32 w = threadIdx.x % W, u = threadIdx.x / W;
@@ -140,10 +140,12 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = p[(size_t)(8 * u + k) * n2];
     ColPos<W> pos{w};
-    inv_pass<S, ColPos<W>, INV_COL_IN>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false);
-    const u64 sc = scale[y], scs = scale_sh[y];
+    // scale[] holds, per slot, (f, shoup(f), f * psi^-brev(1), shoup(.)): the output factor rides on the last stage
+    const ulonglong2 fs = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * y);
+    const ulonglong2 fw = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * y + 1);
+    inv_pass<S, ColPos<W>, INV_COL_IN, true>(a, sm, pos, u, tw, 1u, lc.q, lc.q2 << 1, false, fs, fw);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) p[(size_t)point_of<S - 3>(u, k) * n2] = mul_shoup(a[k], sc, scs, lc.q);
+    for (int k = 0; k < 8; ++k) p[(size_t)point_of<S - 3>(u, k) * n2] = canon4(a[k], lc);
 }
 
 // =========================================================================================================
@@ -854,22 +856,22 @@ void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t
     PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
                                 c, in, in_gs, out, out_gs, d_limb_map, n_g)));
 }
-void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
-                    const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st) {
+void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale4, int n_slots,
+                    int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n2 = 1 << sp.S2;
     if (sp.S1 == sp.S2) {
         PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W, true><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
-                                    c, data, gs, d_limb_map, d_scale, d_scale_sh)));
+                                    c, data, gs, d_limb_map, d_scale4)));
     } else {
         PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W, false><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
-                                    c, data, gs, d_limb_map, d_scale, d_scale_sh)));
+                                    c, data, gs, d_limb_map, d_scale4)));
     }
 }
-void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale, const u64* d_scale_sh,
+void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale4,
                         int n_polys, cudaStream_t st) {
     launch_inv_row(c, data, 0, data, 0, d_limb_ids, n_polys, 1, st);
-    launch_inv_col(c, data, 0, d_limb_ids, d_scale, d_scale_sh, n_polys, 1, st);
+    launch_inv_col(c, data, 0, d_limb_ids, d_scale4, n_polys, 1, st);
 }
 
 void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,

@@ -30,16 +30,18 @@ struct BcJob {
 // ---- plain batched NTT (C-ABI ppq_ntt_forward / ppq_ntt_inverse).  data: [n_polys][N] in place,
 // d_limb_ids: device int[n_polys].  d_scale / d_scale_sh: per-POLY constant folded into the inverse (N^-1).
 void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_polys, cudaStream_t st);
-void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale, const u64* d_scale_sh,
-                        int n_polys, cudaStream_t st);
+// d_scale4: per polynomial (f, shoup(f), f * psi^-brev(1) mod q, shoup(.)) with f the output factor (here N^-1): the
+// last inverse stage applies it (host::scale4 builds the array)
+void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale4, int n_polys,
+                        cudaStream_t st);
 
 // ---- generic strided inverse:  for g < n_g, y < n_slots:
 //   out[g*out_gs + y*N ..] = iNTT(in[g*in_gs + y*N ..]) * scale[y]   (limb = limb_map[y]), canonical.
 // row pass and column pass are separate launches; `tmp` may alias `out`.
 void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
                     int n_slots, int n_g, cudaStream_t st);
-void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale,
-                    const u64* d_scale_sh, int n_slots, int n_g, cudaStream_t st);
+void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale4, int n_slots,
+                    int n_g, cudaStream_t st);
 
 // ---- approximate CRT basis switch, pointwise (ApproxSwitchCRTBasis).  All `n_jobs` jobs share src_first and
 // ns (= `ns`); dst[g][job.dst_slot] = sum_i src[g][src_first+i] * chat[job.chat_off+i] mod q_{job.limb}.

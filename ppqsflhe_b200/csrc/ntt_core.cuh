@@ -163,12 +163,26 @@ __device__ __forceinline__ void fwd_group(u64 (&a)[8], const ulonglong2 (&tws)[7
 }
 
 // Inverse stages on point bits BLO .. LO+2 (register bits BLO-LO .. 2), ascending.
-template <int S, int LO, int BLO, int B = 4>
-__device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2 (&tws)[7], u64 q, u64 q4) {
+// FIN: this group ends the whole transform (COL pass, LO = S-3) and its last stage -- ONE twiddle, psi^-brev(1), for
+// every butterfly -- also applies the per-limb output factor f (N^-1 times the base-conversion pre-factor): the
+// difference is multiplied by fin_w = twiddle * f instead of the twiddle (free), the sum by fin_s = f: four extra lazy
+// products per thread instead of eight exact ones in an epilogue.  Outputs are < 4q.
+template <int S, int LO, int BLO, int B = 4, bool FIN = false>
+__device__ __forceinline__ void inv_group(u64 (&a)[8], const ulonglong2 (&tws)[7], u64 q, u64 q4,
+                                          ulonglong2 fin_s = ulonglong2{0, 0}, ulonglong2 fin_w = ulonglong2{0, 0}) {
     constexpr InvPlan plan = inv_plan(B, BLO - LO);
     (void)plan;
 #pragma unroll
     for (int rb = BLO - LO; rb <= 2; ++rb) {
+        if (FIN && rb == 2) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const u64 sum = a[k] + a[k + 4], dif = a[k] - a[k + 4] + (q4 << 1);
+                a[k] = mul_shoup_lazy4(sum, fin_s.x, fin_s.y, q);
+                a[k + 4] = mul_shoup_lazy4(dif, fin_w.x, fin_w.y, q);
+            }
+            continue;
+        }
 #pragma unroll
         for (int g = 0; g < (4 >> rb); ++g) {
             const ulonglong2 t = tws[(4 >> rb) - 1 + g];
@@ -289,9 +303,10 @@ constexpr int INV_ROW_IN = 1, INV_COL_IN = 8;  // ROW passes read canonical data
 #else
 constexpr int INV_ROW_IN = 4, INV_COL_IN = 4;
 #endif
-template <int S, class Pos, int BIN = 4>
+template <int S, class Pos, int BIN = 4, bool FIN = false>
 __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u32 u, const ulonglong2* __restrict__ tw,
-                                         u32 rowfac, u64 q, u64 q4, bool guard) {
+                                         u32 rowfac, u64 q, u64 q4, bool guard, ulonglong2 fin_s = ulonglong2{0, 0},
+                                         ulonglong2 fin_w = ulonglong2{0, 0}) {
     constexpr int LOL = S - 3;           // last group
     constexpr int LO1 = cmin(3, S - 3);  // second group
     constexpr int B1 = inv_plan(BIN, 0).out;
@@ -306,13 +321,13 @@ __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
     pass_sync<Pos>();
     sm_load<LO1>(a, sm, pos, u);
     inv_group_tw<S, LO1, 3>(t, tw, rowfac, u);
-    inv_group<S, LO1, 3, B1>(a, t, q, q4);
+    inv_group<S, LO1, 3, B1, (FIN && S <= 6)>(a, t, q, q4, fin_s, fin_w);
     if constexpr (S > 6) {
         sm_store<LO1>(a, sm, pos, u);
         pass_sync<Pos>();
         sm_load<LOL>(a, sm, pos, u);
         inv_group_tw<S, LOL, 6>(t, tw, rowfac, u);
-        inv_group<S, LOL, 6, B2>(a, t, q, q4);
+        inv_group<S, LOL, 6, B2, FIN>(a, t, q, q4, fin_s, fin_w);
     }
 }
 

@@ -256,6 +256,20 @@ static inline size_t brev(size_t x, int bits) {
     return r;
 }
 
+std::vector<u64> scale4(const Params& p, const std::vector<int>& limb, const std::vector<u64>& f) {
+    std::vector<u64> o(4 * limb.size());
+    for (size_t i = 0; i < limb.size(); ++i) {
+        const u64 q = p.mod[limb[i]];
+        // inv[1] of build_twiddles: psi^-brev(1) = psi^-(N/2)
+        const u64 w1 = powmod(invmod(p.root[limb[i]], q), (u64)p.N / 2, q);
+        o[4 * i] = f[i];
+        o[4 * i + 1] = shoup(f[i], q);
+        o[4 * i + 2] = mulmod(f[i], w1, q);
+        o[4 * i + 3] = shoup(o[4 * i + 2], q);
+    }
+    return o;
+}
+
 void build_twiddles(const Params& p, int limb, u64* fwd, u64* inv) {
     const u64 q = p.mod[limb], psi = p.root[limb], ipsi = invmod(psi, q);
     u64 pw = 1, ipw = 1;

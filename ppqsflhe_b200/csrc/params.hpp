@@ -41,6 +41,9 @@ std::vector<u64> synthetic_chain(int logN, int depth, int first_bits, int scale_
 bool parse_ccjson(const char* text, size_t len, Params& p, std::string& err);
 
 // twiddle tables of one limb: fwd[k] = (psi^brev(k), shoup), inv[k] = (psi^-brev(k), shoup)
+// (f, shoup(f), f * psi^-brev(1), shoup(.)) per slot: the output factor of an inverse transform, folded into its last
+// stage (k_inv_col); limb[i] is the modulus index of slot i
+std::vector<u64> scale4(const Params& p, const std::vector<int>& limb, const std::vector<u64>& f);
 void build_twiddles(const Params& p, int limb, u64* fwd_pairs /* 2N */, u64* inv_pairs /* 2N */);
 
 struct Job {
