@@ -106,7 +106,16 @@ __device__ __forceinline__ void mac128(u64& hi, u64& lo, u64 a, u64 b) {
 
 // (hi,lo) mod q, canonical.  Requires (hi,lo) < 2^(63 + bitlen(q)).
 __device__ __forceinline__ u64 barrett128(u64 hi, u64 lo, const LimbC& c) {
-    u64 x1 = (hi << (64u - c.sh)) | (lo >> c.sh);
+    // x1 = bits [sh, sh+64) of (hi:lo).  For sh >= 32 (every limb of 33 bits and more; the branch is block-uniform)
+    // two funnel shifts do it; the generic 128-bit shift costs seven instructions.
+    u64 x1;
+    if (c.sh >= 32u) {
+        const u32 s = c.sh - 32u;
+        const u32 l1 = (u32)(lo >> 32), h0 = (u32)hi, h1 = (u32)(hi >> 32);
+        x1 = ((u64)__funnelshift_r(h0, h1, s) << 32) | __funnelshift_r(l1, h0, s);
+    } else {
+        x1 = (hi << (64u - c.sh)) | (lo >> c.sh);
+    }
     u64 qh = __umul64hi(x1, c.mu);
     u64 r = lo - qh * c.q;  // true remainder + {0,1,2} * q
     r = csub(r, c.q2);
