@@ -93,6 +93,7 @@ struct ppq_ctx {
     DevBuf<u64> scratch2;  // rescale / encrypt / decrypt scratch
     DevBuf<int> ids;       // limb ids of the plain NTT API
     DevBuf<u64> ids_scale; // [n][4] output factor N^-1 per poly (host::scale4)
+    std::vector<u64> ntt_scale4;  // [L+K][4], built on first use
     DevBuf<u64> fac;       // [2][L] EvalMult factors
     ckks::Tables fft;
     int wave = 0;
@@ -254,12 +255,19 @@ static int ntt_common(ppq_ctx* c, u64* d, const int32_t* ids, size_t n, void* st
     cudaStream_t st = (cudaStream_t)stream;
     const int M = c->hp.M();
     std::vector<int> h(ids, ids + n);
-    std::vector<u64> f(n);
-    for (size_t i = 0; i < n; ++i) {
+    for (size_t i = 0; i < n; ++i)
         if (h[i] < 0 || h[i] >= M) return fail(PPQ_EINVAL, "ppq_ntt: limb id out of range");
-        f[i] = c->hp.ninv[h[i]];
+    std::vector<u64> sc;
+    if (inverse) {
+        if (c->ntt_scale4.empty()) {  // per limb, once: (N^-1, shoup, N^-1 psi^-brev(1), shoup)
+            std::vector<int> all(M);
+            for (int r = 0; r < M; ++r) all[r] = r;
+            c->ntt_scale4 = host::scale4(c->hp, all, c->hp.ninv);
+        }
+        sc.resize(4 * n);
+        for (size_t i = 0; i < n; ++i)
+            for (int k = 0; k < 4; ++k) sc[4 * i + k] = c->ntt_scale4[4 * h[i] + k];
     }
-    const std::vector<u64> sc = inverse ? host::scale4(c->hp, h, f) : std::vector<u64>();
     CU(c->ids.ensure(n));
     CU(cudaMemcpyAsync(c->ids.p, h.data(), n * sizeof(int), cudaMemcpyHostToDevice, st));
     if (inverse) {
