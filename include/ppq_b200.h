@@ -73,9 +73,13 @@ int ppq_ntt_forward(ppq_ctx*, uint64_t* d_data, const int32_t* h_limb_ids, size_
 int ppq_ntt_inverse(ppq_ctx*, uint64_t* d_data, const int32_t* h_limb_ids, size_t n_polys, void* stream);
 
 /* ---- re-encryption key: replaces Serial::DeserializeFromFile(rekey_path, reKey, SerType::JSON)
- *      (server/src/changeCipherDomain.cpp:40-44).  b, a: [dnum][L+K][N] EVAL (EvalKey B-vector / A-vector). */
+ *      (server/src/changeCipherDomain.cpp:40-44).  b, a: [dnum][L+K][N] EVAL (EvalKey B-vector / A-vector).
+ *      Both calls also prepare, once, the key's Q limbs multiplied by P^-1 mod q_i (the ModDown multiplication is
+ *      folded into the key).  _from_device BORROWS d_b / d_a (never written; they must outlive the handle and be
+ *      complete when the call is made -- it synchronises the default stream) and keeps that product in a private
+ *      [dnum][L][N] pair of buffers. */
 int ppq_rekey_upload(ppq_ctx*, const uint64_t* h_b, const uint64_t* h_a, ppq_rekey** out);
-int ppq_rekey_from_device(ppq_ctx*, const uint64_t* d_b, const uint64_t* d_a, ppq_rekey** out); /* borrows */
+int ppq_rekey_from_device(ppq_ctx*, const uint64_t* d_b, const uint64_t* d_a, ppq_rekey** out);
 void ppq_rekey_destroy(ppq_rekey*);
 
 /* ---- cc->ReEncrypt(ct, reKey) with publicKey == nullptr (server/src/changeCipherDomain.cpp:74,89,105):
