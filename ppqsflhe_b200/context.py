@@ -102,6 +102,21 @@ class EvalKey:
         check(lib().ppq_rekey_from_device(cc.h, _ptr(self.b), _ptr(self.a), C.byref(h)))
         self.h = h
 
+    @classmethod
+    def upload(cls, cc, b, a):
+        """Host arrays -> a handle that owns its device copy (ppq_rekey_upload); nothing is borrowed."""
+        b = np.ascontiguousarray(b, dtype=np.uint64)
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        exp = (cc.dnum, cc.L + cc.K, cc.N)
+        if b.shape != exp or a.shape != exp:
+            raise ValueError(f"rekey must have shape {exp}")
+        self = cls.__new__(cls)
+        self.cc, self.b, self.a = cc, None, None
+        h = vp()
+        check(lib().ppq_rekey_upload(cc.h, b.ctypes.data_as(_capi.u64p), a.ctypes.data_as(_capi.u64p), C.byref(h)))
+        self.h = h
+        return self
+
     def __del__(self):
         if getattr(self, "h", None):
             lib().ppq_rekey_destroy(self.h)

@@ -141,6 +141,29 @@ def test_reencrypt_bit_exact(kind, ell, n):
         assert np.array_equal(out[g][0], want[0]), f"c0' differs (ct {g})"
 
 
+def test_rekey_upload_and_borrowed_key_agree():
+    """ppq_rekey_upload (host buffers, the handle owns its copy) and ppq_rekey_from_device (borrowed device buffers,
+    the handle keeps a private P^-1-scaled copy of the Q limbs) must give the same ciphertexts, and the borrowed
+    buffers must stay untouched (reference: the rekey is read-only in ReEncrypt, Source/server.cpp:101-121)."""
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair((13, 4, 2, 50))
+    rng = np.random.default_rng(29)
+    ct = _rand_ct(rng, o, o.L, 2)
+    kb, ka = _rand_key(rng, o)
+    kb, ka = np.ascontiguousarray(kb), np.ascontiguousarray(ka)
+    rk = EvalKey(cc, kb, ka)
+    batch = CiphertextBatch(to_device_u64(ct, cc.device), CtMeta())
+    out_borrowed = cc.ReEncrypt(batch, rk).numpy()
+    assert np.array_equal(rk.b.cpu().numpy().view(np.uint64), kb), "borrowed key B was modified"
+    assert np.array_equal(rk.a.cpu().numpy().view(np.uint64), ka), "borrowed key A was modified"
+    kb0, ka0 = kb.copy(), ka.copy()
+    up = EvalKey.upload(cc, kb, ka)
+    assert np.array_equal(kb, kb0) and np.array_equal(ka, ka0), "host key buffers were modified"
+    out_upload = cc.ReEncrypt(batch, up).numpy()
+    assert np.array_equal(out_upload, out_borrowed)
+    assert np.array_equal(out_upload[0], o.reencrypt(o.L, ct[0], kb, ka))
+
+
 def test_fused_and_split_inner_product_agree(monkeypatch):
     """The two forms of the key inner product (one fused ROW-pass kernel / forward ROW pass + TMA-staged pointwise
     kernel + inverse ROW pass) must give identical ciphertexts."""
