@@ -297,6 +297,49 @@ inline jmin::Ptr dcrtpoly_to_json(const Poly& p) {
     return o;
 }
 
+// the cereal shared_ptr envelope around a key object: value0 -> ptr_wrapper -> data -> {member}
+inline jmin::Ptr wrap_key_member(const char* member, jmin::Ptr payload) {
+    jmin::Ptr data = jmin::make(jmin::Value::Object);
+    jmin::set(data, "cereal_class_version", jmin::make_u64(0));
+    jmin::set(data, member, payload);
+    jmin::Ptr pw = jmin::make(jmin::Value::Object);
+    jmin::set(pw, "id", jmin::make_u64(2147483649ull));
+    jmin::set(pw, "data", data);
+    jmin::Ptr v0 = jmin::make(jmin::Value::Object);
+    jmin::set(v0, "polymorphic_id", jmin::make_u64(1073741824));
+    jmin::set(v0, "ptr_wrapper", pw);
+    jmin::Ptr root = jmin::make(jmin::Value::Object);
+    jmin::set(root, "value0", v0);
+    return root;
+}
+// [limbs][N] contiguous residues -> Poly (EVALUATION format)
+inline Poly poly_from_flat(const uint64_t* data, size_t limbs, size_t N, const uint64_t* moduli) {
+    Poly p;
+    for (size_t i = 0; i < limbs; ++i) {
+        p.limbs.emplace_back(data + i * N, data + (i + 1) * N);
+        p.moduli.push_back(moduli[i]);
+    }
+    return p;
+}
+// key files as client/src/keyGen.cpp:41-48 and client/src/REkeyGen.cpp:60 write them (SerType::JSON)
+inline void write_private_key(const std::string& path, const Poly& s) {
+    spit(path, jmin::dump(*wrap_key_member("s", dcrtpoly_to_json(s)), 4, false));
+}
+inline void write_public_key(const std::string& path, const Poly& b, const Poly& a) {
+    jmin::Ptr h = jmin::make(jmin::Value::Array);
+    h->arr.push_back(dcrtpoly_to_json(b));
+    h->arr.push_back(dcrtpoly_to_json(a));
+    spit(path, jmin::dump(*wrap_key_member("h", h), 4, false));
+}
+inline void write_eval_key(const std::string& path, const std::vector<Poly>& a, const std::vector<Poly>& b) {
+    jmin::Ptr k = jmin::make(jmin::Value::Array), av = jmin::make(jmin::Value::Array), bv = jmin::make(jmin::Value::Array);
+    for (const Poly& p : a) av->arr.push_back(dcrtpoly_to_json(p));
+    for (const Poly& p : b) bv->arr.push_back(dcrtpoly_to_json(p));
+    k->arr.push_back(av);
+    k->arr.push_back(bv);
+    spit(path, jmin::dump(*wrap_key_member("k", k), 4, false));
+}
+
 // ------------------------------------------------------------------------------------------------ container
 struct Layer {
     jmin::Ptr layer, shape;          // copied through verbatim

@@ -114,39 +114,17 @@ static wire::Poly poly_from(const jmin::Value& limbs, const std::vector<uint64_t
     }
     return p;
 }
-static jmin::Ptr wrap(const char* member, jmin::Ptr payload) {  // value0 -> ptr_wrapper -> data -> {member}
-    jmin::Ptr data = jmin::make(jmin::Value::Object);
-    jmin::set(data, "cereal_class_version", jmin::make_u64(0));
-    jmin::set(data, member, payload);
-    jmin::Ptr pw = jmin::make(jmin::Value::Object);
-    jmin::set(pw, "id", jmin::make_u64(2147483649ull));
-    jmin::set(pw, "data", data);
-    jmin::Ptr v0 = jmin::make(jmin::Value::Object);
-    jmin::set(v0, "polymorphic_id", jmin::make_u64(1073741824));
-    jmin::set(v0, "ptr_wrapper", pw);
-    jmin::Ptr root = jmin::make(jmin::Value::Object);
-    jmin::set(root, "value0", v0);
-    return root;
-}
 static int t_mkkeys(const char* in, const std::string& dir) {
     jmin::Ptr r = jmin::parse(wire::slurp(in));
     std::vector<uint64_t> mod;
     for (const auto& m : r->at("moduli").arr) mod.push_back(m->as_u64());
-    if (const jmin::Value* sk = r->find("sk"))
-        wire::spit(dir + "/private.key", jmin::dump(*wrap("s", wire::dcrtpoly_to_json(poly_from(*sk, mod))), 4, false));
-    if (r->find("pk_b")) {
-        jmin::Ptr h = jmin::make(jmin::Value::Array);
-        h->arr.push_back(wire::dcrtpoly_to_json(poly_from(r->at("pk_b"), mod)));
-        h->arr.push_back(wire::dcrtpoly_to_json(poly_from(r->at("pk_a"), mod)));
-        wire::spit(dir + "/public.key", jmin::dump(*wrap("h", h), 4, false));
-    }
+    if (const jmin::Value* sk = r->find("sk")) wire::write_private_key(dir + "/private.key", poly_from(*sk, mod));
+    if (r->find("pk_b")) wire::write_public_key(dir + "/public.key", poly_from(r->at("pk_b"), mod), poly_from(r->at("pk_a"), mod));
     if (r->find("rk_b")) {
-        jmin::Ptr k = jmin::make(jmin::Value::Array), av = jmin::make(jmin::Value::Array), bv = jmin::make(jmin::Value::Array);
-        for (const auto& d : r->at("rk_a").arr) av->arr.push_back(wire::dcrtpoly_to_json(poly_from(*d, mod)));
-        for (const auto& d : r->at("rk_b").arr) bv->arr.push_back(wire::dcrtpoly_to_json(poly_from(*d, mod)));
-        k->arr.push_back(av);
-        k->arr.push_back(bv);
-        wire::spit(dir + "/rekey.key", jmin::dump(*wrap("k", k), 4, false));
+        std::vector<wire::Poly> av, bv;
+        for (const auto& d : r->at("rk_a").arr) av.push_back(poly_from(*d, mod));
+        for (const auto& d : r->at("rk_b").arr) bv.push_back(poly_from(*d, mod));
+        wire::write_eval_key(dir + "/rekey.key", av, bv);
     }
     return 0;
 }

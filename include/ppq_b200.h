@@ -128,6 +128,22 @@ int ppq_decrypt_core(ppq_ctx*, int ell, const uint64_t* d_sk, const uint64_t* d_
  *      by sf, special FFT; d_vals [n][N/2].  OpenFHE's randomised decode noise is not added. */
 int ppq_decode(ppq_ctx*, int ell, const uint64_t* d_coeff, double sf, double* d_vals, size_t n, void* stream);
 
+/* ---- cc->KeyGen() (client/src/keyGen.cpp:33; OpenFHE base-pke.cpp KeyGenInternal) with the sampled
+ *      polynomials supplied by the caller: d_s, d_e [N] int64 (ternary secret, Gaussian error sigma 3.19),
+ *      d_a [L+K][N] uniform residues (EVAL).  Out: d_sk [L][N] (the secret on the Q limbs, EVAL),
+ *      d_pkb [L+K][N] = e - a*s.  The public key is the pair (d_pkb, d_a) over QP. */
+int ppq_keygen(ppq_ctx*, const int64_t* d_s, const int64_t* d_e, const uint64_t* d_a, uint64_t* d_sk,
+               uint64_t* d_pkb, void* stream);
+/* draws ppq_keygen's inputs on the device (counter-based generator; uniform residues by rejection) */
+int ppq_sample_keygen(ppq_ctx*, uint64_t seed, int64_t* d_s, int64_t* d_e, uint64_t* d_a, void* stream);
+/* ---- cc->ReKeyGen(oldPrivateKey, newPublicKey) (client/src/REkeyGen.cpp:52; OpenFHE keyswitch-hybrid.cpp
+ *      KeySwitchGenInternal(oldSk, newPk)): per level-0 digit j, b_j = pk.b*u + e0 + (P mod q_r)*s_old on the
+ *      limbs of digit j, a_j = pk.a*u + e1.  d_sk_old [L][N], d_pkb / d_pka [L+K][N] (EVAL);
+ *      d_small [dnum][3][N] int64 = (u, e0, e1) per digit (ppq_sample_encrypt_noise(seed, d_small, dnum)
+ *      draws them).  Out: d_kb, d_ka [dnum][L+K][N], the layout ppq_rekey_from_device takes. */
+int ppq_rekeygen(ppq_ctx*, const uint64_t* d_sk_old, const uint64_t* d_pkb, const uint64_t* d_pka,
+                 const int64_t* d_small, uint64_t* d_kb, uint64_t* d_ka, void* stream);
+
 /* ---- host-buffer convenience (the call a drop-in server makes once every client's upload has arrived):
  *      h_cts[client] -> [n_slots][2][ell][N] in host memory (pinned for full PCIe rate); rekeys[n_clients];
  *      h_acc [n_slots][2][ell][N] = sum over clients of ReEncrypt(ct, rekey[client]).  Uploads are double

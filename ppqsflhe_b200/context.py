@@ -293,6 +293,40 @@ class CryptoContext:
                                     e - s, _stream()))
         return CiphertextBatch(ct, replace(pt.meta))
 
+    def KeyGen(self, seed=0, samples=None):
+        """cc->KeyGen() (client/src/keyGen.cpp:33).  Returns (sk [L][N], (pk_b, pk_a) [L+K][N] each), CUDA int64, EVAL.
+        samples: optional (s [N] int64, e [N] int64, a [L+K][N]) CUDA tensors injected for parity tests; drawn on
+        the device from `seed` otherwise."""
+        if samples is None:
+            s = torch.empty(self.N, dtype=torch.int64, device=self.device)
+            e = torch.empty_like(s)
+            a = torch.empty((self.M, self.N), dtype=torch.int64, device=self.device)
+            check(lib().ppq_sample_keygen(self.h, int(seed), _ptr(s), _ptr(e), _ptr(a), _stream()))
+        else:
+            s, e, a = samples
+            if tuple(s.shape) != (self.N,) or tuple(e.shape) != (self.N,) or tuple(a.shape) != (self.M, self.N):
+                raise ValueError("KeyGen: samples must be (s [N], e [N], a [L+K][N])")
+        sk = torch.empty((self.L, self.N), dtype=torch.int64, device=self.device)
+        pkb = torch.empty((self.M, self.N), dtype=torch.int64, device=self.device)
+        check(lib().ppq_keygen(self.h, _ptr(s), _ptr(e), _ptr(a), _ptr(sk), _ptr(pkb), _stream()))
+        return sk, (pkb, a)
+
+    def ReKeyGen(self, sk_old, pk_new, seed=0, small=None):
+        """cc->ReKeyGen(oldPrivateKey, newPublicKey) (client/src/REkeyGen.cpp:52) -> EvalKey resident on the device.
+        small: optional CUDA int64 [dnum][3][N] = injected (u, e0, e1) per digit."""
+        b, a = pk_new
+        if tuple(sk_old.shape) != (self.L, self.N) or tuple(b.shape) != (self.M, self.N) or tuple(a.shape) != tuple(b.shape):
+            raise ValueError("ReKeyGen: sk_old must be [L][N] and the public key two [L+K][N] tensors")
+        if small is None:
+            small = torch.empty((self.dnum, 3, self.N), dtype=torch.int64, device=self.device)
+            check(lib().ppq_sample_encrypt_noise(self.h, int(seed), _ptr(small), self.dnum, _stream()))
+        elif tuple(small.shape) != (self.dnum, 3, self.N):
+            raise ValueError("ReKeyGen: small must be [dnum][3][N]")
+        kb = torch.empty((self.dnum, self.M, self.N), dtype=torch.int64, device=self.device)
+        ka = torch.empty_like(kb)
+        check(lib().ppq_rekeygen(self.h, _ptr(sk_old), _ptr(b), _ptr(a), _ptr(small), _ptr(kb), _ptr(ka), _stream()))
+        return EvalKey(self, kb, ka)
+
     def DecryptCore(self, sk, ct):
         co = torch.empty((ct.n, ct.ell, self.N), dtype=torch.int64, device=self.device)
         step = max(1, 65535 // ct.ell)

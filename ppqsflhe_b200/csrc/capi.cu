@@ -812,6 +812,80 @@ extern "C" int ppq_sample_encrypt_noise(ppq_ctx* c, uint64_t seed, int64_t* d_sm
     return PPQ_OK;
 }
 
+// ---- key generation.  Samples come in as small integers so that the arithmetic is bit-exact
+// against the oracle; ppq_sample_keygen / ppq_sample_encrypt_noise draw them on the device.
+static int small_to_eval(ppq_ctx* c, const int64_t* small, u64* out, int n_small, size_t n_groups, cudaStream_t st) {
+    const int M = c->hp.M();
+    launch_small_to_res(c->k, small, out, n_small, M, n_groups, st);
+    std::vector<int> ids(n_groups * n_small * M);
+    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % M);
+    CU(c->ids.ensure(ids.size()));
+    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    launch_ntt_forward(c->k, out, c->ids.p, (int)ids.size(), st);
+    return PPQ_OK;
+}
+
+extern "C" int ppq_keygen(ppq_ctx* c, const int64_t* d_s, const int64_t* d_e, const uint64_t* d_a, uint64_t* d_sk,
+                          uint64_t* d_pkb, void* stream) {
+    if (!c || !d_s || !d_e || !d_a || !d_sk || !d_pkb) return fail(PPQ_EINVAL, "ppq_keygen: null argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    const int M = c->hp.M();
+    CU(c->scratch2.ensure(2 * (size_t)M * N + 2 * N));
+    u64* se = c->scratch2.p;                                            // [2][M][N]
+    int64_t* small = reinterpret_cast<int64_t*>(se + 2 * (size_t)M * N);  // [2][N]
+    CU(cudaMemcpyAsync(small, d_s, N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(small + N, d_e, N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+    if (int rc = small_to_eval(c, small, se, 2, 1, st)) return rc;
+    launch_keygen_pw(c->k, se, (const u64*)d_a, (u64*)d_sk, (u64*)d_pkb, c->hp.L, M, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+extern "C" int ppq_sample_keygen(ppq_ctx* c, uint64_t seed, int64_t* d_s, int64_t* d_e, uint64_t* d_a, void* stream) {
+    if (!c || !d_s || !d_e || !d_a) return fail(PPQ_EINVAL, "ppq_sample_keygen: null argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    CU(c->scratch2.ensure(3 * N));
+    int64_t* t = reinterpret_cast<int64_t*>(c->scratch2.p);  // (ternary, gauss, gauss)
+    ckks::launch_sample_noise(seed, t, N, 1, 3.19, st);
+    CU(cudaMemcpyAsync(d_s, t, N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(d_e, t + N, N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+    ckks::launch_sample_uniform(seed ^ 0xA5A5A5A5A5A5A5A5ull, c->k, c->hp.M(), d_a, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+extern "C" int ppq_rekeygen(ppq_ctx* c, const uint64_t* d_sk_old, const uint64_t* d_pkb, const uint64_t* d_pka,
+                            const int64_t* d_small, uint64_t* d_kb, uint64_t* d_ka, void* stream) {
+    if (!c || !d_sk_old || !d_pkb || !d_pka || !d_small || !d_kb || !d_ka)
+        return fail(PPQ_EINVAL, "ppq_rekeygen: null argument");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    const int L = c->hp.L, M = c->hp.M(), dnum = c->hp.dnum;
+    CU(c->scratch2.ensure((size_t)dnum * 3 * M * N));
+    u64* uee = c->scratch2.p;  // [dnum][3][M][N]
+    if (int rc = small_to_eval(c, d_small, uee, 3, (size_t)dnum, st)) return rc;
+    std::vector<u64> pm(L);  // P mod q_r
+    for (int r = 0; r < L; ++r) {
+        u64 v = 1;
+        for (int k = 0; k < c->hp.K; ++k) v = host::mulmod(v, c->hp.mod[L + k] % c->hp.mod[r], c->hp.mod[r]);
+        pm[r] = v;
+    }
+    CU(c->fac.ensure(2 * (size_t)L));
+    CU(cudaMemcpyAsync(c->fac.p, pm.data(), L * sizeof(u64), cudaMemcpyHostToDevice, st));
+    launch_rekeygen_pw(c->k, (const u64*)d_pkb, (const u64*)d_pka, uee, (const u64*)d_sk_old, c->fac.p, (u64*)d_kb,
+                       (u64*)d_ka, L, M, c->hp.alpha, dnum, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
 extern "C" int ppq_decrypt_core(ppq_ctx* c, int ell, const uint64_t* sk, const uint64_t* ct, uint64_t* coeff, size_t n,
                                 void* stream) {
     if (!c || !sk || !ct || !coeff) return fail(PPQ_EINVAL, "ppq_decrypt_core: null argument");

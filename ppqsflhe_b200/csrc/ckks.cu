@@ -200,6 +200,28 @@ __global__ void k_sample_noise(unsigned long long seed, long long* __restrict__ 
         out[g * 3 * N + i] = v;
     }
 }
+// uniform residues mod q_r for every limb r of QP (the `a` half of a public key): bits(q_r) random bits per draw,
+// rejected while >= q_r (at most a few rounds; after 64 the draw is reduced instead -- probability 2^-64)
+__global__ void k_sample_uniform(unsigned long long seed, KCtx c, unsigned long long* __restrict__ out) {
+    const size_t N = (size_t)1 << c.logN;
+    const int r = blockIdx.y;
+    const unsigned long long q = c.limbs[r].q;
+    const int drop = __clzll(q);
+    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
+        const unsigned long long ctr = mix64(((unsigned long long)r * N + i) * 64);
+        unsigned long long v = 0;
+        int t = 0;
+        for (; t < 64; ++t) {
+            v = mix64(seed ^ (ctr + t)) >> drop;
+            if (v < q) break;
+        }
+        out[(size_t)r * N + i] = t < 64 ? v : v % q;
+    }
+}
+void launch_sample_uniform(uint64_t seed, const KCtx& k, int n_limbs, uint64_t* d_out, cudaStream_t st) {
+    const unsigned N = 1u << k.logN;
+    k_sample_uniform<<<grid_for(N, n_limbs), 256, 0, st>>>(seed, k, (unsigned long long*)d_out);
+}
 void launch_sample_noise(uint64_t seed, int64_t* d_small, size_t N, size_t n, double sigma, cudaStream_t st) {
     k_sample_noise<<<grid_for(3 * N, n), 256, 0, st>>>(seed, (long long*)d_small, N, sigma);
 }

@@ -29,6 +29,8 @@ void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, co
                    double sf, double2* z, double* d_vals, size_t n, cudaStream_t st);
 // small [n][3][N]: ternary, gauss(sigma), gauss(sigma)
 void launch_sample_noise(uint64_t seed, int64_t* d_small, size_t N, size_t n, double sigma, cudaStream_t st);
+// out [n_limbs][N]: uniform residues mod q_r, r = 0..n_limbs-1 (rejection sampling)
+void launch_sample_uniform(uint64_t seed, const KCtx& k, int n_limbs, uint64_t* d_out, cudaStream_t st);
 
 }  // namespace ckks
 

@@ -768,6 +768,50 @@ __global__ void k_encrypt_pw(KCtx c, const u64* __restrict__ pkb, const u64* __r
         c1[n] = addmod(mulmod_barrett(vv, __ldg(a + n), lc), e1[n], lc.q);
     }
 }
+// KeyGen pointwise step over the L+K limbs of QP: se = [2][M][N] (s, e in EVAL); pkb = e - a*s; the secret key keeps
+// only its Q limbs.  grid.y = limb
+__global__ void k_keygen_pw(KCtx c, const u64* __restrict__ se, const u64* __restrict__ a, u64* __restrict__ sk,
+                            u64* __restrict__ pkb, int L, int M) {
+    const u32 N = 1u << c.logN;
+    const int r = blockIdx.y;
+    const LimbC lc = c.limbs[r];
+    const u64* s = se + (size_t)r * N;
+    const u64* e = se + ((size_t)M + r) * N;
+    const u64* ar = a + (size_t)r * N;
+    u64* br = pkb + (size_t)r * N;
+    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+        const u64 sv = s[n];
+        br[n] = submod(e[n], mulmod_barrett(__ldg(ar + n), sv, lc), lc.q);
+        if (r < L) sk[(size_t)r * N + n] = sv;
+    }
+}
+// ReKeyGen pointwise step: per level-0 digit j and limb r of QP, b_j = pk.b*u + e0 (+ (P mod q_r) * s_old on the limbs
+// of digit j), a_j = pk.a*u + e1.  uee = [dnum][3][M][N] (u, e0, e1 in EVAL).  grid.y = j * M + r
+__global__ void k_rekeygen_pw(KCtx c, const u64* __restrict__ pkb, const u64* __restrict__ pka,
+                              const u64* __restrict__ uee, const u64* __restrict__ sk_old,
+                              const u64* __restrict__ pmod, u64* __restrict__ kb, u64* __restrict__ ka, int L, int M,
+                              int alpha) {
+    const u32 N = 1u << c.logN;
+    const int r = blockIdx.y % M, j = blockIdx.y / M;
+    const LimbC lc = c.limbs[r];
+    const u64* u = uee + (((size_t)j * 3 + 0) * M + r) * N;
+    const u64* e0 = uee + (((size_t)j * 3 + 1) * M + r) * N;
+    const u64* e1 = uee + (((size_t)j * 3 + 2) * M + r) * N;
+    const u64* b = pkb + (size_t)r * N;
+    const u64* a = pka + (size_t)r * N;
+    u64* ob = kb + (size_t)blockIdx.y * N;
+    u64* oa = ka + (size_t)blockIdx.y * N;
+    const bool own = r < L && r >= j * alpha && r < (j + 1) * alpha;  // block-uniform
+    const u64 pm = own ? pmod[r] : 0;
+    const u64* so = sk_old + (size_t)(own ? r : 0) * N;
+    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+        const u64 uv = u[n];
+        u64 bv = addmod(mulmod_barrett(__ldg(b + n), uv, lc), e0[n], lc.q);
+        if (own) bv = addmod(bv, mulmod_barrett(pm, __ldg(so + n), lc), lc.q);
+        ob[n] = bv;
+        oa[n] = addmod(mulmod_barrett(__ldg(a + n), uv, lc), e1[n], lc.q);
+    }
+}
 __global__ void k_decrypt_pw(KCtx c, const u64* __restrict__ ct, const u64* __restrict__ sk, u64* __restrict__ out,
                              int ell) {
     const u32 N = 1u << c.logN;
@@ -1000,6 +1044,13 @@ void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_sm
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee, const u64* pt, u64* ct, int ell,
                        size_t n_ct, cudaStream_t st) {
     k_encrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, pkb, pka, vee, pt, ct, ell);
+}
+void launch_keygen_pw(const KCtx& c, const u64* se, const u64* a, u64* sk, u64* pkb, int L, int M, cudaStream_t st) {
+    k_keygen_pw<<<pw_grid(c, M, 1), 256, 0, st>>>(c, se, a, sk, pkb, L, M);
+}
+void launch_rekeygen_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* uee, const u64* sk_old,
+                        const u64* d_pmod, u64* kb, u64* ka, int L, int M, int alpha, int dnum, cudaStream_t st) {
+    k_rekeygen_pw<<<pw_grid(c, (size_t)dnum * M, 1), 256, 0, st>>>(c, pkb, pka, uee, sk_old, d_pmod, kb, ka, L, M, alpha);
 }
 void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st) {
     k_decrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, ct, sk, out, ell);

@@ -138,6 +138,11 @@ void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64*
                        const u64* pt /*[g][ell][N]*/, u64* ct, int ell, size_t n_ct, cudaStream_t st);
 // decrypt combine: out[g][i] = c0 + c1 * s   (EVAL)
 void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st);
+// key generation: se [2][M][N] EVAL (s, e), a [M][N] -> sk [L][N], pkb [M][N] = e - a*s
+void launch_keygen_pw(const KCtx& c, const u64* se, const u64* a, u64* sk, u64* pkb, int L, int M, cudaStream_t st);
+// uee [dnum][3][M][N] EVAL (u, e0, e1), sk_old [L][N], d_pmod [L] = P mod q_r -> kb, ka [dnum][M][N]
+void launch_rekeygen_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* uee, const u64* sk_old,
+                        const u64* d_pmod, u64* kb, u64* ka, int L, int M, int alpha, int dnum, cudaStream_t st);
 
 const char* kernels_build_info();
 

@@ -406,3 +406,73 @@ def test_end_to_end_golden_round():
     dec1 = cc.Decrypt(to_device_u64(keys[1][0], dev), back).GetRealPackedValue().reshape(-1)[: len(w1)]
     assert np.max(np.abs(dec1 - g["c1_decrypted_values"])) < 2.0 ** -20
     print("e2e max abs err:", np.max(np.abs(dec2 - want)), np.max(np.abs(dec1 - want)))
+
+
+# ---- KeyGen / ReKeyGen on the device
+def _keygen_samples(o, seed):
+    """the oracle's own draws for keygen(seed) (oracle/ppq_oracle.c ppqo_keygen), to inject into the device path"""
+    e = oracle.sample_gauss(seed * 1000003 + 2, o.N)
+    a = np.stack([oracle.sample_uniform(seed * 1000003 + 100 + r, int(o.moduli[r]), o.N) for r in range(o.M)])
+    return e, a
+
+
+def _rekeygen_samples(o, seed):
+    return np.stack([np.stack([oracle.sample_ternary(seed * 7919 + 10 * j + 1, o.N),
+                               oracle.sample_gauss(seed * 7919 + 10 * j + 2, o.N),
+                               oracle.sample_gauss(seed * 7919 + 10 * j + 3, o.N)]) for j in range(o.dnum)])
+
+
+@pytest.mark.parametrize("kind", ["c1", (12, 5, 3, 45), (13, 4, 2, 50), (16, 18, 3, 59)])
+def test_keygen_and_rekeygen_bit_exact_with_injected_samples(kind):
+    """cc->KeyGen() (client/src/keyGen.cpp:33) and cc->ReKeyGen(sk, pk) (client/src/REkeyGen.cpp:52) through the C ABI
+    against the oracle, the oracle's own sampled polynomials injected."""
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    o, cc = _cc_pair(kind)
+    dev = cc.device
+    got = {}
+    want = {}
+    for seed in (61, 62):
+        s, sk, pkb, pka = o.keygen(seed)
+        e, a = _keygen_samples(o, seed)
+        assert np.array_equal(a, pka)
+        gsk, (gb, ga) = cc.KeyGen(samples=(torch.from_numpy(s).to(dev), torch.from_numpy(e).to(dev), to_device_u64(a, dev)))
+        assert np.array_equal(to_host_u64(gsk), sk[: o.L]), "secret key differs"
+        assert np.array_equal(to_host_u64(gb), pkb), "public key b differs"
+        got[seed] = (gsk, (gb, ga))
+        want[seed] = (sk, pkb, pka)
+    # re-encryption key 61 -> 62
+    kb, ka = o.rekeygen(71, want[61][0], want[62][1], want[62][2])
+    small = _rekeygen_samples(o, 71)
+    rk = cc.ReKeyGen(got[61][0], got[62][1], small=torch.from_numpy(small).to(dev))
+    assert np.array_equal(to_host_u64(rk.b), kb), "rekey B differs"
+    assert np.array_equal(to_host_u64(rk.a), ka), "rekey A differs"
+
+
+@pytest.mark.parametrize("kind", ["c1", (15, 6, 3, 50)])
+def test_device_generated_keys_round_trip(kind):
+    """SURVEY 8(c) self-consistency KAT with nothing from the oracle on the data path: keys, re-encryption key and
+    encryption noise all drawn on the device; Decrypt_{sk2}(ReEncrypt_{1->2}(Enc_{pk1}(m))) ~ m within 2^-20."""
+    o, cc = _cc_pair(kind)
+    sk1, pk1 = cc.KeyGen(seed=101)
+    sk2, pk2 = cc.KeyGen(seed=202)
+    # the draws look like what they should be
+    s = cc.KeyGen(seed=101)[0]
+    assert torch.equal(s, sk1), "KeyGen is not deterministic in its seed"
+    q = [int(m) for m in o.moduli]
+    a = pk1[1].cpu().numpy().view(np.uint64)
+    for r in range(o.M):
+        assert a[r].max() < q[r]
+        assert abs(float(a[r].astype(np.float64).mean()) / q[r] - 0.5) < 0.02
+    assert not torch.equal(pk1[1], pk2[1])
+    rk = cc.ReKeyGen(sk1, pk2, seed=303)
+    rng = np.random.default_rng(5)
+    vals = np.clip(rng.normal(0, 0.05, (2, o.N // 2)), -0.3, 0.3)
+    pt = cc.MakeCKKSPackedPlaintext(vals)
+    ct1 = cc.Encrypt(pk1, pt, seed=404)
+    back1 = cc.Decrypt(sk1, ct1).GetRealPackedValue()
+    assert np.max(np.abs(back1 - vals)) < 2.0 ** -20
+    ct2 = cc.ReEncrypt(ct1, rk)
+    back2 = cc.Decrypt(sk2, ct2).GetRealPackedValue()
+    assert np.max(np.abs(back2 - vals)) < 2.0 ** -20
+    wrong = cc.Decrypt(sk1, ct2).GetRealPackedValue()
+    assert np.max(np.abs(wrong - vals)) > 1.0, "the re-encrypted ciphertext still decrypts under the old key"

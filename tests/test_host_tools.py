@@ -82,6 +82,8 @@ def test_real_openfhe_private_key_parses_to_the_golden_limbs(tools, oracle_c1):
     ("aggregateEncryptedWeights", "<cc_path> <client2_encfile> <client1to2_encfile> <output_aggfile>"),
     ("encryptModelWeights", "<cc_path> <pubkey_path> <input_weights> <output_encfile>"),
     ("decryptModelWeights", "<cc_path> <privkey_path> <input_encfile> <output_file>"),
+    ("keyGen", "<cc_path> <pubkey_out> <privkey_out>"),  # client/src/keyGen.cpp:14-18
+    ("REkeyGen", "<cc.json> <client_privkey.json> <peer_pubkey.json> <rekey_out.json>"),  # client/src/REkeyGen.cpp:15-20
 ])
 def test_argv_contract(tools, tool, usage):
     r = run(os.path.join(tools, tool), "only-one-arg")
@@ -193,3 +195,42 @@ def test_reference_round_through_the_binaries(tools, tmp_path, oracle_c1, ccjson
     json.dump(bad, open(tmp_path / "bad.json", "w"))
     r = run(T("decryptModelWeights"), str(cc_path), str(tmp_path / "c2/private.key"), str(tmp_path / "bad.json"), str(tmp_path / "x.json"))
     assert r.returncode == 1 and "[decrypt] ERROR" in r.stderr
+
+
+@pytest.mark.gpu
+def test_round_with_keys_made_by_the_binaries(tools, tmp_path, ccjson_text):
+    """The whole client + server flow with nothing fabricated: keyGen x2 (client_fns.sh key setup), REkeyGen 1->2,
+    encryptModelWeights, changeCipherDomain, aggregateEncryptedWeights, decryptModelWeights under client 2's key."""
+    g = np.load(os.path.join(GOLD, "weights_golden.npz"))
+    cc_path = tmp_path / "CC.json"
+    cc_path.write_text(ccjson_text)
+    T = lambda name: os.path.join(tools, name)  # noqa: E731
+
+    def ok(seed, *a):
+        r = run(*a, env=dict(os.environ, PPQ_SEED=str(seed)))
+        assert r.returncode == 0, r.stdout + r.stderr
+        return r.stdout
+
+    for c in (1, 2):
+        (tmp_path / f"c{c}").mkdir()
+        out = ok(7000 + c, T("keyGen"), str(cc_path), str(tmp_path / f"c{c}/public.key"), str(tmp_path / f"c{c}/private.key"))
+        assert "[keyGen] Public and Private keys generated" in out and "[keyGen] Keys saved" in out
+        _weights_json(tmp_path / f"c{c}/weights.json", g, c)
+    # the private key file parses with the reader that parses the reference's real OpenFHE key, and is ternary
+    r = run(T("wire_selftest"), "privkey", str(tmp_path / "c1/private.key"))
+    assert r.returncode == 0 and r.stdout.splitlines()[0] == "limbs 4 N 16384 format 0"
+    out = ok(7100, T("REkeyGen"), str(cc_path), str(tmp_path / "c1/private.key"), str(tmp_path / "c2/public.key"), str(tmp_path / "c1/rekey.key"))
+    assert "[ReKeyGen] Re-encryption key generated successfully" in out and "[ReKeyGen] Re-encryption key saved" in out
+    for c in (1, 2):
+        ok(7200 + c, T("encryptModelWeights"), str(cc_path), str(tmp_path / f"c{c}/public.key"), str(tmp_path / f"c{c}/weights.json"),
+           str(tmp_path / f"enc_c{c}.json"))
+    ok(0, T("changeCipherDomain"), str(cc_path), str(tmp_path / "c1/rekey.key"), str(tmp_path / "enc_c1.json"), str(tmp_path / "c1_to_c2.json"))
+    ok(0, T("aggregateEncryptedWeights"), str(cc_path), str(tmp_path / "enc_c2.json"), str(tmp_path / "c1_to_c2.json"), str(tmp_path / "agg.json"))
+    ok(0, T("decryptModelWeights"), str(cc_path), str(tmp_path / "c2/private.key"), str(tmp_path / "agg.json"), str(tmp_path / "dec_c2.json"))
+    w1, w2 = g["c1_sample_values"].astype(np.float64), g["c2_sample_values"].astype(np.float64)
+    dec = json.load(open(tmp_path / "dec_c2.json"))["weights_summary"]
+    vals = np.concatenate([np.asarray(d["values"]) for d in dec])
+    assert np.max(np.abs(vals - (w1 + w2) / 2)) < 2.0 ** -20
+    # wrong-domain guard: REkeyGen refuses a public key file in place of the private key
+    r = run(T("REkeyGen"), str(cc_path), str(tmp_path / "c2/public.key"), str(tmp_path / "c2/public.key"), str(tmp_path / "x.key"))
+    assert r.returncode == 1 and "Error loading Client private key" in r.stderr
