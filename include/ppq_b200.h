@@ -90,6 +90,13 @@ int ppq_reencrypt(ppq_ctx*, const ppq_rekey*, int ell, const uint64_t* d_in, uin
  * aggregateEncryptedWeights.cpp:106): d_acc[g] = d_acc[g] + ReEncrypt(d_in[g]) mod q, canonical. */
 int ppq_reencrypt_accumulate(ppq_ctx*, const ppq_rekey*, int ell, const uint64_t* d_in, uint64_t* d_acc, size_t n,
                              void* stream);
+/* fan-out of the aggregate (the second changeCipherDomain pass, orchestration/server_fns.sh:76-80, generalised
+ * to n_keys target domains): d_outs[k][g] = ReEncrypt(d_in[g], rekeys[k]) for k < n_keys.
+ * rekeys and d_outs are HOST arrays of n_keys handles / device pointers ([n][2][ell][N] each).  The digit
+ * decomposition + ModUp of a ciphertext is independent of the key and is computed once per ciphertext; only the key
+ * inner product and the ModDown run per key.  Results are identical to n_keys ppq_reencrypt calls. */
+int ppq_reencrypt_fanout(ppq_ctx*, const ppq_rekey* const* rekeys, int n_keys, int ell, const uint64_t* d_in,
+                         uint64_t* const* d_outs, size_t n, void* stream);
 /* stage-by-stage views of the key switch (EvalKeySwitchPrecomputeCore / EvalFastKeySwitchCoreExt /
  * ApproxModDown) for parity tests: digits [n][parts][ell+K][N] EVAL canonical, ext [n][2][ell+K][N]. */
 int ppq_ks_modup(ppq_ctx*, int ell, const uint64_t* d_c1 /* [n][ell][N] */, uint64_t* d_digits, size_t n,

@@ -64,6 +64,7 @@ _SIGS = {
     "ppq_encode": (C.c_int, [vp, C.c_int, vp, C.c_size_t, C.c_double, vp, C.c_size_t, vp]),
     "ppq_encrypt": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_size_t, vp]),
     "ppq_sample_encrypt_noise": (C.c_int, [vp, C.c_uint64, vp, C.c_size_t, vp]),
+    "ppq_reencrypt_fanout": (C.c_int, [vp, C.POINTER(vp), C.c_int, C.c_int, vp, C.POINTER(vp), C.c_size_t, vp]),
     "ppq_keygen": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "ppq_sample_keygen": (C.c_int, [vp, C.c_uint64, vp, vp, vp, vp]),
     "ppq_rekeygen": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp]),

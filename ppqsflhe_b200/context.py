@@ -206,6 +206,18 @@ class CryptoContext:
         check(lib().ppq_reencrypt(self.h, rekey.h, ct.ell, _ptr(ct.data), _ptr(out), ct.n, _stream()))
         return CiphertextBatch(out, replace(ct.meta))
 
+    def ReEncryptFanOut(self, ct, rekeys):
+        """[ReEncrypt(ct, rk) for rk in rekeys] with the key-independent ModUp shared (ppq_reencrypt_fanout): the
+        second changeCipherDomain pass of orchestration/server_fns.sh:76-80 for C-1 target domains."""
+        rekeys = list(rekeys)
+        if not rekeys:
+            return []
+        outs = [torch.empty_like(ct.data) for _ in rekeys]
+        hk = (vp * len(rekeys))(*[r.h for r in rekeys])
+        ho = (vp * len(rekeys))(*[_ptr(o) for o in outs])
+        check(lib().ppq_reencrypt_fanout(self.h, hk, len(rekeys), ct.ell, _ptr(ct.data), ho, ct.n, _stream()))
+        return [CiphertextBatch(o, replace(ct.meta)) for o in outs]
+
     def ReEncryptAccumulate(self, ct, rekey, acc):
         """acc += ReEncrypt(ct) (fused ReEncrypt + EvalAdd); acc: CiphertextBatch of the same shape."""
         check(lib().ppq_reencrypt_accumulate(self.h, rekey.h, ct.ell, _ptr(ct.data), _ptr(acc.data), ct.n, _stream()))

@@ -114,6 +114,7 @@ struct ppq_ctx {
 };
 struct ppq_rekey {
     ppq_ctx* ctx = nullptr;
+    int device = 0;  // kept here so that a key may be destroyed after its context
     const u64* b = nullptr;
     const u64* a = nullptr;
     // Q limbs multiplied by P^-1 mod q_i (see launch_scale_key): in place for an uploaded key (stride L+K), a private
@@ -332,6 +333,7 @@ extern "C" int ppq_rekey_upload(ppq_ctx* c, const uint64_t* hb, const uint64_t* 
     CU(cudaMemcpy(k->own_b.p, hb, n * sizeof(u64), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(k->own_a.p, ha, n * sizeof(u64), cudaMemcpyHostToDevice));
     k->ctx = c;
+    k->device = c->device;
     k->b = k->own_b.p;
     k->a = k->own_a.p;
     int rc = rekey_scale_q(c, k.get(), true);
@@ -344,6 +346,7 @@ extern "C" int ppq_rekey_from_device(ppq_ctx* c, const uint64_t* db, const uint6
     CU(cudaSetDevice(c->device));
     std::unique_ptr<ppq_rekey> k(new ppq_rekey);
     k->ctx = c;
+    k->device = c->device;
     k->b = (const u64*)db;
     k->a = (const u64*)da;
     int rc = rekey_scale_q(c, k.get(), false);
@@ -353,7 +356,7 @@ extern "C" int ppq_rekey_from_device(ppq_ctx* c, const uint64_t* db, const uint6
 }
 extern "C" void ppq_rekey_destroy(ppq_rekey* k) {
     if (!k) return;
-    if (k->ctx) cudaSetDevice(k->ctx->device);
+    cudaSetDevice(k->device);
     delete k;
 }
 
@@ -392,16 +395,19 @@ static int get_ks_plan(ppq_ctx* c, int ell, KsPlanDev** out) {
 }
 
 struct WaveLayout {
-    size_t y, dig, extq, extp, per_ct;  // sizes in u64 per ciphertext
+    size_t y, dig, extq, extp, conv, per_ct;  // sizes in u64 per ciphertext
 };
-static WaveLayout wave_layout(const ppq_ctx* c, int ell, int parts) {
+// keep_digits: the digits outlive the ModDown of one key (fan-out to several keys), so the ModDown conversion gets
+// its own buffer instead of reusing theirs
+static WaveLayout wave_layout(const ppq_ctx* c, int ell, int parts, bool keep_digits) {
     const size_t N = c->hp.N, K = c->hp.K, M = ell + K;
     WaveLayout w;
     w.y = (size_t)ell * N;
     w.dig = std::max((size_t)parts * M, (size_t)2 * ell) * N;  // digits, later reused for the ModDown conversion
     w.extq = (size_t)2 * ell * N;
     w.extp = (size_t)2 * K * N;
-    w.per_ct = w.y + w.dig + w.extq + w.extp;
+    w.conv = keep_digits ? (size_t)2 * ell * N : 0;
+    w.per_ct = w.y + w.dig + w.extq + w.extp + w.conv;
     return w;
 }
 static int pick_wave(const ppq_ctx* c, const WaveLayout& w, size_t n) {
@@ -475,10 +481,17 @@ extern "C" const char* ppq_profile_stage_name(int s) {
 }
 
 // shared driver: out[g] = (accumulate ? out[g] : 0) + ReEncrypt(in[g])
-static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64* in, u64* out, size_t n, void* stream,
-                            int accumulate) {
-    if (!c || !rk || !in || !out) return fail(PPQ_EINVAL, "ppq_reencrypt: null argument");
-    if (rk->ctx != c) return fail(PPQ_EINVAL, "ppq_reencrypt: rekey belongs to another context");
+// ReEncrypt of n ciphertexts under n_keys re-encryption keys: outs[k] = ReEncrypt(in, rks[k]).  The digit
+// decomposition + ModUp of a ciphertext (steps 1-3b and the forward ROW pass of the digits) does not depend on the
+// key, so with several keys (the fan-out of the aggregate) it is done once per wave and only the
+// inner product and the ModDown are repeated per key.
+static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, int ell, const u64* in, u64* const* outs,
+                           size_t n, void* stream, int accumulate) {
+    if (!c || !rks || !in || !outs || n_keys < 1) return fail(PPQ_EINVAL, "ppq_reencrypt: null argument");
+    for (int k = 0; k < n_keys; ++k) {
+        if (!rks[k] || !outs[k]) return fail(PPQ_EINVAL, "ppq_reencrypt: null argument");
+        if (rks[k]->ctx != c) return fail(PPQ_EINVAL, "ppq_reencrypt: rekey belongs to another context");
+    }
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt: bad limb count");
     if (n == 0) return PPQ_OK;
     CU(cudaSetDevice(c->device));
@@ -488,18 +501,20 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
     if (rc) return rc;
     const size_t N = c->hp.N;
     const int K = c->hp.K, L = c->hp.L, parts = p->h.parts;
-    const WaveLayout w = wave_layout(c, ell, parts);
+    const bool keep = n_keys > 1;
+    const WaveLayout w = wave_layout(c, ell, parts, keep);
     const int G = pick_wave(c, w, n);
     CU(c->scratch.ensure(w.per_ct * G));
     u64* y = c->scratch.p;
     u64* dig = y + w.y * G;
     u64* extq = dig + w.dig * G;
     u64* extp = extq + w.extq * G;
+    u64* conv = keep ? extp + w.extp * G : dig;
+    const size_t conv_gs = keep ? w.conv : w.dig;
     const size_t ct = (size_t)2 * ell * N;
     for (size_t g0 = 0; g0 < n; g0 += G) {
         const int ng = (int)std::min((size_t)G, n - g0);
         const u64* in_g = in + g0 * ct;
-        u64* out_g = out + g0 * ct;
         const int slot = (int)(c->prof_wave % ppq_ctx::RING);
         cudaEvent_t* ev = c->ev[slot];
         const bool prof = c->prof;
@@ -521,6 +536,12 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         launch_fwd_col_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
         if (prof) cudaEventRecord(ev[4], st);
         // 4. forward ROW pass + inner product with the rekey (+ inverse ROW pass on the P limbs)
+        if (c->ip_split) launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
+        if (prof) cudaEventRecord(ev[5], st);
+        for (int key = 0; key < n_keys; ++key) {
+        const ppq_rekey* rk = rks[key];
+        u64* out_g = outs[key] + g0 * ct;
+        const bool pk = prof && key == n_keys - 1;  // stage events: the shared part + the last key of the wave
         IpArgs ia;
         ia.c1 = in_g + (size_t)ell * N;
         ia.c1_gs = ct;
@@ -541,35 +562,32 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ia.parts = parts;
         ia.alpha = c->hp.alpha;
         if (c->ip_split) {
-            launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
-            if (prof) cudaEventRecord(ev[5], st);
             if (!launch_ip_tma(c->k, ia, ng, st)) return fail(PPQ_EINVAL, "ppq_reencrypt: split inner product needs N >= 2048 and <= 6 digits");
-            if (prof) cudaEventRecord(ev[6], st);
+            if (pk) cudaEventRecord(ev[6], st);
             launch_inv_row(c->k, extp, w.extp, extp, w.extp, p->p_limb.p, 2 * K, ng, st);
-            if (prof) cudaEventRecord(ev[7], st);
+            if (pk) cudaEventRecord(ev[7], st);
         } else {
-            if (prof) cudaEventRecord(ev[5], st);
-            launch_fwd_row_ip(c->k, ia, ng, st);
-            if (prof) {
+            launch_fwd_row_ip(c->k, ia, ng, st);  // reads the digits after their COL pass, leaves them as they are
+            if (pk) {
                 cudaEventRecord(ev[6], st);
                 cudaEventRecord(ev[7], st);
             }
         }
         // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
         launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, 2 * K, ng, st);
-        if (prof) cudaEventRecord(ev[8], st);
-        // 6. ModDown conversion P -> Q (pointwise; the digits buffer is dead: reuse it), then its COL pass
-        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data(), ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
+        if (pk) cudaEventRecord(ev[8], st);
+        // 6. ModDown conversion P -> Q (pointwise; with one key the digits buffer is dead and reused), then its COL pass
+        if (!launch_bconv(c->k, extp, w.extp, conv, conv_gs, p->down_jobs.data(), ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
-        if (!launch_bconv(c->k, extp, w.extp, dig, w.dig, p->down_jobs.data() + ell, ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
+        if (!launch_bconv(c->k, extp, w.extp, conv, conv_gs, p->down_jobs.data() + ell, ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
-        if (prof) cudaEventRecord(ev[9], st);
-        launch_fwd_col_plain(c->k, dig, w.dig, p->conv_ids.p, 2 * ell, ng, st);
-        if (prof) cudaEventRecord(ev[10], st);
+        if (pk) cudaEventRecord(ev[9], st);
+        launch_fwd_col_plain(c->k, conv, conv_gs, p->conv_ids.p, 2 * ell, ng, st);
+        if (pk) cudaEventRecord(ev[10], st);
         // 7. forward ROW pass + (x - conv) P^-1 + c0 (+ running sum)
         MdArgs ma;
-        ma.conv = dig;
-        ma.conv_gs = w.dig;
+        ma.conv = conv;
+        ma.conv_gs = conv_gs;
         ma.extq = extq;
         ma.extq_gs = w.extq;
         ma.ct_in = in_g;
@@ -579,6 +597,7 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
         ma.ell = ell;
         ma.accumulate = accumulate;
         launch_fwd_row_moddown(c->k, ma, ng, st);
+        }  // keys
         if (prof) {
             cudaEventRecord(ev[11], st);
             c->ev_used[slot] = true;
@@ -588,10 +607,25 @@ static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64*
     CU(cudaGetLastError());
     return PPQ_OK;
 }
+static int reencrypt_common(ppq_ctx* c, const ppq_rekey* rk, int ell, const u64* in, u64* out, size_t n, void* stream,
+                            int accumulate) {
+    if (!rk || !out) return fail(PPQ_EINVAL, "ppq_reencrypt: null argument");
+    return reencrypt_multi(c, &rk, 1, ell, in, &out, n, stream, accumulate);
+}
 extern "C" int ppq_reencrypt(ppq_ctx* c, const ppq_rekey* rk, int ell, const uint64_t* in, uint64_t* out, size_t n,
                              void* stream) {
     if (in == out) return fail(PPQ_EINVAL, "ppq_reencrypt: d_out may not alias d_in");
     return reencrypt_common(c, rk, ell, (const u64*)in, (u64*)out, n, stream, 0);
+}
+extern "C" int ppq_reencrypt_fanout(ppq_ctx* c, const ppq_rekey* const* rekeys, int n_keys, int ell, const uint64_t* in,
+                                    uint64_t* const* outs, size_t n, void* stream) {
+    if (!rekeys || !outs || n_keys < 1) return fail(PPQ_EINVAL, "ppq_reencrypt_fanout: null argument");
+    for (int k = 0; k < n_keys; ++k) {
+        if (outs[k] == in) return fail(PPQ_EINVAL, "ppq_reencrypt_fanout: an output may not alias d_in");
+        for (int j = 0; j < k; ++j)
+            if (outs[k] == outs[j]) return fail(PPQ_EINVAL, "ppq_reencrypt_fanout: outputs may not alias each other");
+    }
+    return reencrypt_multi(c, rekeys, n_keys, ell, (const u64*)in, (u64* const*)outs, n, stream, 0);
 }
 extern "C" int ppq_reencrypt_accumulate(ppq_ctx* c, const ppq_rekey* rk, int ell, const uint64_t* in, uint64_t* acc,
                                         size_t n, void* stream) {

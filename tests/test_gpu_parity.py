@@ -476,3 +476,36 @@ def test_device_generated_keys_round_trip(kind):
     assert np.max(np.abs(back2 - vals)) < 2.0 ** -20
     wrong = cc.Decrypt(sk1, ct2).GetRealPackedValue()
     assert np.max(np.abs(wrong - vals)) > 1.0, "the re-encrypted ciphertext still decrypts under the old key"
+
+
+# ---- fan-out of one batch to several target domains
+@pytest.mark.parametrize("kind,ell,n,n_keys", [("c1", 3, 3, 3), ("c1", 4, 2, 2), ((13, 4, 2, 50), 5, 2, 4),
+                                               ((16, 18, 3, 59), 19, 2, 3)])
+def test_reencrypt_fanout_bit_exact(kind, ell, n, n_keys, monkeypatch):
+    """ppq_reencrypt_fanout (shared ModUp, per-key inner product + ModDown) against the oracle's ReEncrypt per key and
+    against separate ppq_reencrypt calls; C1 at ell = 3 is the reference's own fan-out level (uneven digits {q0,q1},{q2})."""
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    for fused in ("0", "1"):
+        monkeypatch.setenv("PPQ_IP_FUSED", fused)
+        o, cc = _cc_pair(kind)
+        rng = np.random.default_rng(41)
+        ct = _rand_ct(rng, o, ell, n)
+        keys = [_rand_key(rng, o) for _ in range(n_keys)]
+        rks = [EvalKey(cc, kb, ka) for kb, ka in keys]
+        batch = CiphertextBatch(to_device_u64(ct, cc.device), CtMeta())
+        outs = cc.ReEncryptFanOut(batch, rks)
+        assert len(outs) == n_keys
+        for k in range(n_keys):
+            got = outs[k].numpy()
+            assert np.array_equal(got, cc.ReEncrypt(batch, rks[k]).numpy()), f"key {k}: differs from ppq_reencrypt"
+            want = o.reencrypt(ell, ct[0], keys[k][0], keys[k][1])
+            assert np.array_equal(got[0], want), f"key {k}: differs from the oracle"
+        assert np.array_equal(batch.numpy(), ct), "input modified"
+        # small waves exercise the per-wave reuse of the digit buffers
+        cc.set_wave(1)
+        outs1 = cc.ReEncryptFanOut(batch, rks)
+        cc.set_wave(0)
+        for k in range(n_keys):
+            assert np.array_equal(outs1[k].numpy(), outs[k].numpy())
+        cc.close()  # the keys outlive their context here: ppq_rekey_destroy must not need it
+        del rks
