@@ -123,6 +123,83 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     for (int k = 0; k < 8; ++k) out[(size_t)(8 * u + k) * n2 + col] = a[k];  // lazy (< 16q): consumed by a ROW pass
 }
 
+// Plain forward COL pass, two adjacent columns per thread (ntt_core.cuh fwd_pass_col2), in place.
+// Measured on B200, C3 (tools/stage_times.py): forward 18.5 -> 17.9 and 12.1 -> 11.5 us/ct (768 -> 700 instructions
+// per 8 points at 3 CTAs of 256 threads per SM); the inverse form (936 -> 888) is no faster (6.8 -> 7.0) and stays off.
+#ifndef PPQ_COL2
+#define PPQ_COL2 1
+#endif
+#ifndef PPQ_COL2_INV
+#define PPQ_COL2_INV 0
+#endif
+#ifndef PPQ_COL2_W
+#define PPQ_COL2_W 8  // column pairs per CTA
+#endif
+#ifndef PPQ_COL2_MINB
+#define PPQ_COL2_MINB 3
+#endif
+template <int S, int W2, bool SAME>
+__global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
+    k_fwd_col2(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids) {
+    __shared__ u64 sm[2 * (W2 << S)];
+    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
+    const u32 w = threadIdx.x % W2, u = threadIdx.x / W2;
+    const u32 col = (blockIdx.x * W2 + w) * 2;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const int limb = limb_ids[y];
+    if (limb < 0) return;  // block-uniform
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    u64* p = data + g * gs + (size_t)y * N + col;
+    u64 a[8], b[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const ulonglong2 v = __ldcs(reinterpret_cast<const ulonglong2*>(p + (size_t)point_of<S - 3>(u, k) * n2));
+        a[k] = v.x;
+        b[k] = v.y;
+    }
+    fwd_pass_col2<S, W2, FWD_COL_IN>(a, b, sm, w, u, tw, lc.q, lc.q2 << 1, PPQ_Z(lc));
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {  // lazy (< 16q): consumed by a ROW pass
+#if PPQ_COL2_ST128
+        *reinterpret_cast<ulonglong2*>(p + (size_t)(8 * u + k) * n2) = make_ulonglong2(a[k], b[k]);
+#else
+        p[(size_t)(8 * u + k) * n2] = a[k];
+        p[(size_t)(8 * u + k) * n2 + 1] = b[k];
+#endif
+    }
+}
+
+template <int S, int W2, bool SAME>
+__global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
+    k_inv_col2(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
+               const u64* __restrict__ scale) {
+    __shared__ u64 sm[2 * (W2 << S)];
+    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
+    const u32 w = threadIdx.x % W2, u = threadIdx.x / W2;
+    const u32 col = (blockIdx.x * W2 + w) * 2;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const int limb = limb_map[y];
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twi + (size_t)limb * N;
+    u64* p = data + g * gs + (size_t)y * N + col;
+    u64 a[8], b[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + (size_t)(8 * u + k) * n2);
+        a[k] = v.x;
+        b[k] = v.y;
+    }
+    const ulonglong2 fs = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * y);
+    const ulonglong2 fw = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * y + 1);
+    inv_pass_col2<S, W2, INV_COL_IN>(a, b, sm, w, u, tw, lc.q, lc.q2 << 1, fs, fw);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        p[(size_t)point_of<S - 3>(u, k) * n2] = canon4(a[k], lc);
+        p[(size_t)point_of<S - 3>(u, k) * n2 + 1] = canon4(b[k], lc);
+    }
+}
+
 template <int S, int W, bool SAME>
 __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
@@ -870,6 +947,17 @@ static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* ds
                            const u64* chat, const int* limb_ids, u64 q_src, int ny, int ng, cudaStream_t st) {
     constexpr int W = ColW<S>::W;
     const int n2 = (1 << c.logN) >> S;
+#if PPQ_COL2
+    if constexpr (MODE == 0 && S == 8) {
+        if (src == dst && src_gs == dst_gs) {
+            constexpr int W2 = PPQ_COL2_W;
+            dim3 grid2(n2 / (2 * W2), ny, ng), block2(W2 << (S - 3));
+            if (n2 == (1 << S)) k_fwd_col2<S, W2, true><<<grid2, block2, 0, st>>>(c, dst, dst_gs, limb_ids);
+            else k_fwd_col2<S, W2, false><<<grid2, block2, 0, st>>>(c, dst, dst_gs, limb_ids);
+            return;
+        }
+    }
+#endif
     dim3 grid(n2 / W, ny, ng), block(W << (S - 3));
     if (n2 == (1 << S))
         k_fwd_col<S, W, MODE, true><<<grid, block, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, chat, limb_ids, q_src);
@@ -904,6 +992,15 @@ void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, 
                     int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n2 = 1 << sp.S2;
+#if PPQ_COL2_INV
+    if (sp.S1 == 8) {
+        constexpr int W2 = PPQ_COL2_W;
+        dim3 grid2(n2 / (2 * W2), n_slots, n_g), block2(W2 << 5);
+        if (sp.S2 == 8) k_inv_col2<8, W2, true><<<grid2, block2, 0, st>>>(c, data, gs, d_limb_map, d_scale4);
+        else k_inv_col2<8, W2, false><<<grid2, block2, 0, st>>>(c, data, gs, d_limb_map, d_scale4);
+        return;
+    }
+#endif
     if (sp.S1 == sp.S2) {
         PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W, true><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
                                     c, data, gs, d_limb_map, d_scale4)));

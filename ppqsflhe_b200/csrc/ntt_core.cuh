@@ -296,6 +296,55 @@ __device__ __forceinline__ void fwd_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
     }
 }
 
+// COL pass over TWO adjacent columns per thread.  Every column of a COL pass uses the same twiddles, so a thread that
+// owns the same 8 rows of two neighbouring columns loads each twiddle once for 16 points, moves its data as 16-byte
+// words (global and shared) and pays the address arithmetic of the pass once: the part of a pass that is not
+// butterflies -- a quarter of k_fwd_col's instructions -- shrinks.
+// Shared tile: two planes [column of the pair][point][pair], 8-byte words (a 16-byte store would want its two values
+// in one aligned register quad, which costs ptxas about three MOVs per store -- the values come out of independent
+// butterflies -- and ptxas fuses two adjacent 8-byte stores back into one).
+template <int LO, int W2, int S>
+__device__ __forceinline__ void sm_store2(const u64 (&a)[8], const u64 (&b)[8], u64* sm, u32 w, u32 u) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        u64* s = sm + (point_of<LO>(u, k) * W2 + w);
+        s[0] = a[k];
+        s[W2 << S] = b[k];
+    }
+}
+template <int LO, int W2, int S>
+__device__ __forceinline__ void sm_load2(u64 (&a)[8], u64 (&b)[8], const u64* sm, u32 w, u32 u) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const u64* s = sm + (point_of<LO>(u, k) * W2 + w);
+        a[k] = s[0];
+        b[k] = s[W2 << S];
+    }
+}
+template <int S, int W2, int BIN>
+__device__ __forceinline__ void fwd_pass_col2(u64 (&a)[8], u64 (&b)[8], u64* sm, u32 w, u32 u,
+                                              const ulonglong2* __restrict__ tw, u64 q, u64 q4, u64 z) {
+    static_assert(S > 6, "two-column COL passes are built for S >= 7");
+    constexpr int LO0 = S - 3;
+    constexpr int LO1 = S - 6;
+    ulonglong2 t[7];
+    fwd_group_tw<S, LO0, S>(t, tw, 1u, u);
+    fwd_group<S, LO0, S, BIN>(a, t, q, q4, z);
+    fwd_group<S, LO0, S, BIN>(b, t, q, q4, z);
+    fwd_group_tw<S, LO1, LO0>(t, tw, 1u, u);
+    sm_store2<LO0, W2, S>(a, b, sm, w, u);
+    __syncthreads();
+    sm_load2<LO1, W2, S>(a, b, sm, w, u);
+    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(a, t, q, q4, z);
+    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(b, t, q, q4, z);
+    fwd_group_tw<S, 0, LO1>(t, tw, 1u, u);
+    sm_store2<LO1, W2, S>(a, b, sm, w, u);  // same words this thread just read: no barrier needed before
+    __syncthreads();
+    sm_load2<0, W2, S>(a, b, sm, w, u);
+    fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(a, t, q, q4, z);
+    fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(b, t, q, q4, z);
+}
+
 // Inverse pass.  In: a[k] = point 8u + k, values < BIN q.  Out: a[k] = point_of<S-3>(u,k), < 8q (< 4q for
 // PPQ_BFLY_V == 0).
 #if PPQ_BFLY_V == 2
@@ -329,6 +378,34 @@ __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
         inv_group_tw<S, LOL, 6>(t, tw, rowfac, u);
         inv_group<S, LOL, 6, B2, FIN>(a, t, q, q4, fin_s, fin_w);
     }
+}
+
+// Inverse COL pass over two adjacent columns per thread (see fwd_pass_col2); FIN as in inv_pass.
+template <int S, int W2, int BIN>
+__device__ __forceinline__ void inv_pass_col2(u64 (&a)[8], u64 (&b)[8], u64* sm, u32 w, u32 u,
+                                              const ulonglong2* __restrict__ tw, u64 q, u64 q4, ulonglong2 fin_s,
+                                              ulonglong2 fin_w) {
+    static_assert(S > 6, "two-column COL passes are built for S >= 7");
+    constexpr int LOL = S - 3;
+    constexpr int LO1 = 3;
+    constexpr int B1 = inv_plan(BIN, 0).out;
+    constexpr int B2 = inv_plan(B1, 3 - LO1).out;
+    ulonglong2 t[7];
+    inv_group_tw<S, 0, 0>(t, tw, 1u, u);
+    inv_group<S, 0, 0, BIN>(a, t, q, q4);
+    inv_group<S, 0, 0, BIN>(b, t, q, q4);
+    sm_store2<0, W2, S>(a, b, sm, w, u);
+    __syncthreads();
+    sm_load2<LO1, W2, S>(a, b, sm, w, u);
+    inv_group_tw<S, LO1, 3>(t, tw, 1u, u);
+    inv_group<S, LO1, 3, B1, false>(a, t, q, q4);
+    inv_group<S, LO1, 3, B1, false>(b, t, q, q4);
+    sm_store2<LO1, W2, S>(a, b, sm, w, u);
+    __syncthreads();
+    sm_load2<LOL, W2, S>(a, b, sm, w, u);
+    inv_group_tw<S, LOL, 6>(t, tw, 1u, u);
+    inv_group<S, LOL, 6, B2, true>(a, t, q, q4, fin_s, fin_w);
+    inv_group<S, LOL, 6, B2, true>(b, t, q, q4, fin_s, fin_w);
 }
 
 }  // namespace ppq
