@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
 // Plain forward COL pass, two adjacent columns per thread (ntt_core.cuh fwd_pass_col2), in place.
 // Measured on B200, C3 (tools/stage_times.py): forward 18.5 -> 17.9 and 12.1 -> 11.5 us/ct (768 -> 700 instructions
 // per 8 points at 3 CTAs of 256 threads per SM); the inverse form (936 -> 888) is no faster (6.8 -> 7.0) and stays off.
+// Only for n1 = 256 (N = 2^15, 2^16): at n1 = 128 the form measured 3 % slower (N = 2^13), at n1 = 512 the same.
 #ifndef PPQ_COL2
 #define PPQ_COL2 1
 #endif
@@ -397,6 +398,63 @@ struct RowGeom {
     static constexpr int THREADS = R * TPT;
     static constexpr int SMEM = R * RowPos<S>::PITCH;
 };
+
+// Plain forward ROW pass over PAIRS of ciphertexts: the same (slot, row) of two ciphertexts uses the same twiddles, so
+// a thread that owns 8 points of both loads every twiddle (and computes its address) once for 16 points.  An odd
+// ciphertext at the end of a CTA's range is paired with itself (both copies are read before either is written).
+// Measured on B200, C3: k_fwd_row_plain 21.0 -> 20.1 us/ct (2304 -> 2064 instructions per 16 points; 80 registers, 6
+// CTAs of 128 threads per SM).
+#ifndef PPQ_ROW_X2
+#define PPQ_ROW_X2 1
+#endif
+#ifndef PPQ_ROW_X2_MINB
+#define PPQ_ROW_X2_MINB 6
+#endif
+#ifndef PPQ_ROW_X2_PAIRS
+#define PPQ_ROW_X2_PAIRS 2  // pairs per CTA
+#endif
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_X2_MINB)
+    k_fwd_row_plain2(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids, int n_g) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[2 * G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const u32 y = blockIdx.z;
+    const int limb = limb_ids[y];
+    if (limb < 0) return;  // block-uniform: slot not to be transformed
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const u32 gend = min((u32)n_g, (blockIdx.y + 1) * (2 * PPQ_ROW_X2_PAIRS));
+    for (u32 g = blockIdx.y * (2 * PPQ_ROW_X2_PAIRS); g < gend; g += 2) {
+        u64* p0 = data + g * gs + (size_t)y * N + (size_t)row * n2;
+        u64* p1 = g + 1 < gend ? p0 + gs : p0;
+        u64 a[8], b[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            a[k] = p0[point_of<S - 3>(u, k)];
+            b[k] = p1[point_of<S - 3>(u, k)];
+        }
+        fwd_pass_x2<S, RowPos<S>, FWD_ROW_IN>(a, b, sm, (u32)G::SMEM, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true, PPQ_Z(lc));
+        if (FwdOut<S, FWD_ROW_IN>::B > 8 && lc.sh >= 28u) {  // block-uniform
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                a[k] = canon16_q(a[k], lc);
+                b[k] = canon16_q(b[k], lc);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                a[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+                b[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(b[k], lc);
+            }
+        }
+        st8(p0 + 8 * u, a);
+        st8(p1 + 8 * u, b);
+    }
+}
 
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
@@ -726,6 +784,79 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     }
 }
 
+// The same over pairs of ciphertexts (see k_fwd_row_plain2): twiddles shared by the two transforms.
+// Measured on B200, C3: 19.1 -> 17.6 us/ct at 5 CTAs per SM (96 registers); 4 CTAs 18.2, 6 CTAs 18.7.
+#ifndef PPQ_MD_X2
+#define PPQ_MD_X2 1
+#endif
+#ifndef PPQ_MD_X2_MINB
+#define PPQ_MD_X2_MINB 5
+#endif
+template <int S>
+__device__ __forceinline__ void moddown_epilogue(u64 (&a)[8], const MdArgs& A, u32 g, size_t off, u32 u, int poly,
+                                                 const LimbC& lc) {
+    u64* o = A.out + g * A.out_gs + off + 8 * u;
+    u64 x[8];
+    ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = x[k] + (lc.q2 << 2) - fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+    if (poly == 0) {
+        ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] += x[k];
+    }
+    if (A.accumulate) {
+        ld8(x, o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] += x[k];
+    }
+    if (lc.sh >= 28u) {  // block-uniform
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = canon16_q(a[k], lc);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = canon_b<16>(a[k], lc);
+    }
+    st8(o, a);
+}
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_MD_X2_MINB) k_fwd_row_moddown2(KCtx c, MdArgs A, int n_g) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[2 * G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const int y = blockIdx.z;
+    const int poly = y / A.ell, i = y % A.ell;
+    const LimbC lc = c.limbs[i];
+    const ulonglong2* tw = c.twf + (size_t)i * N;
+    const size_t off = (size_t)y * N + (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const u32 gend = min((u32)n_g, (blockIdx.y + 1) * (2 * PPQ_ROW_X2_PAIRS));
+    for (u32 g = blockIdx.y * (2 * PPQ_ROW_X2_PAIRS); g < gend; g += 2) {
+        const bool two = g + 1 < gend;  // block-uniform
+        const u32 g1 = two ? g + 1 : g;
+        u64 a[8], b[8];
+        const u64* in0 = A.conv + g * A.conv_gs + off;
+        const u64* in1 = A.conv + g1 * A.conv_gs + off;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            a[k] = ld_stream(in0 + point_of<S - 3>(u, k));
+            b[k] = ld_stream(in1 + point_of<S - 3>(u, k));
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const u32 ge = e ? g1 : g;
+            prefetch_l2(A.extq + ge * A.extq_gs + off + 8 * u);
+            if (poly == 0) prefetch_l2(A.ct_in + ge * A.in_gs + off + 8 * u);
+            if (A.accumulate) prefetch_l2(A.out + ge * A.out_gs + off + 8 * u);
+        }
+        fwd_pass_x2<S, RowPos<S>, FWD_ROW_IN>(a, b, sm, (u32)G::SMEM, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true, PPQ_Z(lc));
+        moddown_epilogue<S>(a, A, g, off, u, poly, lc);
+        if (two) moddown_epilogue<S>(b, A, g1, off, u, poly, lc);  // never twice on one ciphertext: it may accumulate
+    }
+}
+
 // Forward ROW pass + rescale combine (DropLastElementAndScale, then the EvalMult constant folded in).
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_rescale(KCtx c, RsArgs A) {
@@ -977,6 +1108,13 @@ void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
                           cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
+#if PPQ_ROW_X2
+    if (n_g > 1 && sp.S2 == 8) {
+        const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
+        k_fwd_row_plain2<8><<<dim3(n1 / RowGeom<8>::R, by, n_slots), RowGeom<8>::THREADS, 0, st>>>(c, data, gs, d_limb_ids, n_g);
+        return;
+    }
+#endif
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
                                 c, data, gs, d_limb_ids, n_g)));
 }
@@ -1101,6 +1239,13 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
+#if PPQ_MD_X2
+    if (n_g > 1 && sp.S2 == 8) {
+        const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
+        k_fwd_row_moddown2<8><<<dim3(n1 / RowGeom<8>::R, by, 2 * a.ell), RowGeom<8>::THREADS, 0, st>>>(c, a, n_g);
+        return;
+    }
+#endif
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), 2 * a.ell), RowGeom<S>::THREADS, 0, st>>>(c, a, n_g)));
 }
 void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st) {

@@ -345,6 +345,39 @@ __device__ __forceinline__ void fwd_pass_col2(u64 (&a)[8], u64 (&b)[8], u64* sm,
     fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(b, t, q, q4, z);
 }
 
+// Forward pass over the SAME transform (same limb, same row) of two ciphertexts: the twiddles and their addresses are
+// shared; the two tiles live in two shared-memory planes `plane` words apart.
+template <int S, class Pos, int BIN>
+__device__ __forceinline__ void fwd_pass_x2(u64 (&a)[8], u64 (&b)[8], u64* sm, u32 plane, const Pos& pos, u32 u,
+                                            const ulonglong2* __restrict__ tw, u32 rowfac, u64 q, u64 q4, bool guard,
+                                            u64 z) {
+    constexpr int LO0 = S - 3;
+    constexpr int LO1 = cmax(S - 6, 0);
+    ulonglong2 t[7];
+    fwd_group_tw<S, LO0, S>(t, tw, rowfac, u);
+    fwd_group<S, LO0, S, BIN>(a, t, q, q4, z);
+    fwd_group<S, LO0, S, BIN>(b, t, q, q4, z);
+    fwd_group_tw<S, LO1, LO0>(t, tw, rowfac, u);
+    if (guard) pass_sync<Pos>();
+    sm_store<LO0>(a, sm, pos, u);
+    sm_store<LO0>(b, sm + plane, pos, u);
+    pass_sync<Pos>();
+    sm_load<LO1>(a, sm, pos, u);
+    sm_load<LO1>(b, sm + plane, pos, u);
+    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(a, t, q, q4, z);
+    fwd_group<S, LO1, LO0, fwd_bound_after(BIN, 3)>(b, t, q, q4, z);
+    if constexpr (S > 6) {
+        fwd_group_tw<S, 0, LO1>(t, tw, rowfac, u);
+        sm_store<LO1>(a, sm, pos, u);
+        sm_store<LO1>(b, sm + plane, pos, u);
+        pass_sync<Pos>();
+        sm_load<0>(a, sm, pos, u);
+        sm_load<0>(b, sm + plane, pos, u);
+        fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(a, t, q, q4, z);
+        fwd_group<S, 0, LO1, fwd_bound_after(BIN, S - LO1)>(b, t, q, q4, z);
+    }
+}
+
 // Inverse pass.  In: a[k] = point 8u + k, values < BIN q.  Out: a[k] = point_of<S-3>(u,k), < 8q (< 4q for
 // PPQ_BFLY_V == 0).
 #if PPQ_BFLY_V == 2
