@@ -410,6 +410,11 @@ struct RowGeom {
 #ifndef PPQ_ROW_X2_MINB
 #define PPQ_ROW_X2_MINB 6
 #endif
+// The paired kernels are used from N = 2^15 on (measured: C2, N = 2^15, 85.1k -> 87.6k ct/s; C1, N = 2^14 with 27
+// ciphertexts per wave, 130k -> 124k ct/s, so smaller rings keep the one-ciphertext form)
+#ifndef PPQ_X2_MIN_LOGN
+#define PPQ_X2_MIN_LOGN 15
+#endif
 #ifndef PPQ_ROW_X2_PAIRS
 #define PPQ_ROW_X2_PAIRS 2  // pairs per CTA
 #endif
@@ -511,6 +516,45 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
     u64* o = out + g * out_gs + off;
 #pragma unroll
     for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy (< 8q): consumed by k_inv_col
+    }
+}
+
+// Inverse ROW pass over pairs of ciphertexts (see k_fwd_row_plain2).
+// Measured on B200, C3: 6.3 + 4.5 -> 6.0 + 4.3 us/ct.
+#ifndef PPQ_INV_X2
+#define PPQ_INV_X2 1
+#endif
+#ifndef PPQ_INV_X2_MINB
+#define PPQ_INV_X2_MINB 6
+#endif
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_INV_X2_MINB)
+    k_inv_row2(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* __restrict__ limb_map, int n_g) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[2 * G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const u32 y = blockIdx.z;
+    const int limb = limb_map[y];
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twi + (size_t)limb * N;
+    const size_t off = (size_t)y * N + (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const u32 gend = min((u32)n_g, (blockIdx.y + 1) * (2 * PPQ_ROW_X2_PAIRS));
+    for (u32 g = blockIdx.y * (2 * PPQ_ROW_X2_PAIRS); g < gend; g += 2) {
+        const u32 g1 = g + 1 < gend ? g + 1 : g;  // an odd tail is paired with itself (read twice, written twice)
+        u64 a[8], b[8];
+        ld8(a, in + g * in_gs + off + 8 * u);
+        ld8(b, in + g1 * in_gs + off + 8 * u);
+        inv_pass_x2<S, RowPos<S>, INV_ROW_IN>(a, b, sm, (u32)G::SMEM, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true);
+        u64* o0 = out + g * out_gs + off;
+        u64* o1 = out + g1 * out_gs + off;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // lazy (< 8q): consumed by k_inv_col
+            o0[point_of<S - 3>(u, k)] = a[k];
+            o1[point_of<S - 3>(u, k)] = b[k];
+        }
     }
 }
 
@@ -1109,9 +1153,9 @@ void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
 #if PPQ_ROW_X2
-    if (n_g > 1 && sp.S2 == 8) {
+    if (n_g > 1 && c.logN >= PPQ_X2_MIN_LOGN) {
         const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
-        k_fwd_row_plain2<8><<<dim3(n1 / RowGeom<8>::R, by, n_slots), RowGeom<8>::THREADS, 0, st>>>(c, data, gs, d_limb_ids, n_g);
+        PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain2<S><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, data, gs, d_limb_ids, n_g)));
         return;
     }
 #endif
@@ -1123,6 +1167,13 @@ void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t
                     int n_slots, int n_g, cudaStream_t st) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
+#if PPQ_INV_X2
+    if (n_g > 1 && c.logN >= PPQ_X2_MIN_LOGN) {
+        const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
+        PPQ_ROW_DISPATCH(sp.S2, (k_inv_row2<S><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, in, in_gs, out, out_gs, d_limb_map, n_g)));
+        return;
+    }
+#endif
     PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
                                 c, in, in_gs, out, out_gs, d_limb_map, n_g)));
 }
@@ -1240,9 +1291,9 @@ void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
 #if PPQ_MD_X2
-    if (n_g > 1 && sp.S2 == 8) {
+    if (n_g > 1 && c.logN >= PPQ_X2_MIN_LOGN) {
         const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
-        k_fwd_row_moddown2<8><<<dim3(n1 / RowGeom<8>::R, by, 2 * a.ell), RowGeom<8>::THREADS, 0, st>>>(c, a, n_g);
+        PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown2<S><<<dim3(n1 / RowGeom<S>::R, by, 2 * a.ell), RowGeom<S>::THREADS, 0, st>>>(c, a, n_g)));
         return;
     }
 #endif

@@ -413,6 +413,39 @@ __device__ __forceinline__ void inv_pass(u64 (&a)[8], u64* sm, const Pos& pos, u
     }
 }
 
+// Inverse pass over the same transform of two ciphertexts (see fwd_pass_x2).
+template <int S, class Pos, int BIN>
+__device__ __forceinline__ void inv_pass_x2(u64 (&a)[8], u64 (&b)[8], u64* sm, u32 plane, const Pos& pos, u32 u,
+                                            const ulonglong2* __restrict__ tw, u32 rowfac, u64 q, u64 q4, bool guard) {
+    constexpr int LOL = S - 3;
+    constexpr int LO1 = cmin(3, S - 3);
+    constexpr int B1 = inv_plan(BIN, 0).out;
+    constexpr int B2 = inv_plan(B1, 3 - LO1).out;
+    ulonglong2 t[7];
+    inv_group_tw<S, 0, 0>(t, tw, rowfac, u);
+    inv_group<S, 0, 0, BIN>(a, t, q, q4);
+    inv_group<S, 0, 0, BIN>(b, t, q, q4);
+    if (guard) pass_sync<Pos>();
+    sm_store<0>(a, sm, pos, u);
+    sm_store<0>(b, sm + plane, pos, u);
+    pass_sync<Pos>();
+    sm_load<LO1>(a, sm, pos, u);
+    sm_load<LO1>(b, sm + plane, pos, u);
+    inv_group_tw<S, LO1, 3>(t, tw, rowfac, u);
+    inv_group<S, LO1, 3, B1>(a, t, q, q4);
+    inv_group<S, LO1, 3, B1>(b, t, q, q4);
+    if constexpr (S > 6) {
+        sm_store<LO1>(a, sm, pos, u);
+        sm_store<LO1>(b, sm + plane, pos, u);
+        pass_sync<Pos>();
+        sm_load<LOL>(a, sm, pos, u);
+        sm_load<LOL>(b, sm + plane, pos, u);
+        inv_group_tw<S, LOL, 6>(t, tw, rowfac, u);
+        inv_group<S, LOL, 6, B2>(a, t, q, q4);
+        inv_group<S, LOL, 6, B2>(b, t, q, q4);
+    }
+}
+
 // Inverse COL pass over two adjacent columns per thread (see fwd_pass_col2); FIN as in inv_pass.
 template <int S, int W2, int BIN>
 __device__ __forceinline__ void inv_pass_col2(u64 (&a)[8], u64 (&b)[8], u64* sm, u32 w, u32 u,
