@@ -257,11 +257,18 @@ __device__ __forceinline__ u64 madw(u32 a, u32 b, u64 c) {
     asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
     return r;
 }
+template <bool LAZY = false>
 __device__ __forceinline__ u64 kara_reduce(u64 A0, u64 A2, u64 A1, const LimbC& lc) {
     const u64 mid = A1 - A0 - A2;  // = sum (y1 c0 + y0 c1) < 2^64: exact modulo 2^64
     unsigned __int128 t = (unsigned __int128)A0 + ((unsigned __int128)mid << 30) + ((unsigned __int128)A2 << 60);
-    return barrett128((u64)(t >> 64), (u64)t, lc);
+    return LAZY ? barrett128_lazy3((u64)(t >> 64), (u64)t, lc) : barrett128((u64)(t >> 64), (u64)t, lc);
 }
+// Conversions of narrow digits write values in [0, 3q): every consumer is a forward COL pass, which reads < 4q
+// (FWD_COL_IN); two conditional subtractions less per output (k_bconv2: 89 -> 79 instructions per output).
+#ifndef PPQ_BCONV_LAZY
+#define PPQ_BCONV_LAZY 1
+#endif
+static_assert(!PPQ_BCONV_LAZY || FWD_COL_IN >= 3, "lazy conversions need a COL pass that accepts 3q");
 
 // Constants of one launch travel as a kernel parameter (constant bank, read with LDC/ULDC by a block-uniform index):
 // per-thread LDG of conversion constants saturated L1TEX (74 % in profiles/r01_notes.md) without doing useful work.
@@ -325,7 +332,7 @@ __global__ void __launch_bounds__(256)
                 A2 += mulw(y1[i], cc.y);
                 A1 += mulw(KEEP ? ys[i] : y0[i] + y1[i], cc.z);
             }
-            r += kara_reduce(A0, A2, A1, lc);
+            r += kara_reduce<(PPQ_BCONV_LAZY && NS <= 8)>(A0, A2, A1, lc);
         }
         if (NS > 8) r = canon4(r, lc);  // at most 4 chunks
         out[(size_t)J.dst_slot * N] = r;
@@ -384,7 +391,7 @@ __global__ void __launch_bounds__(256)
             }
         }
         *reinterpret_cast<ulonglong2*>(out + (size_t)J.dst_slot * N) =
-            make_ulonglong2(kara_reduce(A0[0], A2[0], A1[0], lc), kara_reduce(A0[1], A2[1], A1[1], lc));
+            make_ulonglong2(kara_reduce<PPQ_BCONV_LAZY>(A0[0], A2[0], A1[0], lc), kara_reduce<PPQ_BCONV_LAZY>(A0[1], A2[1], A1[1], lc));
     }
 }
 

@@ -122,6 +122,20 @@ __device__ __forceinline__ u64 barrett128(u64 hi, u64 lo, const LimbC& c) {
     return csub(r, c.q);
 }
 
+// The same without the two conditional subtractions: (hi,lo) mod q + {0,1,2} q, i.e. a value in [0, 3q).  For results
+// that feed a forward COL pass (which accepts < 4q): ten instructions less per reduction.
+__device__ __forceinline__ u64 barrett128_lazy3(u64 hi, u64 lo, const LimbC& c) {
+    u64 x1;
+    if (c.sh >= 32u) {
+        const u32 s = c.sh - 32u;
+        const u32 l1 = (u32)(lo >> 32), h0 = (u32)hi, h1 = (u32)(hi >> 32);
+        x1 = ((u64)__funnelshift_r(h0, h1, s) << 32) | __funnelshift_r(l1, h0, s);
+    } else {
+        x1 = (hi << (64u - c.sh)) | (lo >> c.sh);
+    }
+    return lo - __umul64hi(x1, c.mu) * c.q;
+}
+
 // a * b mod q, canonical, for a < 2^63, b < q (no precomputed companion).
 __device__ __forceinline__ u64 mulmod_barrett(u64 a, u64 b, const LimbC& c) {
     return barrett128(__umul64hi(a, b), a * b, c);
