@@ -481,6 +481,12 @@ extern "C" const char* ppq_profile_stage_name(int s) {
 }
 
 // shared driver: out[g] = (accumulate ? out[g] : 0) + ReEncrypt(in[g])
+// digits may reach k_ip_tma in [0, 2q) when a sum of `parts` products of a 2q-bounded digit and a key residue stays
+// inside the Barrett range (kernels.cu, PPQ_DIGITS_LAZY)
+#ifndef PPQ_DIGITS_LAZY
+#define PPQ_DIGITS_LAZY 1
+#endif
+#define PPQ_DIGITS_LAZY_OK(parts) (PPQ_DIGITS_LAZY && (parts) <= 4)
 // ReEncrypt of n ciphertexts under n_keys re-encryption keys: outs[k] = ReEncrypt(in, rks[k]).  The digit
 // decomposition + ModUp of a ciphertext (steps 1-3b and the forward ROW pass of the digits) does not depend on the
 // key, so with several keys (the fan-out of the aggregate) it is done once per wave and only the
@@ -536,7 +542,7 @@ static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, 
         launch_fwd_col_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
         if (prof) cudaEventRecord(ev[4], st);
         // 4. forward ROW pass + inner product with the rekey (+ inverse ROW pass on the P limbs)
-        if (c->ip_split) launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
+        if (c->ip_split) launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st, PPQ_DIGITS_LAZY_OK(parts));
         if (prof) cudaEventRecord(ev[5], st);
         for (int key = 0; key < n_keys; ++key) {
         const ppq_rekey* rk = rks[key];

@@ -35,7 +35,8 @@ void launch_sample_uniform(uint64_t seed, const KCtx& k, int n_limbs, uint64_t* 
 }  // namespace ckks
 
 // plain forward ROW pass over [n_g] blocks of n_slots polys; slots whose limb id is negative are skipped
+// lazy2: results may stay in [0, 2q) (digits for the key inner product; only the paired kernels honour it)
 void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
-                          cudaStream_t st);
+                          cudaStream_t st, bool lazy2 = false);
 
 }  // namespace ppq

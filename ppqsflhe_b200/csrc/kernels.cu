@@ -425,7 +425,7 @@ struct RowGeom {
 #ifndef PPQ_ROW_X2_PAIRS
 #define PPQ_ROW_X2_PAIRS 2  // pairs per CTA
 #endif
-template <int S>
+template <int S, bool LAZY2>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_X2_MINB)
     k_fwd_row_plain2(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids, int n_g) {
     typedef RowGeom<S> G;
@@ -453,8 +453,8 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_X2_MINB)
         if (FwdOut<S, FWD_ROW_IN>::B > 8 && lc.sh >= 28u) {  // block-uniform
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                a[k] = canon16_q(a[k], lc);
-                b[k] = canon16_q(b[k], lc);
+                a[k] = LAZY2 ? canon16_q_lazy2(a[k], lc) : canon16_q(a[k], lc);
+                b[k] = LAZY2 ? canon16_q_lazy2(b[k], lc) : canon16_q(b[k], lc);
             }
         } else {
 #pragma unroll
@@ -694,7 +694,18 @@ struct KaraAcc {
         A1 += mulw(x.sum, y.sum);
     }
     __device__ __forceinline__ u64 reduce(const LimbC& lc) const { return kara_reduce(A0, A2, A1, lc); }
+    __device__ __forceinline__ u64 reduce_lazy3(const LimbC& lc) const { return kara_reduce<true>(A0, A2, A1, lc); }
 };
+// Q-limb results of the inner product go to the ModDown epilogue, which tolerates [0, 3q) (x' + 8q - conv' + c0 + sum
+// < 13q, canonicalised there); P-limb results feed an inverse ROW pass that wants canonical data.
+#ifndef PPQ_IP_LAZY
+#define PPQ_IP_LAZY 1
+#endif
+// Digits written by the plain forward ROW pass for the inner product may stay in [0, 2q): one conditional subtraction
+// less per point.  Then a sum of `parts` products is < 2 parts q^2, inside Barrett's range 2^(64+sh) for parts <= 4.
+#ifndef PPQ_DIGITS_LAZY
+#define PPQ_DIGITS_LAZY 1
+#endif
 
 #ifndef PPQ_IP_MINB
 #define PPQ_IP_MINB 4  // 64 registers, 4 CTAs/SM (5: 14.3, 6: 15.0 us/ct)
@@ -778,8 +789,13 @@ __global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, i
             a0.mac(dx, Kara3(ka.x, Kara3::Packed{}));
             a1.mac(dy, Kara3(ka.y, Kara3::Packed{}));
         }
-        *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
-        *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
+        if (PPQ_IP_LAZY && r < A.ell) {  // block-uniform
+            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce_lazy3(lc), b1.reduce_lazy3(lc));
+            *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce_lazy3(lc), a1.reduce_lazy3(lc));
+        } else {
+            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
+            *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
+        }
     }
 }
 
@@ -1156,13 +1172,18 @@ void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_p
 }
 
 void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
-                          cudaStream_t st) {
+                          cudaStream_t st, bool lazy2) {
+    (void)lazy2;
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
 #if PPQ_ROW_X2
     if (n_g > 1 && c.logN >= PPQ_X2_MIN_LOGN) {
         const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
-        PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain2<S><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, data, gs, d_limb_ids, n_g)));
+        if (lazy2) {
+            PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain2<S, true><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, data, gs, d_limb_ids, n_g)));
+        } else {
+            PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain2<S, false><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, data, gs, d_limb_ids, n_g)));
+        }
         return;
     }
 #endif

@@ -156,6 +156,13 @@ __device__ __forceinline__ u64 canon16_q(u64 x, const LimbC& c) {
     return csub(x - (u64)k * c.q, c.q);
 }
 
+// the same without the final conditional subtraction: [0, 16q) -> [0, 2q)
+__device__ __forceinline__ u64 canon16_q_lazy2(u64 x, const LimbC& c) {
+    const u32 xs = (u32)(x >> (c.sh - 27u));
+    const u32 k = __umulhi(xs, (u32)(c.mu >> 32)) >> 27;
+    return x - (u64)k * c.q;
+}
+
 __device__ __forceinline__ u64 addmod(u64 a, u64 b, u64 q) { return csub(a + b, q); }
 __device__ __forceinline__ u64 submod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }
 
