@@ -84,5 +84,41 @@ def full(path):
         print(f"| `{short(r[idx['Kernel Name']])}` | " + " | ".join(cells) + f" | {st} |")
 
 
+def traffic(path, n_cts=54, tag=""):
+    """One wave of ReEncrypt (15 launches in pipeline order, as captured by `--launch-skip 15 --launch-count 15` on
+    tools/stage_times.py --clients 1 --reps 1) -> profiles/ncu_traffic.json layout: DRAM bytes per ct and stage."""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    seq = []
+    for r in data:
+        b = 0.0
+        for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            b += float(r[idx[k]].replace(",", "")) * mult[units[idx[k]]]
+        seq.append((short(r[idx["Kernel Name"]]), b))
+    # rotate so that the wave starts at its first kernel (the inverse ROW pass that follows a ModDown pass)
+    names = [n for n, _ in seq]
+    start = next(i for i in range(len(seq)) if names[i].startswith("k_inv_row") and names[i - 1].startswith("k_fwd_row_moddown"))
+    seq = seq[start:] + seq[:start]
+    end = next(i for i in range(len(seq)) if seq[i][0].startswith("k_fwd_row_moddown"))
+    seq = seq[: end + 1]  # exactly one wave
+    stages = ["k_inv_row(c1)", "k_inv_col(c1,scale)", "k_bconv(modup)", "k_fwd_col(modup)", "k_fwd_row(modup)",
+              "k_ip_tma|k_fwd_row_ip", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
+              "k_fwd_row_moddown"]
+    per = dict.fromkeys(stages, 0.0)
+    n_cts = int(n_cts)
+    si, prev = -1, None
+    for n, b in seq:  # consecutive launches of the same kernel family (the conversions) belong to one stage
+        fam = n.split("<")[0]
+        if fam != prev or not fam.startswith("k_bconv"):
+            si += 1
+        prev = fam
+        per[stages[si]] += b / n_cts
+    print(json.dumps({"c3": {"wave_cts": n_cts, "source": tag or path, "dram_bytes_per_ct": per}}, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])
