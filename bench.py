@@ -107,8 +107,40 @@ class ClockSampler:
     def __init__(self, index):
         self.index = index
         self.p = None
+        self.nv = []       # NVML samples taken by a thread of this process: they start at once, so that a timed
+        self.nv_stop = None  # region shorter than nvidia-smi's start-up (8 GPUs: ~0.1 s) still gets its samples
+        self.nv_thread = None
+
+    def _nvml_loop(self, h, pynvml):
+        bits = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+        while not self.nv_stop.is_set():
+            try:
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+                pw = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.nv.append((float(sm), float(mx), pw, {n for n, b in bits.items() if int(r) & b}))
+            except Exception:
+                return
+            self.nv_stop.wait(0.02)
 
     def start(self):
+        try:
+            import threading
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            pr = torch.cuda.get_device_properties(self.index)
+            bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            self.nv_stop = threading.Event()
+            self.nv_thread = threading.Thread(target=self._nvml_loop, args=(h, pynvml), daemon=True)
+            self.nv_thread.start()
+        except Exception:
+            self.nv_thread = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                        "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -116,16 +148,26 @@ class ClockSampler:
             self.p = None
 
     def stop(self):
-        if self.p is None:
+        if self.nv_thread is not None:
+            self.nv_stop.set()
+            self.nv_thread.join(timeout=2)
+        if self.p is None and not self.nv:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.05)
-        self.p.terminate()
-        try:
-            out, _ = self.p.communicate(timeout=5)
-        except Exception:
-            self.p.kill()
-            out = ""
+        out = ""
+        if self.p is not None:
+            time.sleep(0.05)
+            self.p.terminate()
+            try:
+                out, _ = self.p.communicate(timeout=5)
+            except Exception:
+                self.p.kill()
+                out = ""
         sm, mx, pw, reasons = [], [], [], set()
+        for a, b, c, r in self.nv:
+            sm.append(a)
+            mx.append(b)
+            pw.append(c)
+            reasons |= r
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in out.splitlines():
             f = [x.strip() for x in line.split(",")]
