@@ -509,3 +509,30 @@ def test_reencrypt_fanout_bit_exact(kind, ell, n, n_keys, monkeypatch):
             assert np.array_equal(outs1[k].numpy(), outs[k].numpy())
         cc.close()  # the keys outlive their context here: ppq_rekey_destroy must not need it
         del rks
+
+
+@pytest.mark.parametrize("kind", [(15, 3, 2, 50), (16, 6, 3, 59)])
+def test_paired_row_kernels_odd_waves(kind):
+    """From N = 2^15 on the ROW passes take ciphertexts in pairs (k_fwd_row_plain2, k_fwd_row_moddown2, k_inv_row2), an odd
+    one at the end of a CTA's range paired with itself: waves of 1, 2, 3, 5 and 7 ciphertexts must give the same
+    ciphertexts, with and without the fused EvalAdd, and ciphertext 6 (the self-paired tail) must match the oracle."""
+    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(77)
+    ell, n = o.L, 7
+    ct = _rand_ct(rng, o, ell, n)
+    kb, ka = _rand_key(rng, o)
+    rk = EvalKey(cc, kb, ka)
+    b = CiphertextBatch(to_device_u64(ct, cc.device), CtMeta())
+    start = _rand_ct(rng, o, ell, n)
+    ref = cc.ReEncrypt(b, rk).numpy()
+    assert np.array_equal(ref[6], o.reencrypt(ell, ct[6], kb, ka))
+    q = o.moduli[:ell].astype(object).reshape(1, 1, ell, 1)
+    want_acc = ((ref.astype(object) + start.astype(object)) % q).astype(np.uint64)
+    for wave in (1, 2, 3, 5, 7):
+        cc.set_wave(wave)
+        assert np.array_equal(cc.ReEncrypt(b, rk).numpy(), ref), f"wave {wave}"
+        acc = CiphertextBatch(to_device_u64(start, cc.device), CtMeta())
+        cc.ReEncryptAccumulate(b, rk, acc)
+        assert np.array_equal(acc.numpy(), want_acc), f"wave {wave} (accumulate)"
+    cc.set_wave(0)
