@@ -151,12 +151,49 @@ int ppq_sample_keygen(ppq_ctx*, uint64_t seed, int64_t* d_s, int64_t* d_e, uint6
 int ppq_rekeygen(ppq_ctx*, const uint64_t* d_sk_old, const uint64_t* d_pkb, const uint64_t* d_pka,
                  const int64_t* d_small, uint64_t* d_kb, uint64_t* d_ka, void* stream);
 
+/* ---- C-client aggregation: sum over clients of cc->ReEncrypt(ct_c, reKey_c) per ciphertext slot, i.e.
+ *      changeCipherDomain.cpp:105 applied to every client's file followed by the EvalAdd chain of
+ *      aggregateEncryptedWeights.cpp:106 (the reference hard-codes two clients; SURVEY.md 8 rows a1+a2, e).
+ *      The result is BIT-IDENTICAL to ppq_reencrypt + ppq_eval_add per client, but the linear tail of ApproxModDown
+ *      (base conversion P->Q of the integer lifts, forward NTT, subtraction, +c0) is applied to sums: the conversion
+ *      once per group of up to 8 clients, the 2*ell forward NTTs once per slot in ppq_agg_finish.
+ *      d_in: one client's [n_slots][2][ell][N]; d_out: [n_slots][2][ell][N], canonical.  finish resets the handle. */
+typedef struct ppq_agg ppq_agg;
+int ppq_agg_create(ppq_ctx*, int ell, size_t n_slots, ppq_agg** out);
+int ppq_agg_add(ppq_agg*, const ppq_rekey*, const uint64_t* d_in, void* stream);
+int ppq_agg_finish(ppq_agg*, uint64_t* d_out, void* stream);
+size_t ppq_agg_count(const ppq_agg*); /* clients added since the last finish */
+void ppq_agg_destroy(ppq_agg*);
+
+/* ---- cross-GPU sum of per-rank partial aggregates (SURVEY.md 8 rows b, e): one process (or thread) per GPU, clients
+ *      sharded over ranks, ONE ncclReduce(ncclUint64, ncclSum) of canonical residues (< 2^60, so up to 15 ranks
+ *      cannot wrap) + a mod-q kernel on the root.  NCCL is bound at first use (dlopen of libnccl.so.2).
+ *      ppq_comm_unique_id: rank 0 makes the 128-byte id and hands it to the other ranks by any means;
+ *      ppq_comm_from_nccl wraps a communicator the host already owns (ncclComm_t passed as void*, not destroyed). */
+typedef struct ppq_comm ppq_comm;
+int ppq_comm_unique_id(uint8_t* id128);
+int ppq_comm_init(ppq_ctx*, int world, int rank, const uint8_t* id128, ppq_comm** out);
+int ppq_comm_from_nccl(void* nccl_comm, int world, int rank, int device, ppq_comm** out);
+void ppq_comm_destroy(ppq_comm*);
+/* d_acc [n][2][ell][N] in place: the sum lands on `root` (root < 0: on every rank), canonical */
+int ppq_reduce_across_ranks(ppq_ctx*, ppq_comm*, int ell, uint64_t* d_acc, size_t n, int root, void* stream);
+
 /* ---- host-buffer convenience (the call a drop-in server makes once every client's upload has arrived):
  *      h_cts[client] -> [n_slots][2][ell][N] in host memory (pinned for full PCIe rate); rekeys[n_clients];
- *      h_acc [n_slots][2][ell][N] = sum over clients of ReEncrypt(ct, rekey[client]).  Uploads are double
- *      buffered against the kernels.  Synchronous. */
+ *      h_acc [n_slots][2][ell][N] = sum over clients of ReEncrypt(ct, rekey[client]) (ppq_agg_* inside).  Uploads
+ *      are double buffered against the kernels; device buffers, streams and events live in the context and are
+ *      reused from call to call.  Synchronous.
+ *      _ranks: this rank's clients only; the per-rank sums are combined with ppq_reduce_across_ranks and h_acc is
+ *      written on `root` (may be NULL elsewhere); n_clients may be 0 on a rank.
+ *      ppq_copy_ceiling_host: the same uploads and download on the same streams without any kernel -- what the
+ *      box's host->device path allows (bench.py reports e2e against it). */
 int ppq_reencrypt_aggregate_host(ppq_ctx*, const ppq_rekey* const* rekeys, int ell, const uint64_t* const* h_cts,
                                  size_t n_clients, size_t n_slots, uint64_t* h_acc);
+int ppq_reencrypt_aggregate_host_ranks(ppq_ctx*, ppq_comm*, int root, const ppq_rekey* const* rekeys, int ell,
+                                       const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                       uint64_t* h_acc);
+int ppq_copy_ceiling_host(ppq_ctx*, int ell, const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                          uint64_t* h_acc);
 
 /* ---- per-stage device timing of the key-switch pipeline (CUDA events on the caller's stream).
  *      stage s < PPQ_PROFILE_STAGES: see ppq_profile_stage_name.  ms / launches: arrays of that length. */
@@ -164,6 +201,8 @@ int ppq_reencrypt_aggregate_host(ppq_ctx*, const ppq_rekey* const* rekeys, int e
 int ppq_profile_enable(ppq_ctx*, int on);
 int ppq_profile_read(ppq_ctx*, double* ms, uint64_t* launches, int reset);
 const char* ppq_profile_stage_name(int stage);
+/* kernels launched by the library since it was loaded (bench.py's gpu_launches) */
+uint64_t ppq_launch_count(void);
 
 #ifdef __cplusplus
 }

@@ -9,7 +9,7 @@ from ._capi import LIB_PATH, PPQError, build, lib  # noqa: F401
 
 def __getattr__(name):  # torch is imported lazily so that `build()` works without touching CUDA
     if name in ("CryptoContext", "CiphertextBatch", "PlaintextBatch", "EvalKey", "CtMeta", "to_device_u64",
-                "to_host_u64"):
+                "to_host_u64", "Aggregator", "Communicator"):
         from . import context
         return getattr(context, name)
     raise AttributeError(name)

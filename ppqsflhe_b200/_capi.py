@@ -71,6 +71,20 @@ _SIGS = {
     "ppq_decrypt_core": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_size_t, vp]),
     "ppq_decode": (C.c_int, [vp, C.c_int, vp, C.c_double, vp, C.c_size_t, vp]),
     "ppq_reencrypt_aggregate_host": (C.c_int, [vp, C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
+    "ppq_agg_create": (C.c_int, [vp, C.c_int, C.c_size_t, C.POINTER(vp)]),
+    "ppq_agg_add": (C.c_int, [vp, vp, vp, vp]),
+    "ppq_agg_finish": (C.c_int, [vp, vp, vp]),
+    "ppq_agg_count": (C.c_size_t, [vp]),
+    "ppq_agg_destroy": (None, [vp]),
+    "ppq_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "ppq_comm_init": (C.c_int, [vp, C.c_int, C.c_int, C.c_char_p, C.POINTER(vp)]),
+    "ppq_comm_from_nccl": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
+    "ppq_comm_destroy": (None, [vp]),
+    "ppq_reduce_across_ranks": (C.c_int, [vp, vp, C.c_int, vp, C.c_size_t, C.c_int, vp]),
+    "ppq_reencrypt_aggregate_host_ranks": (C.c_int, [vp, vp, C.c_int, C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_size_t,
+                                                     C.c_size_t, vp]),
+    "ppq_copy_ceiling_host": (C.c_int, [vp, C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
+    "ppq_launch_count": (C.c_uint64, []),
     "ppq_profile_enable": (C.c_int, [vp, C.c_int]),
     "ppq_profile_read": (C.c_int, [vp, f64p, u64p, C.c_int]),
     "ppq_profile_stage_name": (C.c_char_p, [C.c_int]),

@@ -123,6 +123,73 @@ class EvalKey:
             self.h = None
 
 
+class Aggregator:
+    """Running sum over clients of ReEncrypt(ct_c, rk_c) per ciphertext slot (ppq_agg_*): the reference's
+    changeCipherDomain (server/src/changeCipherDomain.cpp:105) on every client's file followed by the EvalAdd chain of
+    aggregateEncryptedWeights (server/src/aggregateEncryptedWeights.cpp:106), generalised from 2 to C clients.
+    Bit-identical to cc.ReEncrypt + cc.EvalAdd per client; the linear tail of ModDown runs on sums."""
+
+    def __init__(self, cc, ell, n_slots):
+        self.cc, self.ell, self.n_slots = cc, int(ell), int(n_slots)
+        h = vp()
+        check(lib().ppq_agg_create(cc.h, self.ell, self.n_slots, C.byref(h)))
+        self.h = h
+
+    def add(self, ct, rekey):
+        if ct.n != self.n_slots or ct.ell != self.ell:
+            raise ValueError("Aggregator.add: batch shape differs from the aggregator's")
+        check(lib().ppq_agg_add(self.h, rekey.h, _ptr(ct.data), _stream()))
+        return self
+
+    @property
+    def count(self):
+        return int(lib().ppq_agg_count(self.h))
+
+    def finish(self, out=None, meta=None):
+        if out is None:
+            out = self.cc.empty_cts(self.n_slots, self.ell)
+        check(lib().ppq_agg_finish(self.h, _ptr(out), _stream()))
+        return CiphertextBatch(out, meta if meta is not None else CtMeta())
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().ppq_agg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+class Communicator:
+    """One NCCL communicator per rank for the cross-GPU sum (ppq_comm_*, ppq_reduce_across_ranks).  The 128-byte id
+    made on rank 0 travels through whatever channel the host has (bench.py: torch.distributed broadcast)."""
+
+    def __init__(self, cc, world, rank, unique_id):
+        self.cc, self.world, self.rank = cc, int(world), int(rank)
+        h = vp()
+        check(lib().ppq_comm_init(cc.h, self.world, self.rank, bytes(unique_id), C.byref(h)))
+        self.h = h
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        check(lib().ppq_comm_unique_id(buf))
+        return buf.raw
+
+    def reduce(self, acc, root=0):
+        """acc: CiphertextBatch of canonical partial sums, summed in place onto `root` (root < 0: every rank)."""
+        check(lib().ppq_reduce_across_ranks(self.cc.h, self.h, acc.ell, _ptr(acc.data), acc.n, int(root), _stream()))
+        return acc
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().ppq_comm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
 class CryptoContext:
     def __init__(self, handle, device):
         self.h = handle

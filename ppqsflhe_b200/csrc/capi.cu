@@ -1,6 +1,8 @@
 // capi.cu -- the C ABI of libppq_b200.so (include/ppq_b200.h): context/key/scratch management and the
 // orchestration of kernel launches for each reference-facing operation.  No CPU fallback: every compute entry
 // point needs a CUDA device and fails loudly otherwise.
+#include <dlfcn.h>
+
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -98,19 +100,19 @@ struct ppq_ctx {
     ckks::Tables fft;
     int wave = 0;
     bool ip_split = true;  // inner product as k_fwd_row_plain + k_ip_tma + k_inv_row (PPQ_IP_FUSED=1: one fused kernel)
-    // per-stage CUDA-event profiling of the key-switch pipeline (ppq_profile_*)
-    static const int NSTAGE = 11, RING = 64;
+    // per-stage CUDA-event profiling of the key-switch pipeline (ppq_profile_*): a chain of events on the launching
+    // stream; the time between two consecutive marks is attributed to the stage named by the later one
+    static const int NSTAGE = 11;
     bool prof = false;
-    cudaEvent_t ev[RING][NSTAGE + 1] = {};
-    bool ev_made = false, ev_used[RING] = {};
-    unsigned long long prof_wave = 0;
+    struct Mark { int stage; cudaEvent_t ev; };  // stage -1 starts a chain
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    std::vector<Mark> marks;
     double prof_ms[NSTAGE] = {};
     unsigned long long prof_launches[NSTAGE] = {};
-    ~ppq_ctx() {
-        if (ev_made)
-            for (int i = 0; i < RING; ++i)
-                for (int j = 0; j <= NSTAGE; ++j) cudaEventDestroy(ev[i][j]);
-    }
+    struct HostPath;
+    HostPath* hostpath = nullptr;  // persistent buffers / streams of ppq_reencrypt_aggregate_host
+    ~ppq_ctx();
 };
 struct ppq_rekey {
     ppq_ctx* ctx = nullptr;
@@ -432,36 +434,45 @@ static int pick_wave(const ppq_ctx* c, const WaveLayout& w, size_t n) {
     return (int)g;
 }
 
-static void prof_collect(ppq_ctx* c, int slot) {
-    if (!c->ev_used[slot]) return;
-    cudaEventSynchronize(c->ev[slot][ppq_ctx::NSTAGE]);
-    for (int s = 0; s < ppq_ctx::NSTAGE; ++s) {
+static void prof_collect(ppq_ctx* c) {
+    if (c->marks.empty()) return;
+    cudaEventSynchronize(c->marks.back().ev);
+    for (size_t i = 1; i < c->marks.size(); ++i) {
+        const int s = c->marks[i].stage;
+        if (s < 0) continue;
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, c->ev[slot][s], c->ev[slot][s + 1]) == cudaSuccess) {
+        if (cudaEventElapsedTime(&ms, c->marks[i - 1].ev, c->marks[i].ev) == cudaSuccess) {
             c->prof_ms[s] += ms;
             c->prof_launches[s] += 1;
         }
     }
-    c->ev_used[slot] = false;
+    c->marks.clear();
+    c->ev_used = 0;
+}
+// stage < 0: start of a chain (before the first launch of a call); stage >= 0: the launches since the previous mark
+static void prof_mark(ppq_ctx* c, cudaStream_t st, int stage) {
+    if (!c->prof) return;
+    if (c->ev_used >= 8192) prof_collect(c);
+    if (c->ev_used == c->ev_pool.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        c->ev_pool.push_back(e);
+    }
+    cudaEvent_t e = c->ev_pool[c->ev_used++];
+    cudaEventRecord(e, st);
+    c->marks.push_back({stage, e});
 }
 extern "C" int ppq_profile_enable(ppq_ctx* c, int on) {
     if (!c) return fail(PPQ_EINVAL, "null");
     CU(cudaSetDevice(c->device));
-    if (on && !c->ev_made) {
-        for (int i = 0; i < ppq_ctx::RING; ++i)
-            for (int j = 0; j <= ppq_ctx::NSTAGE; ++j) CU(cudaEventCreate(&c->ev[i][j]));
-        c->ev_made = true;
-    }
-    if (c->ev_made)
-        for (int i = 0; i < ppq_ctx::RING; ++i) prof_collect(c, i);
+    prof_collect(c);
     c->prof = on != 0;
     return PPQ_OK;
 }
 extern "C" int ppq_profile_read(ppq_ctx* c, double* ms, uint64_t* launches, int reset) {
     if (!c || !ms || !launches) return fail(PPQ_EINVAL, "null");
     CU(cudaSetDevice(c->device));
-    if (c->ev_made)
-        for (int i = 0; i < ppq_ctx::RING; ++i) prof_collect(c, i);
+    prof_collect(c);
     for (int s = 0; s < ppq_ctx::NSTAGE; ++s) {
         ms[s] = c->prof_ms[s];
         launches[s] = c->prof_launches[s];
@@ -472,11 +483,13 @@ extern "C" int ppq_profile_read(ppq_ctx* c, double* ms, uint64_t* launches, int 
     }
     return PPQ_OK;
 }
+extern "C" uint64_t ppq_launch_count(void) { return (uint64_t)kernels_launch_count(); }
 extern "C" const char* ppq_profile_stage_name(int s) {
     static const char* names[ppq_ctx::NSTAGE] = {"k_inv_row(c1)",      "k_inv_col(c1,scale)", "k_bconv(modup)",
                                                  "k_fwd_col(modup)",   "k_fwd_row(modup)",    "k_ip_tma|k_fwd_row_ip",
                                                  "k_inv_row(P)",       "k_inv_col(P,scale)",  "k_bconv(moddown)",
                                                  "k_fwd_col(moddown)", "k_fwd_row_moddown"};
+    // (ppq_agg_*: stage 8 is k_bconv_wide once per group of clients, stages 9-10 run once per ppq_agg_finish)
     return (s >= 0 && s < ppq_ctx::NSTAGE) ? names[s] : "";
 }
 
@@ -521,33 +534,27 @@ static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, 
     for (size_t g0 = 0; g0 < n; g0 += G) {
         const int ng = (int)std::min((size_t)G, n - g0);
         const u64* in_g = in + g0 * ct;
-        const int slot = (int)(c->prof_wave % ppq_ctx::RING);
-        cudaEvent_t* ev = c->ev[slot];
-        const bool prof = c->prof;
-        if (prof) {
-            prof_collect(c, slot);
-            cudaEventRecord(ev[0], st);
-        }
+        prof_mark(c, st, -1);
         // 1-2. c1 -> COEFF, scaled by N^-1 (D_j/q_i)^-1
         launch_inv_row(c->k, in_g + (size_t)ell * N, ct, y, w.y, p->c1_limb.p, ell, ng, st);
-        if (prof) cudaEventRecord(ev[1], st);
+        prof_mark(c, st, 0);
         launch_inv_col(c->k, y, w.y, p->c1_limb.p, p->c1_scale.p, ell, ng, st);
-        if (prof) cudaEventRecord(ev[2], st);
+        prof_mark(c, st, 1);
         // 3. ModUp: approximate basis switch of every digit to its complementary limbs (pointwise)
         for (const auto& d : p->digits)
             if (!launch_bconv(c->k, y, w.y, dig, w.dig, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, ng, st))
                 return fail(PPQ_EINVAL, "digit wider than 32 limbs");
-        if (prof) cudaEventRecord(ev[3], st);
+        prof_mark(c, st, 2);
         // 3b. forward COL pass of the converted limbs (the digit's own limbs stay as they are in c1)
         launch_fwd_col_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
-        if (prof) cudaEventRecord(ev[4], st);
+        prof_mark(c, st, 3);
         // 4. forward ROW pass + inner product with the rekey (+ inverse ROW pass on the P limbs)
         if (c->ip_split) launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st, PPQ_DIGITS_LAZY_OK(parts));
-        if (prof) cudaEventRecord(ev[5], st);
+        prof_mark(c, st, 4);
         for (int key = 0; key < n_keys; ++key) {
         const ppq_rekey* rk = rks[key];
         u64* out_g = outs[key] + g0 * ct;
-        const bool pk = prof && key == n_keys - 1;  // stage events: the shared part + the last key of the wave
+        if (key > 0) prof_mark(c, st, -1);
         IpArgs ia;
         ia.c1 = in_g + (size_t)ell * N;
         ia.c1_gs = ct;
@@ -569,27 +576,24 @@ static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, 
         ia.alpha = c->hp.alpha;
         if (c->ip_split) {
             if (!launch_ip_tma(c->k, ia, ng, st)) return fail(PPQ_EINVAL, "ppq_reencrypt: split inner product needs N >= 2048 and <= 6 digits");
-            if (pk) cudaEventRecord(ev[6], st);
+            prof_mark(c, st, 5);
             launch_inv_row(c->k, extp, w.extp, extp, w.extp, p->p_limb.p, 2 * K, ng, st);
-            if (pk) cudaEventRecord(ev[7], st);
+            prof_mark(c, st, 6);
         } else {
             launch_fwd_row_ip(c->k, ia, ng, st);  // reads the digits after their COL pass, leaves them as they are
-            if (pk) {
-                cudaEventRecord(ev[6], st);
-                cudaEventRecord(ev[7], st);
-            }
+            prof_mark(c, st, 5);
         }
         // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
         launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, 2 * K, ng, st);
-        if (pk) cudaEventRecord(ev[8], st);
+        prof_mark(c, st, 7);
         // 6. ModDown conversion P -> Q (pointwise; with one key the digits buffer is dead and reused), then its COL pass
         if (!launch_bconv(c->k, extp, w.extp, conv, conv_gs, p->down_jobs.data(), ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
         if (!launch_bconv(c->k, extp, w.extp, conv, conv_gs, p->down_jobs.data() + ell, ell, p->h.down_chat.data(), c->h_limbs.data(), K, ng, st))
             return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
-        if (pk) cudaEventRecord(ev[9], st);
+        prof_mark(c, st, 8);
         launch_fwd_col_plain(c->k, conv, conv_gs, p->conv_ids.p, 2 * ell, ng, st);
-        if (pk) cudaEventRecord(ev[10], st);
+        prof_mark(c, st, 9);
         // 7. forward ROW pass + (x - conv) P^-1 + c0 (+ running sum)
         MdArgs ma;
         ma.conv = conv;
@@ -603,12 +607,8 @@ static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, 
         ma.ell = ell;
         ma.accumulate = accumulate;
         launch_fwd_row_moddown(c->k, ma, ng, st);
+        prof_mark(c, st, 10);
         }  // keys
-        if (prof) {
-            cudaEventRecord(ev[11], st);
-            c->ev_used[slot] = true;
-            c->prof_wave++;
-        }
     }
     CU(cudaGetLastError());
     return PPQ_OK;
@@ -969,51 +969,428 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     return PPQ_OK;
 }
 
+// ------------------------------------------------------------------------------------------- aggregation (deferred ModDown)
+// sum_c ReEncrypt(ct_c, rk_c) for the ciphertexts of one slot, bit-identical to re-encrypting every client's
+// ciphertext and adding the results (changeCipherDomain.cpp:105 followed by aggregateEncryptedWeights.cpp:106), with
+// the LINEAR tail of ApproxModDown taken out of the per-client loop:
+//   ReEncrypt(ct)_poly = c0[poly==0] + (x - NTT(conv(u))) * P^-1,   x = <digits, key> on the Q limbs,
+//   u_k = canonical iNTT of the P limbs times (P/p_k)^-1,  conv(u)_i = sum_k u_k [P/p_k]_{q_i}  (no correction).
+// Modulo q_i both the NTT and conv are linear (conv in the integer lifts u_k), so
+//   sum_c ReEncrypt(ct_c) = sum_c (c0_c + x_c P^-1)  -  NTT( sum_k (sum_c u_{k,c}) [P/p_k]_{q_i} P^-1 ).
+// Per client only the non-linear part runs (ModUp, inner product, inverse NTT of the P limbs); the inner product
+// adds its Q-limb results and c0 into accE; the conversion runs once per `group` <= 8 clients on the integer sum of
+// their u (k_bconv_wide) into accW; ppq_agg_finish runs the 2*ell forward NTTs once per slot.
+struct ppq_agg {
+    ppq_ctx* ctx = nullptr;
+    int ell = 0;
+    size_t n_slots = 0;
+    DevBuf<u64> accE, accW, ring;  // [n_slots][2*ell][N] each; ring: [group][n_slots][2K][N] COEFF u of the open group
+    int group = 8, in_group = 0;
+    size_t count = 0;     // clients added since the last finish
+    bool w_valid = false; // accW holds a sum
+    bool legacy = false;  // shapes the split inner product does not cover: plain ppq_reencrypt_accumulate into accE
+};
+
+extern "C" int ppq_agg_create(ppq_ctx* c, int ell, size_t n_slots, ppq_agg** out) {
+    if (!c || !out) return fail(PPQ_EINVAL, "ppq_agg_create: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_agg_create: bad limb count");
+    if (n_slots < 1 || n_slots > 32768) return fail(PPQ_EINVAL, "ppq_agg_create: 1..32768 slots");
+    CU(cudaSetDevice(c->device));
+    std::unique_ptr<ppq_agg> a(new ppq_agg);
+    a->ctx = c;
+    a->ell = ell;
+    a->n_slots = n_slots;
+    const size_t N = c->hp.N, K = c->hp.K;
+    a->legacy = !c->ip_split || K > 16;
+    int grp = 8;
+    if (const char* e = std::getenv("PPQ_AGG_GROUP")) grp = std::atoi(e);
+    a->group = grp < 1 ? 1 : grp > 8 ? 8 : grp;
+    CU(a->accE.ensure(n_slots * 2 * ell * N));
+    if (!a->legacy) {
+        CU(a->accW.ensure(n_slots * 2 * ell * N));
+        CU(a->ring.ensure((size_t)a->group * n_slots * 2 * K * N));
+    }
+    *out = a.release();
+    return PPQ_OK;
+}
+extern "C" void ppq_agg_destroy(ppq_agg* a) {
+    if (!a) return;
+    cudaSetDevice(a->ctx->device);
+    delete a;
+}
+extern "C" size_t ppq_agg_count(const ppq_agg* a) { return a ? a->count : 0; }
+
+static int agg_flush(ppq_agg* a, KsPlanDev* p, cudaStream_t st) {
+    ppq_ctx* c = a->ctx;
+    if (a->in_group == 0) return PPQ_OK;
+    const size_t N = c->hp.N;
+    const int K = c->hp.K, ell = a->ell;
+    const size_t ext_gs = (size_t)2 * K * N, ring_stride = a->n_slots * ext_gs, ct = (size_t)2 * ell * N;
+    prof_mark(c, st, -1);
+    for (int poly = 0; poly < 2; ++poly)
+        if (!launch_bconv_wide(c->k, a->ring.p, ext_gs, ring_stride, a->in_group, a->accW.p, ct, a->w_valid ? 0 : 1,
+                               p->down_jobs.data() + (size_t)poly * ell, ell, p->h.down_chat.data(), c->h_limbs.data(), K,
+                               (int)a->n_slots, st))
+            return fail(PPQ_EINVAL, "ppq_agg: more than 16 auxiliary limbs");
+    prof_mark(c, st, 8);
+    a->w_valid = true;
+    a->in_group = 0;
+    return PPQ_OK;
+}
+
+extern "C" int ppq_agg_add(ppq_agg* a, const ppq_rekey* rk, const uint64_t* d_in, void* stream) {
+    if (!a || !rk || !d_in) return fail(PPQ_EINVAL, "ppq_agg_add: null argument");
+    ppq_ctx* c = a->ctx;
+    if (rk->ctx != c) return fail(PPQ_EINVAL, "ppq_agg_add: rekey belongs to another context");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ell = a->ell;
+    const size_t N = c->hp.N, n = a->n_slots;
+    const size_t ct = (size_t)2 * ell * N;
+    if (a->legacy) {
+        if (a->count == 0) CU(cudaMemsetAsync(a->accE.p, 0, n * ct * sizeof(u64), st));
+        int rc = reencrypt_common(c, rk, ell, (const u64*)d_in, a->accE.p, n, stream, 1);
+        if (rc == PPQ_OK) a->count++;
+        return rc;
+    }
+    KsPlanDev* p;
+    int rc = get_ks_plan(c, ell, &p);
+    if (rc) return rc;
+    const int K = c->hp.K, L = c->hp.L, parts = p->h.parts, M = ell + K;
+    WaveLayout w;  // only the ModUp half needs wave scratch: COEFF c1 and the digits
+    w.y = (size_t)ell * N;
+    w.dig = (size_t)parts * M * N;
+    w.extq = w.extp = w.conv = 0;
+    w.per_ct = w.y + w.dig;
+    const int G = pick_wave(c, w, n);
+    CU(c->scratch.ensure(w.per_ct * G));
+    u64* y = c->scratch.p;
+    u64* dig = y + w.y * G;
+    const size_t ext_gs = (size_t)2 * K * N;
+    u64* ring_e = a->ring.p + (size_t)a->in_group * n * ext_gs;
+    const u64* in = (const u64*)d_in;
+    for (size_t g0 = 0; g0 < n; g0 += G) {
+        const int ng = (int)std::min((size_t)G, n - g0);
+        const u64* in_g = in + g0 * ct;
+        u64* extp = ring_e + g0 * ext_gs;
+        prof_mark(c, st, -1);
+        launch_inv_row(c->k, in_g + (size_t)ell * N, ct, y, w.y, p->c1_limb.p, ell, ng, st);
+        prof_mark(c, st, 0);
+        launch_inv_col(c->k, y, w.y, p->c1_limb.p, p->c1_scale.p, ell, ng, st);
+        prof_mark(c, st, 1);
+        for (const auto& d : p->digits)
+            if (!launch_bconv(c->k, y, w.y, dig, w.dig, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, ng, st))
+                return fail(PPQ_EINVAL, "digit wider than 32 limbs");
+        prof_mark(c, st, 2);
+        launch_fwd_col_plain(c->k, dig, w.dig, p->dig_ids.p, parts * M, ng, st);
+        prof_mark(c, st, 3);
+        launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * M, ng, st, PPQ_DIGITS_LAZY_OK(parts));
+        prof_mark(c, st, 4);
+        IpArgs ia;
+        ia.c1 = in_g + (size_t)ell * N;
+        ia.c1_gs = ct;
+        ia.digits = dig;
+        ia.dig_gs = w.dig;
+        ia.key_b = rk->b;
+        ia.key_a = rk->a;
+        ia.key_qb = rk->qb;
+        ia.key_qa = rk->qa;
+        ia.key_q_stride = rk->q_stride;
+        ia.extq = nullptr;
+        ia.extq_gs = 0;
+        ia.extp = extp;
+        ia.extp_gs = ext_gs;
+        ia.ell = ell;
+        ia.K = K;
+        ia.L = L;
+        ia.parts = parts;
+        ia.alpha = c->hp.alpha;
+        ia.agg = a->count == 0 ? 1 : 2;
+        ia.acc = a->accE.p + g0 * ct;
+        ia.acc_gs = ct;
+        ia.c0 = in_g;
+        ia.c0_gs = ct;
+        if (!launch_ip_tma(c->k, ia, ng, st)) return fail(PPQ_EINVAL, "ppq_agg_add: unsupported shape");
+        prof_mark(c, st, 5);
+        launch_inv_row(c->k, extp, ext_gs, extp, ext_gs, p->p_limb.p, 2 * K, ng, st);
+        prof_mark(c, st, 6);
+        launch_inv_col(c->k, extp, ext_gs, p->p_limb.p, p->p_scale.p, 2 * K, ng, st);
+        prof_mark(c, st, 7);
+    }
+    a->in_group++;
+    a->count++;
+    if (a->in_group == a->group) rc = agg_flush(a, p, st);
+    if (rc == PPQ_OK) CU(cudaGetLastError());
+    return rc;
+}
+
+extern "C" int ppq_agg_finish(ppq_agg* a, uint64_t* d_out, void* stream) {
+    if (!a || !d_out) return fail(PPQ_EINVAL, "ppq_agg_finish: null argument");
+    if (a->count == 0) return fail(PPQ_EINVAL, "ppq_agg_finish: nothing was added");
+    ppq_ctx* c = a->ctx;
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ell = a->ell;
+    const size_t N = c->hp.N, n = a->n_slots, ct = (size_t)2 * ell * N;
+    if (a->legacy) {
+        CU(cudaMemcpyAsync(d_out, a->accE.p, n * ct * sizeof(u64), cudaMemcpyDeviceToDevice, st));
+        a->count = 0;
+        return PPQ_OK;
+    }
+    KsPlanDev* p;
+    int rc = get_ks_plan(c, ell, &p);
+    if (rc) return rc;
+    rc = agg_flush(a, p, st);
+    if (rc) return rc;
+    prof_mark(c, st, -1);
+    launch_fwd_col_plain(c->k, a->accW.p, ct, p->conv_ids.p, 2 * ell, (int)n, st);
+    prof_mark(c, st, 9);
+    MdArgs ma;
+    ma.conv = a->accW.p;
+    ma.conv_gs = ct;
+    ma.extq = a->accE.p;
+    ma.extq_gs = ct;
+    ma.ct_in = nullptr;  // c0 is already inside accE
+    ma.in_gs = 0;
+    ma.out = (u64*)d_out;
+    ma.out_gs = ct;
+    ma.ell = ell;
+    ma.accumulate = 0;
+    launch_fwd_row_moddown(c->k, ma, (int)n, st);
+    prof_mark(c, st, 10);
+    a->count = 0;
+    a->w_valid = false;
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+
+// ------------------------------------------------------------------------------------------- cross-GPU sum (NCCL)
+// NCCL is bound at first use with dlopen: inside a process that already carries a libnccl.so.2 (torch's) that copy is
+// the one used; a plain C++ host gets the system library.  No link-time dependency, no second copy.
+namespace {
+struct Nccl {
+    void* h = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, char[128], int) = nullptr;  // ncclUniqueId is passed BY VALUE (128-byte struct)
+    int (*CommDestroy)(void*) = nullptr;
+    int (*Reduce)(const void*, void*, size_t, int, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+struct NcclId { char internal[128]; };
+typedef int (*InitRankFn)(void**, int, NcclId, int);
+Nccl g_nccl;
+int nccl_load() {
+    if (g_nccl.h) return PPQ_OK;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(PPQ_ECUDA, std::string("cannot load libnccl.so.2: ") + dlerror());
+    Nccl n;
+    n.h = h;
+    n.GetUniqueId = (int (*)(void*))dlsym(h, "ncclGetUniqueId");
+    n.CommInitRank = (int (*)(void**, int, char[128], int))dlsym(h, "ncclCommInitRank");
+    n.CommDestroy = (int (*)(void*))dlsym(h, "ncclCommDestroy");
+    n.Reduce = (int (*)(const void*, void*, size_t, int, int, int, void*, cudaStream_t))dlsym(h, "ncclReduce");
+    n.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(h, "ncclAllReduce");
+    n.GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+    if (!n.GetUniqueId || !n.CommInitRank || !n.CommDestroy || !n.Reduce || !n.AllReduce || !n.GetErrorString)
+        return fail(PPQ_ECUDA, "libnccl.so.2 lacks an expected symbol");
+    g_nccl = n;
+    return PPQ_OK;
+}
+const int kNcclUint64 = 5, kNcclSum = 0;  // ncclDataType_t / ncclRedOp_t values of nccl.h (stable ABI since 2.0)
+}  // namespace
+#define NC(call)                                                                                          \
+    do {                                                                                                  \
+        int e_ = (call);                                                                                  \
+        if (e_ != 0) return fail(PPQ_ECUDA, std::string(#call) + ": " + g_nccl.GetErrorString(e_));       \
+    } while (0)
+
+struct ppq_comm {
+    void* comm = nullptr;  // ncclComm_t
+    int world = 1, rank = 0, device = 0;
+    bool owned = false;
+};
+extern "C" int ppq_comm_unique_id(uint8_t* id128) {
+    if (!id128) return fail(PPQ_EINVAL, "ppq_comm_unique_id: null");
+    if (int rc = nccl_load()) return rc;
+    NC(g_nccl.GetUniqueId(id128));
+    return PPQ_OK;
+}
+extern "C" int ppq_comm_init(ppq_ctx* c, int world, int rank, const uint8_t* id128, ppq_comm** out) {
+    if (!c || !id128 || !out || world < 1 || rank < 0 || rank >= world) return fail(PPQ_EINVAL, "ppq_comm_init: bad arguments");
+    if (world > 15) return fail(PPQ_EINVAL, "ppq_comm_init: a u64 sum of canonical residues (< 2^60) holds for at most 15 ranks");
+    if (int rc = nccl_load()) return rc;
+    CU(cudaSetDevice(c->device));
+    std::unique_ptr<ppq_comm> m(new ppq_comm);
+    NcclId id;
+    std::memcpy(id.internal, id128, 128);
+    NC(((InitRankFn)g_nccl.CommInitRank)(&m->comm, world, id, rank));
+    m->world = world;
+    m->rank = rank;
+    m->device = c->device;
+    m->owned = true;
+    *out = m.release();
+    return PPQ_OK;
+}
+extern "C" int ppq_comm_from_nccl(void* nccl_comm, int world, int rank, int device, ppq_comm** out) {
+    if (!nccl_comm || !out || world < 1 || world > 15 || rank < 0 || rank >= world) return fail(PPQ_EINVAL, "ppq_comm_from_nccl: bad arguments");
+    if (int rc = nccl_load()) return rc;
+    std::unique_ptr<ppq_comm> m(new ppq_comm);
+    m->comm = nccl_comm;
+    m->world = world;
+    m->rank = rank;
+    m->device = device;
+    *out = m.release();
+    return PPQ_OK;
+}
+extern "C" void ppq_comm_destroy(ppq_comm* m) {
+    if (!m) return;
+    if (m->owned && m->comm && g_nccl.CommDestroy) {
+        cudaSetDevice(m->device);
+        g_nccl.CommDestroy(m->comm);
+    }
+    delete m;
+}
+// sum of the ranks' canonical partial aggregates, in place on `root` (all ranks when root < 0), then mod q
+extern "C" int ppq_reduce_across_ranks(ppq_ctx* c, ppq_comm* m, int ell, uint64_t* d_acc, size_t n, int root,
+                                       void* stream) {
+    if (!c || !m || !d_acc) return fail(PPQ_EINVAL, "ppq_reduce_across_ranks: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reduce_across_ranks: bad limb count");
+    if (root >= m->world) return fail(PPQ_EINVAL, "ppq_reduce_across_ranks: bad root");
+    if (n == 0) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cnt = n * 2 * (size_t)ell * c->hp.N;
+    if (m->world > 1) {
+        if (root < 0) NC(g_nccl.AllReduce(d_acc, d_acc, cnt, kNcclUint64, kNcclSum, m->comm, st));
+        else NC(g_nccl.Reduce(d_acc, d_acc, cnt, kNcclUint64, kNcclSum, root, m->comm, st));
+    }
+    if (m->world > 1 && (root < 0 || root == m->rank)) {
+        const size_t step = 65535 / (2 * (size_t)ell) ? 65535 / (2 * (size_t)ell) : 1;
+        for (size_t s0 = 0; s0 < n; s0 += step)
+            launch_finalize_mod(c->k, (u64*)d_acc + s0 * 2 * ell * c->hp.N, ell, std::min(step, n - s0), st);
+    }
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+
 // ------------------------------------------------------------------------------------------- host-buffer path
+// Persistent per-context resources of the host-buffer calls: two device upload buffers, the device aggregate, two
+// streams and the hand-over events.  Created on first use, reused while the shape fits, freed with the context:
+// nothing is allocated inside a steady-state call and no early return can leak.
+struct ppq_ctx::HostPath {
+    DevBuf<u64> in[2], out;
+    cudaStream_t sc = nullptr, sx = nullptr;
+    cudaEvent_t up[2] = {}, done[2] = {};
+    bool made = false;
+    ppq_agg* agg = nullptr;
+    ~HostPath() {
+        if (agg) ppq_agg_destroy(agg);
+        if (made) {
+            for (int i = 0; i < 2; ++i) {
+                cudaEventDestroy(up[i]);
+                cudaEventDestroy(done[i]);
+            }
+            cudaStreamDestroy(sc);
+            cudaStreamDestroy(sx);
+        }
+    }
+};
+ppq_ctx::~ppq_ctx() {
+    delete hostpath;
+    for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+}
+
+static int hostpath_get(ppq_ctx* c, int ell, size_t n_slots, ppq_ctx::HostPath** out) {
+    if (!c->hostpath) c->hostpath = new ppq_ctx::HostPath;
+    ppq_ctx::HostPath* h = c->hostpath;
+    if (!h->made) {
+        CU(cudaStreamCreateWithFlags(&h->sc, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&h->sx, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            CU(cudaEventCreateWithFlags(&h->up[i], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->done[i], cudaEventDisableTiming));
+        }
+        h->made = true;
+    }
+    const size_t blk = (size_t)2 * ell * c->hp.N * n_slots;
+    CU(h->in[0].ensure(blk));
+    CU(h->in[1].ensure(blk));
+    CU(h->out.ensure(blk));
+    if (h->agg && (h->agg->ell != ell || h->agg->n_slots != n_slots || h->agg->count != 0)) {
+        ppq_agg_destroy(h->agg);
+        h->agg = nullptr;
+    }
+    if (!h->agg)
+        if (int rc = ppq_agg_create(c, ell, n_slots, &h->agg)) return rc;
+    *out = h;
+    return PPQ_OK;
+}
+
+// copy_only: the same uploads/downloads on the same streams without any kernel (the box's copy ceiling for e2e)
+static int aggregate_host_impl(ppq_ctx* c, ppq_comm* comm, int root, const ppq_rekey* const* rekeys, int ell,
+                               const uint64_t* const* h_cts, size_t n_clients, size_t n_slots, uint64_t* h_acc,
+                               bool copy_only) {
+    if (!c || !h_cts || (!rekeys && !copy_only)) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: bad limb count");
+    if (!n_slots) return PPQ_OK;
+    if (!n_clients && !comm) return PPQ_OK;
+    for (size_t cl = 0; cl < n_clients; ++cl)
+        if (!h_cts[cl] || (!copy_only && !rekeys[cl])) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null client entry");
+    const bool is_root = !comm || root < 0 || comm->rank == root;
+    if (is_root && !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null output");
+    CU(cudaSetDevice(c->device));
+    ppq_ctx::HostPath* h;
+    if (int rc = hostpath_get(c, ell, n_slots, &h)) return rc;
+    const size_t blk = (size_t)2 * ell * c->hp.N * n_slots;
+    int rc = PPQ_OK;
+    cudaError_t ce = cudaSuccess;
+#define HP(call) do { if (rc == PPQ_OK && ce == cudaSuccess) ce = (call); } while (0)
+    // double-buffered upload: client c+1 is copied while client c is re-encrypted
+    for (size_t cl = 0; cl < n_clients && rc == PPQ_OK && ce == cudaSuccess; ++cl) {
+        const int b = (int)(cl & 1);
+        if (cl >= 2) HP(cudaStreamWaitEvent(h->sc, h->done[b], 0));
+        HP(cudaMemcpyAsync(h->in[b].p, h_cts[cl], blk * sizeof(u64), cudaMemcpyHostToDevice, h->sc));
+        HP(cudaEventRecord(h->up[b], h->sc));
+        HP(cudaStreamWaitEvent(h->sx, h->up[b], 0));
+        if (!copy_only && rc == PPQ_OK && ce == cudaSuccess) rc = ppq_agg_add(h->agg, rekeys[cl], (const uint64_t*)h->in[b].p, h->sx);
+        HP(cudaEventRecord(h->done[b], h->sx));
+    }
+    if (!copy_only && rc == PPQ_OK && ce == cudaSuccess) {
+        if (n_clients) rc = ppq_agg_finish(h->agg, (uint64_t*)h->out.p, h->sx);
+        else HP(cudaMemsetAsync(h->out.p, 0, blk * sizeof(u64), h->sx));  // a rank without clients contributes zero
+        if (rc == PPQ_OK && comm) rc = ppq_reduce_across_ranks(c, comm, ell, (uint64_t*)h->out.p, n_slots, root, h->sx);
+    }
+    if (is_root) HP(cudaMemcpyAsync(h_acc, h->out.p, blk * sizeof(u64), cudaMemcpyDeviceToHost, h->sx));
+#undef HP
+    // always drain both streams: the caller's host buffers must not be in flight when this returns, error or not
+    const cudaError_t e1 = cudaStreamSynchronize(h->sc), e2 = cudaStreamSynchronize(h->sx);
+    if (rc != PPQ_OK) {
+        if (h->agg) {  // leave no half-built sum behind
+            ppq_agg_destroy(h->agg);
+            h->agg = nullptr;
+        }
+        return rc;
+    }
+    if (ce != cudaSuccess) return fail(PPQ_ECUDA, std::string("ppq_reencrypt_aggregate_host: ") + cudaGetErrorString(ce));
+    if (e1 != cudaSuccess || e2 != cudaSuccess)
+        return fail(PPQ_ECUDA, std::string("ppq_reencrypt_aggregate_host: ") + cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    return PPQ_OK;
+}
 extern "C" int ppq_reencrypt_aggregate_host(ppq_ctx* c, const ppq_rekey* const* rekeys, int ell,
                                             const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
                                             uint64_t* h_acc) {
-    if (!c || !rekeys || !h_cts || !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null argument");
-    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: bad limb count");
-    if (!n_clients || !n_slots) return PPQ_OK;
-    CU(cudaSetDevice(c->device));
-    const size_t ct = (size_t)2 * ell * c->hp.N, blk = ct * n_slots;
-    // double-buffered upload: client c+1 is copied while client c is re-encrypted
-    DevBuf<u64> in[2], acc;
-    CU(in[0].ensure(blk));
-    CU(in[1].ensure(blk));
-    CU(acc.ensure(blk));
-    cudaStream_t sc, sx;
-    CU(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
-    cudaEvent_t up[2], done[2];
-    for (int i = 0; i < 2; ++i) {
-        CU(cudaEventCreateWithFlags(&up[i], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
-    }
-    int rc = PPQ_OK;
-    CU(cudaMemsetAsync(acc.p, 0, blk * sizeof(u64), sx));
-    for (size_t cl = 0; cl < n_clients && rc == PPQ_OK; ++cl) {
-        const int b = (int)(cl & 1);
-        if (cl >= 2) CU(cudaStreamWaitEvent(sc, done[b], 0));
-        if (!h_cts[cl] || !rekeys[cl]) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null client entry");
-        CU(cudaMemcpyAsync(in[b].p, h_cts[cl], blk * sizeof(u64), cudaMemcpyHostToDevice, sc));
-        CU(cudaEventRecord(up[b], sc));
-        CU(cudaStreamWaitEvent(sx, up[b], 0));
-        rc = reencrypt_common(c, rekeys[cl], ell, in[b].p, acc.p, n_slots, sx, 1);
-        CU(cudaEventRecord(done[b], sx));
-    }
-    if (rc == PPQ_OK) {
-        CU(cudaMemcpyAsync(h_acc, acc.p, blk * sizeof(u64), cudaMemcpyDeviceToHost, sx));
-        CU(cudaStreamSynchronize(sx));
-    }
-    cudaStreamSynchronize(sc);
-    cudaStreamSynchronize(sx);
-    for (int i = 0; i < 2; ++i) {
-        cudaEventDestroy(up[i]);
-        cudaEventDestroy(done[i]);
-    }
-    cudaStreamDestroy(sc);
-    cudaStreamDestroy(sx);
-    return rc;
+    if (!rekeys || !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null argument");
+    return aggregate_host_impl(c, nullptr, 0, rekeys, ell, h_cts, n_clients, n_slots, h_acc, false);
+}
+extern "C" int ppq_reencrypt_aggregate_host_ranks(ppq_ctx* c, ppq_comm* comm, int root, const ppq_rekey* const* rekeys,
+                                                  int ell, const uint64_t* const* h_cts, size_t n_clients,
+                                                  size_t n_slots, uint64_t* h_acc) {
+    if (!comm) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host_ranks: null communicator");
+    return aggregate_host_impl(c, comm, root, rekeys, ell, h_cts, n_clients, n_slots, h_acc, false);
+}
+extern "C" int ppq_copy_ceiling_host(ppq_ctx* c, int ell, const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                     uint64_t* h_acc) {
+    return aggregate_host_impl(c, nullptr, 0, nullptr, ell, h_cts, n_clients, n_slots, h_acc, true);
 }

@@ -405,6 +405,114 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// [0, B q) -> [0, q) for B <= 16 and any limb width (the quotient-estimate form needs bitlen(q) >= 29; block-uniform)
+__device__ __forceinline__ u64 canon_any16(u64 x, const LimbC& lc) {
+    return lc.sh >= 28u ? canon16_q(x, lc) : canon_b<16>(x, lc);
+}
+
+// =========================================================================================================
+// Wide base conversion for the deferred ModDown (ppq_agg_*).  ApproxModDown's conversion P -> Q is linear in the
+// INTEGER lifts u_k in [0, p_k):  sum_c sum_k u_{k,c} chat_k = sum_k (sum_c u_{k,c}) chat_k (mod q_i), so the
+// conversions of up to 8 clients' ciphertexts of one slot cost one conversion of U_k = sum_c u_{k,c} < 2^63.
+// U is split into 21-bit pieces, chat into its 30-bit halves: six IMAD.WIDE per term, partial sums < 16 2^52; the
+// exact 128-bit total V = hi 2^64 + lo (< 16 2^63 2^60) is reduced as hi * (2^64 mod q) + lo: one Shoup product
+// (any 64-bit operand) and one Barrett estimate, for every limb width.
+// =========================================================================================================
+template <int NS>
+struct BwPack {
+    struct J {
+        u64 q, mu, r64, r64s;  // modulus, Barrett constant, 2^64 mod q and its Shoup companion
+        u32 sh;
+        int dst_slot;
+        uint2 c[NS];  // (c0, c1): 30-bit halves of the conversion constant per source limb
+    };
+    static constexpr int MAXJ = (12288 / (int)sizeof(J)) < 48 ? (12288 / (int)sizeof(J)) : 48;
+    int n_jobs, src_first;
+    J j[MAXJ];
+};
+template <int NS>
+__global__ void __launch_bounds__(256)
+    k_bconv_wide(int logN, const u64* __restrict__ src, size_t src_gs, size_t in_stride, int n_in,
+                 u64* __restrict__ dst, size_t dst_gs, int first, const __grid_constant__ BwPack<NS> P) {
+    constexpr int E = NS <= 8 ? 2 : 1;  // coefficients per thread
+    const u32 N = 1u << logN;
+    const u32 n = (blockIdx.x * 256 + threadIdx.x) * E;
+    const u32 g = blockIdx.z;
+    const u64* in = src + g * src_gs + (size_t)P.src_first * N + n;
+    u32 u0[E][NS], u1[E][NS], u2[E][NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+        u64 U[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) U[e] = 0;
+        for (int cl = 0; cl < n_in; ++cl) {
+            const u64* p = in + (size_t)cl * in_stride + (size_t)i * N;
+            if (E == 2) {
+                const ulonglong2 y = __ldcs(reinterpret_cast<const ulonglong2*>(p));
+                U[0] += y.x;
+                U[E - 1] += y.y;
+            } else {
+                U[0] += ld_stream(p);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            u0[e][i] = (u32)U[e] & 0x1fffffu;
+            u1[e][i] = (u32)(U[e] >> 21) & 0x1fffffu;
+            u2[e][i] = (u32)(U[e] >> 42);
+        }
+    }
+    u64* out = dst + g * dst_gs + n;
+#pragma unroll 1
+    for (int t = 0; t < P.n_jobs; ++t) {
+        const typename BwPack<NS>::J& J = P.j[t];
+        LimbC lc;
+        lc.q = J.q;
+        lc.q2 = J.q << 1;
+        lc.mu = J.mu;
+        lc.sh = J.sh;
+        u64 S[E][6];
+#pragma unroll
+        for (int i = 0; i < NS; ++i) {
+            const uint2 cc = J.c[i];
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                if (i == 0) {
+                    S[e][0] = mulw(u0[e][i], cc.x);
+                    S[e][1] = mulw(u1[e][i], cc.x);
+                    S[e][2] = mulw(u2[e][i], cc.x);
+                    S[e][3] = mulw(u0[e][i], cc.y);
+                    S[e][4] = mulw(u1[e][i], cc.y);
+                    S[e][5] = mulw(u2[e][i], cc.y);
+                } else {
+                    S[e][0] += mulw(u0[e][i], cc.x);
+                    S[e][1] += mulw(u1[e][i], cc.x);
+                    S[e][2] += mulw(u2[e][i], cc.x);
+                    S[e][3] += mulw(u0[e][i], cc.y);
+                    S[e][4] += mulw(u1[e][i], cc.y);
+                    S[e][5] += mulw(u2[e][i], cc.y);
+                }
+            }
+        }
+        u64 r[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            typedef unsigned __int128 u128;
+            const u128 X0 = (u128)S[e][0] + ((u128)S[e][1] << 21) + ((u128)S[e][2] << 42);  // sum U c0
+            const u128 X1 = (u128)S[e][3] + ((u128)S[e][4] << 21) + ((u128)S[e][5] << 42);  // sum U c1
+            const u128 V = X0 + (X1 << 30);
+            u64 v = mul_shoup_lazy((u64)(V >> 64), J.r64, J.r64s, lc.q) + barrett128_lazy3(0ull, (u64)V, lc);  // < 5q
+            if (!first) v += out[(size_t)J.dst_slot * N + e];
+            r[e] = canon_any16(v, lc);
+        }
+        if (E == 2) {
+            *reinterpret_cast<ulonglong2*>(out + (size_t)J.dst_slot * N) = make_ulonglong2(r[0], r[E - 1]);
+        } else {
+            out[(size_t)J.dst_slot * N] = r[0];
+        }
+    }
+}
+
 // =========================================================================================================
 // ROW passes
 // =========================================================================================================
@@ -720,8 +828,13 @@ struct KaraAcc {
 #ifndef PPQ_IP_MINB
 #define PPQ_IP_MINB 4  // 64 registers, 4 CTAs/SM (5: 14.3, 6: 15.0 us/ct)
 #endif
-template <int PARTS>
-__global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
+// AGG (deferred ModDown, ppq_agg_*): the Q-limb results are not written out per ciphertext but summed, together with
+// c0 on poly 0, into the running EVAL accumulator of the slot (A.acc; A.agg == 1: first client, plain store).
+#ifndef PPQ_IP_AGG_MINB
+#define PPQ_IP_AGG_MINB 3
+#endif
+template <int PARTS, bool AGG>
+__global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
     extern __shared__ __align__(128) unsigned char ip_smem[];
     u64* keys = reinterpret_cast<u64*>(ip_smem);              // [PARTS][2][IPT]
     u64* bar = keys + (size_t)PARTS * 2 * IPT;
@@ -751,6 +864,8 @@ __global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, i
     const int g1 = min(n_g, g0 + g_per_cta);
     // digits of the next (ciphertext, chunk) are fetched while the current one is multiplied: with two CTAs per
     // SM the loads in flight would otherwise not cover the HBM latency
+    const bool aggq = AGG && r < A.ell;  // block-uniform
+    ulonglong2 xn[3];  // AGG, Q limbs: c0, running sum of poly 0, running sum of poly 1 (fetched with the digits)
     auto fetch = [&](int it, ulonglong2 (&d)[PARTS]) {
         const int g = g0 + it / IPC;
         const u32 pt = (u32)(it % IPC) * 512 + threadIdx.x * 2;
@@ -759,6 +874,14 @@ __global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, i
             const u64* dp = (j == own) ? A.c1 + g * A.c1_gs + (size_t)r * N + off
                                        : A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
             d[j] = __ldcs(reinterpret_cast<const ulonglong2*>(dp + pt));
+        }
+        if (aggq) {
+            xn[0] = __ldcs(reinterpret_cast<const ulonglong2*>(A.c0 + g * A.c0_gs + (size_t)r * N + off + pt));
+            if (A.agg == 2) {
+                const u64* ap = A.acc + g * A.acc_gs + (size_t)r * N + off + pt;
+                xn[1] = *reinterpret_cast<const ulonglong2*>(ap);
+                xn[2] = *reinterpret_cast<const ulonglong2*>(ap + (size_t)A.ell * N);
+            }
         }
     };
     const int n_it = (g1 - g0) * IPC;
@@ -776,12 +899,21 @@ __global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, i
         ulonglong2 d[PARTS];
 #pragma unroll
         for (int j = 0; j < PARTS; ++j) d[j] = dn[j];
+        ulonglong2 xc[3];
+        if (AGG) {
+            xc[0] = xn[0];
+            xc[1] = xn[1];
+            xc[2] = xn[2];
+        }
         if (it + 1 < n_it) fetch(it + 1, dn);
         const int g = g0 + it / IPC;
         const u32 pt = (u32)(it % IPC) * 512 + threadIdx.x * 2;  // two adjacent points per 16-byte access
         u64* o0;
         u64* o1;
-        if (r < A.ell) {
+        if (aggq) {
+            o0 = A.acc + g * A.acc_gs + (size_t)r * N + off;
+            o1 = o0 + (size_t)A.ell * N;
+        } else if (r < A.ell) {
             o0 = A.extq + g * A.extq_gs + (size_t)r * N + off;
             o1 = o0 + (size_t)A.ell * N;
         } else {
@@ -799,7 +931,18 @@ __global__ void __launch_bounds__(256, PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, i
             a0.mac(dx, Kara3(ka.x, Kara3::Packed{}));
             a1.mac(dy, Kara3(ka.y, Kara3::Packed{}));
         }
-        if (PPQ_IP_LAZY && r < A.ell) {  // block-uniform
+        if (aggq) {  // block-uniform: x' (< 3q) + c0 (+ running sum) < 5q, canonicalised once
+            u64 v0 = b0.reduce_lazy3(lc) + xc[0].x, v1 = b1.reduce_lazy3(lc) + xc[0].y;
+            u64 w0 = a0.reduce_lazy3(lc), w1 = a1.reduce_lazy3(lc);
+            if (A.agg == 2) {
+                v0 += xc[1].x;
+                v1 += xc[1].y;
+                w0 += xc[2].x;
+                w1 += xc[2].y;
+            }
+            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(canon_any16(v0, lc), canon_any16(v1, lc));
+            *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(canon_any16(w0, lc), canon_any16(w1, lc));
+        } else if (PPQ_IP_LAZY && r < A.ell) {  // block-uniform
             *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce_lazy3(lc), b1.reduce_lazy3(lc));
             *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce_lazy3(lc), a1.reduce_lazy3(lc));
         } else {
@@ -831,7 +974,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + point_of<S - 3>(u, k));
     u64* o = A.out + g * A.out_gs + off + 8 * u;
     prefetch_l2(A.extq + g * A.extq_gs + off + 8 * u);
-    if (poly == 0) prefetch_l2(A.ct_in + g * A.in_gs + off + 8 * u);
+    if (poly == 0 && A.ct_in) prefetch_l2(A.ct_in + g * A.in_gs + off + 8 * u);
     if (A.accumulate) prefetch_l2(o);
     fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, PPQ_ROW_GPC > 1, PPQ_Z(lc));
     u64 x[8];
@@ -840,7 +983,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_m
     // x' + 8q - conv' (+ c0) (+ running sum) < 11q, canonicalised once.
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = x[k] + (lc.q2 << 2) - fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
-    if (poly == 0) {
+    if (poly == 0 && A.ct_in) {
         ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] += x[k];
@@ -877,7 +1020,7 @@ __device__ __forceinline__ void moddown_epilogue(u64 (&a)[8], const MdArgs& A, u
     ld8(x, A.extq + g * A.extq_gs + off + 8 * u);
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = x[k] + (lc.q2 << 2) - fold8_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
-    if (poly == 0) {
+    if (poly == 0 && A.ct_in) {
         ld8(x, A.ct_in + g * A.in_gs + off + 8 * u);
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] += x[k];
@@ -925,7 +1068,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_MD_X2_MINB) k_fwd_row
         for (int e = 0; e < 2; ++e) {
             const u32 ge = e ? g1 : g;
             prefetch_l2(A.extq + ge * A.extq_gs + off + 8 * u);
-            if (poly == 0) prefetch_l2(A.ct_in + ge * A.in_gs + off + 8 * u);
+            if (poly == 0 && A.ct_in) prefetch_l2(A.ct_in + ge * A.in_gs + off + 8 * u);
             if (A.accumulate) prefetch_l2(A.out + ge * A.out_gs + off + 8 * u);
         }
         fwd_pass_x2<S, RowPos<S>, FWD_ROW_IN>(a, b, sm, (u32)G::SMEM, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true, PPQ_Z(lc));
@@ -1114,6 +1257,10 @@ __global__ void k_decrypt_pw(KCtx c, const u64* __restrict__ ct, const u64* __re
 // =========================================================================================================
 // launchers
 // =========================================================================================================
+static unsigned long long g_launches = 0;
+static inline void count_launch(int n = 1) { g_launches += (unsigned long long)n; }
+unsigned long long kernels_launch_count() { return g_launches; }
+
 struct Split {
     int S1, S2;
 };
@@ -1153,6 +1300,7 @@ static inline int gpc_blocks(int n_g) { return (n_g + PPQ_ROW_GPC - 1) / PPQ_ROW
 template <int S, int MODE>
 static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* jobs,
                            const u64* chat, const int* limb_ids, u64 q_src, int ny, int ng, cudaStream_t st) {
+    count_launch();
     constexpr int W = ColW<S>::W;
     const int n2 = (1 << c.logN) >> S;
 #if PPQ_COL2
@@ -1174,6 +1322,7 @@ static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* ds
 }
 
 void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_polys, cudaStream_t st) {
+    count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
     PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 0>(c, data, 0, data, 0, nullptr, nullptr, d_limb_ids, 0, n_polys, 1, st)));
@@ -1183,6 +1332,7 @@ void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_p
 
 void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
                           cudaStream_t st, bool lazy2) {
+    count_launch();
     (void)lazy2;
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
@@ -1203,6 +1353,7 @@ void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
 
 void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
                     int n_slots, int n_g, cudaStream_t st) {
+    count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
 #if PPQ_INV_X2
@@ -1217,6 +1368,7 @@ void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t
 }
 void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale4, int n_slots,
                     int n_g, cudaStream_t st) {
+    count_launch();
     const Split sp = split_of(c.logN);
     const int n2 = 1 << sp.S2;
 #if PPQ_COL2_INV
@@ -1274,6 +1426,7 @@ static void bconv_launch(const KCtx& c, const u64* src, size_t src_gs, u64* dst,
             J.pad[0] = J.pad[1] = 0;
             for (int i = 0; i < NS; ++i) J.c[i] = chat_split(chat[jb.chat_off + i]);
         }
+        count_launch();
         if (PPQ_BCONV_PAIR && NS <= 8 && (1u << c.logN) >= 256u * PPQ_BCONV_E) {
             dim3 grid((1u << c.logN) / (256 * PPQ_BCONV_E), 1, n_g);
             k_bconv2<(NS <= 8 ? NS : 1)><<<grid, 256, 0, st>>>(c.logN, src, src_gs, dst, dst_gs,
@@ -1297,7 +1450,52 @@ bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t
 #undef PPQ_BC
 }
 
+
+template <int NS>
+static void bconv_wide_launch(const KCtx& c, const u64* src, size_t src_gs, size_t in_stride, int n_in, u64* dst,
+                              size_t dst_gs, int first, const BcJob* jobs, int n_jobs, const u64* chat,
+                              const LimbC* limbs, int n_g, cudaStream_t st) {
+    typedef BwPack<NS> P;
+    constexpr int E = NS <= 8 ? 2 : 1;
+    for (int j0 = 0; j0 < n_jobs; j0 += P::MAXJ) {
+        P pk;
+        pk.n_jobs = n_jobs - j0 < P::MAXJ ? n_jobs - j0 : P::MAXJ;
+        pk.src_first = jobs[j0].src_first;
+        for (int t = 0; t < pk.n_jobs; ++t) {
+            const BcJob& jb = jobs[j0 + t];
+            const LimbC& lc = limbs[jb.limb];
+            typename P::J& J = pk.j[t];
+            J.q = lc.q;
+            J.mu = lc.mu;
+            J.sh = lc.sh;
+            J.dst_slot = jb.dst_slot;
+            J.r64 = (u64)((((unsigned __int128)1) << 64) % lc.q);
+            J.r64s = (u64)((((unsigned __int128)J.r64) << 64) / lc.q);
+            for (int i = 0; i < NS; ++i) {
+                const u64 cv = chat[jb.chat_off + i];
+                J.c[i] = make_uint2((u32)(cv & 0x3fffffffull), (u32)(cv >> 30));
+            }
+        }
+        dim3 grid((1u << c.logN) / (256 * E), 1, n_g);
+        count_launch();
+        k_bconv_wide<NS><<<grid, 256, 0, st>>>(c.logN, src, src_gs, in_stride, n_in, dst, dst_gs, first, pk);
+    }
+}
+bool launch_bconv_wide(const KCtx& c, const u64* src, size_t src_gs, size_t in_stride, int n_in, u64* dst,
+                       size_t dst_gs, int first, const BcJob* h_jobs, int n_jobs, const u64* h_chat,
+                       const LimbC* h_limbs, int ns, int n_g, cudaStream_t st) {
+    if (n_in < 1 || n_in > 8) return false;
+#define PPQ_BW(NSV) case NSV: bconv_wide_launch<NSV>(c, src, src_gs, in_stride, n_in, dst, dst_gs, first, h_jobs, n_jobs, h_chat, h_limbs, n_g, st); return true;
+    switch (ns) {
+        PPQ_BW(1) PPQ_BW(2) PPQ_BW(3) PPQ_BW(4) PPQ_BW(5) PPQ_BW(6) PPQ_BW(7) PPQ_BW(8)
+        PPQ_BW(9) PPQ_BW(10) PPQ_BW(11) PPQ_BW(12) PPQ_BW(13) PPQ_BW(14) PPQ_BW(15) PPQ_BW(16)
+        default: return false;
+    }
+#undef PPQ_BW
+}
+
 void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
+    count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_ip<S><<<dim3(n1 / RowGeom<S>::R, n_g, a.ell + a.K), RowGeom<S>::THREADS, 0, st>>>(c, a)));
@@ -1312,11 +1510,17 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
     const int g_per = (n_g + gz - 1) / gz;
     gz = (n_g + g_per - 1) / g_per;
     dim3 grid(tiles, M, gz);
+    count_launch();
 #define PPQ_IP(P)                                                                                          \
     case P: {                                                                                              \
         const size_t sm = (size_t)P * 2 * IPT * sizeof(u64) + 16;                                          \
-        cudaFuncSetAttribute(k_ip_tma<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);           \
-        k_ip_tma<P><<<grid, 256, sm, st>>>(c, a, n_g, g_per);                                             \
+        if (a.agg) {                                                                                       \
+            cudaFuncSetAttribute(k_ip_tma<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); \
+            k_ip_tma<P, true><<<grid, 256, sm, st>>>(c, a, n_g, g_per);                                    \
+        } else {                                                                                           \
+            cudaFuncSetAttribute(k_ip_tma<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);\
+            k_ip_tma<P, false><<<grid, 256, sm, st>>>(c, a, n_g, g_per);                                   \
+        }                                                                                                  \
         return true;                                                                                       \
     }
     switch (a.parts) {
@@ -1326,6 +1530,7 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
 #undef PPQ_IP
 }
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
+    count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
 #if PPQ_MD_X2
@@ -1338,6 +1543,7 @@ void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_moddown<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), 2 * a.ell), RowGeom<S>::THREADS, 0, st>>>(c, a, n_g)));
 }
 void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st) {
+    count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_rescale<S><<<dim3(n1 / RowGeom<S>::R, n_g, 2 * (a.ell - 1)), RowGeom<S>::THREADS, 0, st>>>(c, a)));
@@ -1350,40 +1556,50 @@ static dim3 pw_grid(const KCtx& c, size_t ny, int per_thread) {
     return dim3(gx, (unsigned)ny, 1);
 }
 void launch_eval_add(const KCtx& c, const u64* a, const u64* b, u64* out, int ell, size_t n_ct, cudaStream_t st) {
+    count_launch();
     k_eval_add<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, a, b, out, ell);
 }
 void launch_finalize_mod(const KCtx& c, u64* x, int ell, size_t n_ct, cudaStream_t st) {
+    count_launch();
     k_finalize_mod<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, x, ell);
 }
 void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                         size_t n_ct, cudaStream_t st) {
+    count_launch();
     k_mult_scalar<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
 }
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st) {
+    count_launch();
     k_mult_scalar<<<pw_grid(c, n_polys, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
 }
 void launch_scale_key(const KCtx& c, const u64* in, int in_stride, u64* out, int out_stride, const u64* d_pinv,
                       const u64* d_pinv_sh, int L, int dnum, cudaStream_t st) {
+    count_launch();
     const u32 N = 1u << c.logN;
     k_scale_key<<<dim3((N / 2 + 255) / 256, L, dnum), 256, 0, st>>>(c, in, in_stride, out, out_stride, d_pinv, d_pinv_sh);
 }
 void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
                          cudaStream_t st) {
+    count_launch();
     k_small_to_res<<<pw_grid(c, n_ct * n_small * ell, 1), 256, 0, st>>>(c, (const long long*)small, out, n_small, ell);
 }
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee, const u64* pt, u64* ct, int ell,
                        size_t n_ct, cudaStream_t st) {
+    count_launch();
     k_encrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, pkb, pka, vee, pt, ct, ell);
 }
 void launch_keygen_pw(const KCtx& c, const u64* se, const u64* a, u64* sk, u64* pkb, int L, int M, cudaStream_t st) {
+    count_launch();
     k_keygen_pw<<<pw_grid(c, M, 1), 256, 0, st>>>(c, se, a, sk, pkb, L, M);
 }
 void launch_rekeygen_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* uee, const u64* sk_old,
                         const u64* d_pmod, u64* kb, u64* ka, int L, int M, int alpha, int dnum, cudaStream_t st) {
+    count_launch();
     k_rekeygen_pw<<<pw_grid(c, (size_t)dnum * M, 1), 256, 0, st>>>(c, pkb, pka, uee, sk_old, d_pmod, kb, ka, L, M, alpha);
 }
 void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st) {
+    count_launch();
     k_decrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, ct, sk, out, ell);
 }
 

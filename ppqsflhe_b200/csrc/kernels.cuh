@@ -49,6 +49,13 @@ void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, 
 // (constant bank) by the launcher.  Returns false if ns is outside 1..32.
 bool launch_bconv(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* h_jobs,
                   int n_jobs, const u64* h_chat, const LimbC* h_limbs, int ns, int n_g, cudaStream_t st);
+// ---- the same conversion over the INTEGER SUM of n_in <= 8 source sets (deferred ModDown, ppq_agg_*): the conversion
+// is linear in the integer lifts, so sum_c conv(u_c) = conv(sum_c u_c) mod q exactly; the sum of up to 8 canonical
+// residues (< 2^63) is formed on the fly from src + c*in_stride, c < n_in, and reduced with a 128-bit-wide reduction.
+// dst (canonical) is overwritten when `first`, else incremented mod q.  ns <= 16.
+bool launch_bconv_wide(const KCtx& c, const u64* src, size_t src_gs, size_t in_stride, int n_in, u64* dst,
+                       size_t dst_gs, int first, const BcJob* h_jobs, int n_jobs, const u64* h_chat,
+                       const LimbC* h_limbs, int ns, int n_g, cudaStream_t st);
 // (c0, c1, c0 + c1, 0) of a conversion constant c < 2^60 (30-bit Karatsuba split, see k_bconv)
 inline uint4 chat_split(u64 c) {
     const u32 c0 = (u32)(c & 0x3fffffffull), c1 = (u32)(c >> 30);
@@ -79,6 +86,13 @@ struct IpArgs {
     u64* extp;           // out, P limbs after the inverse ROW pass: extp + g*extp_gs + (poly*K + k)*N
     size_t extp_gs;
     int ell, K, L, parts, alpha;
+    // deferred ModDown (ppq_agg_*): agg != 0 sums the Q-limb results (+ c0 on poly 0) into the slot's running EVAL
+    // accumulator acc + g*acc_gs + (poly*ell + r)*N instead of writing extq (1: first client, store; 2: add)
+    int agg = 0;
+    u64* acc = nullptr;
+    size_t acc_gs = 0;
+    const u64* c0 = nullptr;  // c0 + g*c0_gs + r*N
+    size_t c0_gs = 0;
 };
 void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
 // ---- split form: digits already in EVAL (k_fwd_row_plain on a.digits); pointwise inner product with the key tile
@@ -145,5 +159,7 @@ void launch_rekeygen_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64
                         const u64* d_pmod, u64* kb, u64* ka, int L, int M, int alpha, int dnum, cudaStream_t st);
 
 const char* kernels_build_info();
+// kernels launched by this library since load (bench.py's gpu_launches)
+unsigned long long kernels_launch_count();
 
 }  // namespace ppq

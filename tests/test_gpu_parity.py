@@ -236,6 +236,113 @@ def test_reencrypt_accumulate_matches_oracle_batch():
     assert np.array_equal(acc.numpy(), want)
 
 
+@pytest.mark.parametrize("kind,ell,n_clients,n_slots", [("c1", 4, 2, 3), ("c1", 3, 9, 2), ("c1", 1, 3, 1),
+                                                        ((12, 5, 3, 45), 7, 17, 2), ((13, 4, 2, 50), 5, 8, 3),
+                                                        ((13, 38, 3, 59), 40, 9, 1), ((15, 6, 3, 50), 8, 3, 5),
+                                                        ((16, 18, 3, 59), 20, 9, 2), ((16, 18, 3, 59), 19, 2, 3)])
+def test_aggregator_bit_exact(kind, ell, n_clients, n_slots):
+    """ppq_agg_* (deferred ModDown: the linear tail of ApproxModDown applied to sums over clients) against the oracle's
+    per-client ReEncrypt followed by EvalAdd, client by client -- the reference's order of operations
+    (server/src/changeCipherDomain.cpp:105, server/src/aggregateEncryptedWeights.cpp:106).  Client counts cross the
+    group-of-8 boundary of the wide conversion; the handle is reused for a second aggregation."""
+    from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(1000 + n_clients * 7 + ell)
+    cts = np.stack([_rand_ct(rng, o, ell, n_slots) for _ in range(n_clients)])
+    keys = [_rand_key(rng, o) for _ in range(n_clients)]
+    rks = [EvalKey(cc, *k) for k in keys]
+    agg = Aggregator(cc, ell, n_slots)
+    for c in range(n_clients):
+        agg.add(CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()), rks[c])
+    assert agg.count == n_clients
+    got = agg.finish().numpy()
+    want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+    assert np.array_equal(got, want), "aggregate differs from per-client ReEncrypt + EvalAdd"
+    # second use of the same handle, fewer clients, reversed order (the sum commutes; state must have been reset)
+    assert agg.count == 0
+    sub = list(range(min(n_clients, 3)))[::-1]
+    for c in sub:
+        agg.add(CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()), rks[c])
+    got2 = agg.finish().numpy()
+    want2 = o.reencrypt_accumulate_batch(ell, cts[sub], [keys[c][0] for c in sub], [keys[c][1] for c in sub])
+    assert np.array_equal(got2, want2)
+    agg.close()
+
+
+@pytest.mark.parametrize("group,wave", [(1, 0), (3, 1), (8, 2)])
+def test_aggregator_group_and_wave_independent(group, wave, monkeypatch):
+    from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    monkeypatch.setenv("PPQ_AGG_GROUP", str(group))
+    o, cc = _cc_pair((13, 4, 2, 50))
+    cc.set_wave(wave)
+    rng = np.random.default_rng(77)
+    ell, n_clients, n_slots = o.L, 7, 3
+    cts = np.stack([_rand_ct(rng, o, ell, n_slots) for _ in range(n_clients)])
+    keys = [_rand_key(rng, o) for _ in range(n_clients)]
+    agg = Aggregator(cc, ell, n_slots)
+    for c in range(n_clients):
+        agg.add(CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()), EvalKey(cc, *keys[c]))
+    want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+    assert np.array_equal(agg.finish().numpy(), want)
+    cc.set_wave(0)
+
+
+def test_aggregator_extreme_residues():
+    """All-(q-1) and all-zero inputs and keys: the largest operands every lazy bound has to hold."""
+    from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    for kind in ("c1", (12, 5, 3, 45)):
+        o, cc = _cc_pair(kind)
+        ell, n_clients, n_slots = o.L, 9, 1
+        q = o.moduli
+        top_ct = np.stack([np.stack([np.stack([np.full(o.N, q[i] - np.uint64(1), dtype=np.uint64) for i in range(ell)])
+                                     for _ in range(2)]) for _ in range(n_slots)])
+        top_k = np.stack([np.stack([np.full(o.N, q[r] - np.uint64(1), dtype=np.uint64) for r in range(o.M)])
+                          for _ in range(o.dnum)])
+        rng = np.random.default_rng(5)
+        cts, keys = [], []
+        for c in range(n_clients):
+            if c % 3 == 0:
+                cts.append(top_ct)
+                keys.append((top_k, top_k))
+            elif c % 3 == 1:
+                cts.append(np.zeros_like(top_ct))
+                keys.append(_rand_key(rng, o))
+            else:
+                cts.append(_rand_ct(rng, o, ell, n_slots))
+                keys.append((top_k, np.zeros_like(top_k)))
+        cts = np.stack(cts)
+        agg = Aggregator(cc, ell, n_slots)
+        for c in range(n_clients):
+            agg.add(CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()), EvalKey(cc, *keys[c]))
+        want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+        assert np.array_equal(agg.finish().numpy(), want)
+
+
+def test_aggregator_equals_sequential_gpu_path_full_c3_size():
+    """At BASELINE.json's C3 shape (N=2^16, 20 limbs, 54 slots) the oracle is too slow for a whole client, so the
+    size-independent property is checked instead: ppq_agg_* == the per-client ppq_reencrypt_accumulate chain (itself
+    oracle-checked at small sizes), bit for bit, over 10 clients (one full group of 8 + a partial one)."""
+    from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey
+    _, cc = _cc_pair((16, 18, 3, 59))
+    dev, ell, n_slots, n_clients = cc.device, cc.L, 54, 10
+    qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
+    torch.manual_seed(9)
+
+    def rr(shape, q):
+        return torch.randint(0, 1 << 62, shape, dtype=torch.int64, device=dev).remainder_(q)
+
+    acc = CiphertextBatch(torch.zeros((n_slots, 2, ell, cc.N), dtype=torch.int64, device=dev), CtMeta())
+    agg = Aggregator(cc, ell, n_slots)
+    for _ in range(n_clients):
+        ct = CiphertextBatch(rr((n_slots, 2, ell, cc.N), qv[:ell].view(1, 1, ell, 1)), CtMeta())
+        rk = EvalKey(cc, rr((cc.dnum, cc.M, cc.N), qv.view(1, cc.M, 1)), rr((cc.dnum, cc.M, cc.N), qv.view(1, cc.M, 1)))
+        cc.ReEncryptAccumulate(ct, rk, acc)
+        agg.add(ct, rk)
+        del rk
+    out = agg.finish()
+    assert torch.equal(out.data, acc.data)
+
+
 def test_host_buffer_aggregate_entry_point():
     import ctypes as C
     from ppqsflhe_b200 import EvalKey

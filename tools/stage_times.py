@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--clients", type=int, default=2)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--wave", type=int, default=0)
+    ap.add_argument("--legacy", action="store_true", help="per-client full ModDown (ppq_reencrypt_accumulate) instead of ppq_agg_*")
     ap.add_argument("--tag", default=os.environ.get("PPQ_B200_LIB", "default"))
     a = ap.parse_args()
     cfg = CONFIGS[a.config]
@@ -43,9 +44,17 @@ def main():
     keys = [EvalKey(cc, rr((cc.dnum, M, N), qv.view(1, M, 1)), rr((cc.dnum, M, N), qv.view(1, M, 1))) for _ in range(a.clients)]
     acc = CiphertextBatch(torch.zeros((n, 2, ell, N), dtype=torch.int64, device=dev), CtMeta())
 
+    from ppqsflhe_b200 import Aggregator
+    agg = None if a.legacy else Aggregator(cc, ell, n)
+
     def step():
-        for ct, rk in zip(cts, keys):
-            cc.ReEncryptAccumulate(ct, rk, acc)
+        if a.legacy:
+            for ct, rk in zip(cts, keys):
+                cc.ReEncryptAccumulate(ct, rk, acc)
+        else:
+            for ct, rk in zip(cts, keys):
+                agg.add(ct, rk)
+            agg.finish(out=acc.data)
 
     step()
     torch.cuda.synchronize()
