@@ -39,6 +39,9 @@ CONFIGS = {
                desc="C4: 16 clients x 16 cts, CKKS N=2^17, 40 limbs, dnum 3"),
 }
 METRIC = "ciphertexts/s ReEncrypt+EvalAdd at N=2^16"
+# Integer-issue floor of the path in us per ciphertext on one B200 ("Integer co-bound": butterflies and
+# multiply-adds at 100 % of the fmaheavy pipe with the measured issue intervals), for the deferred-ModDown algorithm.
+FLOOR_US = {"c3": 76.0}
 UNIT = "ciphertexts/s"
 
 
@@ -75,11 +78,27 @@ def bind_near_gpu(local):
         return None, 0
 
 
-def stage_alg_words(ell, K, parts, bk, split=True):
+def stage_alg_words(ell, K, parts, bk, split=True, agg=False, group=8, clients=1):
     """Algorithmic (compulsory) u64 words per ciphertext, in units of N, for each of the 11 pipeline stages
-    (DESIGN.md 'kernels').  bk = ciphertexts sharing one rekey inside a call (key traffic is amortised)."""
+    (DESIGN.md 'kernels').  bk = ciphertexts sharing one rekey inside a call (key traffic is amortised).
+    agg: the deferred-ModDown pipeline (ppq_agg_*): stage 8 runs once per `group` clients, stages 9-10 once per
+    slot for all `clients` of a GPU."""
     M = ell + K
     conv = parts * M - ell
+    if agg:
+        return [
+            2 * ell,                                   # k_inv_row(c1):        R ell + W ell
+            2 * ell,                                   # k_inv_col(c1):        R ell + W ell
+            ell + conv,                                # k_bconv(modup):       R ell (COEFF digits) + W converted limbs
+            2 * conv,                                  # k_fwd_col(modup):     R + W converted limbs
+            2 * conv,                                  # k_fwd_row(modup):     R + W converted limbs
+            conv + ell + 2 * parts * M / bk + ell + 4 * ell + 2 * K,  # k_ip_tma: R digits, own c1, keys/bk, c0; RMW accE; W 2K
+            4 * K,                                     # k_inv_row(P):         R 2K + W 2K
+            4 * K,                                     # k_inv_col(P):         R 2K + W 2K
+            2 * K + 4.0 * ell / group,                 # k_bconv_wide:         R 2K per client; RMW accW per group
+            4.0 * ell / clients,                       # k_fwd_col(moddown):   once per slot
+            6.0 * ell / clients,                       # k_fwd_row_moddown:    R accW 2l + R accE 2l + W 2l, once per slot
+        ]
     return [
         2 * ell,                                   # k_inv_row(c1):        R ell + W ell
         2 * ell,                                   # k_inv_col(c1):        R ell + W ell
@@ -213,6 +232,9 @@ def cpu_run(cfg, steps, warmup, sample_slots=None):
             times.append(dt)
     t = float(np.median(times))
     return {"value": sample_slots / t, "unit": UNIT, "cores": T, "kind": "port",
+            "note": "unoptimised restatement: unsigned __int128 products reduced with % (__umodti3) in the NTT and base "
+                    "conversion loops; a Barrett/Shoup CPU implementation such as OpenFHE's would be several times "
+                    "faster, so GPU/CPU ratios over this arm are upper bounds",
             "sample": f"{sample_slots} ciphertexts of 1 client (ell={ell}, N=2^{o.logN}, K={o.K}, dnum={o.dnum}) per step, "
                       f"{steps} steps after {warmup} warm-up, median; OpenFHE-algorithm CPU restatement (oracle/), "
                       f"OpenMP over ciphertexts",
@@ -238,6 +260,180 @@ def reference_arm(args, cfg):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
+def _rand_res(torch, dev, shape, q):  # uniform-ish canonical residues
+    return torch.randint(0, 1 << 62, shape, dtype=torch.int64, device=dev).remainder_(q)
+
+
+def int_pipe_of(kernel_name):
+    """fmaheavy pipe utilisation (%) of a kernel from the committed ncu --set full capture (profiles/ncu_int_pipe.json)."""
+    p = os.path.join(ROOT, "profiles", "ncu_int_pipe.json")
+    try:
+        return json.load(open(p)).get(kernel_name)
+    except Exception:
+        return None
+
+
+def run_aggregation(torch, cc, cfg, clients, steps, warmup, comm=None, world=1, rank=0, profile=True, barrier=None,
+                    allmax=None, sampler=None):
+    """Device-resident ReEncrypt+EvalAdd of `clients` (this rank's) x cfg['slots'] ciphertexts per step through
+    ppq_agg_* (+ ppq_reduce_across_ranks).  Returns timing, per-stage CUDA-event times and the data (for e2e)."""
+    from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey
+    from ppqsflhe_b200._capi import check, lib
+    dev = cc.device
+    ell, N, M = cc.L, cc.N, cc.M
+    n_slots = cfg["slots"]
+    qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
+    cts = [CiphertextBatch(_rand_res(torch, dev, (n_slots, 2, ell, N), qv[:ell].view(1, 1, ell, 1)), CtMeta()) for _ in clients]
+    keys = [EvalKey(cc, _rand_res(torch, dev, (cc.dnum, M, N), qv.view(1, M, 1)), _rand_res(torch, dev, (cc.dnum, M, N), qv.view(1, M, 1)))
+            for _ in clients]
+    acc = CiphertextBatch(torch.zeros((n_slots, 2, ell, N), dtype=torch.int64, device=dev), CtMeta())
+    agg = Aggregator(cc, ell, n_slots)
+    torch.cuda.synchronize()
+
+    def step():
+        for ct, rk in zip(cts, keys):
+            agg.add(ct, rk)
+        if cts:
+            agg.finish(out=acc.data)
+        else:
+            acc.data.zero_()
+        if comm is not None:
+            comm.reduce(acc, root=0)  # one ncclReduce of canonical residues (< 2^60) + mod q on the root
+
+    def timed(fn, k):
+        if barrier:
+            barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if barrier:
+            barrier()
+        ms = e0.elapsed_time(e1)
+        return allmax(ms) if allmax else ms
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    if profile:
+        check(lib().ppq_profile_enable(cc.h, 1))
+    l0 = int(lib().ppq_launch_count())
+    if sampler is not None:
+        sampler.start()
+    total_ms = timed(step, steps)
+    clocks = sampler.stop() if sampler is not None else None
+    launches = int(lib().ppq_launch_count()) - l0
+    NST = 11
+    pms, pl = (C.c_double * NST)(), (C.c_uint64 * NST)()
+    if profile:
+        check(lib().ppq_profile_read(cc.h, pms, pl, 1))
+        check(lib().ppq_profile_enable(cc.h, 0))
+    return {"total_ms": total_ms, "stage_ms": list(pms), "stage_launches": list(pl), "launches": launches, "clocks": clocks, "cts": cts,
+            "keys": keys, "acc": acc, "agg": agg, "step": step, "timed": timed}
+
+
+def side_config(torch, name, steps=2, warmup=3):
+    """Short device-resident run of another BASELINE.json configuration on this GPU (parity-tested shapes; these are
+    context for the headline, not the headline)."""
+    from ppqsflhe_b200 import CryptoContext
+    cfg = dict(CONFIGS[name])
+    cc = CryptoContext.synthetic(cfg["logN"], cfg["depth"], cfg["first"], cfg["scale"], cfg["extra"], cfg["dnum"], torch.cuda.current_device())
+    r = None
+    try:
+        r = run_aggregation(torch, cc, cfg, list(range(cfg["clients"])), steps, warmup, profile=False)
+        n = cfg["clients"] * cfg["slots"]
+        ms = r["total_ms"] / steps
+        v = n / (ms * 1e-3)
+        peak, _ = peaks()
+        w = path_alg_bytes(cc.N, cc.L, cc.K, cc.dnum, cfg["slots"])
+        return {"workload": cfg["desc"], "value": v, "unit": UNIT, "ms_per_step": ms, "steps": steps, "warmup": warmup,
+                "alg_bytes_per_ct": w, "path_frac": v * w / 1e9 / peak, "limbs": cc.L, "aux_limbs": cc.K,
+                "l2": "cold inputs: %.0f MiB per step" % (n * 2 * cc.L * cc.N * 8 / 2 ** 20)}
+    finally:
+        del r
+        cc.close()
+        torch.cuda.empty_cache()
+
+
+def ntt_sweep_summary(torch, limbs=16):
+    """C5 summary (BASELINE.json configs[4]): batched forward/inverse NTT through ppq_ntt_forward / ppq_ntt_inverse,
+    logN 12..17 at `limbs` limbs, working set >= 256 MiB, GB/s at the algorithmic 16 N bytes per limb transform."""
+    from ppqsflhe_b200 import CryptoContext
+    peak, _ = peaks()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    rows = []
+    for logN in (12, 13, 14, 15, 16, 17):
+        N = 1 << logN
+        cc = CryptoContext.synthetic(logN, limbs - 2, 60, 59, 20, 2, dev.index)
+        nl = cc.L
+        reps = max(1, (256 << 20) // (nl * N * 8))
+        ids = np.tile(np.arange(nl, dtype=np.int32), reps)
+        qv = torch.from_numpy(cc.moduli[:nl].astype(np.int64)).to(dev).repeat(reps).view(-1, 1)
+        buf = _rand_res(torch, dev, (len(ids), N), qv)
+        row = {"logN": logN, "limbs": nl, "polys": int(len(ids)), "MiB": int(buf.numel() * 8 >> 20)}
+        for name, inv in (("fwd", False), ("inv", True)):
+            for _ in range(3):
+                cc.ntt(buf, ids, inverse=inv)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                cc.ntt(buf, ids, inverse=inv)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 5
+            row[name + "_gbs"] = 16.0 * N * len(ids) / (ms * 1e-3) / 1e9
+            row[name + "_frac"] = row[name + "_gbs"] / peak
+        rows.append(row)
+        del buf, qv
+        cc.close()
+        torch.cuda.empty_cache()
+    return rows
+
+
+def client_leg(torch, name, n_ct):
+    """Client half of north_star: batched encode+Encrypt (client/src/encryptModelWeights.cpp:109-110) and
+    Decrypt+decode (client/src/decryptModelWeights.cpp:108-109) of n_ct full ciphertexts, device-resident.
+    Compulsory bytes per ciphertext: N/2 doubles on one side, the 2*ell*N residues of the ciphertext on the other."""
+    from ppqsflhe_b200 import CryptoContext
+    cfg = CONFIGS[name]
+    peak, _ = peaks()
+    dev_i = torch.cuda.current_device()
+    cc = CryptoContext.synthetic(cfg["logN"], cfg["depth"], cfg["first"], cfg["scale"], cfg["extra"], cfg["dnum"], dev_i)
+    try:
+        sk, pk = cc.KeyGen()
+        vals = torch.empty((n_ct, cc.N // 2), dtype=torch.float64, device=cc.device).normal_(0, 0.05).clamp_(-0.3, 0.3)
+        out = {"workload": cfg["desc"], "cts": n_ct, "limbs": cc.L, "logN": cc.logN}
+        alg = 16.0 * cc.L * cc.N + 4.0 * cc.N
+
+        def t(fn, reps=3):
+            fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                r = fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / reps, r
+
+        ms, ct = t(lambda: cc.Encrypt(pk, cc.MakeCKKSPackedPlaintext(vals)))
+        out["encode_encrypt"] = {"cts_per_s": n_ct / (ms * 1e-3), "ms": ms, "alg_bytes_per_ct": alg,
+                                 "hbm_frac": n_ct * alg / (ms * 1e-3) / 1e9 / peak}
+        ms, pt = t(lambda: cc.Decrypt(sk, ct))
+        out["decrypt_decode"] = {"cts_per_s": n_ct / (ms * 1e-3), "ms": ms, "alg_bytes_per_ct": alg,
+                                 "hbm_frac": n_ct * alg / (ms * 1e-3) / 1e9 / peak}
+        err = float((pt.values - vals).abs().max().item())
+        out["max_abs_err"] = err
+        return out
+    finally:
+        cc.close()
+        torch.cuda.empty_cache()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -250,6 +446,7 @@ def main():
     ap.add_argument("--wave", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the configs / C5 / client blocks (N = 1 only)")
     args = ap.parse_args()
     cfg = dict(CONFIGS[args.config])
     if args.clients:
@@ -263,9 +460,9 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from ppqsflhe_b200 import CiphertextBatch, CryptoContext, CtMeta, EvalKey
+    from ppqsflhe_b200 import Communicator, CryptoContext
     from ppqsflhe_b200._capi import check, lib, vp
-    from ppqsflhe_b200.aggregate import clients_of_rank, reduce_partial_sums
+    from ppqsflhe_b200.aggregate import clients_of_rank
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -284,109 +481,85 @@ def main():
     parts = cc.num_parts(ell)
     n_slots = cfg["slots"]
     my_clients = clients_of_rank(cfg["clients"], world, rank)
-    qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
-
-    def rand_res(shape, q):  # uniform-ish residues, canonical
-        x = torch.randint(0, 1 << 62, shape, dtype=torch.int64, device=dev)
-        return x.remainder_(q)
-
     torch.manual_seed(42 + rank)
-    cts = [CiphertextBatch(rand_res((n_slots, 2, ell, N), qv[:ell].view(1, 1, ell, 1)), CtMeta()) for _ in my_clients]
-    keys = [EvalKey(cc, rand_res((cc.dnum, M, N), qv.view(1, M, 1)), rand_res((cc.dnum, M, N), qv.view(1, M, 1)))
-            for _ in my_clients]
-    acc = CiphertextBatch(torch.zeros((n_slots, 2, ell, N), dtype=torch.int64, device=dev), CtMeta())
-    torch.cuda.synchronize()
 
-    def step():
-        acc.data.zero_()
-        for ct, rk in zip(cts, keys):
-            cc.ReEncryptAccumulate(ct, rk, acc)
-        if world > 1:
-            reduce_partial_sums(acc.data, world, dst=0)  # residues < 2^60: an 8-way u64 sum cannot wrap
-            if rank == 0:
-                cc.finalize_sum(acc)
+    comm = None
+    barrier = allmax = None
+    if world > 1:
+        # the library's own communicator (ppq_comm_*): rank 0 makes the NCCL id, torch.distributed only carries it
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(Communicator.unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        comm = Communicator(cc, world, rank, bytes(idt.cpu().numpy().tobytes()))
+        barrier = dist.barrier
 
-    def timed(fn, k):
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(k):
-            fn()
-        e1.record()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+        def allmax(ms):
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
 
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
-    check(lib().ppq_profile_enable(cc.h, 1))
-    sampler = ClockSampler(local)
-    sampler.start()
-    total_ms = timed(step, args.steps)
-    clocks = sampler.stop()
-    NST = 11  # PPQ_PROFILE_STAGES
-    pms = (C.c_double * NST)()
-    pl = (C.c_uint64 * NST)()
-    check(lib().ppq_profile_read(cc.h, pms, pl, 1))
-    check(lib().ppq_profile_enable(cc.h, 0))
-    stage_ms, stage_launches = list(pms), list(pl)
+    R = run_aggregation(torch, cc, cfg, my_clients, args.steps, args.warmup, comm, world, rank, True, barrier, allmax,
+                        ClockSampler(local))
+    clocks = R["clocks"]
+    total_ms, stage_ms, stage_launches = R["total_ms"], R["stage_ms"], R["stage_launches"]
+    cts, keys, timed = R["cts"], R["keys"], R["timed"]
     n_ct_step = cfg["clients"] * n_slots
     ms_per_step = total_ms / args.steps
     value = n_ct_step / (ms_per_step * 1e-3)
 
-    # ---- roofline of the dominant kernel (CUDA events around every launch of it, inside the timed region)
+    # ---- roofline.  `frac` is SURVEY 8(d)'s figure: whole-path W_alg (ideal fusion) x ct/s per GPU against the HBM
+    # peak.  The dominant kernel (largest CUDA-event share inside the timed region) is reported beside it against the
+    # bytes of ITS pass (`pass_frac`), with its integer-pipe utilisation from the committed ncu capture.
     peak, peak_src = peaks()
-    names = [lib().ppq_profile_stage_name(i).decode() for i in range(NST)]
+    names = [lib().ppq_profile_stage_name(i).decode() for i in range(11)]
     dom = int(np.argmax(stage_ms))
-    words = stage_alg_words(ell, K, parts, n_slots, split=os.environ.get("PPQ_IP_FUSED", "0") in ("", "0"))
+    words = stage_alg_words(ell, K, parts, n_slots, agg=True, clients=max(1, len(my_clients)))
     local_ct = len(my_clients) * n_slots * args.steps
     dom_bytes = words[dom] * 8.0 * N * local_ct
-    achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
-    # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/ncu_traffic.json holds
-    # dram__bytes_read.sum + dram__bytes_write.sum per ciphertext), scaled to this run's ciphertexts per launch
+    dom_gbs = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
     traffic = None
+    traffic_path = None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     cts_per_launch = local_ct / max(1, stage_launches[dom])
     if os.path.exists(tpath):
         try:
-            per_ct = json.load(open(tpath)).get(args.config, {}).get("dram_bytes_per_ct", {}).get(names[dom])
+            tj = json.load(open(tpath)).get(args.config, {})
+            per_ct = tj.get("dram_bytes_per_ct", {}).get(names[dom])
             traffic = per_ct * cts_per_launch if per_ct is not None else None
+            traffic_path = tj.get("path_dram_bytes_per_ct")
         except Exception:
             traffic = None
     w_alg = path_alg_bytes(N, ell, K, cc.dnum, n_slots)
+    per_gpu = value / world
+    us_per_ct = 1e6 / per_gpu if per_gpu > 0 else None
     roofline = {
-        "bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-        "launch_avg_ms": stage_ms[dom] / max(1, stage_launches[dom]),
-        "alg_bytes_per_ct": words[dom] * 8.0 * N, "alg_bytes_per_launch": words[dom] * 8.0 * N * cts_per_launch,
-        "cts_per_launch": cts_per_launch,
+        "bound": "hbm", "achieved": per_gpu * w_alg / 1e9, "peak": peak, "unit": "GB/s",
+        "frac": per_gpu * w_alg / 1e9 / peak, "peak_source": peak_src,
+        "alg_bytes_per_ct": w_alg, "us_per_ct": us_per_ct,
+        "note": "whole ReEncrypt+EvalAdd path per GPU: ct/s x SURVEY 8(d) W_alg = 8N(13 ell + 4K + 2 dnum (ell+K)/B_k) "
+                "(ideal fusion) against the measured HBM peak",
+        "traffic": traffic_path, "traffic_note": "dram__bytes read+write per ciphertext summed over the path's kernels "
+                                                 "(ncu --set full, profiles/ncu_traffic.json)",
+        "kernel": names[dom], "pass_achieved": dom_gbs, "pass_frac": dom_gbs / peak,
+        "pass_alg_bytes_per_ct": words[dom] * 8.0 * N, "pass_traffic_per_launch": traffic,
+        "launch_avg_ms": stage_ms[dom] / max(1, stage_launches[dom]), "cts_per_launch": cts_per_launch,
+        "int_pipe": int_pipe_of(names[dom]),
+        "int_pipe_note": "sm__inst_executed_pipe_fmaheavy % of the dominant kernel (committed ncu capture); the path is "
+                         "integer-issue bound (DESIGN.md 4), so this, not the HBM fraction, is the binding roofline",
+        "floor_us_per_ct": FLOOR_US.get(args.config),
         "stage_share": {n: (m / max(1e-9, sum(stage_ms))) for n, m in zip(names, stage_ms)},
-        "stage_gbs": {n: (w * 8.0 * N * local_ct / (m * 1e-3) / 1e9 if m > 0 else 0.0)
-                      for n, w, m in zip(names, words, stage_ms)},
-        "path": {"alg_bytes_per_ct": w_alg, "achieved": value / world * w_alg / 1e9, "frac": value / world * w_alg / 1e9 / peak,
-                 "note": "whole ReEncrypt+EvalAdd path per GPU against SURVEY 8(d) W_alg (ideal fusion)"},
+        "stage_us_per_ct": {n: (m * 1e3 / max(1, local_ct)) for n, m in zip(names, stage_ms)},
     }
-    # kernels of ours launched inside the timed region: per wave 2 (c1 inverse) + `parts` ModUp conversions + COL pass
-    # + inner product (3 kernels in the split form, 1 fused) + P inverse COL + 2 ModDown conversions + COL + ROW pass,
-    # plus the final mod-q kernel on the root after the cross-GPU reduce
-    split = os.environ.get("PPQ_IP_FUSED", "0") in ("", "0")
-    per_wave = 2 + parts + 1 + (3 if split else 1) + 1 + 2 + 1 + 1
-    gpu_launches = int(stage_launches[0]) * per_wave + (args.steps if (world > 1 and rank == 0) else 0)
+    gpu_launches = R["launches"]
 
     # ---- standalone batched NTT / iNTT (second half of BASELINE.json's metric: "NTT HBM GB/s"), rank 0 only.
-    # Algorithmic bytes per limb transform = 16 N (read N u64 + write N u64; a transform is two HBM passes here).
     ntt = None
     if rank == 0:
         reps = 20
-        ids = np.tile(np.arange(M, dtype=np.int32), reps)          # every limb of Q u P, `reps` polys each
-        buf = rand_res((len(ids), N), qv.repeat(reps).view(-1, 1))  # 27 x 20 x 512 KiB = 270 MiB > L2
+        qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
+        ids = np.tile(np.arange(M, dtype=np.int32), reps)
+        buf = _rand_res(torch, dev, (len(ids), N), qv.repeat(reps).view(-1, 1))
         res = {}
         for name, inv in (("fwd", False), ("inv", True)):
             cc.ntt(buf, ids, inverse=inv)
@@ -406,7 +579,9 @@ def main():
         del buf
         torch.cuda.empty_cache()
 
-    # ---- e2e: host buffers in, aggregate out, copies inside the timed region
+    # ---- e2e: host buffers in, aggregate out, every copy inside the timed region, through ONE C-ABI call per step
+    # (ppq_reencrypt_aggregate_host; N > 1: ppq_reencrypt_aggregate_host_ranks, which ends in the NCCL reduce).
+    # The copy-only leg runs the same uploads/download on the same streams without kernels: the box's ceiling.
     e2e = None
     if not args.no_e2e:
         blk = n_slots * 2 * ell * N
@@ -414,62 +589,77 @@ def main():
         pool_n = max(1, min(len(my_clients), 4))
         pool = [torch.empty(blk, dtype=torch.int64).pin_memory() for _ in range(pool_n)]
         for i, p in enumerate(pool):
-            p.copy_(cts[i].data.view(-1))
+            if i < len(cts):
+                p.copy_(cts[i].data.view(-1))
         h_acc = torch.empty(blk, dtype=torch.int64).pin_memory()
         h2d = len(my_clients) * blk * 8
         d2h = blk * 8 if rank == 0 else 0
+        nk = len(keys)
+        rks = (vp * max(1, nk))(*[k.h for k in keys])
+        ptrs = (vp * max(1, nk))(*[pool[i % pool_n].data_ptr() for i in range(nk)])
         if world == 1:
-            rks = (vp * len(keys))(*[k.h for k in keys])
-            ptrs = (vp * len(keys))(*[pool[i % pool_n].data_ptr() for i in range(len(keys))])
-
             def e2e_step():
-                check(lib().ppq_reencrypt_aggregate_host(cc.h, rks, ell, ptrs, len(keys), n_slots, vp(h_acc.data_ptr())))
+                check(lib().ppq_reencrypt_aggregate_host(cc.h, rks, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
         else:
-            side = torch.cuda.Stream()
-            dbuf = [torch.empty((n_slots, 2, ell, N), dtype=torch.int64, device=dev) for _ in range(2)]
-            up = [torch.cuda.Event() for _ in range(2)]
-            done = [torch.cuda.Event() for _ in range(2)]
-
             def e2e_step():
-                main_s = torch.cuda.current_stream()
-                acc.data.zero_()
-                for i, rk in enumerate(keys):
-                    b = i & 1
-                    with torch.cuda.stream(side):
-                        if i >= 2:
-                            side.wait_event(done[b])
-                        dbuf[b].view(-1).copy_(pool[i % pool_n], non_blocking=True)
-                        up[b].record(side)
-                    main_s.wait_event(up[b])
-                    cc.ReEncryptAccumulate(CiphertextBatch(dbuf[b], CtMeta()), rk, acc)
-                    done[b].record(main_s)
-                reduce_partial_sums(acc.data, world, dst=0)
-                if rank == 0:
-                    cc.finalize_sum(acc)
-                    h_acc.copy_(acc.data.view(-1), non_blocking=True)
-                torch.cuda.synchronize()
+                check(lib().ppq_reencrypt_aggregate_host_ranks(cc.h, comm.h, 0, rks, ell, ptrs, nk, n_slots,
+                                                               vp(h_acc.data_ptr())))
+
+        def copy_step():
+            check(lib().ppq_copy_ceiling_host(cc.h, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
 
         for _ in range(args.warmup):
             e2e_step()
         e_ms = timed(e2e_step, args.steps)
+        copy_step()
+        c_ms = timed(copy_step, args.steps)
         tot = torch.tensor([float(h2d), float(d2h)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(tot)
-        e2e = {"value": n_ct_step / (e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(tot[0].item()),
+        bytes_step = float(tot[0].item() + tot[1].item())
+        e_val = n_ct_step / (e_ms / args.steps * 1e-3)
+        c_val = n_ct_step / (c_ms / args.steps * 1e-3)
+        e2e = {"value": e_val, "unit": UNIT, "h2d_bytes_per_step": int(tot[0].item()),
                "d2h_bytes_per_step": int(tot[1].item()), "ms_per_step": e_ms / args.steps,
                "api": "ppq_reencrypt_aggregate_host (C ABI, pinned host buffers)" if world == 1 else
-                      "CryptoContext.ReEncryptAccumulate over pinned host buffers + NCCL reduce",
+                      "ppq_reencrypt_aggregate_host_ranks (C ABI, pinned host buffers, ends in ppq_reduce_across_ranks)",
                "note": f"every client's {blk * 8 >> 20} MiB upload is copied each step from a pool of {pool_n} pinned buffers",
-               "host_cpus_near_gpu": near_cpus}
+               "host_cpus_near_gpu": near_cpus,
+               "copy_gbs": bytes_step / (e_ms / args.steps * 1e-3) / 1e9,
+               "h2d_ceiling_gbs": bytes_step / (c_ms / args.steps * 1e-3) / 1e9,
+               "ceiling_value": c_val, "frac_of_copy_ceiling": e_val / c_val,
+               "ceiling_note": "ppq_copy_ceiling_host: the same pinned pools, streams and copies with no kernel launched"}
         del pool, h_acc
         if old_aff is not None:
             os.sched_setaffinity(0, old_aff)  # the CPU baseline below uses every host core again
 
+    # ---- the other BASELINE.json configurations, C5 and the client half: N = 1 only, after the headline is measured
+    del R, cts, keys
+    torch.cuda.empty_cache()
+    extras = {}
+    if world == 1 and not args.no_extras:
+        for name in ("c1", "c2", "c4"):
+            if name == args.config:
+                continue
+            try:
+                extras[name] = side_config(torch, name)
+            except Exception as e:  # an extra must never take the headline down
+                extras[name] = {"error": repr(e)}
+        try:
+            extras["c5_ntt_sweep"] = ntt_sweep_summary(torch)
+        except Exception as e:
+            extras["c5_ntt_sweep"] = {"error": repr(e)}
+        client = {}
+        for name, n_ct in (("c1", 216), ("c3", 54)):
+            try:
+                client[name] = client_leg(torch, name, n_ct)
+            except Exception as e:
+                client[name] = {"error": repr(e)}
+        extras["client"] = client
+
     # ---- CPU baseline on rank 0, N = 1 only
     cpu = None
     if world == 1 and not args.no_cpu:
-        del cts, keys
-        torch.cuda.empty_cache()
         r = cpu_run(cfg, 1, 1)
         cpu = {k: v for k, v in r.items() if not k.startswith("_") and k != "ms_per_step"}
 
@@ -482,10 +672,17 @@ def main():
                        "limbs": ell, "aux_limbs": K, "dnum": cc.dnum, "parallelism": f"clients sharded over {world} GPU(s)",
                        "l2": "inputs per step (%.1f GiB per GPU) >> 126 MB L2; no flush needed" %
                              (len(my_clients) * n_slots * 2 * ell * N * 8 / 2 ** 30),
-                       "residues": "uniform random canonical residues (timing is data independent)"},
+                       "residues": "uniform random canonical residues (timing is data independent)",
+                       "algorithm": "ppq_agg_*: per client ModUp + key inner product + inverse NTT of the P limbs; the "
+                                    "linear tail of ModDown (P->Q conversion, forward NTT, subtraction) runs on sums over "
+                                    "clients; output bit-identical to per-client ReEncrypt then EvalAdd"},
             "roofline": roofline, "ntt": ntt, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
+            "configs": {k: v for k, v in extras.items() if k in ("c1", "c2", "c3", "c4")},
+            "c5_ntt_sweep": extras.get("c5_ntt_sweep"), "client": extras.get("client"),
         }
         print(json.dumps(line), flush=True)
+    if comm is not None:
+        comm.close()
     if world > 1:
         dist.destroy_process_group()
 

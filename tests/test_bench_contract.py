@@ -41,3 +41,9 @@ def test_algorithmic_bytes_match_survey():
     w = bench.stage_alg_words(20, 7, 3, 54, split=True)
     assert len(w) == 11 and w[0] == 40 and w[3] == 2 * 61 and w[10] == 180
     assert bench.stage_alg_words(20, 7, 3, 54, split=False)[4] == 0
+    # deferred-ModDown pipeline (ppq_agg_*): the inner product also reads c0 and read-modify-writes the EVAL sum; the
+    # conversion runs per group of 8 clients, the last two stages once per slot
+    a = bench.stage_alg_words(20, 7, 3, 54, agg=True, group=8, clients=64)
+    assert len(a) == 11 and a[:5] == w[:5] and a[6:8] == w[6:8]
+    assert abs(a[5] - (61 + 20 + 2 * 3 * 27 / 54 + 20 + 80 + 14)) < 1e-9
+    assert a[8] == 14 + 10 and abs(a[9] - 80 / 64) < 1e-9 and abs(a[10] - 120 / 64) < 1e-9
