@@ -120,5 +120,55 @@ def traffic(path, n_cts=54, tag=""):
     print(json.dumps({"c3": {"wave_cts": n_cts, "source": tag or path, "dram_bytes_per_ct": per}}, indent=1))
 
 
+def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, tag=""):
+    """Deferred-ModDown pipeline (ppq_agg_*): the capture holds the LAST client's add of a step of `cap_clients`
+    clients, the group conversion (k_bconv_wide x2) and ppq_agg_finish (k_fwd_col2, k_fwd_row_moddown2), in launch
+    order.  Prints the profiles/ncu_traffic.json + ncu_int_pipe.json content: DRAM bytes per ciphertext and stage, the
+    path total for a GPU that aggregates `job_clients` clients, and fmaheavy % per stage."""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    n_slots, cap_clients, job_clients, group = int(n_slots), int(cap_clients), int(job_clients), int(group)
+    stages = ["k_inv_row(c1)", "k_inv_col(c1,scale)", "k_bconv(modup)", "k_fwd_col(modup)", "k_fwd_row(modup)",
+              "k_ip_tma|k_fwd_row_ip", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
+              "k_fwd_row_moddown"]
+    per_launch = dict.fromkeys(stages, 0.0)
+    fma = {}
+    tms = dict.fromkeys(stages, 0.0)
+    si, prev = -1, None
+    for r in data:
+        n = short(r[idx["Kernel Name"]])
+        fam = n.split("<")[0]
+        if fam != prev or not fam.startswith("k_bconv"):
+            si += 1
+        prev = fam
+        b = sum(float(r[idx[k]].replace(",", "")) * mult[units[idx[k]]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        per_launch[stages[si]] += b
+        f = float(r[idx["sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed"]].replace(",", ""))
+        t = float(r[idx["gpu__time_duration.sum"]].replace(",", ""))
+        fma[stages[si]] = max(fma.get(stages[si], 0.0), f)
+        tms[stages[si]] += t
+    assert si == len(stages) - 1, f"expected one add + group conversion + finish, got {si + 1} stages"
+    div = {s: n_slots for s in stages}
+    div["k_bconv(moddown)"] = n_slots * group
+    per_ct_cap = {}
+    path = 0.0
+    for s in stages:
+        d = div[s]
+        if s in ("k_fwd_col(moddown)", "k_fwd_row_moddown"):
+            per_ct_cap[s] = per_launch[s] / (n_slots * cap_clients)
+            path += per_launch[s] / (n_slots * job_clients)
+        else:
+            per_ct_cap[s] = per_launch[s] / d
+            path += per_launch[s] / d
+    print(json.dumps({"traffic": {"c3": {"wave_cts": n_slots, "source": tag or path, "capture_clients": cap_clients,
+                                         "job_clients": job_clients, "group": group, "dram_bytes_per_ct": per_ct_cap,
+                                         "path_dram_bytes_per_ct": path}},
+                      "int_pipe": fma}, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])
+    {"launches": launches, "full": full, "traffic": traffic, "traffic_agg": traffic_agg}[sys.argv[1]](*sys.argv[2:])
