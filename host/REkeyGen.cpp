@@ -1,6 +1,6 @@
 // REkeyGen -- drop-in for the reference's client/src/REkeyGen.cpp (same argv, exit codes, progress lines, cereal-JSON
 // key files), with cc->ReKeyGen(privKey, pubKey) (:52) replaced by ppq_sample_encrypt_noise + ppq_rekeygen through the
-// C ABI of libppq_b200.so.  Seed: std::random_device unless PPQ_SEED is set (tests).  No CPU fallback.
+// C ABI of libppq_b200.so.  Sampler key: 256 bits from getrandom(2) inside the library per call; PPQ_SEED is a test-only override.  No CPU fallback.
 #include <random>
 
 #include "ppq_session.hpp"
@@ -45,20 +45,14 @@ int main(int argc, char* argv[]) {
         std::cout << "[ReKeyGen] Peer Public Key loaded from " << client_pk << std::endl;
 
         // reference :52 -- dnum digits of (u, e0, e1) drawn on the device, then the key itself
-        uint64_t seed;
-        if (const char* e = std::getenv("PPQ_SEED")) {
-            seed = std::strtoull(e, nullptr, 0);
-        } else {
-            std::random_device rd;
-            seed = ((uint64_t)rd() << 32) ^ rd();
-        }
+        const ppqhost::SamplerSeed seed;  // NULL (fresh OS entropy per call) unless the test-only PPQ_SEED is set
         Dev<uint64_t> d_sk(L * N), d_pkb(M * N), d_pka(M * N), d_kb(dnum * M * N), d_ka(dnum * M * N);
         Dev<int64_t> d_small(dnum * 3 * N);
         d_sk.upload(sk.data(), sk.size());
         d_pkb.upload(pkb.data(), pkb.size());
         d_pka.upload(pka.data(), pka.size());
         try {
-            ck(ppq_sample_encrypt_noise(s->cc, seed, d_small.p, dnum, nullptr), "ppq_sample_encrypt_noise");
+            ck(ppq_sample_encrypt_noise(s->cc, seed.ptr(), d_small.p, dnum, nullptr), "ppq_sample_encrypt_noise");
             ck(ppq_rekeygen(s->cc, d_sk.p, d_pkb.p, d_pka.p, d_small.p, d_kb.p, d_ka.p, nullptr), "ppq_rekeygen");
             ck(ppq_sync(s->cc, nullptr), "ppq_sync");
         } catch (const std::exception& e) {

@@ -86,14 +86,8 @@ int main(int argc, char* argv[]) {
             d_vals.upload(vals.data(), vals.size());
             d_b.upload(pkb.data(), pkb.size());
             d_a.upload(pka.data(), pka.size());
-            uint64_t seed;
-            if (const char* e = std::getenv("PPQ_SEED")) {
-                seed = std::strtoull(e, nullptr, 10);  // reproducible runs for tests
-            } else {
-                std::random_device rd;
-                seed = ((uint64_t)rd() << 32) ^ rd();
-            }
-            ck(ppq_sample_encrypt_noise(s->cc, seed, d_small.p, n, nullptr), "ppq_sample_encrypt_noise");
+            const ppqhost::SamplerSeed seed;  // NULL (fresh OS entropy per call) unless the test-only PPQ_SEED is set
+            ck(ppq_sample_encrypt_noise(s->cc, seed.ptr(), d_small.p, n, nullptr), "ppq_sample_encrypt_noise");
             const size_t step = std::max<size_t>(1, 65535 / (3 * ell));
             for (size_t k0 = 0; k0 < n; k0 += step) {
                 const size_t k1 = std::min(n, k0 + step);

@@ -1,6 +1,6 @@
 // keyGen -- drop-in for the reference's client/src/keyGen.cpp (same argv, exit codes, progress lines, cereal-JSON key
 // files), with cc->KeyGen() (:33) replaced by ppq_sample_keygen + ppq_keygen through the C ABI of libppq_b200.so.
-// The seed comes from std::random_device unless PPQ_SEED is set (tests).  No CPU fallback.
+// Sampler key: 256 bits from getrandom(2) inside the library per call; PPQ_SEED is a test-only override.  No CPU fallback.
 #include <random>
 
 #include "ppq_session.hpp"
@@ -25,17 +25,11 @@ int main(int argc, char* argv[]) {
         std::cout << "[keyGen] CryptoContext loaded from " << cc_path << std::endl;
 
         // Step 2: key pair (reference :33-38), sampled and computed on the device
-        uint64_t seed;
-        if (const char* e = std::getenv("PPQ_SEED")) {
-            seed = std::strtoull(e, nullptr, 0);
-        } else {
-            std::random_device rd;
-            seed = ((uint64_t)rd() << 32) ^ rd();
-        }
+        const ppqhost::SamplerSeed seed;  // NULL (fresh OS entropy per call) unless the test-only PPQ_SEED is set
         const size_t N = s->N, L = (size_t)s->L, M = L + (size_t)s->K;
         Dev<int64_t> d_s(N), d_e(N);
         Dev<uint64_t> d_a(M * N), d_sk(L * N), d_pkb(M * N);
-        ck(ppq_sample_keygen(s->cc, seed, d_s.p, d_e.p, d_a.p, nullptr), "ppq_sample_keygen");
+        ck(ppq_sample_keygen(s->cc, seed.ptr(), d_s.p, d_e.p, d_a.p, nullptr), "ppq_sample_keygen");
         ck(ppq_keygen(s->cc, d_s.p, d_e.p, d_a.p, d_sk.p, d_pkb.p, nullptr), "ppq_keygen");
         ck(ppq_sync(s->cc, nullptr), "ppq_sync");
         std::vector<uint64_t> sk(L * N), pkb(M * N), pka(M * N);

@@ -6,6 +6,8 @@
 
 #include <cstdio>
 #include <iostream>
+#include <cstdlib>
+#include <cstring>
 #include <map>
 #include <stdexcept>
 #include <string>
@@ -126,5 +128,23 @@ inline void encode_back(const Session& s, const Batch& b, uint32_t ell_out, cons
     for (size_t k = 0; k < b.n(); ++k)
         *refs[b.index[k]].slot = wire::encode_ct(meta[k], ell_out, (uint32_t)s.N, s.moduli.data(), data.data() + k * ct);
 }
+
+// Key material for the device samplers.  Production: NULL, i.e. the library draws a fresh 256-bit ChaCha20 key from
+// getrandom(2) for every call.  PPQ_SEED (an integer) is a TEST-ONLY switch for reproducible runs: it is widened to
+// 32 bytes, `salt` separating the calls of one process.  Never set it when generating real keys or ciphertexts.
+struct SamplerSeed {
+    uint8_t bytes[32];
+    bool fixed = false;
+    explicit SamplerSeed(uint64_t salt = 0) {
+        std::memset(bytes, 0, sizeof(bytes));
+        if (const char* e = std::getenv("PPQ_SEED")) {
+            const uint64_t v = std::strtoull(e, nullptr, 0);
+            std::memcpy(bytes, &v, 8);
+            std::memcpy(bytes + 8, &salt, 8);
+            fixed = true;
+        }
+    }
+    const uint8_t* ptr() const { return fixed ? bytes : nullptr; }
+};
 
 }  // namespace ppqhost

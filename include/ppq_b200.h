@@ -125,8 +125,14 @@ int ppq_encode(ppq_ctx*, int ell, const double* d_vals, size_t n_vals, double sf
  *      d_pkb / d_pka: [>=ell][N] EVAL (first ell limbs of the QP public key). */
 int ppq_encrypt(ppq_ctx*, int ell, const uint64_t* d_pkb, const uint64_t* d_pka, const uint64_t* d_pt,
                 const int64_t* d_small, uint64_t* d_ct, size_t n, void* stream);
-/* fills d_small [n][3][N] with (ternary, gauss, gauss) samples (counter-based generator, sigma = 3.19) */
-int ppq_sample_encrypt_noise(ppq_ctx*, uint64_t seed, int64_t* d_small, size_t n, void* stream);
+/* fills d_small [n][3][N] with (ternary, discrete Gaussian sigma 3.19, Gaussian) polynomials: ChaCha20 streams keyed
+ * by seed32 (32 bytes), one stream per polynomial; ternary by rejection on 2-bit draws, Gaussian by inversion of a
+ * 64-bit cumulative table (csrc/sampler.cu).  seed32 == NULL draws a fresh 256-bit key from getrandom(2) for this
+ * call -- the only mode for real keys and ciphertexts; a caller-supplied seed is for tests and reproducible runs. */
+int ppq_sample_encrypt_noise(ppq_ctx*, const uint8_t* seed32, int64_t* d_small, size_t n, void* stream);
+/* the samplers' generator, exposed for known-answer tests: one ChaCha20 block (RFC 8439 2.3), computed on the host
+ * by the same inline function the device kernels use */
+int ppq_chacha20_block(const uint32_t* key8, uint32_t counter, const uint32_t* nonce3, uint32_t* out16);
 /* ---- cc->Decrypt(privateKey, ct, &pt) core (client/src/decryptModelWeights.cpp:81,90,108):
  *      d_coeff [n][ell][N] = COEFF residues of c0 + c1*s.  d_sk: [>=ell][N] EVAL. */
 int ppq_decrypt_core(ppq_ctx*, int ell, const uint64_t* d_sk, const uint64_t* d_ct, uint64_t* d_coeff, size_t n,
@@ -141,8 +147,10 @@ int ppq_decode(ppq_ctx*, int ell, const uint64_t* d_coeff, double sf, double* d_
  *      d_pkb [L+K][N] = e - a*s.  The public key is the pair (d_pkb, d_a) over QP. */
 int ppq_keygen(ppq_ctx*, const int64_t* d_s, const int64_t* d_e, const uint64_t* d_a, uint64_t* d_sk,
                uint64_t* d_pkb, void* stream);
-/* draws ppq_keygen's inputs on the device (counter-based generator; uniform residues by rejection) */
-int ppq_sample_keygen(ppq_ctx*, uint64_t seed, int64_t* d_s, int64_t* d_e, uint64_t* d_a, void* stream);
+/* draws ppq_keygen's inputs on the device.  The secret half (s, e) and the public half (a, uniform residues by
+ * rejection) come from DIFFERENT ChaCha20 keys -- two independent getrandom(2) draws when seed32 == NULL, two
+ * KDF sub-keys of seed32 otherwise (tests) -- so the published `a` carries no information about s. */
+int ppq_sample_keygen(ppq_ctx*, const uint8_t* seed32, int64_t* d_s, int64_t* d_e, uint64_t* d_a, void* stream);
 /* ---- cc->ReKeyGen(oldPrivateKey, newPublicKey) (client/src/REkeyGen.cpp:52; OpenFHE keyswitch-hybrid.cpp
  *      KeySwitchGenInternal(oldSk, newPk)): per level-0 digit j, b_j = pk.b*u + e0 + (P mod q_r)*s_old on the
  *      limbs of digit j, a_j = pk.a*u + e1.  d_sk_old [L][N], d_pkb / d_pka [L+K][N] (EVAL);

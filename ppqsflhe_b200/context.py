@@ -31,6 +31,18 @@ def _stream():
     return vp(torch.cuda.current_stream().cuda_stream)
 
 
+def _seed32(seed):
+    """None -> NULL (the library draws a fresh 256-bit key from the OS for this call); an int or bytes -> 32 bytes of
+    key material for tests and reproducible runs."""
+    if seed is None:
+        return None
+    if isinstance(seed, (bytes, bytearray)):
+        if len(seed) != 32:
+            raise ValueError("a byte seed must be 32 bytes")
+        return bytes(seed)
+    return int(seed).to_bytes(32, "little", signed=False)
+
+
 def to_device_u64(a, device):
     """numpy uint64 array -> torch int64 CUDA tensor with the same bits."""
     a = np.ascontiguousarray(a, dtype=np.uint64)
@@ -356,14 +368,20 @@ class CryptoContext:
         meta = CtMeta(noise_scale_deg=2, level=0, scaling_factor=sf, slots=self.N // 2)
         return PlaintextBatch(data=pt, meta=meta)
 
-    def Encrypt(self, pk, pt, small=None, seed=0):
+    def Encrypt(self, pk, pt, small=None, seed=None):
         """pk = (b, a) CUDA int64 [>=ell][N] each (QP public key; only the first ell limbs are used).
-        small: optional CUDA int64 [n][3][N] = injected (v, e0, e1) samples; sampled on the device otherwise."""
+        small: optional CUDA int64 [n][3][N] = injected (v, e0, e1) samples; sampled on the device otherwise, under a
+        fresh OS-entropy key per call unless `seed` (tests only: a fixed seed repeats the same noise) is given."""
         b, a = pk
         n, ell = pt.data.shape[0], pt.data.shape[1]
         if small is None:
             small = torch.empty((n, 3, self.N), dtype=torch.int64, device=self.device)
-            check(lib().ppq_sample_encrypt_noise(self.h, int(seed), _ptr(small), n, _stream()))
+            for s0 in range(0, n, 16384):  # one key per call of the library: chunks of a seeded draw get distinct seeds
+                e0 = min(n, s0 + 16384)
+                sd = _seed32(seed)
+                if sd is not None and s0:
+                    sd = _seed32((int.from_bytes(sd, "little") + s0) % (1 << 256))
+                check(lib().ppq_sample_encrypt_noise(self.h, sd, _ptr(small[s0:e0]), e0 - s0, _stream()))
         ct = self.empty_cts(n, ell)
         step = max(1, 65535 // (3 * ell))
         for s in range(0, n, step):
@@ -372,15 +390,15 @@ class CryptoContext:
                                     e - s, _stream()))
         return CiphertextBatch(ct, replace(pt.meta))
 
-    def KeyGen(self, seed=0, samples=None):
+    def KeyGen(self, seed=None, samples=None):
         """cc->KeyGen() (client/src/keyGen.cpp:33).  Returns (sk [L][N], (pk_b, pk_a) [L+K][N] each), CUDA int64, EVAL.
         samples: optional (s [N] int64, e [N] int64, a [L+K][N]) CUDA tensors injected for parity tests; drawn on
-        the device from `seed` otherwise."""
+        the device otherwise (fresh OS entropy per call; `seed` is for tests only)."""
         if samples is None:
             s = torch.empty(self.N, dtype=torch.int64, device=self.device)
             e = torch.empty_like(s)
             a = torch.empty((self.M, self.N), dtype=torch.int64, device=self.device)
-            check(lib().ppq_sample_keygen(self.h, int(seed), _ptr(s), _ptr(e), _ptr(a), _stream()))
+            check(lib().ppq_sample_keygen(self.h, _seed32(seed), _ptr(s), _ptr(e), _ptr(a), _stream()))
         else:
             s, e, a = samples
             if tuple(s.shape) != (self.N,) or tuple(e.shape) != (self.N,) or tuple(a.shape) != (self.M, self.N):
@@ -390,7 +408,7 @@ class CryptoContext:
         check(lib().ppq_keygen(self.h, _ptr(s), _ptr(e), _ptr(a), _ptr(sk), _ptr(pkb), _stream()))
         return sk, (pkb, a)
 
-    def ReKeyGen(self, sk_old, pk_new, seed=0, small=None):
+    def ReKeyGen(self, sk_old, pk_new, seed=None, small=None):
         """cc->ReKeyGen(oldPrivateKey, newPublicKey) (client/src/REkeyGen.cpp:52) -> EvalKey resident on the device.
         small: optional CUDA int64 [dnum][3][N] = injected (u, e0, e1) per digit."""
         b, a = pk_new
@@ -398,7 +416,7 @@ class CryptoContext:
             raise ValueError("ReKeyGen: sk_old must be [L][N] and the public key two [L+K][N] tensors")
         if small is None:
             small = torch.empty((self.dnum, 3, self.N), dtype=torch.int64, device=self.device)
-            check(lib().ppq_sample_encrypt_noise(self.h, int(seed), _ptr(small), self.dnum, _stream()))
+            check(lib().ppq_sample_encrypt_noise(self.h, _seed32(seed), _ptr(small), self.dnum, _stream()))
         elif tuple(small.shape) != (self.dnum, 3, self.N):
             raise ValueError("ReKeyGen: small must be [dnum][3][N]")
         kb = torch.empty((self.dnum, self.M, self.N), dtype=torch.int64, device=self.device)

@@ -2,6 +2,7 @@
 // orchestration of kernel launches for each reference-facing operation.  No CPU fallback: every compute entry
 // point needs a CUDA device and fails loudly otherwise.
 #include <dlfcn.h>
+#include <sys/random.h>
 
 #include <cmath>
 #include <cstdio>
@@ -16,6 +17,7 @@
 #include "ckks.cuh"
 #include "kernels.cuh"
 #include "params.hpp"
+#include "sampler.cuh"
 
 using namespace ppq;
 
@@ -97,6 +99,7 @@ struct ppq_ctx {
     DevBuf<u64> ids_scale; // [n][4] output factor N^-1 per poly (host::scale4)
     std::vector<u64> ntt_scale4;  // [L+K][4], built on first use
     DevBuf<u64> fac;       // [2][L] EvalMult factors
+    DevBuf<int> kinds3;    // {ternary, gauss, gauss}: the polynomial kinds of one (v, e0, e1) / (u, e0, e1) triple
     ckks::Tables fft;
     int wave = 0;
     bool ip_split = true;  // inner product as k_fwd_row_plain + k_ip_tma + k_inv_row (PPQ_IP_FUSED=1: one fused kernel)
@@ -171,6 +174,8 @@ static int ctx_finish(std::unique_ptr<ppq_ctx>& c, int device, ppq_ctx** out) {
     }
     std::string err;
     if (!ckks::build_tables(hp.logN, c->fft, err)) return fail(PPQ_ECUDA, err);
+    CU(c->kinds3.upload(std::vector<int>{0, 1, 1}));
+    CU(sampler::upload_gauss_table(device, 3.19));
     *out = c.release();
     return PPQ_OK;
 }
@@ -843,11 +848,35 @@ extern "C" int ppq_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint6
     return PPQ_OK;
 }
 
-extern "C" int ppq_sample_encrypt_noise(ppq_ctx* c, uint64_t seed, int64_t* d_small, size_t n, void* stream) {
+// known-answer hook for the samplers' generator (RFC 8439 section 2.3.2 vector in tests/test_capi_exports.py); host only
+extern "C" int ppq_chacha20_block(const uint32_t* key8, uint32_t counter, const uint32_t* nonce3, uint32_t* out16) {
+    if (!key8 || !nonce3 || !out16) return fail(PPQ_EINVAL, "ppq_chacha20_block: null argument");
+    sampler::chacha20_block_host(key8, counter, nonce3, out16);
+    return PPQ_OK;
+}
+// 32 bytes of key material for the samplers: the caller's (tests, reproducible runs) or fresh OS entropy per call
+static int sampler_key(const uint8_t* seed32, sampler::Key& k) {
+    if (seed32) {
+        std::memcpy(k.w, seed32, 32);
+        return PPQ_OK;
+    }
+    size_t got = 0;
+    while (got < 32) {
+        const ssize_t r = getrandom(reinterpret_cast<uint8_t*>(k.w) + got, 32 - got, 0);
+        if (r < 0) return fail(PPQ_EINVAL, "getrandom failed: no entropy source for key material");
+        got += (size_t)r;
+    }
+    return PPQ_OK;
+}
+extern "C" int ppq_sample_encrypt_noise(ppq_ctx* c, const uint8_t* seed32, int64_t* d_small, size_t n, void* stream) {
     if (!c || !d_small) return fail(PPQ_EINVAL, "ppq_sample_encrypt_noise: null argument");
     if (n == 0) return PPQ_OK;
+    if (n * 3 > 65535) return fail(PPQ_EINVAL, "ppq_sample_encrypt_noise: at most 21845 triples per call");
     CU(cudaSetDevice(c->device));
-    ckks::launch_sample_noise(seed, d_small, c->hp.N, n, 3.19, (cudaStream_t)stream);
+    sampler::Key master;
+    if (int rc = sampler_key(seed32, master)) return rc;
+    const sampler::Key k = sampler::derive_key(master, 0x454e4352u /* "ENCR" */);
+    sampler::launch_sample_small(k, sampler::DOM_SMALL, 0, c->kinds3.p, 3, d_small, c->hp.N, n * 3, (cudaStream_t)stream);
     CU(cudaGetLastError());
     return PPQ_OK;
 }
@@ -884,19 +913,26 @@ extern "C" int ppq_keygen(ppq_ctx* c, const int64_t* d_s, const int64_t* d_e, co
     return PPQ_OK;
 }
 
-extern "C" int ppq_sample_keygen(ppq_ctx* c, uint64_t seed, int64_t* d_s, int64_t* d_e, uint64_t* d_a, void* stream) {
+extern "C" int ppq_sample_keygen(ppq_ctx* c, const uint8_t* seed32, int64_t* d_s, int64_t* d_e, uint64_t* d_a, void* stream) {
     if (!c || !d_s || !d_e || !d_a) return fail(PPQ_EINVAL, "ppq_sample_keygen: null argument");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t N = c->hp.N;
-    CU(c->scratch2.ensure(3 * N));
-    int64_t* t = reinterpret_cast<int64_t*>(c->scratch2.p);  // (ternary, gauss, gauss)
-    ckks::launch_sample_noise(seed, t, N, 1, 3.19, st);
-    CU(cudaMemcpyAsync(d_s, t, N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
-    CU(cudaMemcpyAsync(d_e, t + N, N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
-    ckks::launch_sample_uniform(seed ^ 0xA5A5A5A5A5A5A5A5ull, c->k, c->hp.M(), d_a, st);
+    // the secret half (s, e) and the public half (a) are drawn under DIFFERENT keys: sub-keys of the seed by a
+    // domain-separated KDF, or two independent 256-bit draws from the OS when no seed is given
+    sampler::Key ksec, kpub;
+    if (seed32) {
+        sampler::Key master;
+        if (int rc = sampler_key(seed32, master)) return rc;
+        ksec = sampler::derive_key(master, 0x53454352u /* "SECR" */);
+        kpub = sampler::derive_key(master, 0x5055424cu /* "PUBL" */);
+    } else {
+        if (int rc = sampler_key(nullptr, ksec)) return rc;
+        if (int rc = sampler_key(nullptr, kpub)) return rc;
+    }
+    sampler::launch_sample_small(ksec, sampler::DOM_SMALL, 0, c->kinds3.p, 1, d_s, c->hp.N, 1, st);      // ternary
+    sampler::launch_sample_small(ksec, sampler::DOM_SMALL, 1, c->kinds3.p + 1, 1, d_e, c->hp.N, 1, st);  // Gaussian
+    sampler::launch_sample_uniform(kpub, sampler::DOM_UNIFORM, c->k, c->hp.M(), d_a, st);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 

@@ -1,4 +1,4 @@
-// ckks.cu -- CKKS encode/decode kernels (FP64 special FFT) and the noise sampler.  See ckks.cuh.
+// ckks.cu -- CKKS encode/decode kernels (FP64 special FFT).  See ckks.cuh; the samplers live in sampler.cu.
 // Client-side path (encryptModelWeights / decryptModelWeights): one launch per FFT stage over the whole batch.
 #include "ckks.cuh"
 
@@ -174,56 +174,6 @@ void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, co
     for (unsigned len = 2; len <= Nh; len <<= 1)
         k_fft_fwd_stage<<<grid_for(Nh / 2, n), 256, 0, st>>>(z, Nh, len, t.rot, t.ksi, m);
     k_take_real<<<grid_for(Nh, n), 256, 0, st>>>(z, d_vals, Nh);
-}
-
-// ---- counter-based sampler (splitmix64 of (seed, index)); ternary / rounded Gaussian (Box-Muller)
-__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
-    z += 0x9E3779B97F4A7C15ULL;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-    return z ^ (z >> 31);
-}
-__global__ void k_sample_noise(unsigned long long seed, long long* __restrict__ out, size_t N, double sigma) {
-    const size_t g = blockIdx.y;
-    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * N; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t which = i / N;
-        const unsigned long long ctr = (g * 3 * N + i) * 2;
-        const unsigned long long r1 = mix64(seed ^ mix64(ctr)), r2 = mix64(seed ^ mix64(ctr + 1));
-        long long v;
-        if (which == 0) {
-            v = (long long)(r1 % 3) - 1;
-        } else {
-            const double u1 = ((double)(r1 >> 11) + 1.0) / 9007199254740993.0;
-            const double u2 = (double)(r2 >> 11) / 9007199254740992.0;
-            v = llround(sigma * sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
-        }
-        out[g * 3 * N + i] = v;
-    }
-}
-// uniform residues mod q_r for every limb r of QP (the `a` half of a public key): bits(q_r) random bits per draw,
-// rejected while >= q_r (at most a few rounds; after 64 the draw is reduced instead -- probability 2^-64)
-__global__ void k_sample_uniform(unsigned long long seed, KCtx c, unsigned long long* __restrict__ out) {
-    const size_t N = (size_t)1 << c.logN;
-    const int r = blockIdx.y;
-    const unsigned long long q = c.limbs[r].q;
-    const int drop = __clzll(q);
-    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
-        const unsigned long long ctr = mix64(((unsigned long long)r * N + i) * 64);
-        unsigned long long v = 0;
-        int t = 0;
-        for (; t < 64; ++t) {
-            v = mix64(seed ^ (ctr + t)) >> drop;
-            if (v < q) break;
-        }
-        out[(size_t)r * N + i] = t < 64 ? v : v % q;
-    }
-}
-void launch_sample_uniform(uint64_t seed, const KCtx& k, int n_limbs, uint64_t* d_out, cudaStream_t st) {
-    const unsigned N = 1u << k.logN;
-    k_sample_uniform<<<grid_for(N, n_limbs), 256, 0, st>>>(seed, k, (unsigned long long*)d_out);
-}
-void launch_sample_noise(uint64_t seed, int64_t* d_small, size_t N, size_t n, double sigma, cudaStream_t st) {
-    k_sample_noise<<<grid_for(3 * N, n), 256, 0, st>>>(seed, (long long*)d_small, N, sigma);
 }
 
 }  // namespace ckks

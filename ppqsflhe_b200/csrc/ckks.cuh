@@ -27,11 +27,6 @@ void launch_encode_fft(const Tables& t, const double* d_vals, size_t n_vals, dou
 // coeff [n][ell][N] canonical COEFF residues -> vals [n][N/2]
 void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const double* d_unused,
                    double sf, double2* z, double* d_vals, size_t n, cudaStream_t st);
-// small [n][3][N]: ternary, gauss(sigma), gauss(sigma)
-void launch_sample_noise(uint64_t seed, int64_t* d_small, size_t N, size_t n, double sigma, cudaStream_t st);
-// out [n_limbs][N]: uniform residues mod q_r, r = 0..n_limbs-1 (rejection sampling)
-void launch_sample_uniform(uint64_t seed, const KCtx& k, int n_limbs, uint64_t* d_out, cudaStream_t st);
-
 }  // namespace ckks
 
 // plain forward ROW pass over [n_g] blocks of n_slots polys; slots whose limb id is negative are skipped

@@ -76,3 +76,28 @@ def test_product_never_imports_the_oracle():
                 text = open(os.path.join(base, f), errors="ignore").read()
                 assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f
                 assert "ppq_oracle" not in text and "ppqo_" not in text, f
+
+
+def test_sampler_generator_is_chacha20_rfc8439_vector():
+    """The samplers (csrc/sampler.cu) draw from ChaCha20: the block function must reproduce RFC 8439 section 2.3.2."""
+    from ppqsflhe_b200 import _capi
+    L = _capi.lib()
+    key = (C.c_uint32 * 8)(*[int.from_bytes(bytes(range(4 * i, 4 * i + 4)), "little") for i in range(8)])
+    nonce = (C.c_uint32 * 3)(0x09000000, 0x4A000000, 0x00000000)
+    out = (C.c_uint32 * 16)()
+    assert L.ppq_chacha20_block(key, 1, nonce, out) == 0
+    want = [0xE4E7F110, 0x15593BD1, 0x1FDD0F50, 0xC47120A3, 0xC7F4D1C7, 0x0368C033, 0x9AAA2204, 0x4E6CD4C3,
+            0x466482D2, 0x09AA9F07, 0x05D7C214, 0xA2028BD9, 0xD19C12B5, 0xB94E16DE, 0xE883D0CB, 0x4E3C50A2]
+    assert list(out) == want
+
+
+def test_python_mirror_defaults_to_os_entropy():
+    """KeyGen / Encrypt / ReKeyGen must not default to a constant seed: seed=None -> NULL -> the library
+    draws a fresh 256-bit key from getrandom(2) per call."""
+    import inspect
+    from ppqsflhe_b200 import context
+    for fn in (context.CryptoContext.KeyGen, context.CryptoContext.Encrypt, context.CryptoContext.ReKeyGen):
+        assert inspect.signature(fn).parameters["seed"].default is None
+    assert context._seed32(None) is None and len(context._seed32(5)) == 32
+    src = open(os.path.join(ROOT, "ppqsflhe_b200", "csrc", "capi.cu")).read()
+    assert "getrandom(" in src and "splitmix" not in open(os.path.join(ROOT, "ppqsflhe_b200", "csrc", "sampler.cu")).read()

@@ -643,3 +643,50 @@ def test_paired_row_kernels_odd_waves(kind):
         cc.ReEncryptAccumulate(b, rk, acc)
         assert np.array_equal(acc.numpy(), want_acc), f"wave {wave} (accumulate)"
     cc.set_wave(0)
+
+
+def test_sampler_statistics_and_keying():
+    """Device samplers (csrc/sampler.cu: ChaCha20 streams, ternary by rejection, discrete Gaussian sigma 3.19 by table
+    inversion, uniform residues by rejection) -- distribution checks on 3 x 2^20 draws and keying behaviour."""
+    from ppqsflhe_b200._capi import check, lib, vp
+    _, cc = _cc_pair((16, 2, 2, 50))
+    n = 16
+    small = torch.empty((n, 3, cc.N), dtype=torch.int64, device=cc.device)
+    seed = (12345).to_bytes(32, "little")
+    check(lib().ppq_sample_encrypt_noise(cc.h, seed, vp(small.data_ptr()), n, None))
+    torch.cuda.synchronize()
+    x = small.cpu().numpy()
+    tern, g = x[:, 0, :].ravel(), x[:, 1:, :].ravel()
+    cnt = np.array([(tern == v).sum() for v in (-1, 0, 1)], dtype=np.float64)
+    assert cnt.sum() == tern.size
+    chi2 = ((cnt - tern.size / 3) ** 2 / (tern.size / 3)).sum()
+    assert chi2 < 20.0, f"ternary not uniform: {cnt}"                      # 2 degrees of freedom
+    sigma = 3.19
+    ks = np.arange(-60, 61)
+    pmf = np.exp(-ks.astype(np.float64) ** 2 / (2 * sigma * sigma))
+    pmf /= pmf.sum()
+    assert np.abs(g).max() <= 40 and abs(g.mean()) < 0.02
+    assert abs(g.var() - (pmf * ks ** 2).sum()) < 0.08
+    sel = np.abs(ks) <= 9
+    obs = np.array([(g == k).sum() for k in ks[sel]], dtype=np.float64)
+    exp = pmf[sel] * g.size
+    assert ((obs - exp) ** 2 / exp).sum() < 60.0, "Gaussian histogram off"  # 18 degrees of freedom
+    # every polynomial has its own stream; a fixed seed repeats; no seed = fresh OS entropy per call
+    assert len({x[i, j, :64].tobytes() for i in range(n) for j in range(3)}) == 3 * n
+    again = torch.empty_like(small)
+    check(lib().ppq_sample_encrypt_noise(cc.h, seed, vp(again.data_ptr()), n, None))
+    assert torch.equal(again, small)
+    a1, a2 = torch.empty_like(small), torch.empty_like(small)
+    check(lib().ppq_sample_encrypt_noise(cc.h, None, vp(a1.data_ptr()), n, None))
+    check(lib().ppq_sample_encrypt_noise(cc.h, None, vp(a2.data_ptr()), n, None))
+    assert not torch.equal(a1, a2) and not torch.equal(a1, small)
+    # keygen: s ternary, e Gaussian, a uniform in [0, q_r) on every limb of QP; two unseeded key pairs differ
+    sk1, (b1, pa1) = cc.KeyGen()
+    sk2, (b2, pa2) = cc.KeyGen()
+    assert not torch.equal(sk1, sk2) and not torch.equal(pa1, pa2)
+    a = pa1.cpu().numpy().view(np.uint64)
+    for r in range(cc.M):
+        q = int(cc.moduli[r])
+        assert int(a[r].max()) < q
+        assert abs(float(a[r].astype(np.float64).mean()) / q - 0.5) < 0.01
+        assert abs(float((a[r] > np.uint64(q // 2)).mean()) - 0.5) < 0.01
