@@ -102,6 +102,19 @@ int ppq_reencrypt_fanout(ppq_ctx*, const ppq_rekey* const* rekeys, int n_keys, i
 int ppq_ks_modup(ppq_ctx*, int ell, const uint64_t* d_c1 /* [n][ell][N] */, uint64_t* d_digits, size_t n,
                  void* stream);
 
+/* d_digits [n][parts][ell+K][N] (as ppq_ks_modup writes them) -> d_ext [n][2][ell+K][N] =
+ * (sum_j digit_j * b_j, sum_j digit_j * a_j), canonical: EvalFastKeySwitchCoreExt on the key as uploaded */
+int ppq_ks_inner_product(ppq_ctx*, const ppq_rekey*, int ell, const uint64_t* d_digits, uint64_t* d_ext, size_t n,
+                         void* stream);
+/* d_ext [n][2][ell+K][N] -> d_out [n][2][ell][N]: ApproxModDown of both polynomials */
+int ppq_ks_moddown(ppq_ctx*, int ell, const uint64_t* d_ext, uint64_t* d_out, size_t n, void* stream);
+/* every constant the library derives from (N, Q chain, dnum) at `ell` present limbs, as JSON text (residues as decimal
+ * strings): P primes, roots, scaling factors, ModUp / ModDown / rescale tables.  Host only -- no device is touched --
+ * so independent big-integer checks (tests/test_params_bigint.py) run anywhere.  *need = bytes incl. NUL; buf may be
+ * NULL to query the size. */
+int ppq_params_dump(int logN, int L, const uint64_t* q_moduli, int dnum, int aux_bits, int extra_bits, int ell,
+                    char* buf, size_t cap, size_t* need);
+
 /* ---- cc->EvalAdd(ct1, ct2) (server/src/aggregateEncryptedWeights.cpp:82,91,106) */
 int ppq_eval_add(ppq_ctx*, int ell, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, size_t n,
                  void* stream);

@@ -58,6 +58,10 @@ _SIGS = {
     "ppq_reencrypt": (C.c_int, [vp, vp, C.c_int, vp, vp, C.c_size_t, vp]),
     "ppq_reencrypt_accumulate": (C.c_int, [vp, vp, C.c_int, vp, vp, C.c_size_t, vp]),
     "ppq_ks_modup": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, vp]),
+    "ppq_ks_inner_product": (C.c_int, [vp, vp, C.c_int, vp, vp, C.c_size_t, vp]),
+    "ppq_ks_moddown": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, vp]),
+    "ppq_params_dump": (C.c_int, [C.c_int, C.c_int, u64p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_size_t,
+                                  C.POINTER(C.c_size_t)]),
     "ppq_eval_add": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_size_t, vp]),
     "ppq_finalize_sum": (C.c_int, [vp, C.c_int, vp, C.c_size_t, vp]),
     "ppq_eval_mult_const": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, C.c_double, C.c_double, C.c_int, vp]),

@@ -687,6 +687,191 @@ extern "C" int ppq_ks_modup(ppq_ctx* c, int ell, const uint64_t* d_c1, uint64_t*
     return PPQ_OK;
 }
 
+// stage view of EvalFastKeySwitchCoreExt: ext[g][poly][r] = sum_j digits[g][j][r] * key_j[r] mod q_r, canonical, on the
+// plain (unscaled) key.  d_digits as written by ppq_ks_modup.
+extern "C" int ppq_ks_inner_product(ppq_ctx* c, const ppq_rekey* rk, int ell, const uint64_t* d_digits, uint64_t* d_ext,
+                                    size_t n, void* stream) {
+    if (!c || !rk || !d_digits || !d_ext) return fail(PPQ_EINVAL, "ppq_ks_inner_product: null argument");
+    if (rk->ctx != c) return fail(PPQ_EINVAL, "ppq_ks_inner_product: rekey belongs to another context");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_ks_inner_product: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n * 2 * (size_t)ell > 65535) return fail(PPQ_EINVAL, "ppq_ks_inner_product: batch too large");
+    if (!c->ip_split) return fail(PPQ_EINVAL, "ppq_ks_inner_product: needs N >= 2048 and <= 6 digits");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    KsPlanDev* p;
+    if (int rc = get_ks_plan(c, ell, &p)) return rc;
+    const size_t N = c->hp.N;
+    const int K = c->hp.K, L = c->hp.L, M = ell + K, parts = p->h.parts, alpha = c->hp.alpha;
+    const size_t ds = (size_t)parts * M * N, c1s = (size_t)ell * N, qs = (size_t)2 * ell * N, ps = (size_t)2 * K * N;
+    CU(c->scratch2.ensure((c1s + qs + ps) * n));
+    u64* c1 = c->scratch2.p;
+    u64* extq = c1 + c1s * n;
+    u64* extp = extq + qs * n;
+    for (int j = 0; j < parts; ++j) {  // the digit's own limbs are read from a c1-shaped block by the kernel
+        const int s0 = j * alpha, e0 = std::min(s0 + alpha, ell);
+        CU(cudaMemcpy2DAsync(c1 + (size_t)s0 * N, c1s * sizeof(u64), (const u64*)d_digits + ((size_t)j * M + s0) * N,
+                             ds * sizeof(u64), (size_t)(e0 - s0) * N * sizeof(u64), n, cudaMemcpyDeviceToDevice, st));
+    }
+    IpArgs ia;
+    ia.c1 = c1;
+    ia.c1_gs = c1s;
+    ia.digits = (const u64*)d_digits;
+    ia.dig_gs = ds;
+    ia.key_b = rk->b;
+    ia.key_a = rk->a;
+    ia.key_qb = rk->b;  // unscaled Q limbs: this view returns the textbook inner product
+    ia.key_qa = rk->a;
+    ia.key_q_stride = L + K;
+    ia.extq = extq;
+    ia.extq_gs = qs;
+    ia.extp = extp;
+    ia.extp_gs = ps;
+    ia.ell = ell;
+    ia.K = K;
+    ia.L = L;
+    ia.parts = parts;
+    ia.alpha = alpha;
+    if (!launch_ip_tma(c->k, ia, (int)n, st)) return fail(PPQ_EINVAL, "ppq_ks_inner_product: unsupported shape");
+    launch_finalize_mod(c->k, extq, ell, n, st);  // Q-limb results leave the kernel in [0, 3q)
+    u64* ext = (u64*)d_ext;
+    const size_t es = (size_t)2 * M * N;
+    for (int poly = 0; poly < 2; ++poly) {
+        CU(cudaMemcpy2DAsync(ext + (size_t)poly * M * N, es * sizeof(u64), extq + (size_t)poly * ell * N, qs * sizeof(u64),
+                             (size_t)ell * N * sizeof(u64), n, cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpy2DAsync(ext + ((size_t)poly * M + ell) * N, es * sizeof(u64), extp + (size_t)poly * K * N, ps * sizeof(u64),
+                             (size_t)K * N * sizeof(u64), n, cudaMemcpyDeviceToDevice, st));
+    }
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+// stage view of ApproxModDown: out[g][poly][i] = (ext[g][poly][i] - NTT(conv_{P->q_i}(iNTT(P limbs)))) * P^-1 mod q_i
+extern "C" int ppq_ks_moddown(ppq_ctx* c, int ell, const uint64_t* d_ext, uint64_t* d_out, size_t n, void* stream) {
+    if (!c || !d_ext || !d_out) return fail(PPQ_EINVAL, "ppq_ks_moddown: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_ks_moddown: bad limb count");
+    if (n == 0) return PPQ_OK;
+    if (n * 2 * (size_t)ell > 65535) return fail(PPQ_EINVAL, "ppq_ks_moddown: batch too large");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    KsPlanDev* p;
+    if (int rc = get_ks_plan(c, ell, &p)) return rc;
+    const size_t N = c->hp.N;
+    const int K = c->hp.K, M = ell + K;
+    const size_t qs = (size_t)2 * ell * N, ps = (size_t)2 * K * N, es = (size_t)2 * M * N;
+    CU(c->scratch2.ensure((2 * qs + ps) * n));
+    u64* extq = c->scratch2.p;
+    u64* conv = extq + qs * n;
+    u64* extp = conv + qs * n;
+    const u64* ext = (const u64*)d_ext;
+    for (int poly = 0; poly < 2; ++poly) {
+        CU(cudaMemcpy2DAsync(extq + (size_t)poly * ell * N, qs * sizeof(u64), ext + (size_t)poly * M * N, es * sizeof(u64),
+                             (size_t)ell * N * sizeof(u64), n, cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpy2DAsync(extp + (size_t)poly * K * N, ps * sizeof(u64), ext + ((size_t)poly * M + ell) * N, es * sizeof(u64),
+                             (size_t)K * N * sizeof(u64), n, cudaMemcpyDeviceToDevice, st));
+    }
+    // the product path folds P^-1 into the key and into the conversion constants; here the Q limbs get it explicitly
+    launch_mult_scalar(c->k, extq, extq, p->pinv.p, p->pinv_sh.p, ell, n, st);
+    launch_inv_row(c->k, extp, ps, extp, ps, p->p_limb.p, 2 * K, (int)n, st);
+    launch_inv_col(c->k, extp, ps, p->p_limb.p, p->p_scale.p, 2 * K, (int)n, st);
+    for (int poly = 0; poly < 2; ++poly)
+        if (!launch_bconv(c->k, extp, ps, conv, qs, p->down_jobs.data() + (size_t)poly * ell, ell, p->h.down_chat.data(),
+                          c->h_limbs.data(), K, (int)n, st))
+            return fail(PPQ_EINVAL, "more than 32 auxiliary limbs");
+    launch_fwd_col_plain(c->k, conv, qs, p->conv_ids.p, 2 * ell, (int)n, st);
+    MdArgs ma;
+    ma.conv = conv;
+    ma.conv_gs = qs;
+    ma.extq = extq;
+    ma.extq_gs = qs;
+    ma.ct_in = nullptr;
+    ma.in_gs = 0;
+    ma.out = (u64*)d_out;
+    ma.out_gs = qs;
+    ma.ell = ell;
+    ma.accumulate = 0;
+    launch_fwd_row_moddown(c->k, ma, (int)n, st);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    return PPQ_OK;
+}
+
+// Host-only view of everything the library derives from (N, Q chain, dnum): no device needed.  JSON text.
+static void js_arr(std::string& o, const char* name, const std::vector<u64>& v) {
+    o += "\"";
+    o += name;
+    o += "\": [";
+    for (size_t i = 0; i < v.size(); ++i) {
+        if (i) o += ", ";
+        o += "\"" + std::to_string(v[i]) + "\"";
+    }
+    o += "]";
+}
+extern "C" int ppq_params_dump(int logN, int L, const uint64_t* q, int dnum, int aux_bits, int extra_bits, int ell,
+                               char* buf, size_t cap, size_t* need) {
+    if (!q || L < 1 || !need) return fail(PPQ_EINVAL, "ppq_params_dump: bad arguments");
+    host::Params hp;
+    hp.logN = logN;
+    hp.L = L;
+    hp.dnum = dnum;
+    hp.aux_bits = aux_bits;
+    hp.extra_bits = extra_bits;
+    hp.mod.assign(q, q + L);
+    std::string err;
+    if (!host::derive(hp, err)) return fail(PPQ_EINVAL, err);
+    if (ell < 1 || ell > L) return fail(PPQ_EINVAL, "ppq_params_dump: bad ell");
+    host::KsPlan ks;
+    host::build_ks_plan(hp, ell, ks);
+    std::string o = "{";
+    o += "\"logN\": " + std::to_string(hp.logN) + ", \"L\": " + std::to_string(hp.L) + ", \"K\": " + std::to_string(hp.K) +
+         ", \"dnum\": " + std::to_string(hp.dnum) + ", \"alpha\": " + std::to_string(hp.alpha) + ", \"ell\": " +
+         std::to_string(ell) + ", \"parts\": " + std::to_string(ks.parts) + ", ";
+    js_arr(o, "moduli", hp.mod);
+    o += ", ";
+    js_arr(o, "roots", hp.root);
+    o += ", ";
+    js_arr(o, "ninv", hp.ninv);
+    o += ", \"sf\": [";
+    char tmp[64];
+    for (size_t i = 0; i < hp.sf.size(); ++i) {
+        std::snprintf(tmp, sizeof(tmp), "%s%.17g", i ? ", " : "", hp.sf[i]);
+        o += tmp;
+    }
+    o += "], \"sfbig\": [";
+    for (size_t i = 0; i < hp.sfbig.size(); ++i) {
+        std::snprintf(tmp, sizeof(tmp), "%s%.17g", i ? ", " : "", hp.sfbig[i]);
+        o += tmp;
+    }
+    o += "], ";
+    js_arr(o, "c1_scale", ks.c1_scale);   // N^-1 (D_j/q_i)^-1 mod q_i, i < ell
+    o += ", ";
+    js_arr(o, "p_scale", ks.p_scale);     // N^-1 (P/p_k)^-1 mod p_k, twice (one per polynomial)
+    o += ", ";
+    js_arr(o, "pinv", ks.pinv);           // P^-1 mod q_i
+    o += ", ";
+    js_arr(o, "up_chat", ks.up_chat);     // per ModUp job, the digit's (D_j/q_i) mod t
+    o += ", ";
+    js_arr(o, "down_chat", ks.down_chat); // per ModDown job, (P/p_k) P^-1 mod q_i
+    o += ", \"up_jobs\": [";
+    for (size_t i = 0; i < ks.up_jobs.size(); ++i) {
+        const host::Job& j = ks.up_jobs[i];
+        o += (i ? ", [" : "[") + std::to_string(j.src_first) + ", " + std::to_string(j.ns) + ", " + std::to_string(j.dst_slot) +
+             ", " + std::to_string(j.limb) + ", " + std::to_string(j.chat_off) + "]";
+    }
+    o += "]";
+    if (ell >= 2) {
+        host::RsPlan rs;
+        host::build_rs_plan(hp, ell, rs);
+        o += ", ";
+        js_arr(o, "rescale_qlinv", rs.qlinv);
+    }
+    o += "}";
+    *need = o.size() + 1;
+    if (buf && cap >= o.size() + 1) std::memcpy(buf, o.c_str(), o.size() + 1);
+    return PPQ_OK;
+}
+
 // ------------------------------------------------------------------------------------------- EvalAdd / EvalMult
 extern "C" int ppq_eval_add(ppq_ctx* c, int ell, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n,
                             void* stream) {

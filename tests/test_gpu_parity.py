@@ -144,7 +144,7 @@ def test_reencrypt_bit_exact(kind, ell, n):
 def test_rekey_upload_and_borrowed_key_agree():
     """ppq_rekey_upload (host buffers, the handle owns its copy) and ppq_rekey_from_device (borrowed device buffers,
     the handle keeps a private P^-1-scaled copy of the Q limbs) must give the same ciphertexts, and the borrowed
-    buffers must stay untouched (reference: the rekey is read-only in ReEncrypt, Source/server.cpp:101-121)."""
+    buffers must stay untouched (reference: the rekey is only read by cc->ReEncrypt, server/src/changeCipherDomain.cpp:40-44,74,89,105)."""
     from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
     o, cc = _cc_pair((13, 4, 2, 50))
     rng = np.random.default_rng(29)
@@ -385,7 +385,8 @@ def test_eval_add_and_finalize_bit_exact():
 
 
 @pytest.mark.parametrize("kind,ell,c", [("c1", 4, 0.5), ("c1", 3, 0.25), ((12, 5, 3, 45), 7, 1.0 / 3.0),
-                                        ((16, 6, 3, 59), 8, 1.0 / 64.0)])
+                                        ((16, 6, 3, 59), 8, 1.0 / 64.0), ((16, 18, 3, 59), 20, 1.0 / 64.0),
+                                        ((16, 18, 3, 59), 19, 0.5), ((17, 38, 3, 59), 40, 1.0 / 16.0)])
 def test_eval_mult_rescale_bit_exact(kind, ell, c):
     from ppqsflhe_b200 import CiphertextBatch, CtMeta, to_device_u64
     o, cc = _cc_pair(kind)
@@ -690,3 +691,155 @@ def test_sampler_statistics_and_keying():
         assert int(a[r].max()) < q
         assert abs(float(a[r].astype(np.float64).mean()) / q - 0.5) < 0.01
         assert abs(float((a[r] > np.uint64(q // 2)).mean()) - 0.5) < 0.01
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Stage views and big-integer properties: checks that do NOT go through the C oracle's arithmetic (Python integers only)
+# ---------------------------------------------------------------------------------------------------------------------
+def _crt_lift(res, mods):
+    """exact lift in [0, prod mods) of per-limb residue arrays (object arrays of Python ints)"""
+    import math
+    Q = math.prod(mods)
+    x = np.zeros(len(res[0]), dtype=object)
+    for r, q in zip(res, mods):
+        h = Q // q
+        x = (x + np.array([int(v) for v in r], dtype=object) * (h * pow(h % q, -1, q))) % Q
+    return x, Q
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 3), ((12, 5, 3, 45), 7), ((13, 4, 2, 50), 5), ((16, 18, 3, 59), 20)])
+def test_inner_product_stage_bit_exact(kind, ell):
+    """k_ip_tma alone (EvalFastKeySwitchCoreExt) through ppq_ks_inner_product against oracle.inner_product."""
+    from ppqsflhe_b200 import EvalKey, to_device_u64, to_host_u64
+    from ppqsflhe_b200._capi import check, lib, vp
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(31)
+    n = 2
+    c1 = np.stack([_rand_poly(rng, o, range(ell)) for _ in range(n)])
+    digits = cc.KeySwitchModUp(to_device_u64(c1, cc.device))
+    kb, ka = _rand_key(rng, o)
+    rk = EvalKey(cc, kb, ka)
+    M = ell + o.K
+    ext = torch.empty((n, 2, M, cc.N), dtype=torch.int64, device=cc.device)
+    check(lib().ppq_ks_inner_product(cc.h, rk.h, ell, vp(digits.data_ptr()), vp(ext.data_ptr()), n, None))
+    got = to_host_u64(ext)
+    dh = to_host_u64(digits)
+    for g in range(n):
+        w0, w1 = o.inner_product(ell, dh[g], kb, ka)
+        assert np.array_equal(got[g][0], w0) and np.array_equal(got[g][1], w1)
+    if o.N <= 8192:  # the same in Python integers on a few coefficients of every limb
+        idx = rng.integers(0, o.N, 16)
+        lim = o.ext_limbs(ell)
+        for r, gl in enumerate(lim):
+            q = int(o.moduli[gl])
+            for i in idx:
+                acc = sum(int(dh[0][j][r][i]) * int(kb[j][gl][i]) for j in range(dh.shape[1])) % q
+                assert int(got[0][0][r][i]) == acc
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 3), ((12, 5, 3, 45), 7), ((12, 5, 3, 45), 3), ((13, 38, 3, 59), 40)])
+def test_moddown_stage_bit_exact_and_big_integer_property(kind, ell):
+    """ppq_ks_moddown against oracle.moddown, and against the DEFINITION in Python integers: with X the exact lift of
+    the extended polynomial over Q_ell x P, ApproxModDown returns floor(X / P) - u (mod q_i) with one 0 <= u < K per
+    coefficient, the same u on every limb (the uncorrected overflow of the approximate conversion)."""
+    import math
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    from ppqsflhe_b200._capi import check, lib, vp
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(37)
+    n = 2
+    lim = o.ext_limbs(ell)
+    M = len(lim)
+    ext = np.stack([np.stack([_rand_poly(rng, o, lim) for _ in range(2)]) for _ in range(n)])
+    d_ext = to_device_u64(ext, cc.device)
+    out = torch.empty((n, 2, ell, cc.N), dtype=torch.int64, device=cc.device)
+    check(lib().ppq_ks_moddown(cc.h, ell, vp(d_ext.data_ptr()), vp(out.data_ptr()), n, None))
+    got = to_host_u64(out)
+    for g in range(n):
+        for poly in range(2):
+            assert np.array_equal(got[g][poly], o.moddown(ell, ext[g][poly]))
+    if o.N > 4096 or M > 12:
+        return
+    # big-integer definition, polynomial (0, 0): bring every limb to COEFF with the GPU's own inverse NTT (pinned to
+    # OpenFHE by the secret-key golden), lift, divide
+    mods = [int(o.moduli[r]) for r in lim]
+    P = math.prod(mods[ell:])
+    co = to_device_u64(ext[0][0], cc.device)
+    cc.ntt(co, lim, inverse=True)
+    X, _ = _crt_lift(to_host_u64(co), mods)
+    oc = out[0][0].clone()
+    cc.ntt(oc, list(range(ell)), inverse=True)
+    res = to_host_u64(oc)
+    F = X // P
+    K = o.K
+    u0 = None
+    for i in range(ell):
+        q = mods[i]
+        u = (F - np.array([int(v) for v in res[i]], dtype=object)) % q
+        assert all(0 <= int(v) < K for v in u), "ModDown is not floor(X/P) - u with 0 <= u < K"
+        if u0 is None:
+            u0 = u
+        assert all(int(a) == int(b) for a, b in zip(u, u0)), "u differs between limbs"
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 3), ((12, 5, 3, 45), 7), ((12, 5, 3, 45), 5)])
+def test_modup_big_integer_property(kind, ell):
+    """ApproxSwitchCRTBasis in Python integers: limb t of digit j (COEFF) = (x + u D_j) mod t, x the exact lift of the
+    digit's own limbs in [0, D_j), one 0 <= u < |digit j| per coefficient for every target limb t."""
+    import math
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(41)
+    c1 = np.stack([_rand_poly(rng, o, range(ell))])
+    dig = cc.KeySwitchModUp(to_device_u64(c1, cc.device))[0]          # [parts][M][N] EVAL
+    lim = o.ext_limbs(ell)
+    M = len(lim)
+    parts = dig.shape[0]
+    co = dig.clone().view(parts * M, cc.N)
+    cc.ntt(co, lim * parts, inverse=True)
+    co = to_host_u64(co).reshape(parts, M, o.N)
+    for j in range(parts):
+        own = list(range(j * o.alpha, min((j + 1) * o.alpha, ell)))
+        mods = [int(o.moduli[i]) for i in own]
+        x, D = _crt_lift([co[j][i] for i in own], mods)
+        y = [np.array([int(v) for v in co[j][i]], dtype=object) * pow(D // q % q, -1, q) % q for i, q in zip(own, mods)]
+        v = sum(yi * (D // q) for yi, q in zip(y, mods))
+        u = (v - x) // D
+        assert all(int(a) * D + int(b) == int(c) for a, b, c in zip(u, x, v)) and all(0 <= int(a) < len(own) for a in u)
+        for r, gl in enumerate(lim):
+            if r in own:
+                continue
+            t = int(o.moduli[gl])
+            assert all(int(a) == int(b) for a, b in zip(co[j][r], v % t)), f"digit {j} limb {r}"
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 3), ((12, 5, 3, 45), 7)])
+def test_rescale_is_exact_centred_division_big_integers(kind, ell):
+    """DropLastElementAndScale in Python integers: with X the exact lift over q_0..q_{ell-1} and r the CENTRED residue of
+    X mod q_last, the result is (X - r) / q_last reduced modulo every remaining limb.  (c = 1/sf makes the EvalMult
+    constant 1, so ppq_eval_mult_const with rescale = 1 is the bare rescale.)"""
+    import math
+    from ppqsflhe_b200 import to_device_u64, to_host_u64
+    from ppqsflhe_b200._capi import check, lib, vp
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(43)
+    ct = _rand_ct(rng, o, ell, 1)
+    d_in = to_device_u64(ct, cc.device)
+    out = torch.empty((1, 2, ell - 1, cc.N), dtype=torch.int64, device=cc.device)
+    sf = cc.sf(o.L - ell + 1)
+    check(lib().ppq_eval_mult_const(cc.h, ell, vp(d_in.data_ptr()), vp(out.data_ptr()), 1, 1.0 / sf, sf, 1, None))
+    mods = [int(o.moduli[i]) for i in range(ell)]
+    ql = mods[-1]
+    co = d_in[0][0].clone()
+    cc.ntt(co, list(range(ell)), inverse=True)
+    X, _ = _crt_lift(to_host_u64(co), mods)
+    r = X % ql
+    r = np.array([int(v) - ql if int(v) > ql // 2 else int(v) for v in r], dtype=object)
+    Y = (X - r) // ql
+    assert all((int(a) - int(b)) % ql == 0 for a, b in zip(X, r))
+    oc = out[0][0].clone()
+    cc.ntt(oc, list(range(ell - 1)), inverse=True)
+    res = to_host_u64(oc)
+    for i in range(ell - 1):
+        q = mods[i]
+        assert all(int(a) == int(b) % q for a, b in zip(res[i], Y)), f"limb {i}"
