@@ -34,8 +34,11 @@ int main(int argc, char* argv[]) {
         std::cout << "[ReKeyGen] Client Private Key loaded from " << client_sk << std::endl;
 
         std::vector<uint64_t> pkb, pka;
+        std::string peer_tag;  // the re-encryption key carries the tag of the key it switches TO
         try {
-            const std::vector<wire::Poly> h = wire::read_public_key(wire::slurp(client_pk));
+            const std::string pk_text = wire::slurp(client_pk);
+            peer_tag = wire::read_key_tag(pk_text);
+            const std::vector<wire::Poly> h = wire::read_public_key(pk_text);
             pkb = s->flatten(h[0], M, "public key b");
             pka = s->flatten(h[1], M, "public key a");
         } catch (const std::exception& e) {
@@ -70,7 +73,7 @@ int main(int argc, char* argv[]) {
                 av.push_back(wire::poly_from_flat(ka.data() + j * M * N, M, N, s->moduli.data()));
                 bv.push_back(wire::poly_from_flat(kb.data() + j * M * N, M, N, s->moduli.data()));
             }
-            wire::write_eval_key(rekey_path, av, bv);
+            wire::write_eval_key(rekey_path, av, bv, peer_tag);
         } catch (const std::exception&) {
             std::cerr << "[ReKeyGen] Failed to save re-encryption key to " << rekey_path << std::endl;
             return 1;

@@ -57,7 +57,7 @@ int main(int argc, char* argv[]) {
         struct Group { std::vector<size_t> idx; std::vector<wire::CtMeta> meta; std::vector<uint64_t> a, b; };
         std::map<uint32_t, Group> groups;
         for (size_t i = 0; i < lhs.size(); ++i) {
-            wire::Ct x = wire::decode_ct(*lhs[i]), y = wire::decode_ct(*rhs[i]);
+            wire::Ct x = s->codec.decode(*lhs[i]), y = s->codec.decode(*rhs[i]);
             if (x.N != s->N || y.N != s->N) throw std::runtime_error("ciphertext ring dimension differs from CC.json");
             if (x.ell != y.ell || x.meta.level != y.meta.level || x.meta.noise_scale_deg != y.meta.noise_scale_deg)
                 throw std::runtime_error("EvalAdd operands differ in level / noise scale degree");
@@ -114,7 +114,7 @@ int main(int argc, char* argv[]) {
                     }
                     mo.noise_scale_deg += 1;
                     mo.scaling_factor *= sf;
-                    *dst[g.idx[sel[k]]] = wire::encode_ct(mo, lo, (uint32_t)s->N, s->moduli.data(), ho.data() + k * ct_out);
+                    *dst[g.idx[sel[k]]] = s->codec.encode(mo, lo, ho.data() + k * ct_out);
                 }
             }
         }

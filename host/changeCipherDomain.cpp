@@ -1,7 +1,7 @@
 // changeCipherDomain -- drop-in for the reference's server/src/changeCipherDomain.cpp (same argv, exit codes,
 // progress lines and file schema), with cc->ReEncrypt (:74,89,105) replaced by ONE batched ppq_reencrypt call
 // through the C ABI of libppq_b200.so.  No CPU fallback: without a B200 the context load fails and the tool exits 1.
-#include "ppq_session.hpp"
+#include "ppq_ops.hpp"
 
 using namespace ppqhost;
 
@@ -24,17 +24,9 @@ int main(int argc, char* argv[]) {
 
         // Step 2: re-encryption key (reference :40-44) -> device-resident [dnum][L+K][N] B and A vectors
         ppq_rekey* rk = nullptr;
+        std::string rekey_tag;  // a re-encrypted ciphertext carries the tag of the key domain it now lives in
         try {
-            const wire::EvalKeyPolys ek = wire::read_eval_key(wire::slurp(rekey_path));
-            if ((int)ek.a.size() != s->dnum) throw std::runtime_error("key has " + std::to_string(ek.a.size()) + " digits, context dnum is " + std::to_string(s->dnum));
-            const size_t M = (size_t)s->L + s->K, per = M * s->N;
-            std::vector<uint64_t> b(per * s->dnum), a(per * s->dnum);
-            for (int j = 0; j < s->dnum; ++j) {
-                const std::vector<uint64_t> bj = s->flatten(ek.b[j], M, "rekey B"), aj = s->flatten(ek.a[j], M, "rekey A");
-                std::copy(bj.begin(), bj.end(), b.begin() + j * per);
-                std::copy(aj.begin(), aj.end(), a.begin() + j * per);
-            }
-            ck(ppq_rekey_upload(s->cc, b.data(), a.data(), &rk), "ppq_rekey_upload");
+            rk = load_rekey(*s, rekey_path, &rekey_tag);
         } catch (const std::exception& e) {
             std::cerr << "[recrypt] ERROR: Failed to load ReKey from " << rekey_path << " (" << e.what() << ")" << std::endl;
             return 1;
@@ -60,6 +52,8 @@ int main(int argc, char* argv[]) {
             ck(ppq_reencrypt(s->cc, rk, (int)b.ell, d_in.p, d_out.p, b.n(), nullptr), "ppq_reencrypt");
             ck(ppq_sync(s->cc, nullptr), "ppq_sync");
             d_out.download(b.data.data(), b.data.size());
+            if (!rekey_tag.empty())
+                for (auto& m : b.meta) m.key_tag = rekey_tag;
             encode_back(*s, b, b.ell, b.meta, b.data, refs);  // level / scale / slots unchanged by a key switch
         }
         ppq_rekey_destroy(rk);

@@ -45,7 +45,7 @@ int main(int argc, char* argv[]) {
 
         std::vector<BlobRef> refs = blob_refs(layers);
         std::map<uint32_t, Batch> groups = decode_all(*s, refs);
-        const size_t slots = s->N / 2;
+        const size_t slots = s->batch_size;  // CC.json "bs" (full packing is enforced by Session)
         std::vector<std::vector<double>> plain(refs.size());
         Dev<uint64_t> d_sk(sk.size());
         d_sk.upload(sk.data(), sk.size());

@@ -23,12 +23,15 @@ int main(int argc, char* argv[]) {
             return 1;
         }
         std::cout << "[encrypt] CryptoContext loaded from " << cc_path << std::endl;
-        const size_t batchSize = s->N / 2;  // full packing: GetEncodingParams()->GetBatchSize() (:39)
+        const size_t batchSize = s->batch_size;  // cc->GetEncodingParams()->GetBatchSize() (:39-40): CC.json "bs"
         std::cout << "[encrypt] Batch size from CryptoContext = " << batchSize << std::endl;
 
         std::vector<uint64_t> pkb, pka;
+        std::string key_tag;
         try {
-            const std::vector<wire::Poly> h = wire::read_public_key(wire::slurp(pubkey_path));
+            const std::string pk_text = wire::slurp(pubkey_path);
+            key_tag = wire::read_key_tag(pk_text);  // a ciphertext carries the tag of the key it was made under
+            const std::vector<wire::Poly> h = wire::read_public_key(pk_text);
             const size_t M = (size_t)s->L + s->K;
             pkb = s->flatten(h[0], M, "public key b");
             pka = s->flatten(h[1], M, "public key a");
@@ -102,8 +105,9 @@ int main(int argc, char* argv[]) {
             m.level = 0;
             m.scaling_factor = sf;
             m.slots = (uint32_t)batchSize;
+            m.key_tag = key_tag;
             for (size_t k = 0; k < n; ++k)
-                *dst[k] = wire::encode_ct(m, (uint32_t)ell, (uint32_t)s->N, s->moduli.data(), h_ct.data() + k * ct);
+                *dst[k] = s->codec.encode(m, (uint32_t)ell, h_ct.data() + k * ct);
         }
         try {
             wire::write_container(output_encfile, out);

@@ -39,15 +39,16 @@ int main(int argc, char* argv[]) {
         std::cout << "[keyGen] Public and Private keys generated" << std::endl;
 
         // Step 3: key files (reference :41-48)
+        const std::string tag = new_key_tag();  // both halves of the pair carry the same CryptoObject key tag
         try {
-            wire::write_private_key(privkey_out, wire::poly_from_flat(sk.data(), L, N, s->moduli.data()));
+            wire::write_private_key(privkey_out, wire::poly_from_flat(sk.data(), L, N, s->moduli.data()), tag);
         } catch (const std::exception&) {
             std::cerr << "[keyGen] ERROR: Failed to save private key to " << privkey_out << std::endl;
             return 1;
         }
         try {
             wire::write_public_key(pubkey_out, wire::poly_from_flat(pkb.data(), M, N, s->moduli.data()),
-                                   wire::poly_from_flat(pka.data(), M, N, s->moduli.data()));
+                                   wire::poly_from_flat(pka.data(), M, N, s->moduli.data()), tag);
         } catch (const std::exception&) {
             std::cerr << "[keyGen] ERROR: Failed to save public key to " << pubkey_out << std::endl;
             return 1;

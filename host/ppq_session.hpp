@@ -50,6 +50,9 @@ struct Session {
     size_t N = 0;
     int L = 0, K = 0, dnum = 0;
     std::vector<uint64_t> moduli;  // L + K
+    std::vector<uint64_t> roots;   // L + K
+    wire::Codec codec;             // ciphertext blobs <-> [2][ell][N]
+    uint32_t batch_size = 0;       // EncodingParams "bs" of CC.json
 
     explicit Session(const std::string& cc_path) {
         const std::string text = wire::slurp(cc_path);
@@ -63,6 +66,16 @@ struct Session {
         dnum = info.dnum;
         moduli.resize((size_t)L + K);
         ck(ppq_ctx_moduli(cc, moduli.data()), "ppq_ctx_moduli");
+        roots.resize((size_t)L + K);
+        ck(ppq_ctx_roots(cc, roots.data()), "ppq_ctx_roots");
+        codec.init(text, (uint32_t)N, moduli.data(), roots.data(), (size_t)L);
+        // CC.json's EncodingParams batch size (client/src/encryptModelWeights.cpp:40 GetBatchSize): the chunking of
+        // `values`.  Sparse packing (bs < N/2) is not implemented -- fail loudly instead of diverging silently.
+        if (const jmin::Value* enp = wire::find_member_any(*codec.cx.cc_root, "enp"))
+            if (const jmin::Value* bs = wire::find_member_any(*enp, "bs")) batch_size = (uint32_t)bs->as_u64();
+        if (batch_size == 0) batch_size = (uint32_t)(N / 2);
+        if (batch_size != N / 2)
+            throw std::runtime_error("CC.json batch size " + std::to_string(batch_size) + " != N/2: sparse packing is not supported");
     }
     Session(const Session&) = delete;
     ~Session() { if (cc) ppq_ctx_destroy(cc); }
@@ -109,7 +122,7 @@ struct Batch {
 inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<BlobRef>& refs) {
     std::map<uint32_t, Batch> groups;
     for (size_t i = 0; i < refs.size(); ++i) {
-        wire::Ct c = wire::decode_ct(*refs[i].slot);
+        wire::Ct c = s.codec.decode(*refs[i].slot);
         if (c.N != s.N) throw std::runtime_error("ciphertext ring dimension differs from CC.json");
         if ((int)c.ell > s.L) throw std::runtime_error("ciphertext has more limbs than the context");
         for (uint32_t k = 0; k < c.ell; ++k)
@@ -126,9 +139,29 @@ inline void encode_back(const Session& s, const Batch& b, uint32_t ell_out, cons
                         const std::vector<uint64_t>& data, const std::vector<BlobRef>& refs) {
     const size_t ct = (size_t)2 * ell_out * s.N;
     for (size_t k = 0; k < b.n(); ++k)
-        *refs[b.index[k]].slot = wire::encode_ct(meta[k], ell_out, (uint32_t)s.N, s.moduli.data(), data.data() + k * ct);
+        *refs[b.index[k]].slot = s.codec.encode(meta[k], ell_out, data.data() + k * ct);
 }
 
+// CryptoObject::keyTag of a new key pair: 32 hex digits (OpenFHE's GenerateUniqueKeyID writes 128 random bits this way)
+inline std::string new_key_tag() {
+    unsigned char b[16];
+    if (const char* e = std::getenv("PPQ_SEED")) {
+        const uint64_t v = std::strtoull(e, nullptr, 0) * 0x9E3779B97F4A7C15ull + 1;
+        std::memcpy(b, &v, 8);
+        std::memcpy(b + 8, &v, 8);
+    } else {
+        FILE* f = std::fopen("/dev/urandom", "rb");
+        if (!f || std::fread(b, 1, 16, f) != 16) throw std::runtime_error("cannot read /dev/urandom");
+        std::fclose(f);
+    }
+    static const char* hx = "0123456789abcdef";
+    std::string t;
+    for (unsigned char c : b) {
+        t += hx[c >> 4];
+        t += hx[c & 15];
+    }
+    return t;
+}
 // Key material for the device samplers.  Production: NULL, i.e. the library draws a fresh 256-bit ChaCha20 key from
 // getrandom(2) for every call.  PPQ_SEED (an integer) is a TEST-ONLY switch for reproducible runs: it is widened to
 // 32 bytes, `salt` separating the calls of one process.  Never set it when generating real keys or ciphertexts.

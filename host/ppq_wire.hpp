@@ -9,15 +9,15 @@
 //     client/storage/client_1/private/client_1-private.key:  {"v":[{"v":{"ptr_wrapper":{"data":{"v":[residues],
 //     "m":{"v":modulus}}}},"f":format,"p":...}, ...],"f":format,"p":...}.
 //   * ciphertext blob: the reference stores base64(cereal PortableBinary(Ciphertext<DCRTPoly>)), which embeds the
-//     whole crypto context per blob.  No sample blob exists in the reference tree, cereal and
-//     OpenFHE are absent, so that byte layout cannot be verified here; instead of shipping an unverifiable
-//     imitation this codec writes a self-describing blob ("PPQCT1\0\0" magic, the ciphertext scalars of
-//     CiphertextImpl -- noiseScaleDeg, level, hopslevel, encoding, slots, scalingFactor, scalingFactorInt -- then
-//     per polynomial and limb: modulus, length, raw little-endian residues, i.e. the same payload order as a
-//     serialized DCRTPoly).  decode_ct() rejects anything else loudly.  The codec is isolated in this header so a
-//     cereal-exact one can replace it when a real blob is available.
+//     whole crypto context per blob.  ppq_cereal.hpp writes and reads that layout (field order from
+//     the two real cereal-JSON files in the reference tree, total size pinned by the recorded file sizes; byte identity
+//     with a real OpenFHE blob UNVERIFIED -- none exists in the tree).  It is the default on write; PPQ_BLOB=ppqct1
+//     selects the older self-describing private blob ("PPQCT1\0\0" magic, the CiphertextImpl scalars, then per
+//     polynomial and limb: modulus, length, raw residues).  Codec::decode detects either.
 #pragma once
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
@@ -26,6 +26,7 @@
 #include <vector>
 
 #include "json_min.hpp"
+#include "ppq_cereal.hpp"
 
 namespace wire {
 
@@ -102,6 +103,7 @@ struct CtMeta {  // the scalar members of lbcrypto::CiphertextImpl (SURVEY.md 5.
     uint32_t noise_scale_deg = 2, level = 0, hops_level = 0, encoding = 3 /* CKKS_PACKED_ENCODING */, slots = 0;
     double scaling_factor = 1.0;
     uint64_t scaling_factor_int = 1;
+    std::string key_tag;  // CryptoObject::keyTag (cereal blobs only; the private blob does not carry it)
 };
 struct Ct {
     CtMeta meta;
@@ -193,6 +195,63 @@ inline Ct decode_ct(const std::string& b64) {
     return c;
 }
 
+// ------------------------------------------------------------------------------------------------ blob codec
+// One per session: knows the crypto context the blobs embed.  encode: cereal PortableBinary unless PPQ_BLOB=ppqct1;
+// decode: whichever of the two the blob is.
+struct Codec {
+    cerealpb::Context cx;
+    bool write_cereal = true;
+    mutable bool warned = false;
+    void init(const std::string& ccjson_text, uint32_t N, const uint64_t* moduli, const uint64_t* roots, size_t L) {
+        cx.init(jmin::parse(ccjson_text), N, moduli, roots, L);
+        const char* e = std::getenv("PPQ_BLOB");
+        write_cereal = !(e && std::string(e) == "ppqct1");
+    }
+    void warn_once() const {
+        if (!warned && !std::getenv("PPQ_QUIET"))
+            std::fprintf(stderr, "[ppq] note: cereal PortableBinary ciphertext blobs are written/read to a layout derived from the "
+                                 "reference's own cereal-JSON files and file sizes; byte identity is unverified against OpenFHE\n");
+        warned = true;
+    }
+    std::string encode(const CtMeta& m, uint32_t ell, const uint64_t* data) const {
+        if (!write_cereal) return encode_ct(m, ell, cx.N, cx.moduli.data(), data);
+        warn_once();
+        cerealpb::Meta cm;
+        cm.noise_scale_deg = m.noise_scale_deg;
+        cm.level = m.level;
+        cm.hops_level = m.hops_level;
+        cm.encoding = m.encoding;
+        cm.slots = m.slots;
+        cm.scaling_factor = m.scaling_factor;
+        cm.scaling_factor_int = m.scaling_factor_int;
+        cm.key_tag = m.key_tag.empty() ? std::string(32, '0') : m.key_tag;
+        const std::string raw = cerealpb::encode(cx, cm, ell, data);
+        return base64_encode(reinterpret_cast<const unsigned char*>(raw.data()), raw.size());
+    }
+    Ct decode(const std::string& b64) const {
+        if (b64.compare(0, 8, "UFBRQ1Qx") == 0) return decode_ct(b64);  // base64 of "PPQCT1"
+        const std::vector<unsigned char> raw = base64_decode(b64);
+        if (!cerealpb::looks_like_cereal(raw.data(), raw.size()))
+            throw std::runtime_error("ciphertext blob is neither a cereal PortableBinary Ciphertext archive nor PPQCT1");
+        warn_once();
+        cerealpb::Ct c = cerealpb::decode(cx, raw.data(), raw.size());
+        Ct o;
+        o.meta.noise_scale_deg = c.meta.noise_scale_deg;
+        o.meta.level = c.meta.level;
+        o.meta.hops_level = c.meta.hops_level;
+        o.meta.encoding = c.meta.encoding;
+        o.meta.slots = c.meta.slots;
+        o.meta.scaling_factor = c.meta.scaling_factor;
+        o.meta.scaling_factor_int = c.meta.scaling_factor_int;
+        o.meta.key_tag = c.meta.key_tag;
+        o.ell = c.ell;
+        o.N = c.N;
+        o.moduli = std::move(c.moduli);
+        o.data = std::move(c.data);
+        return o;
+    }
+};
+
 // ------------------------------------------------------------------------------------------------ cereal JSON keys
 struct Poly {  // one DCRTPoly: limbs[i] has N residues mod moduli[i]
     std::vector<uint64_t> moduli;
@@ -233,6 +292,19 @@ inline const jmin::Value* find_member(const jmin::Value& v, const std::string& k
     } else if (v.is_array()) {
         for (const auto& x : v.arr)
             if (const jmin::Value* r = find_member(*x, key)) return r;
+    }
+    return nullptr;
+}
+// the same without skipping the embedded context (for CC.json itself)
+inline const jmin::Value* find_member_any(const jmin::Value& v, const std::string& key) {
+    if (v.is_object()) {
+        for (const auto& kv : v.obj)
+            if (kv.first == key) return kv.second.get();
+        for (const auto& kv : v.obj)
+            if (const jmin::Value* r = find_member_any(*kv.second, key)) return r;
+    } else if (v.is_array()) {
+        for (const auto& x : v.arr)
+            if (const jmin::Value* r = find_member_any(*x, key)) return r;
     }
     return nullptr;
 }
@@ -297,10 +369,30 @@ inline jmin::Ptr dcrtpoly_to_json(const Poly& p) {
     return o;
 }
 
-// the cereal shared_ptr envelope around a key object: value0 -> ptr_wrapper -> data -> {member}
-inline jmin::Ptr wrap_key_member(const char* member, jmin::Ptr payload) {
+// CryptoObject::keyTag of a key file ("kt" as a STRING; the "kt" inside the embedded context is the scheme object)
+inline std::string read_key_tag(const std::string& text) {
+    jmin::Ptr root = jmin::parse(text);
+    std::string tag;
+    std::vector<const jmin::Value*> stack{root.get()};
+    while (!stack.empty() && tag.empty()) {
+        const jmin::Value* v = stack.back();
+        stack.pop_back();
+        if (v->is_object()) {
+            for (const auto& kv : v->obj) {
+                if (kv.first == "kt" && kv.second->is_string()) tag = kv.second->s;
+                else if (kv.first != "cc" && !(kv.second->is_array() && kv.second->size() > 64)) stack.push_back(kv.second.get());
+            }
+        } else if (v->is_array()) {
+            for (const auto& x : v->arr) stack.push_back(x.get());
+        }
+    }
+    return tag;
+}
+// the cereal shared_ptr envelope around a key object: value0 -> ptr_wrapper -> data -> {kt, member}
+inline jmin::Ptr wrap_key_member(const char* member, jmin::Ptr payload, const std::string& key_tag = "") {
     jmin::Ptr data = jmin::make(jmin::Value::Object);
     jmin::set(data, "cereal_class_version", jmin::make_u64(0));
+    if (!key_tag.empty()) jmin::set(data, "kt", jmin::make_string(key_tag));
     jmin::set(data, member, payload);
     jmin::Ptr pw = jmin::make(jmin::Value::Object);
     jmin::set(pw, "id", jmin::make_u64(2147483649ull));
@@ -322,22 +414,23 @@ inline Poly poly_from_flat(const uint64_t* data, size_t limbs, size_t N, const u
     return p;
 }
 // key files as client/src/keyGen.cpp:41-48 and client/src/REkeyGen.cpp:60 write them (SerType::JSON)
-inline void write_private_key(const std::string& path, const Poly& s) {
-    spit(path, jmin::dump(*wrap_key_member("s", dcrtpoly_to_json(s)), 4, false));
+inline void write_private_key(const std::string& path, const Poly& s, const std::string& key_tag = "") {
+    spit(path, jmin::dump(*wrap_key_member("s", dcrtpoly_to_json(s), key_tag), 4, false));
 }
-inline void write_public_key(const std::string& path, const Poly& b, const Poly& a) {
+inline void write_public_key(const std::string& path, const Poly& b, const Poly& a, const std::string& key_tag = "") {
     jmin::Ptr h = jmin::make(jmin::Value::Array);
     h->arr.push_back(dcrtpoly_to_json(b));
     h->arr.push_back(dcrtpoly_to_json(a));
-    spit(path, jmin::dump(*wrap_key_member("h", h), 4, false));
+    spit(path, jmin::dump(*wrap_key_member("h", h, key_tag), 4, false));
 }
-inline void write_eval_key(const std::string& path, const std::vector<Poly>& a, const std::vector<Poly>& b) {
+inline void write_eval_key(const std::string& path, const std::vector<Poly>& a, const std::vector<Poly>& b,
+                           const std::string& key_tag = "") {
     jmin::Ptr k = jmin::make(jmin::Value::Array), av = jmin::make(jmin::Value::Array), bv = jmin::make(jmin::Value::Array);
     for (const Poly& p : a) av->arr.push_back(dcrtpoly_to_json(p));
     for (const Poly& p : b) bv->arr.push_back(dcrtpoly_to_json(p));
     k->arr.push_back(av);
     k->arr.push_back(bv);
-    spit(path, jmin::dump(*wrap_key_member("k", k), 4, false));
+    spit(path, jmin::dump(*wrap_key_member("k", k, key_tag), 4, false));
 }
 
 // ------------------------------------------------------------------------------------------------ container

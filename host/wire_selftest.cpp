@@ -69,6 +69,78 @@ static int t_blob() {
     return fails;
 }
 
+// cereal PortableBinary ciphertext codec (ppq_cereal.hpp) against the context of a real CC.json: exhaustive self round
+// trip, the two byte counts pinned by the reference's recorded file sizes, rejection of damaged blobs, auto-detection
+static int t_cereal(const char* ccjson_path) {
+    const std::string text = wire::slurp(ccjson_path);
+    jmin::Ptr root = jmin::parse(text);
+    const jmin::Value* elp = wire::find_member_any(*root, "elp");
+    const jmin::Value& top = elp->at("ptr_wrapper").at("data");
+    const uint32_t N = (uint32_t)top.at("value0").at("rd").as_u64();
+    std::vector<uint64_t> mod, ru;
+    for (const auto& np : top.at("p").arr) {
+        const jmin::Value& v = np->at("ptr_wrapper").at("data").at("value0");
+        mod.push_back(v.at("cm").at("v").as_u64());
+        ru.push_back(v.at("ru").at("v").as_u64());
+    }
+    const uint32_t L = (uint32_t)mod.size();
+    setenv("PPQ_QUIET", "1", 1);
+    wire::Codec codec;
+    codec.init(text, N, mod.data(), ru.data(), L);
+    CHECK(codec.write_cereal);
+    std::mt19937_64 rng(5);
+    for (uint32_t ell = L; ell >= 1; --ell) {
+        for (uint32_t level : {0u, 1u}) {
+            std::vector<uint64_t> data((size_t)2 * ell * N);
+            for (size_t i = 0; i < data.size(); ++i) data[i] = rng() % mod[(i / N) % ell];
+            wire::CtMeta m;
+            m.noise_scale_deg = 2 - level;
+            m.level = level;
+            m.slots = N / 2;
+            m.scaling_factor = level ? 1.2089e24 : 6.124908131173663e17;
+            m.scaling_factor_int = 1;
+            m.key_tag = "8857ae2821d966b1c2d1cc2bde17d2f1";
+            const std::string b64 = codec.encode(m, ell, data.data());
+            const std::vector<unsigned char> raw = wire::base64_decode(b64);
+            wire::Ct c = codec.decode(b64);
+            CHECK(c.ell == ell && c.N == N && c.data == data);
+            CHECK(std::vector<uint64_t>(mod.begin(), mod.begin() + ell) == c.moduli);
+            CHECK(c.meta.level == level && c.meta.noise_scale_deg == 2 - level && c.meta.slots == N / 2);
+            CHECK(c.meta.scaling_factor == m.scaling_factor && c.meta.key_tag == m.key_tag);
+            const size_t overhead = raw.size() - data.size() * 8;
+            // orchestration/metrics/comm_metrics.csv:10-13 -> a fresh 4-limb blob carries 1551..1553 bytes besides its
+            // residues (base64 length 1,400,172), an aggregated 3-limb one 1549..1551 (base64 length 1,050,644)
+            if (L == 4 && N == 16384 && ell == 4 && level == 0) CHECK(overhead == 1553 && b64.size() == 1400172);
+            if (L == 4 && N == 16384 && ell == 3 && level == 1) CHECK(overhead == 1551 && b64.size() == 1050644);
+            // damaged blobs must be rejected, never mis-read: truncations and a flipped byte in every structural region
+            for (size_t cut : {(size_t)0, (size_t)8, (size_t)700, raw.size() / 2, raw.size() - 1}) {
+                bool threw = false;
+                try { codec.decode(wire::base64_encode(raw.data(), cut)); } catch (const std::exception&) { threw = true; }
+                CHECK(threw);
+            }
+            for (size_t pos : {(size_t)0, (size_t)3, (size_t)20, (size_t)300, (size_t)690}) {
+                std::vector<unsigned char> bad = raw;
+                bad[pos] ^= 0x5a;
+                bool threw = false;
+                try { codec.decode(wire::base64_encode(bad.data(), bad.size())); } catch (const std::exception&) { threw = true; }
+                CHECK(threw);
+            }
+            {   // trailing garbage
+                std::vector<unsigned char> bad = raw;
+                bad.push_back(0);
+                bool threw = false;
+                try { codec.decode(wire::base64_encode(bad.data(), bad.size())); } catch (const std::exception&) { threw = true; }
+                CHECK(threw);
+            }
+            // the private blob is still understood by the same entry point
+            wire::Ct d = codec.decode(wire::encode_ct(m, ell, N, mod.data(), data.data()));
+            CHECK(d.data == data && d.meta.level == level);
+        }
+    }
+    std::cout << "cereal codec: context " << codec.cx.ctx_bytes.size() << " bytes, " << codec.cx.ctx_ids << " pointer ids\n";
+    return fails;
+}
+
 static int t_json() {
     const std::string src = "{\"weights_summary\":[{\"values\":[\"QQ==\"],\"shape\":[2,3],\"layer\":\"gru/kernel\",\"mean\":\"TQ==\",\"std_dev\":\"Uw==\"}],\"x\":18446744073709551615,\"y\":-1.5e-3,\"z\":\"a\\\"b\\n\"}";
     jmin::Ptr v = jmin::parse(src);
@@ -135,9 +207,10 @@ int main(int argc, char** argv) {
         if (mode == "base64") return t_base64() ? 1 : 0;
         if (mode == "blob") return t_blob() ? 1 : 0;
         if (mode == "json") return t_json() ? 1 : 0;
+        if (mode == "cereal" && argc == 3) return t_cereal(argv[2]) ? 1 : 0;
         if (mode == "privkey" && argc == 3) return t_privkey(argv[2]);
         if (mode == "mkkeys" && argc == 4) return t_mkkeys(argv[2], argv[3]);
-        std::cerr << "usage: wire_selftest base64|blob|json|privkey <file>|mkkeys <in.json> <dir>\n";
+        std::cerr << "usage: wire_selftest base64|blob|json|cereal <CC.json>|privkey <file>|mkkeys <in.json> <dir>\n";
         return 2;
     } catch (const std::exception& e) {
         std::cerr << "wire_selftest: " << e.what() << "\n";

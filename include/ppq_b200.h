@@ -115,6 +115,10 @@ int ppq_ks_moddown(ppq_ctx*, int ell, const uint64_t* d_ext, uint64_t* d_out, si
 int ppq_params_dump(int logN, int L, const uint64_t* q_moduli, int dnum, int aux_bits, int extra_bits, int ell,
                     char* buf, size_t cap, size_t* need);
 
+/* the Q chain GenCryptoContext builds under FLEXIBLEAUTOEXT (server/src/genCC.cpp:46-68): host only */
+int ppq_params_chain(int logN, int depth, int first_bits, int scale_bits, int extra_bits, uint64_t* q_out, int cap,
+                     int* n_out);
+
 /* ---- cc->EvalAdd(ct1, ct2) (server/src/aggregateEncryptedWeights.cpp:82,91,106) */
 int ppq_eval_add(ppq_ctx*, int ell, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, size_t n,
                  void* stream);

@@ -62,6 +62,7 @@ _SIGS = {
     "ppq_ks_moddown": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, vp]),
     "ppq_params_dump": (C.c_int, [C.c_int, C.c_int, u64p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_size_t,
                                   C.POINTER(C.c_size_t)]),
+    "ppq_params_chain": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u64p, C.c_int, C.POINTER(C.c_int)]),
     "ppq_eval_add": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_size_t, vp]),
     "ppq_finalize_sum": (C.c_int, [vp, C.c_int, vp, C.c_size_t, vp]),
     "ppq_eval_mult_const": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, C.c_double, C.c_double, C.c_int, vp]),

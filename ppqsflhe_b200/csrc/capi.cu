@@ -797,6 +797,18 @@ extern "C" int ppq_ks_moddown(ppq_ctx* c, int ell, const uint64_t* d_ext, uint64
     return PPQ_OK;
 }
 
+// FLEXIBLEAUTOEXT prime chain of GenCryptoContext for (depth, firstModSize, scalingModSize, extraBits): host only
+extern "C" int ppq_params_chain(int logN, int depth, int first_bits, int scale_bits, int extra_bits, uint64_t* q_out,
+                                int cap, int* n_out) {
+    if (!q_out || !n_out || depth < 1 || logN < 10 || logN > 17 || first_bits > 60 || scale_bits > 60 || scale_bits < 16)
+        return fail(PPQ_EINVAL, "ppq_params_chain: bad arguments");
+    const std::vector<host::u64> q = host::synthetic_chain(logN, depth, first_bits, scale_bits, extra_bits);
+    *n_out = (int)q.size();
+    if ((int)q.size() > cap) return fail(PPQ_EINVAL, "ppq_params_chain: output array too small");
+    for (size_t i = 0; i < q.size(); ++i) q_out[i] = q[i];
+    return PPQ_OK;
+}
+
 // Host-only view of everything the library derives from (N, Q chain, dnum): no device needed.  JSON text.
 static void js_arr(std::string& o, const char* name, const std::vector<u64>& v) {
     o += "\"";

@@ -44,6 +44,42 @@ def test_wire_selftests(tools, mode):
     assert r.returncode == 0, r.stderr
 
 
+def test_cereal_ciphertext_codec_selftest(tools):
+    """ppq_cereal.hpp: self round trip at every limb count / sharing pattern, damaged blobs rejected, and the two byte
+    counts the reference's recorded file sizes pin (orchestration/metrics/comm_metrics.csv:10-13): 1553 bytes around a
+    fresh 4-limb ciphertext, 1551 around an aggregated 3-limb one."""
+    r = run(os.path.join(tools, "wire_selftest"), "cereal", os.path.join(GOLD, "CC.json"))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "context 676 bytes, 9 pointer ids" in r.stdout
+
+
+def test_gencc_reproduces_the_reference_cc_json_byte_for_byte(tools, tmp_path):
+    """host/genCC on the reference's own config (server/config/config_cc.json: depth 2, scaling 40, batch 8192, INDCPA)
+    must write server/storage/CC.json (= tests/golden/CC.json, 15,199 bytes) exactly: ring dimension from the security
+    table, the four primes and roots, the 160-bit composite modulus, cereal's field order, ids and number formatting."""
+    cfg = tmp_path / "config_cc.json"
+    cfg.write_text(json.dumps({"MultiplicativeDepth": 2, "ScalingModSize": 40, "BatchSize": 8192, "PREMode": "INDCPA"}))
+    out = tmp_path / "CC.json"
+    r = run(os.path.join(tools, "genCC"), str(cfg), str(out))
+    assert r.returncode == 0 and "CryptoContext Generated and saved to" in r.stdout, r.stderr
+    want = open(os.path.join(GOLD, "CC.json"), "rb").read()
+    assert len(want) == 15199 and out.read_bytes() == want
+    # the reference's FIXED_NOISE quirk (genCC.cpp:59-60 -> FIXEDMANUAL) is refused, unknown modes exit 1 like the reference
+    cfg.write_text(json.dumps({"MultiplicativeDepth": 2, "ScalingModSize": 40, "PREMode": "FIXED_NOISE"}))
+    assert run(os.path.join(tools, "genCC"), str(cfg), str(out)).returncode == 1
+    cfg.write_text(json.dumps({"PREMode": "nope"}))
+    r = run(os.path.join(tools, "genCC"), str(cfg), str(out))
+    assert r.returncode == 1 and "Unknown PREMode in config: nope" in r.stderr
+    r = run(os.path.join(tools, "genCC"), str(tmp_path / "missing.json"), str(out))
+    assert r.returncode == 1 and "Failed to open" in r.stderr
+    # a deeper context: loads back through the library's own CC.json reader with the chain the library derives
+    cfg.write_text(json.dumps({"MultiplicativeDepth": 6, "ScalingModSize": 50, "BatchSize": 16384, "PREMode": "INDCPA"}))
+    assert run(os.path.join(tools, "genCC"), str(cfg), str(out)).returncode == 0
+    import oracle
+    cc = oracle.parse_ccjson(out.read_text())
+    assert cc["logN"] == 15 and len(cc["moduli"]) == 8 and cc["dnum"] == 3
+
+
 def _sk_eval(o, c):
     tern = np.load(os.path.join(GOLD, "openfhe_sk_golden.npz"))[f"c{c}_ternary"].astype(np.int64)
     return np.stack([o.small_to_eval(r, tern) for r in range(o.M)])
@@ -175,6 +211,15 @@ def test_reference_round_through_the_binaries(tools, tmp_path, oracle_c1, ccjson
     # wire sizes: fresh ct = 2 x 4 limbs, aggregated = 2 x 3 limbs (comm_metrics.csv:10-13 ratio 37.8 MB : 28.4 MB)
     s_enc, s_agg = os.path.getsize(tmp_path / "enc_c1.json"), os.path.getsize(tmp_path / "agg.json")
     assert abs(s_agg / s_enc - 0.75) < 0.01
+    # ... and, with the cereal PortableBinary blobs (default), the files have EXACTLY the sizes the reference recorded for
+    # this model (comm_metrics.csv:10-13): 37,806,011 bytes encrypted, 28,368,755 bytes aggregated / domain-changed
+    assert s_enc == 37806011 and os.path.getsize(tmp_path / "enc_c2.json") == 37806011
+    assert s_agg == 28368755 and os.path.getsize(tmp_path / "agg_to_c1.json") == 28368755
+    # the private PPQCT1 blob is still written on request and read back by the same tools
+    r = run(T("changeCipherDomain"), str(cc_path), str(tmp_path / "c2/rekey.key"), str(tmp_path / "agg.json"), str(tmp_path / "agg_p.json"),
+            env=dict(env, PPQ_BLOB="ppqct1"))
+    assert r.returncode == 0 and os.path.getsize(tmp_path / "agg_p.json") < 28368755
+    ok(T("decryptModelWeights"), str(cc_path), str(tmp_path / "c1/private.key"), str(tmp_path / "agg_p.json"), str(tmp_path / "dec_p.json"))
     # client_fns.sh:90-102
     ok(T("decryptModelWeights"), str(cc_path), str(tmp_path / "c2/private.key"), str(tmp_path / "agg.json"), str(tmp_path / "dec_c2.json"))
     ok(T("decryptModelWeights"), str(cc_path), str(tmp_path / "c1/private.key"), str(tmp_path / "agg_to_c1.json"), str(tmp_path / "dec_c1.json"))
@@ -234,3 +279,112 @@ def test_round_with_keys_made_by_the_binaries(tools, tmp_path, ccjson_text):
     # wrong-domain guard: REkeyGen refuses a public key file in place of the private key
     r = run(T("REkeyGen"), str(cc_path), str(tmp_path / "c2/public.key"), str(tmp_path / "c2/public.key"), str(tmp_path / "x.key"))
     assert r.returncode == 1 and "Error loading Client private key" in r.stderr
+
+
+class _Served:
+    """a resident ppq_served process driven over its stdin/stdout line protocol"""
+
+    def __init__(self, tools, cc_path, env):
+        self.p = subprocess.Popen([os.path.join(tools, "ppq_served"), str(cc_path)], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
+                                  stderr=subprocess.PIPE, text=True, env=env)
+        seen = []
+        while True:
+            line = self.p.stdout.readline()
+            assert line, "ppq_served died: " + self.p.stderr.read()
+            seen.append(line)
+            if line.startswith("[served] ready"):
+                break
+
+    def ask(self, line):
+        self.p.stdin.write(line + "\n")
+        self.p.stdin.flush()
+        r = self.p.stdout.readline().strip()
+        return r
+
+    def close(self):
+        r = self.ask("QUIT")
+        self.p.wait(timeout=30)
+        return r
+
+
+def _kv(reply):
+    return {k: v for k, v in (t.split("=", 1) for t in reply.split()[1:] if "=" in t)}
+
+
+@pytest.mark.gpu
+def test_resident_server_three_clients_two_rounds(tools, tmp_path, ccjson_text):
+    """host/ppq_served: context and re-encryption keys parsed ONCE, then whole rounds per request --
+    for 3 clients (the reference hard-codes 2): clients 1, 2 -> domain 3, + client 3's own, x 1/3 with rescale, fan-out
+    of the aggregate back to domains 1 and 2.  Round 2 runs without any key re-parse.  The 2-client request is checked
+    against the tool-by-tool flow of orchestration/server_fns.sh:62-80 (decrypted outputs identical)."""
+    g = np.load(os.path.join(GOLD, "weights_golden.npz"))
+    cc_path = tmp_path / "CC.json"
+    cc_path.write_text(ccjson_text)
+    T = lambda name: os.path.join(tools, name)  # noqa: E731
+
+    def ok(seed, *a):
+        r = run(*a, env=dict(os.environ, PPQ_SEED=str(seed), PPQ_QUIET="1"))
+        assert r.returncode == 0, r.stdout + r.stderr
+        return r.stdout
+
+    w = {}
+    for c in (1, 2, 3):
+        d = tmp_path / f"c{c}"
+        d.mkdir()
+        ok(8000 + c, T("keyGen"), str(cc_path), str(d / "public.key"), str(d / "private.key"))
+        src = 1 if c != 2 else 2
+        plain = _weights_json(d / "weights.json", g, src)
+        if c == 3:  # a third model: client 1's weights negated and shifted
+            doc = json.load(open(d / "weights.json"))
+            for t in doc["weights_summary"]:
+                t["values"] = [0.125 - v for v in t["values"]]
+                t["mean"] = 0.125 - t["mean"]
+            json.dump(doc, open(d / "weights.json", "w"))
+        doc = json.load(open(d / "weights.json"))["weights_summary"][:-1]
+        w[c] = np.concatenate([np.asarray(t["values"]) for t in doc])
+    for a, b in ((1, 3), (2, 3), (3, 1), (3, 2), (1, 2), (2, 1)):
+        ok(8100 + 10 * a + b, T("REkeyGen"), str(cc_path), str(tmp_path / f"c{a}/private.key"), str(tmp_path / f"c{b}/public.key"),
+           str(tmp_path / f"rk_{a}_{b}.key"))
+    for c in (1, 2, 3):
+        ok(8200 + c, T("encryptModelWeights"), str(cc_path), str(tmp_path / f"c{c}/public.key"), str(tmp_path / f"c{c}/weights.json"),
+           str(tmp_path / f"enc_c{c}.json"))
+    sv = _Served(tools, cc_path, dict(os.environ, PPQ_QUIET="1"))
+    try:
+        for a, b in ((1, 3), (2, 3), (3, 1), (3, 2), (1, 2), (2, 1)):
+            r = sv.ask(f"LOAD_REKEY rk{a}{b} {tmp_path}/rk_{a}_{b}.key")
+            assert r.startswith("OK rekey"), r
+        assert sv.ask("ROUND target=nofile out=x").startswith("ERR"), "a bad request must not kill the server"
+        assert sv.ask(f"ROUND target={tmp_path}/enc_c3.json out={tmp_path}/x.json up=nokey:{tmp_path}/enc_c1.json").startswith("ERR unknown rekey")
+        rounds = []
+        for rnd in (1, 2):
+            r = sv.ask(f"ROUND target={tmp_path}/enc_c3.json out={tmp_path}/agg3_r{rnd}.json up=rk13:{tmp_path}/enc_c1.json "
+                       f"up=rk23:{tmp_path}/enc_c2.json down=rk31:{tmp_path}/agg1_r{rnd}.json down=rk32:{tmp_path}/agg2_r{rnd}.json")
+            assert r.startswith("OK clients=3 cts=27 limbs_out=3"), r
+            rounds.append(_kv(r))
+        st = _kv(sv.ask("STATS"))
+        assert st["rounds"] == "2" and st["rekeys"] == "6" and st["key_parses"] == "6", st  # no key parsed after the LOAD_REKEYs
+        # 2-client request == the reference's three tool invocations
+        r = sv.ask(f"ROUND target={tmp_path}/enc_c2.json out={tmp_path}/sv_agg.json up=rk12:{tmp_path}/enc_c1.json "
+                   f"down=rk21:{tmp_path}/sv_agg_to_c1.json")
+        assert r.startswith("OK clients=2 cts=27"), r
+    finally:
+        assert sv.close() == "OK bye"
+    want = (w[1] + w[2] + w[3]) / 3
+    for c in (1, 2, 3):
+        for rnd in (1, 2):
+            ok(0, T("decryptModelWeights"), str(cc_path), str(tmp_path / f"c{c}/private.key"), str(tmp_path / f"agg{c}_r{rnd}.json"),
+               str(tmp_path / f"dec{c}_r{rnd}.json"))
+            dec = json.load(open(tmp_path / f"dec{c}_r{rnd}.json"))["weights_summary"]
+            vals = np.concatenate([np.asarray(d["values"]) for d in dec])
+            assert np.max(np.abs(vals - want)) < 2.0 ** -20, (c, rnd)
+        assert open(tmp_path / f"agg{c}_r1.json", "rb").read() == open(tmp_path / f"agg{c}_r2.json", "rb").read()  # deterministic
+    assert os.path.getsize(tmp_path / "agg3_r1.json") == 28368755
+    # tool-by-tool flow for clients 1, 2 and the served result decrypt to the same numbers, bit for bit
+    ok(0, T("changeCipherDomain"), str(cc_path), str(tmp_path / "rk_1_2.key"), str(tmp_path / "enc_c1.json"), str(tmp_path / "t_c1_to_c2.json"))
+    ok(0, T("aggregateEncryptedWeights"), str(cc_path), str(tmp_path / "enc_c2.json"), str(tmp_path / "t_c1_to_c2.json"), str(tmp_path / "t_agg.json"))
+    ok(0, T("changeCipherDomain"), str(cc_path), str(tmp_path / "rk_2_1.key"), str(tmp_path / "t_agg.json"), str(tmp_path / "t_agg_to_c1.json"))
+    for who, a, b in ((2, "sv_agg.json", "t_agg.json"), (1, "sv_agg_to_c1.json", "t_agg_to_c1.json")):
+        ok(0, T("decryptModelWeights"), str(cc_path), str(tmp_path / f"c{who}/private.key"), str(tmp_path / a), str(tmp_path / "da.json"))
+        ok(0, T("decryptModelWeights"), str(cc_path), str(tmp_path / f"c{who}/private.key"), str(tmp_path / b), str(tmp_path / "db.json"))
+        assert open(tmp_path / "da.json", "rb").read() == open(tmp_path / "db.json", "rb").read()
+    print("ppq_served rounds:", rounds)
