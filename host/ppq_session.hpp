@@ -120,9 +120,21 @@ struct Batch {
 };
 // decode all blobs, grouped by limb count (one group in every file the reference flow produces)
 inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<BlobRef>& refs) {
+    // base64 + blob decoding is the host-side cost of a file (a 38 MB container holds 27 blobs): one blob per thread
+    std::vector<wire::Ct> cts(refs.size());
+    std::vector<std::string> errs(refs.size());
+#pragma omp parallel for schedule(dynamic)
+    for (size_t i = 0; i < refs.size(); ++i) {
+        try {
+            cts[i] = s.codec.decode(*refs[i].slot);
+        } catch (const std::exception& e) {
+            errs[i] = e.what()[0] ? e.what() : "decode error";
+        }
+    }
     std::map<uint32_t, Batch> groups;
     for (size_t i = 0; i < refs.size(); ++i) {
-        wire::Ct c = s.codec.decode(*refs[i].slot);
+        if (!errs[i].empty()) throw std::runtime_error(errs[i]);
+        wire::Ct& c = cts[i];
         if (c.N != s.N) throw std::runtime_error("ciphertext ring dimension differs from CC.json");
         if ((int)c.ell > s.L) throw std::runtime_error("ciphertext has more limbs than the context");
         for (uint32_t k = 0; k < c.ell; ++k)
@@ -131,15 +143,22 @@ inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<
         b.ell = c.ell;
         b.index.push_back(i);
         b.meta.push_back(c.meta);
-        b.data.insert(b.data.end(), c.data.begin(), c.data.end());
+    }
+    for (auto& kv : groups) {  // gather: [n][2][ell][N]
+        Batch& b = kv.second;
+        const size_t ct = (size_t)2 * b.ell * s.N;
+        b.data.resize(b.n() * ct);
+#pragma omp parallel for schedule(static)
+        for (size_t k = 0; k < b.n(); ++k) std::memcpy(b.data.data() + k * ct, cts[b.index[k]].data.data(), ct * sizeof(uint64_t));
     }
     return groups;
 }
 inline void encode_back(const Session& s, const Batch& b, uint32_t ell_out, const std::vector<wire::CtMeta>& meta,
                         const std::vector<uint64_t>& data, const std::vector<BlobRef>& refs) {
     const size_t ct = (size_t)2 * ell_out * s.N;
-    for (size_t k = 0; k < b.n(); ++k)
-        *refs[b.index[k]].slot = s.codec.encode(meta[k], ell_out, data.data() + k * ct);
+    s.codec.warn_once();
+#pragma omp parallel for schedule(dynamic)
+    for (size_t k = 0; k < b.n(); ++k) *refs[b.index[k]].slot = s.codec.encode(meta[k], ell_out, data.data() + k * ct);
 }
 
 // CryptoObject::keyTag of a new key pair: 32 hex digits (OpenFHE's GenerateUniqueKeyID writes 128 random bits this way)

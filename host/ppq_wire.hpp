@@ -208,10 +208,15 @@ struct Codec {
         write_cereal = !(e && std::string(e) == "ppqct1");
     }
     void warn_once() const {
-        if (!warned && !std::getenv("PPQ_QUIET"))
+        bool first;
+#pragma omp critical(ppq_codec_warn)
+        {
+            first = !warned;
+            warned = true;
+        }
+        if (first && !std::getenv("PPQ_QUIET"))
             std::fprintf(stderr, "[ppq] note: cereal PortableBinary ciphertext blobs are written/read to a layout derived from the "
                                  "reference's own cereal-JSON files and file sizes; byte identity is unverified against OpenFHE\n");
-        warned = true;
     }
     std::string encode(const CtMeta& m, uint32_t ell, const uint64_t* data) const {
         if (!write_cereal) return encode_ct(m, ell, cx.N, cx.moduli.data(), data);
