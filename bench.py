@@ -296,8 +296,7 @@ def run_aggregation(torch, cc, cfg, clients, steps, warmup, comm=None, world=1, 
 
     def step():
         for r in range(rounds):
-            for ct, rk in zip(cts[r * nc:(r + 1) * nc], keys[r * nc:(r + 1) * nc]):
-                agg.add(ct, rk)
+            agg.add_many(cts[r * nc:(r + 1) * nc], keys[r * nc:(r + 1) * nc])
             if nc:
                 agg.finish(out=acc.data)
             else:

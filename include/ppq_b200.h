@@ -186,6 +186,10 @@ int ppq_rekeygen(ppq_ctx*, const uint64_t* d_sk_old, const uint64_t* d_pkb, cons
 typedef struct ppq_agg ppq_agg;
 int ppq_agg_create(ppq_ctx*, int ell, size_t n_slots, ppq_agg** out);
 int ppq_agg_add(ppq_agg*, const ppq_rekey*, const uint64_t* d_in, void* stream);
+/* several clients at once (HOST arrays of n_clients handles / device pointers): identical result; the library takes
+ * them a few per pass so that the slot sums are read and written once per pass instead of once per client */
+int ppq_agg_add_many(ppq_agg*, const ppq_rekey* const* rekeys, const uint64_t* const* d_ins, size_t n_clients,
+                     void* stream);
 int ppq_agg_finish(ppq_agg*, uint64_t* d_out, void* stream);
 size_t ppq_agg_count(const ppq_agg*); /* clients added since the last finish */
 void ppq_agg_destroy(ppq_agg*);

@@ -79,6 +79,7 @@ _SIGS = {
     "ppq_reencrypt_aggregate_host": (C.c_int, [vp, C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
     "ppq_agg_create": (C.c_int, [vp, C.c_int, C.c_size_t, C.POINTER(vp)]),
     "ppq_agg_add": (C.c_int, [vp, vp, vp, vp]),
+    "ppq_agg_add_many": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.c_size_t, vp]),
     "ppq_agg_finish": (C.c_int, [vp, vp, vp]),
     "ppq_agg_count": (C.c_size_t, [vp]),
     "ppq_agg_destroy": (None, [vp]),

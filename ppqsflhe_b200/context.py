@@ -153,6 +153,20 @@ class Aggregator:
         check(lib().ppq_agg_add(self.h, rekey.h, _ptr(ct.data), _stream()))
         return self
 
+    def add_many(self, cts, rekeys):
+        """Several clients in one call (ppq_agg_add_many): same result as add() per client."""
+        cts, rekeys = list(cts), list(rekeys)
+        if len(cts) != len(rekeys):
+            raise ValueError("Aggregator.add_many: one rekey per client batch")
+        for ct in cts:
+            if ct.n != self.n_slots or ct.ell != self.ell:
+                raise ValueError("Aggregator.add_many: batch shape differs from the aggregator's")
+        if cts:
+            hk = (vp * len(cts))(*[r.h for r in rekeys])
+            hp = (vp * len(cts))(*[_ptr(ct.data) for ct in cts])
+            check(lib().ppq_agg_add_many(self.h, hk, hp, len(cts), _stream()))
+        return self
+
     @property
     def count(self):
         return int(lib().ppq_agg_count(self.h))

@@ -1357,6 +1357,110 @@ extern "C" int ppq_agg_add(ppq_agg* a, const ppq_rekey* rk, const uint64_t* d_in
     return rc;
 }
 
+// several clients per pass (device-resident inputs): the ModUp half runs over nb x n_slots ciphertexts per launch and the
+// inner product sums the nb clients of a slot in registers before it touches the running sum (k_ip_agg)
+static int agg_add_batch(ppq_agg* a, const ppq_rekey* const* rks, const uint64_t* const* ins, int nb, cudaStream_t st) {
+    ppq_ctx* c = a->ctx;
+    const int ell = a->ell;
+    const size_t N = c->hp.N, n = a->n_slots, ct = (size_t)2 * ell * N;
+    KsPlanDev* p;
+    if (int rc = get_ks_plan(c, ell, &p)) return rc;
+    const int K = c->hp.K, L = c->hp.L, parts = p->h.parts, M = ell + K;
+    const size_t ys = (size_t)ell * N, ds = (size_t)parts * M * N, ng = n * nb;
+    CU(c->scratch.ensure((ys + ds) * ng));
+    u64* y = c->scratch.p;
+    u64* dig = y + ys * ng;
+    const size_t ext_gs = (size_t)2 * K * N, ring_stride = n * ext_gs;
+    u64* extp = a->ring.p + (size_t)a->in_group * ring_stride;
+    prof_mark(c, st, -1);
+    for (int cl = 0; cl < nb; ++cl)
+        launch_inv_row(c->k, (const u64*)ins[cl] + (size_t)ell * N, ct, y + (size_t)cl * n * ys, ys, p->c1_limb.p, ell, (int)n, st);
+    prof_mark(c, st, 0);
+    launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, ell, (int)ng, st);
+    prof_mark(c, st, 1);
+    for (const auto& d : p->digits)
+        if (!launch_bconv(c->k, y, ys, dig, ds, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, (int)ng, st))
+            return fail(PPQ_EINVAL, "digit wider than 32 limbs");
+    prof_mark(c, st, 2);
+    launch_fwd_col_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st);
+    prof_mark(c, st, 3);
+    launch_fwd_row_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st, PPQ_DIGITS_LAZY_OK(parts));
+    prof_mark(c, st, 4);
+    IpArgs ia;
+    ia.c1 = nullptr;
+    ia.c1_gs = ct;
+    ia.digits = dig;
+    ia.dig_gs = ds;
+    ia.key_b = ia.key_a = ia.key_qb = ia.key_qa = nullptr;
+    ia.key_q_stride = 0;
+    ia.extq = nullptr;
+    ia.extq_gs = 0;
+    ia.extp = extp;
+    ia.extp_gs = ext_gs;
+    ia.ell = ell;
+    ia.K = K;
+    ia.L = L;
+    ia.parts = parts;
+    ia.alpha = c->hp.alpha;
+    ia.agg = a->count == 0 ? 1 : 2;
+    ia.acc = a->accE.p;
+    ia.acc_gs = ct;
+    IpMulti X;
+    X.nb = nb;
+    X.extp_cs = ring_stride;
+    for (int cl = 0; cl < nb; ++cl) {
+        X.ct_in[cl] = (const u64*)ins[cl];
+        X.key_b[cl] = rks[cl]->b;
+        X.key_a[cl] = rks[cl]->a;
+        X.key_qb[cl] = rks[cl]->qb;
+        X.key_qa[cl] = rks[cl]->qa;
+        X.key_q_stride[cl] = rks[cl]->q_stride;
+    }
+    if (!launch_ip_agg(c->k, ia, X, (int)n, st)) return fail(PPQ_EINVAL, "ppq_agg_add_many: unsupported shape");
+    prof_mark(c, st, 5);
+    launch_inv_row(c->k, extp, ext_gs, extp, ext_gs, p->p_limb.p, 2 * K, (int)ng, st);
+    prof_mark(c, st, 6);
+    launch_inv_col(c->k, extp, ext_gs, p->p_limb.p, p->p_scale.p, 2 * K, (int)ng, st);
+    prof_mark(c, st, 7);
+    a->in_group += nb;
+    a->count += (size_t)nb;
+    if (a->in_group == a->group) return agg_flush(a, p, st);
+    return PPQ_OK;
+}
+
+extern "C" int ppq_agg_add_many(ppq_agg* a, const ppq_rekey* const* rks, const uint64_t* const* d_ins, size_t n_clients,
+                                void* stream) {
+    if (!a || !rks || !d_ins) return fail(PPQ_EINVAL, "ppq_agg_add_many: null argument");
+    ppq_ctx* c = a->ctx;
+    for (size_t i = 0; i < n_clients; ++i) {
+        if (!rks[i] || !d_ins[i]) return fail(PPQ_EINVAL, "ppq_agg_add_many: null client entry");
+        if (rks[i]->ctx != c) return fail(PPQ_EINVAL, "ppq_agg_add_many: rekey belongs to another context");
+    }
+    CU(cudaSetDevice(c->device));
+    int want = 2;  // clients per pass (measured on B200, profiles/r10_notes.md)
+    if (const char* e = std::getenv("PPQ_AGG_NB")) want = std::atoi(e);
+    const size_t per_client = ((size_t)a->ell + (size_t)ppq_ctx_num_parts(c, a->ell) * (a->ell + c->hp.K)) * c->hp.N * a->n_slots * sizeof(u64);
+    size_t i = 0;
+    while (i < n_clients) {
+        int nb = 1;
+        if (!a->legacy && c->wave == 0 && !std::getenv("PPQ_WAVE")) {
+            for (int cand : {4, 2}) {
+                if (cand > want || (size_t)cand > n_clients - i || a->in_group + cand > a->group) continue;
+                if (per_client * cand > ((size_t)24 << 30)) continue;  // scratch budget
+                nb = cand;
+                break;
+            }
+        }
+        int rc;
+        if (nb == 1) rc = ppq_agg_add(a, rks[i], d_ins[i], stream);
+        else rc = agg_add_batch(a, rks + i, d_ins + i, nb, (cudaStream_t)stream);
+        if (rc) return rc;
+        i += (size_t)nb;
+    }
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+
 extern "C" int ppq_agg_finish(ppq_agg* a, uint64_t* d_out, void* stream) {
     if (!a || !d_out) return fail(PPQ_EINVAL, "ppq_agg_finish: null argument");
     if (a->count == 0) return fail(PPQ_EINVAL, "ppq_agg_finish: nothing was added");

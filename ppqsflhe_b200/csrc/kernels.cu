@@ -952,6 +952,132 @@ __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip
     }
 }
 
+// Inner product of NB clients' digits with their keys for the deferred-ModDown aggregator (ppq_agg_add_many).
+// Same tiling as k_ip_tma (one CTA = limb r x IPT points, key tiles by TMA bulk copies, reused for every slot), but the
+// CTA holds the tiles of NB clients and walks (slot, client): the Q-limb results of a slot's NB clients (+ their c0) are
+// summed in registers and the slot's running EVAL sum is read and written ONCE per NB clients -- the read-modify-write
+// of the sum was 40 % of the kernel's HBM traffic with one client per launch, and the kernel is HBM-bound.
+#ifndef PPQ_IP_AGG_NB_MINB
+#define PPQ_IP_AGG_NB_MINB 2
+#endif
+template <int PARTS, int NB>
+__global__ void __launch_bounds__(256, PPQ_IP_AGG_NB_MINB) k_ip_agg(KCtx c, IpArgs A, IpMulti X, int n_g, int g_per_cta) {
+    static_assert(IPC == 1, "k_ip_agg walks one 512-point step per (slot, client)");
+    extern __shared__ __align__(128) unsigned char ip_smem[];
+    u64* keys = reinterpret_cast<u64*>(ip_smem);  // [NB][PARTS][2][IPT]
+    u64* bar = keys + (size_t)NB * PARTS * 2 * IPT;
+    const u32 N = 1u << c.logN;
+    const int r = blockIdx.y;
+    const int M = A.ell + A.K;
+    const int limb = r < A.ell ? r : A.L + (r - A.ell);
+    const size_t off = (size_t)blockIdx.x * IPT;
+    const LimbC lc = c.limbs[limb];
+    const bool isq = r < A.ell;  // block-uniform
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, (u32)(NB * PARTS * 2 * IPT * sizeof(u64)));
+#pragma unroll
+        for (int cl = 0; cl < NB; ++cl)
+#pragma unroll
+            for (int j = 0; j < PARTS; ++j) {
+                const size_t koff = ((size_t)j * (isq ? X.key_q_stride[cl] : A.L + A.K) + limb) * N + off;
+                u64* kt = keys + ((size_t)cl * PARTS + j) * 2 * IPT;
+                tma_bulk_g2s(kt, (isq ? X.key_qb[cl] : X.key_b[cl]) + koff, IPT * sizeof(u64), bar);
+                tma_bulk_g2s(kt + IPT, (isq ? X.key_qa[cl] : X.key_a[cl]) + koff, IPT * sizeof(u64), bar);
+            }
+    }
+    const int own = isq ? r / A.alpha : -1;
+    const int g0 = blockIdx.z * g_per_cta;
+    const int g1 = min(n_g, g0 + g_per_cta);
+    const u32 pt = threadIdx.x * 2;
+    ulonglong2 xn[3];
+    auto fetch = [&](int it, ulonglong2 (&d)[PARTS]) {
+        const int g = g0 + it / NB, cl = it % NB;
+        const u64* cin = X.ct_in[cl] + g * A.c1_gs;
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) {
+            const u64* dp = (j == own) ? cin + (size_t)(A.ell + r) * N + off
+                                       : A.digits + ((size_t)cl * n_g + g) * A.dig_gs + ((size_t)j * M + r) * N + off;
+            d[j] = __ldcs(reinterpret_cast<const ulonglong2*>(dp + pt));
+        }
+        if (isq) {
+            xn[0] = __ldcs(reinterpret_cast<const ulonglong2*>(cin + (size_t)r * N + off + pt));
+            if (cl == 0 && A.agg == 2) {
+                const u64* ap = A.acc + g * A.acc_gs + (size_t)r * N + off + pt;
+                xn[1] = *reinterpret_cast<const ulonglong2*>(ap);
+                xn[2] = *reinterpret_cast<const ulonglong2*>(ap + (size_t)A.ell * N);
+            }
+        }
+    };
+    const int n_it = (g1 - g0) * NB;
+    ulonglong2 dn[PARTS];
+    if (n_it > 0) fetch(0, dn);
+    mbar_wait(bar, 0);
+    for (int i = threadIdx.x; i < NB * PARTS * 2 * IPT / 2; i += 256) {  // Karatsuba halves, once, in place
+        ulonglong2* kp = reinterpret_cast<ulonglong2*>(keys) + i;
+        const ulonglong2 v = *kp;
+        *kp = make_ulonglong2(kara_pack(v.x), kara_pack(v.y));
+    }
+    __syncthreads();
+    u64 v0 = 0, v1 = 0, w0 = 0, w1 = 0;
+    for (int it = 0; it < n_it; ++it) {
+        ulonglong2 d[PARTS], xc[3];
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) d[j] = dn[j];
+        xc[0] = xn[0];
+        xc[1] = xn[1];
+        xc[2] = xn[2];
+        if (it + 1 < n_it) fetch(it + 1, dn);
+        const int g = g0 + it / NB, cl = it % NB;
+        const u64* kt = keys + (size_t)cl * PARTS * 2 * IPT;
+        KaraAcc b0, b1, a0, a1;
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) {
+            const ulonglong2 kb = *reinterpret_cast<const ulonglong2*>(kt + (size_t)(2 * j) * IPT + pt);
+            const ulonglong2 ka = *reinterpret_cast<const ulonglong2*>(kt + (size_t)(2 * j + 1) * IPT + pt);
+            const Kara3 dx(d[j].x), dy(d[j].y);
+            b0.mac(dx, Kara3(kb.x, Kara3::Packed{}));
+            b1.mac(dy, Kara3(kb.y, Kara3::Packed{}));
+            a0.mac(dx, Kara3(ka.x, Kara3::Packed{}));
+            a1.mac(dy, Kara3(ka.y, Kara3::Packed{}));
+        }
+        if (isq) {
+            if (cl == 0) {
+                const bool have = A.agg == 2;
+                v0 = have ? xc[1].x : 0ull;
+                v1 = have ? xc[1].y : 0ull;
+                w0 = have ? xc[2].x : 0ull;
+                w1 = have ? xc[2].y : 0ull;
+            }
+            // per client x' + c0 < 4q (lazy) or < 2q (canonical x'): NB (x' + c0) + sum stays below 16q
+            if (NB <= 2) {
+                v0 += b0.reduce_lazy3(lc) + xc[0].x;
+                v1 += b1.reduce_lazy3(lc) + xc[0].y;
+                w0 += a0.reduce_lazy3(lc);
+                w1 += a1.reduce_lazy3(lc);
+            } else {
+                v0 += b0.reduce(lc) + xc[0].x;
+                v1 += b1.reduce(lc) + xc[0].y;
+                w0 += a0.reduce(lc);
+                w1 += a1.reduce(lc);
+            }
+            if (cl == NB - 1) {
+                u64* o0 = A.acc + g * A.acc_gs + (size_t)r * N + off;
+                *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(canon_any16(v0, lc), canon_any16(v1, lc));
+                *reinterpret_cast<ulonglong2*>(o0 + (size_t)A.ell * N + pt) = make_ulonglong2(canon_any16(w0, lc), canon_any16(w1, lc));
+            }
+        } else {
+            u64* o0 = A.extp + (size_t)cl * X.extp_cs + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
+            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
+            *reinterpret_cast<ulonglong2*>(o0 + (size_t)A.K * N + pt) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
+        }
+    }
+}
+
 // Forward ROW pass + ModDown combine: out = (x - conv) * P^-1 (+ c0 on poly 0) (+ running sum).
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_moddown(KCtx c, MdArgs A, int n_g) {
@@ -1528,6 +1654,35 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
         default: return false;
     }
 #undef PPQ_IP
+}
+bool launch_ip_agg(const KCtx& c, const IpArgs& a, const IpMulti& m, int n_g, cudaStream_t st) {
+    const int N = 1 << c.logN;
+    if (N % IPT || m.nb < 1 || m.nb > 4 || m.nb == 3) return false;
+    const int tiles = N / IPT, M = a.ell + a.K;
+    int gz = 1;
+    while (tiles * M * gz < 148 * 4 * (2048 / IPT) && gz < n_g) gz *= 2;
+    const int g_per = (n_g + gz - 1) / gz;
+    gz = (n_g + g_per - 1) / g_per;
+    dim3 grid(tiles, M, gz);
+    count_launch();
+#define PPQ_IPA(P, NBV)                                                                                        \
+    {                                                                                                          \
+        const size_t sm = (size_t)NBV * P * 2 * IPT * sizeof(u64) + 16;                                        \
+        cudaFuncSetAttribute(k_ip_agg<P, NBV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);          \
+        k_ip_agg<P, NBV><<<grid, 256, sm, st>>>(c, a, m, n_g, g_per);                                          \
+        return true;                                                                                           \
+    }
+#define PPQ_IPA_P(P)                       \
+    case P:                                \
+        if (m.nb == 1) PPQ_IPA(P, 1)       \
+        if (m.nb == 2) PPQ_IPA(P, 2)       \
+        PPQ_IPA(P, 4)
+    switch (a.parts) {
+        PPQ_IPA_P(1) PPQ_IPA_P(2) PPQ_IPA_P(3) PPQ_IPA_P(4) PPQ_IPA_P(5) PPQ_IPA_P(6)
+        default: return false;
+    }
+#undef PPQ_IPA_P
+#undef PPQ_IPA
 }
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
     count_launch();

@@ -95,6 +95,20 @@ struct IpArgs {
     size_t c0_gs = 0;
 };
 void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
+// ---- several clients per inner-product launch (ppq_agg_add_many): client cl < nb has its own input ciphertexts, key
+// and P-limb output block; digits of client cl, slot g sit at a.digits + (cl*n_g + g)*a.dig_gs.  A CTA sums the Q-limb
+// results of the nb clients of a slot in registers, so the slot's running sum is read and written once per nb clients.
+struct IpMulti {
+    int nb = 1;
+    const u64* ct_in[4] = {};   // [n_g][2][ell][N] of each client (c0 then c1 limbs), slot stride a.c1_gs
+    const u64* key_b[4] = {};
+    const u64* key_a[4] = {};
+    const u64* key_qb[4] = {};
+    const u64* key_qa[4] = {};
+    int key_q_stride[4] = {};
+    size_t extp_cs = 0;         // client stride of the P-limb output: a.extp + cl*extp_cs + g*a.extp_gs
+};
+bool launch_ip_agg(const KCtx& c, const IpArgs& a, const IpMulti& m, int n_g, cudaStream_t st);
 // ---- split form: digits already in EVAL (k_fwd_row_plain on a.digits); pointwise inner product with the key tile
 // staged in shared memory by TMA bulk copies and reused across the wave.  extp receives EVAL P limbs (run
 // launch_inv_row on it afterwards).  Returns false if the shape is unsupported (parts > 6 or N < 2048).

@@ -287,6 +287,28 @@ def test_aggregator_group_and_wave_independent(group, wave, monkeypatch):
     cc.set_wave(0)
 
 
+@pytest.mark.parametrize("kind,ell,n_clients,n_slots,nb", [("c1", 4, 5, 3, 2), ("c1", 3, 9, 2, 4), ((12, 5, 3, 45), 7, 11, 2, 4),
+                                                           ((13, 38, 3, 59), 40, 6, 1, 2), ((16, 18, 3, 59), 20, 7, 2, 2),
+                                                           ((16, 18, 3, 59), 20, 9, 2, 4)])
+def test_aggregator_add_many_bit_exact(kind, ell, n_clients, n_slots, nb, monkeypatch):
+    """ppq_agg_add_many (k_ip_agg: nb clients per inner-product pass, slot sums touched once per pass) against the oracle's
+    per-client ReEncrypt + EvalAdd, with client counts that leave odd remainders and cross the group-of-8 boundary."""
+    from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey, to_device_u64
+    monkeypatch.setenv("PPQ_AGG_NB", str(nb))
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(2000 + n_clients * 7 + ell)
+    cts = np.stack([_rand_ct(rng, o, ell, n_slots) for _ in range(n_clients)])
+    keys = [_rand_key(rng, o) for _ in range(n_clients)]
+    rks = [EvalKey(cc, *k) if i % 2 else EvalKey.upload(cc, *k) for i, k in enumerate(keys)]  # both key layouts
+    agg = Aggregator(cc, ell, n_slots)
+    batches = [CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()) for c in range(n_clients)]
+    agg.add_many(batches[:1], rks[:1])
+    agg.add_many(batches[1:], rks[1:])
+    assert agg.count == n_clients
+    want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+    assert np.array_equal(agg.finish().numpy(), want)
+
+
 def test_aggregator_extreme_residues():
     """All-(q-1) and all-zero inputs and keys: the largest operands every lazy bound has to hold."""
     from ppqsflhe_b200 import Aggregator, CiphertextBatch, CtMeta, EvalKey, to_device_u64
@@ -315,6 +337,9 @@ def test_aggregator_extreme_residues():
         for c in range(n_clients):
             agg.add(CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()), EvalKey(cc, *keys[c]))
         want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+        assert np.array_equal(agg.finish().numpy(), want)
+        rks = [EvalKey(cc, *keys[c]) for c in range(n_clients)]  # the several-clients-per-pass form on the same extremes
+        agg.add_many([CiphertextBatch(to_device_u64(cts[c], cc.device), CtMeta()) for c in range(n_clients)], rks)
         assert np.array_equal(agg.finish().numpy(), want)
 
 

@@ -52,8 +52,7 @@ def main():
             for ct, rk in zip(cts, keys):
                 cc.ReEncryptAccumulate(ct, rk, acc)
         else:
-            for ct, rk in zip(cts, keys):
-                agg.add(ct, rk)
+            agg.add_many(cts, keys)
             agg.finish(out=acc.data)
 
     step()
