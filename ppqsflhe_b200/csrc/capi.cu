@@ -1384,7 +1384,8 @@ static int agg_add_batch(ppq_agg* a, const ppq_rekey* const* rks, const uint64_t
     prof_mark(c, st, 2);
     launch_fwd_col_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st);
     prof_mark(c, st, 3);
-    launch_fwd_row_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st, PPQ_DIGITS_LAZY_OK(parts));
+    // digits canonical here: k_ip_agg puts the products of two clients into one Barrett operand (2 parts terms)
+    launch_fwd_row_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st, false);
     prof_mark(c, st, 4);
     IpArgs ia;
     ia.c1 = nullptr;
@@ -1437,7 +1438,7 @@ extern "C" int ppq_agg_add_many(ppq_agg* a, const ppq_rekey* const* rks, const u
         if (rks[i]->ctx != c) return fail(PPQ_EINVAL, "ppq_agg_add_many: rekey belongs to another context");
     }
     CU(cudaSetDevice(c->device));
-    int want = 2;  // clients per pass (measured on B200, profiles/r10_notes.md)
+    int want = 4;  // clients per pass: 1 / 2 / 4 = 96.7 / 94.4 / 93.8 us per ciphertext at C3 (profiles/r10_notes.md)
     if (const char* e = std::getenv("PPQ_AGG_NB")) want = std::atoi(e);
     const size_t per_client = ((size_t)a->ell + (size_t)ppq_ctx_num_parts(c, a->ell) * (a->ell + c->hp.K)) * c->hp.N * a->n_slots * sizeof(u64);
     size_t i = 0;

@@ -1,5 +1,5 @@
 // ckks.cu -- CKKS encode/decode kernels (FP64 special FFT).  See ckks.cuh; the samplers live in sampler.cu.
-// Client-side path (encryptModelWeights / decryptModelWeights): one launch per FFT stage over the whole batch.
+// Client-side path (encryptModelWeights / decryptModelWeights): the stages that fit a shared-memory tile run in one kernel.
 #include "ckks.cuh"
 
 #include <cmath>
@@ -77,30 +77,6 @@ __global__ void k_fft_fwd_stage(double2* __restrict__ z, unsigned Nh, unsigned l
         a[i + j + lenh] = make_double2(u.x - v.x, u.y - v.y);
     }
 }
-__global__ void k_bitrev(double2* __restrict__ z, unsigned Nh, int bits) {
-    const size_t g = blockIdx.y;
-    double2* a = z + g * Nh;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < Nh; i += gridDim.x * blockDim.x) {
-        const unsigned j = __brev(i) >> (32 - bits);
-        if (i < j) {
-            const double2 t = a[i];
-            a[i] = a[j];
-            a[j] = t;
-        }
-    }
-}
-// co[g][i] = llround(re(z[br(i)]) / Nh * sf), co[g][Nh + i] = same for the imaginary part
-__global__ void k_finish_encode(const double2* __restrict__ z, long long* __restrict__ co, unsigned Nh, int bits,
-                                double sf) {
-    const size_t g = blockIdx.y;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < Nh; i += gridDim.x * blockDim.x) {
-        const unsigned j = __brev(i) >> (32 - bits);
-        const double2 v = z[g * Nh + j];
-        co[g * 2 * Nh + i] = llround(v.x / (double)Nh * sf);
-        co[g * 2 * Nh + Nh + i] = llround(v.y / (double)Nh * sf);
-    }
-}
-
 static dim3 grid_for(size_t work, size_t n) {
     unsigned gx = (unsigned)((work + 255) / 256);
     if (gx > 1024) gx = 1024;
@@ -108,14 +84,97 @@ static dim3 grid_for(size_t work, size_t n) {
     return dim3(gx, (unsigned)n, 1);
 }
 
+// ---- shared-memory FFT blocks.  The stages whose butterflies stay inside a contiguous block of 2^FB_LOG points run
+// in ONE kernel on a tile held in shared memory (128 KiB of double2 for 8192 points): a whole transform for N <= 2^14,
+// all but log2(Nh) - 13 stages above (N = 2^16: 13 of 15 stages in one launch instead of 13 HBM round trips).
+// Round 1 launched one kernel per stage.  The arithmetic per butterfly is unchanged, so the results are the same.
+constexpr int FB_LOG = 13;
+constexpr int FB_THREADS = 1024;
+__device__ __forceinline__ unsigned brev_n(unsigned x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0u; }
+
+// FFTSpecialInv stages len = B, B/2, .., 2 on block blockIdx.x of ciphertext blockIdx.y (B = min(Nh, 2^FB_LOG)).
+// FROM_VALS: the tile is loaded from the real input vector (zero padded), i.e. no global stage ran before (Nh <= B).
+// Then the encode epilogue: co[i] = llround(re(z[brev(i)]) / Nh * sf), co[Nh + i] = the same for the imaginary part.
+template <bool FROM_VALS>
+__global__ void __launch_bounds__(FB_THREADS)
+    k_fft_inv_block(const double* __restrict__ vals, size_t n_vals, const double2* __restrict__ z, long long* __restrict__ co,
+                    unsigned Nh, int bits, unsigned logB, const unsigned* __restrict__ rot, const double2* __restrict__ ksi,
+                    unsigned m, double sf) {
+    extern __shared__ double2 tile[];
+    const unsigned B = 1u << logB, blk = blockIdx.x;
+    const size_t g = blockIdx.y;
+    for (unsigned t = threadIdx.x; t < B; t += FB_THREADS) {
+        const unsigned i = blk * B + t;
+        tile[t] = FROM_VALS ? make_double2(i < n_vals ? vals[g * n_vals + i] : 0.0, 0.0) : z[g * Nh + i];
+    }
+    __syncthreads();
+    for (unsigned len = B; len >= 2; len >>= 1) {
+        const unsigned lenh = len >> 1, lenq = len << 2, gap = m / lenq;
+        for (unsigned t = threadIdx.x; t < B / 2; t += FB_THREADS) {
+            const unsigned j = t % lenh, i = (t / lenh) * len;
+            const unsigned idx = (lenq - (rot[j] % lenq)) * gap;
+            const double2 x = tile[i + j], y = tile[i + j + lenh];
+            tile[i + j] = make_double2(x.x + y.x, x.y + y.y);
+            tile[i + j + lenh] = cmul(make_double2(x.x - y.x, x.y - y.y), ksi[idx]);
+        }
+        __syncthreads();
+    }
+    // element j = blk*B + jl goes to coefficient i = brev(j) = brev(jl, logB) << hb | brev(blk, hb); walk i upwards
+    const int hb = bits - (int)logB;
+    const unsigned ib = brev_n(blk, hb);
+    for (unsigned t = threadIdx.x; t < B; t += FB_THREADS) {
+        const double2 v = tile[brev_n(t, (int)logB)];
+        const unsigned i = (t << hb) | ib;
+        co[g * 2 * Nh + i] = llround(v.x / (double)Nh * sf);
+        co[g * 2 * Nh + Nh + i] = llround(v.y / (double)Nh * sf);
+    }
+}
+
 void launch_encode_fft(const Tables& t, const double* d_vals, size_t n_vals, double sf, double2* z, int64_t* co,
                        size_t n, cudaStream_t st) {
     const unsigned N = 1u << t.logN, Nh = N / 2, m = 2 * N;
     const int bits = t.logN - 1;
+    const unsigned logB = bits < FB_LOG ? (unsigned)bits : (unsigned)FB_LOG, B = 1u << logB;
+    const size_t smem = (size_t)B * sizeof(double2);
+    dim3 grid(Nh / B, (unsigned)n, 1);
+    if (Nh <= B) {
+        cudaFuncSetAttribute(k_fft_inv_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_fft_inv_block<true><<<grid, FB_THREADS, smem, st>>>(d_vals, n_vals, nullptr, (long long*)co, Nh, bits, logB, t.rot, t.ksi, m, sf);
+        return;
+    }
     k_load_vals<<<grid_for(Nh, n), 256, 0, st>>>(d_vals, n_vals, z, Nh);
-    for (unsigned len = Nh; len >= 2; len >>= 1)
+    for (unsigned len = Nh; len > B; len >>= 1)
         k_fft_inv_stage<<<grid_for(Nh / 2, n), 256, 0, st>>>(z, Nh, len, t.rot, t.ksi, m);
-    k_finish_encode<<<grid_for(Nh, n), 256, 0, st>>>(z, (long long*)co, Nh, bits, sf);
+    cudaFuncSetAttribute(k_fft_inv_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_fft_inv_block<false><<<grid, FB_THREADS, smem, st>>>(nullptr, 0, z, (long long*)co, Nh, bits, logB, t.rot, t.ksi, m, sf);
+}
+
+// FFTSpecial stages len = 2, 4, .., B on a block of the BIT-REVERSED input (k_crt_to_complex stores it that way).
+// TAKE_REAL: Nh <= B, the transform ends here: the real parts go straight to the output.
+template <bool TAKE_REAL>
+__global__ void __launch_bounds__(FB_THREADS)
+    k_fft_fwd_block(double2* __restrict__ z, double* __restrict__ out, unsigned Nh, unsigned logB,
+                    const unsigned* __restrict__ rot, const double2* __restrict__ ksi, unsigned m) {
+    extern __shared__ double2 tile[];
+    const unsigned B = 1u << logB, blk = blockIdx.x;
+    const size_t g = blockIdx.y;
+    for (unsigned t = threadIdx.x; t < B; t += FB_THREADS) tile[t] = z[g * Nh + blk * B + t];
+    __syncthreads();
+    for (unsigned len = 2; len <= B; len <<= 1) {
+        const unsigned lenh = len >> 1, lenq = len << 2, gap = m / lenq;
+        for (unsigned t = threadIdx.x; t < B / 2; t += FB_THREADS) {
+            const unsigned j = t % lenh, i = (t / lenh) * len;
+            const unsigned idx = (rot[j] % lenq) * gap;
+            const double2 u = tile[i + j], v = cmul(tile[i + j + lenh], ksi[idx]);
+            tile[i + j] = make_double2(u.x + v.x, u.y + v.y);
+            tile[i + j + lenh] = make_double2(u.x - v.x, u.y - v.y);
+        }
+        __syncthreads();
+    }
+    for (unsigned t = threadIdx.x; t < B; t += FB_THREADS) {
+        if (TAKE_REAL) out[g * Nh + blk * B + t] = tile[t].x;
+        else z[g * Nh + blk * B + t] = tile[t];
+    }
 }
 
 // CRT interpolation by Garner's mixed-radix digits, centred, as a double (Poly::CRTInterpolate + the
@@ -155,8 +214,9 @@ __global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell,
         }
         if (neg) d = -(d + 1.0);
         d /= sf;
-        if (n < Nh) z[g * Nh + n].x = d;
-        else z[g * Nh + (n - Nh)].y = d;
+        // stored at the bit-reversed position: FFTSpecial starts with that permutation (k_fft_fwd_block reads contiguously)
+        if (n < Nh) z[g * Nh + (__brev(n) >> (33 - c.logN))].x = d;
+        else z[g * Nh + (__brev(n - Nh) >> (33 - c.logN))].y = d;
     }
 }
 __global__ void k_take_real(const double2* __restrict__ z, double* __restrict__ out, unsigned Nh) {
@@ -169,9 +229,18 @@ void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, co
                    double sf, double2* z, double* d_vals, size_t n, cudaStream_t st) {
     const unsigned N = 1u << t.logN, Nh = N / 2, m = 2 * N;
     const int bits = t.logN - 1;
+    const unsigned logB = bits < FB_LOG ? (unsigned)bits : (unsigned)FB_LOG, B = 1u << logB;
+    const size_t smem = (size_t)B * sizeof(double2);
     k_crt_to_complex<<<grid_for(N, n), 256, 0, st>>>(k, coeff, ell, d_ginv, sf, z);
-    k_bitrev<<<grid_for(Nh, n), 256, 0, st>>>(z, Nh, bits);
-    for (unsigned len = 2; len <= Nh; len <<= 1)
+    dim3 grid(Nh / B, (unsigned)n, 1);
+    if (Nh <= B) {
+        cudaFuncSetAttribute(k_fft_fwd_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_fft_fwd_block<true><<<grid, FB_THREADS, smem, st>>>(z, d_vals, Nh, logB, t.rot, t.ksi, m);
+        return;
+    }
+    cudaFuncSetAttribute(k_fft_fwd_block<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_fft_fwd_block<false><<<grid, FB_THREADS, smem, st>>>(z, d_vals, Nh, logB, t.rot, t.ksi, m);
+    for (unsigned len = 2 * B; len <= Nh; len <<= 1)
         k_fft_fwd_stage<<<grid_for(Nh / 2, n), 256, 0, st>>>(z, Nh, len, t.rot, t.ksi, m);
     k_take_real<<<grid_for(Nh, n), 256, 0, st>>>(z, d_vals, Nh);
 }
