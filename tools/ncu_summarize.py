@@ -120,7 +120,7 @@ def traffic(path, n_cts=54, tag=""):
     print(json.dumps({"c3": {"wave_cts": n_cts, "source": tag or path, "dram_bytes_per_ct": per}}, indent=1))
 
 
-def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, tag=""):
+def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, nb=4, tag=""):
     """Deferred-ModDown pipeline (ppq_agg_*): the capture holds the LAST client's add of a step of `cap_clients`
     clients, the group conversion (k_bconv_wide x2) and ppq_agg_finish (k_fwd_col2, k_fwd_row_moddown2), in launch
     order.  Prints the profiles/ncu_traffic.json + ncu_int_pipe.json content: DRAM bytes per ciphertext and stage, the
@@ -131,7 +131,7 @@ def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, tag=""
     hdr, units, data = rows[0], rows[1], rows[2:]
     idx = {h: i for i, h in enumerate(hdr)}
     mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    n_slots, cap_clients, job_clients, group = int(n_slots), int(cap_clients), int(job_clients), int(group)
+    n_slots, cap_clients, job_clients, group, nb = int(n_slots), int(cap_clients), int(job_clients), int(group), int(nb)
     stages = ["k_inv_row(c1)", "k_inv_col(c1,scale)", "k_bconv(modup)", "k_fwd_col(modup)", "k_fwd_row(modup)",
               "k_ip_tma|k_fwd_row_ip", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
               "k_fwd_row_moddown"]
@@ -142,8 +142,8 @@ def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, tag=""
     for r in data:
         n = short(r[idx["Kernel Name"]])
         fam = n.split("<")[0]
-        if fam != prev or not fam.startswith("k_bconv"):
-            si += 1
+        if fam != prev or not (fam.startswith("k_bconv") or fam.startswith("k_inv_row")):
+            si += 1  # consecutive launches of the conversions / of the per-client inverse ROW pass are one stage
         prev = fam
         b = sum(float(r[idx[k]].replace(",", "")) * mult[units[idx[k]]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
         per_launch[stages[si]] += b
@@ -152,7 +152,7 @@ def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, tag=""
         fma[stages[si]] = max(fma.get(stages[si], 0.0), f)
         tms[stages[si]] += t
     assert si == len(stages) - 1, f"expected one add + group conversion + finish, got {si + 1} stages"
-    div = {s: n_slots for s in stages}
+    div = {s: n_slots * nb for s in stages}  # the per-pass kernels cover nb clients x n_slots ciphertexts
     div["k_bconv(moddown)"] = n_slots * group
     per_ct_cap = {}
     path = 0.0
@@ -165,7 +165,7 @@ def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, tag=""
             per_ct_cap[s] = per_launch[s] / d
             path += per_launch[s] / d
     print(json.dumps({"traffic": {"c3": {"wave_cts": n_slots, "source": tag or path, "capture_clients": cap_clients,
-                                         "job_clients": job_clients, "group": group, "dram_bytes_per_ct": per_ct_cap,
+                                         "job_clients": job_clients, "group": group, "clients_per_pass": nb, "dram_bytes_per_ct": per_ct_cap,
                                          "path_dram_bytes_per_ct": path}},
                       "int_pipe": fma}, indent=1))
 
