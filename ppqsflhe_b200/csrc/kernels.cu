@@ -831,7 +831,7 @@ struct KaraAcc {
 // AGG (deferred ModDown, ppq_agg_*): the Q-limb results are not written out per ciphertext but summed, together with
 // c0 on poly 0, into the running EVAL accumulator of the slot (A.acc; A.agg == 1: first client, plain store).
 #ifndef PPQ_IP_AGG_MINB
-#define PPQ_IP_AGG_MINB 3
+#define PPQ_IP_AGG_MINB 2
 #endif
 template <int PARTS, bool AGG>
 __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
@@ -859,34 +859,53 @@ __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip
             tma_bulk_g2s(keys + (size_t)(2 * j + 1) * IPT, (isq ? A.key_qa : A.key_a) + koff, IPT * sizeof(u64), bar);
         }
     }
+    static_assert(IPC == 1, "one 512-point step per ciphertext (PPQ_IPT = 512)");
     const int own = r < A.ell ? r / A.alpha : -1;  // the digit whose own limb r is (taken from c1 as it is)
     const int g0 = blockIdx.z * g_per_cta;
     const int g1 = min(n_g, g0 + g_per_cta);
-    // digits of the next (ciphertext, chunk) are fetched while the current one is multiplied: with two CTAs per
-    // SM the loads in flight would otherwise not cover the HBM latency
+    // digits of the next ciphertext are fetched while the current one is multiplied.  Address arithmetic is hoisted out
+    // of the loop (thread-invariant bases, running slot offsets): recomputing every 64-bit address per iteration was
+    // most of this kernel's instructions (profiles/r10_notes.md).
     const bool aggq = AGG && r < A.ell;  // block-uniform
-    ulonglong2 xn[3];  // AGG, Q limbs: c0, running sum of poly 0, running sum of poly 1 (fetched with the digits)
-    auto fetch = [&](int it, ulonglong2 (&d)[PARTS]) {
-        const int g = g0 + it / IPC;
-        const u32 pt = (u32)(it % IPC) * 512 + threadIdx.x * 2;
+    const u32 pt = threadIdx.x * 2;      // two adjacent points per 16-byte access
+    const size_t in_row = (size_t)r * N + off + pt;
+    const u64* dsrc[PARTS];
+    size_t dstep[PARTS];
 #pragma unroll
-        for (int j = 0; j < PARTS; ++j) {
-            const u64* dp = (j == own) ? A.c1 + g * A.c1_gs + (size_t)r * N + off
-                                       : A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
-            d[j] = __ldcs(reinterpret_cast<const ulonglong2*>(dp + pt));
-        }
+    for (int j = 0; j < PARTS; ++j) {
+        const bool o = j == own;
+        dsrc[j] = (o ? A.c1 + in_row : A.digits + ((size_t)j * M + r) * N + off + pt) + (size_t)g0 * (o ? A.c1_gs : A.dig_gs);
+        dstep[j] = o ? A.c1_gs : A.dig_gs;
+    }
+    const u64* c0p = aggq ? A.c0 + (size_t)g0 * A.c0_gs + in_row : nullptr;
+    u64* o0;
+    size_t ostep;
+    if (aggq) {
+        o0 = A.acc + (size_t)g0 * A.acc_gs + in_row;
+        ostep = A.acc_gs;
+    } else if (r < A.ell) {
+        o0 = A.extq + (size_t)g0 * A.extq_gs + in_row;
+        ostep = A.extq_gs;
+    } else {
+        o0 = A.extp + (size_t)g0 * A.extp_gs + (size_t)(r - A.ell) * N + off + pt;
+        ostep = A.extp_gs;
+    }
+    const size_t o1off = (size_t)(r < A.ell ? A.ell : A.K) * N;
+    ulonglong2 xn[3];  // AGG, Q limbs: c0, running sum of poly 0, running sum of poly 1 (fetched with the digits)
+    auto fetch = [&](size_t k, ulonglong2 (&d)[PARTS]) {  // k = slots ahead of the current output position
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) d[j] = __ldcs(reinterpret_cast<const ulonglong2*>(dsrc[j] + k * dstep[j]));
         if (aggq) {
-            xn[0] = __ldcs(reinterpret_cast<const ulonglong2*>(A.c0 + g * A.c0_gs + (size_t)r * N + off + pt));
+            xn[0] = __ldcs(reinterpret_cast<const ulonglong2*>(c0p + k * A.c0_gs));
             if (A.agg == 2) {
-                const u64* ap = A.acc + g * A.acc_gs + (size_t)r * N + off + pt;
+                const u64* ap = o0 + k * ostep;
                 xn[1] = *reinterpret_cast<const ulonglong2*>(ap);
-                xn[2] = *reinterpret_cast<const ulonglong2*>(ap + (size_t)A.ell * N);
+                xn[2] = *reinterpret_cast<const ulonglong2*>(ap + o1off);
             }
         }
     };
-    const int n_it = (g1 - g0) * IPC;
     ulonglong2 dn[PARTS];
-    if (n_it > 0) fetch(0, dn);
+    if (g0 < g1) fetch(0, dn);
     mbar_wait(bar, 0);
     // the key tile is reused for every ciphertext of the wave: split it into Karatsuba halves ONCE, in place
     for (int i = threadIdx.x; i < PARTS * 2 * IPT / 2; i += 256) {
@@ -895,7 +914,7 @@ __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip
         *kp = make_ulonglong2(kara_pack(v.x), kara_pack(v.y));
     }
     __syncthreads();
-    for (int it = 0; it < n_it; ++it) {
+    for (int g = g0; g < g1; ++g) {
         ulonglong2 d[PARTS];
 #pragma unroll
         for (int j = 0; j < PARTS; ++j) d[j] = dn[j];
@@ -905,21 +924,8 @@ __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip
             xc[1] = xn[1];
             xc[2] = xn[2];
         }
-        if (it + 1 < n_it) fetch(it + 1, dn);
-        const int g = g0 + it / IPC;
-        const u32 pt = (u32)(it % IPC) * 512 + threadIdx.x * 2;  // two adjacent points per 16-byte access
-        u64* o0;
-        u64* o1;
-        if (aggq) {
-            o0 = A.acc + g * A.acc_gs + (size_t)r * N + off;
-            o1 = o0 + (size_t)A.ell * N;
-        } else if (r < A.ell) {
-            o0 = A.extq + g * A.extq_gs + (size_t)r * N + off;
-            o1 = o0 + (size_t)A.ell * N;
-        } else {
-            o0 = A.extp + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
-            o1 = o0 + (size_t)A.K * N;
-        }
+        if (g + 1 < g1) fetch(1, dn);
+        u64* o1 = o0 + o1off;
         KaraAcc b0, b1, a0, a1;
 #pragma unroll
         for (int j = 0; j < PARTS; ++j) {
@@ -940,15 +946,19 @@ __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip
                 w0 += xc[2].x;
                 w1 += xc[2].y;
             }
-            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(canon_any16(v0, lc), canon_any16(v1, lc));
-            *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(canon_any16(w0, lc), canon_any16(w1, lc));
+            *reinterpret_cast<ulonglong2*>(o0) = make_ulonglong2(canon_any16(v0, lc), canon_any16(v1, lc));
+            *reinterpret_cast<ulonglong2*>(o1) = make_ulonglong2(canon_any16(w0, lc), canon_any16(w1, lc));
         } else if (PPQ_IP_LAZY && r < A.ell) {  // block-uniform
-            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce_lazy3(lc), b1.reduce_lazy3(lc));
-            *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce_lazy3(lc), a1.reduce_lazy3(lc));
+            *reinterpret_cast<ulonglong2*>(o0) = make_ulonglong2(b0.reduce_lazy3(lc), b1.reduce_lazy3(lc));
+            *reinterpret_cast<ulonglong2*>(o1) = make_ulonglong2(a0.reduce_lazy3(lc), a1.reduce_lazy3(lc));
         } else {
-            *reinterpret_cast<ulonglong2*>(o0 + pt) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
-            *reinterpret_cast<ulonglong2*>(o1 + pt) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
+            *reinterpret_cast<ulonglong2*>(o0) = make_ulonglong2(b0.reduce(lc), b1.reduce(lc));
+            *reinterpret_cast<ulonglong2*>(o1) = make_ulonglong2(a0.reduce(lc), a1.reduce(lc));
         }
+#pragma unroll
+        for (int j = 0; j < PARTS; ++j) dsrc[j] += dstep[j];
+        if (aggq) c0p += A.c0_gs;
+        o0 += ostep;
     }
 }
 
