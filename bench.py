@@ -105,7 +105,7 @@ def stage_alg_words(ell, K, parts, bk, split=True, agg=False, group=8, clients=1
         ell + conv,                                # k_bconv(modup):       R ell (COEFF digits) + W converted limbs
         2 * conv,                                  # k_fwd_col(modup):     R + W converted limbs
         (2 * conv) if split else 0,                # k_fwd_row(modup):     R + W converted limbs (split form only)
-        conv + ell + 2 * parts * M / bk + 2 * M,   # k_ip_tma / k_fwd_row_ip: R digits + R own c1 + R keys/bk + W 2(ell+K)
+        conv + ell + 2 * parts * M / bk + 2 * M,   # k_ip_tma: R digits + R own c1 + R keys/bk + W 2(ell+K)
         (4 * K) if split else 0,                   # k_inv_row(P):         R 2K + W 2K (split form only)
         4 * K,                                     # k_inv_col(P):         R 2K + W 2K
         2 * K + 2 * ell,                           # k_bconv(moddown):     R 2K + W 2 ell

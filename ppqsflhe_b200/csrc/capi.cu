@@ -102,7 +102,6 @@ struct ppq_ctx {
     DevBuf<int> kinds3;    // {ternary, gauss, gauss}: the polynomial kinds of one (v, e0, e1) / (u, e0, e1) triple
     ckks::Tables fft;
     int wave = 0;
-    bool ip_split = true;  // inner product as k_fwd_row_plain + k_ip_tma + k_inv_row (PPQ_IP_FUSED=1: one fused kernel)
     // per-stage CUDA-event profiling of the key-switch pipeline (ppq_profile_*): a chain of events on the launching
     // stream; the time between two consecutive marks is attributed to the stage named by the later one
     static const int NSTAGE = 11;
@@ -168,10 +167,6 @@ static int ctx_finish(std::unique_ptr<ppq_ctx>& c, int device, ppq_ctx** out) {
     c->k.twf = c->twf.p;
     c->k.twi = c->twi.p;
     c->k.logN = hp.logN;
-    {
-        const char* e = std::getenv("PPQ_IP_FUSED");
-        c->ip_split = !(e && std::atoi(e) != 0) && hp.N >= 2048 && hp.dnum <= 6;
-    }
     std::string err;
     if (!ckks::build_tables(hp.logN, c->fft, err)) return fail(PPQ_ECUDA, err);
     CU(c->kinds3.upload(std::vector<int>{0, 1, 1}));
@@ -491,7 +486,7 @@ extern "C" int ppq_profile_read(ppq_ctx* c, double* ms, uint64_t* launches, int 
 extern "C" uint64_t ppq_launch_count(void) { return (uint64_t)kernels_launch_count(); }
 extern "C" const char* ppq_profile_stage_name(int s) {
     static const char* names[ppq_ctx::NSTAGE] = {"k_inv_row(c1)",      "k_inv_col(c1,scale)", "k_bconv(modup)",
-                                                 "k_fwd_col(modup)",   "k_fwd_row(modup)",    "k_ip_tma|k_fwd_row_ip",
+                                                 "k_fwd_col(modup)",   "k_fwd_row(modup)",    "k_ip_tma|k_ip_agg",
                                                  "k_inv_row(P)",       "k_inv_col(P,scale)",  "k_bconv(moddown)",
                                                  "k_fwd_col(moddown)", "k_fwd_row_moddown"};
     // (ppq_agg_*: stage 8 is k_bconv_wide once per group of clients, stages 9-10 run once per ppq_agg_finish)
@@ -554,7 +549,7 @@ static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, 
         launch_fwd_col_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st);
         prof_mark(c, st, 3);
         // 4. forward ROW pass + inner product with the rekey (+ inverse ROW pass on the P limbs)
-        if (c->ip_split) launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st, PPQ_DIGITS_LAZY_OK(parts));
+        launch_fwd_row_plain(c->k, dig, w.dig, p->dig_ids.p, parts * (ell + K), ng, st, PPQ_DIGITS_LAZY_OK(parts));
         prof_mark(c, st, 4);
         for (int key = 0; key < n_keys; ++key) {
         const ppq_rekey* rk = rks[key];
@@ -579,15 +574,10 @@ static int reencrypt_multi(ppq_ctx* c, const ppq_rekey* const* rks, int n_keys, 
         ia.L = L;
         ia.parts = parts;
         ia.alpha = c->hp.alpha;
-        if (c->ip_split) {
-            if (!launch_ip_tma(c->k, ia, ng, st)) return fail(PPQ_EINVAL, "ppq_reencrypt: split inner product needs N >= 2048 and <= 6 digits");
-            prof_mark(c, st, 5);
-            launch_inv_row(c->k, extp, w.extp, extp, w.extp, p->p_limb.p, 2 * K, ng, st);
-            prof_mark(c, st, 6);
-        } else {
-            launch_fwd_row_ip(c->k, ia, ng, st);  // reads the digits after their COL pass, leaves them as they are
-            prof_mark(c, st, 5);
-        }
+        if (!launch_ip_tma(c->k, ia, ng, st)) return fail(PPQ_EINVAL, "ppq_reencrypt: the inner product supports at most 8 digits");
+        prof_mark(c, st, 5);
+        launch_inv_row(c->k, extp, w.extp, extp, w.extp, p->p_limb.p, 2 * K, ng, st);
+        prof_mark(c, st, 6);
         // 5. P limbs: inverse COL pass, scaled by N^-1 (P/p_k)^-1
         launch_inv_col(c->k, extp, w.extp, p->p_limb.p, p->p_scale.p, 2 * K, ng, st);
         prof_mark(c, st, 7);
@@ -696,7 +686,6 @@ extern "C" int ppq_ks_inner_product(ppq_ctx* c, const ppq_rekey* rk, int ell, co
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_ks_inner_product: bad limb count");
     if (n == 0) return PPQ_OK;
     if (n * 2 * (size_t)ell > 65535) return fail(PPQ_EINVAL, "ppq_ks_inner_product: batch too large");
-    if (!c->ip_split) return fail(PPQ_EINVAL, "ppq_ks_inner_product: needs N >= 2048 and <= 6 digits");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     KsPlanDev* p;
@@ -1234,7 +1223,7 @@ extern "C" int ppq_agg_create(ppq_ctx* c, int ell, size_t n_slots, ppq_agg** out
     a->ell = ell;
     a->n_slots = n_slots;
     const size_t N = c->hp.N, K = c->hp.K;
-    a->legacy = !c->ip_split || K > 16;
+    a->legacy = K > 16;  // the wide conversion holds <= 16 source limbs
     int grp = 8;
     if (const char* e = std::getenv("PPQ_AGG_GROUP")) grp = std::atoi(e);
     a->group = grp < 1 ? 1 : grp > 8 ? 8 : grp;

@@ -7,6 +7,8 @@
 // is expressed here as NTT passes (ntt_core.cuh) with the surrounding RNS arithmetic fused in as the
 // prologue or epilogue of a pass.  Integer modular arithmetic only: no tensor cores (nothing here is a dense
 // floating-point contraction).  Layouts are limb-major: a polynomial limb is N contiguous u64 residues.
+#include <cstdlib>
+
 #include "kernels.cuh"
 #include "ckks.cuh"
 #include "ntt_core.cuh"
@@ -74,7 +76,7 @@ __device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
 // SAME: the ROW size equals the COL size (n2 = 2^S), else n2 = 2^(S-1) (split_of): with n2 known at compile time the
 // eight strided accesses of a thread share one base register and use immediate offsets.
 template <int S, int W, int MODE, bool SAME>
-__global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
+__global__ void __launch_bounds__(W << (S - 3), (MODE == 2 && S == 6) ? 4 : PPQ_COL_MINB)
     k_fwd_col(KCtx c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs,
               const BcJob* __restrict__ jobs, const u64* __restrict__ chat, const int* __restrict__ limb_ids,
               u64 q_src) {
@@ -125,13 +127,10 @@ __global__ void __launch_bounds__(W << (S - 3), PPQ_COL_MINB)
 
 // Plain forward COL pass, two adjacent columns per thread (ntt_core.cuh fwd_pass_col2), in place.
 // Measured on B200, C3 (tools/stage_times.py): forward 18.5 -> 17.9 and 12.1 -> 11.5 us/ct (768 -> 700 instructions
-// per 8 points at 3 CTAs of 256 threads per SM); the inverse form (936 -> 888) is no faster (6.8 -> 7.0) and stays off.
+// per 8 points at 3 CTAs of 256 threads per SM); the inverse form (936 -> 888) was no faster (6.8 -> 7.0) and has been removed.
 // Only for n1 = 256 (N = 2^15, 2^16): at n1 = 128 the form measured 3 % slower (N = 2^13), at n1 = 512 the same.
 #ifndef PPQ_COL2
 #define PPQ_COL2 1
-#endif
-#ifndef PPQ_COL2_INV
-#define PPQ_COL2_INV 0
 #endif
 #ifndef PPQ_COL2_W
 #define PPQ_COL2_W 8  // column pairs per CTA
@@ -168,36 +167,6 @@ __global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
         p[(size_t)(8 * u + k) * n2] = a[k];
         p[(size_t)(8 * u + k) * n2 + 1] = b[k];
 #endif
-    }
-}
-
-template <int S, int W2, bool SAME>
-__global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
-    k_inv_col2(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
-               const u64* __restrict__ scale) {
-    __shared__ u64 sm[2 * (W2 << S)];
-    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
-    const u32 w = threadIdx.x % W2, u = threadIdx.x / W2;
-    const u32 col = (blockIdx.x * W2 + w) * 2;
-    const u32 y = blockIdx.y, g = blockIdx.z;
-    const int limb = limb_map[y];
-    const LimbC lc = c.limbs[limb];
-    const ulonglong2* tw = c.twi + (size_t)limb * N;
-    u64* p = data + g * gs + (size_t)y * N + col;
-    u64 a[8], b[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + (size_t)(8 * u + k) * n2);
-        a[k] = v.x;
-        b[k] = v.y;
-    }
-    const ulonglong2 fs = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * y);
-    const ulonglong2 fw = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * y + 1);
-    inv_pass_col2<S, W2, INV_COL_IN>(a, b, sm, w, u, tw, lc.q, lc.q2 << 1, fs, fw);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        p[(size_t)point_of<S - 3>(u, k) * n2] = canon4(a[k], lc);
-        p[(size_t)point_of<S - 3>(u, k) * n2 + 1] = canon4(b[k], lc);
     }
 }
 
@@ -586,8 +555,9 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_X2_MINB)
     }
 }
 
+// (S = 6, N = 2^12 / 2^13: 16 short rows per CTA; 64 registers spilled 132 bytes, so 6 CTAs/SM there)
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 6 : PPQ_ROW_MINB)
     k_fwd_row_plain(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
@@ -619,7 +589,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
 }
 
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB)
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB)
     k_inv_row(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs,
               const int* __restrict__ limb_map, int n_g) {
     typedef RowGeom<S> G;
@@ -680,79 +650,6 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_INV_X2_MINB)
             o0[point_of<S - 3>(u, k)] = a[k];
             o1[point_of<S - 3>(u, k)] = b[k];
         }
-    }
-}
-
-// Forward ROW pass + inner product with the re-encryption key (+ inverse ROW pass on the P limbs).
-template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_ip(KCtx c, IpArgs A) {
-    typedef RowGeom<S> G;
-    __shared__ u64 sm[G::SMEM];
-    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
-    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
-    const u32 row = blockIdx.x * G::R + w;
-    const int r = blockIdx.z;
-    const u32 g = blockIdx.y;
-    const int M = A.ell + A.K;
-    const int limb = r < A.ell ? r : A.L + (r - A.ell);
-    const LimbC lc = c.limbs[limb];
-    const ulonglong2* tw = c.twf + (size_t)limb * N;
-    const size_t off = (size_t)row * n2;
-    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
-
-    u64 h0[8], l0[8], h1[8], l1[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) h0[k] = l0[k] = h1[k] = l1[k] = 0;
-
-    for (int j = 0; j < A.parts; ++j) {
-        const int s = j * A.alpha, e = min(s + A.alpha, A.ell);
-        u64 d[8];
-        if (r >= s && r < e) {  // own digit: the original EVAL limb of c1 (block-uniform branch)
-            ld8(d, A.c1 + g * A.c1_gs + (size_t)r * N + off + 8 * u);
-        } else {
-            const u64* in = A.digits + g * A.dig_gs + ((size_t)j * M + r) * N + off;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) d[k] = ld_stream(in + point_of<S - 3>(u, k));
-            fwd_pass<S, RowPos<S>, FWD_ROW_IN>(d, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true, PPQ_Z(lc));
-#pragma unroll
-            for (int k = 0; k < 8; ++k) d[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(d[k], lc);
-        }
-        u64 kb[8], ka[8];
-        if (r < A.ell) {
-            const size_t koff = ((size_t)j * A.key_q_stride + limb) * N + off + 8 * u;
-            ld8_ro(kb, A.key_qb + koff);
-            ld8_ro(ka, A.key_qa + koff);
-        } else {
-            const size_t koff = ((size_t)j * (A.L + A.K) + limb) * N + off + 8 * u;
-            ld8_ro(kb, A.key_b + koff);
-            ld8_ro(ka, A.key_a + koff);
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            mac128(h0[k], l0[k], d[k], kb[k]);
-            mac128(h1[k], l1[k], d[k], ka[k]);
-        }
-    }
-    u64 e0[8], e1[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        e0[k] = barrett128(h0[k], l0[k], lc);
-        e1[k] = barrett128(h1[k], l1[k], lc);
-    }
-    if (r < A.ell) {
-        u64* o = A.extq + g * A.extq_gs + (size_t)r * N + off + 8 * u;
-        st8(o, e0);
-        st8(o + (size_t)A.ell * N, e1);
-    } else {  // P limb: ModDown needs it in COEFF -> run the inverse ROW pass while the tile is in registers
-        const ulonglong2* twi = c.twi + (size_t)limb * N;
-        u64* o = A.extp + g * A.extp_gs + (size_t)(r - A.ell) * N + off;
-        inv_pass<S, RowPos<S>, INV_ROW_IN>(e0, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e0[k];
-        o += (size_t)A.K * N;
-        inv_pass<S, RowPos<S>, INV_ROW_IN>(e1, sm, pos, u, twi, n1 + row, lc.q, lc.q2 << 1, true);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = e1[k];
     }
 }
 
@@ -833,8 +730,9 @@ struct KaraAcc {
 #ifndef PPQ_IP_AGG_MINB
 #define PPQ_IP_AGG_MINB 2
 #endif
+// (more than 3 digits: the per-digit source pointers no longer fit 64 registers -- 3 CTAs/SM instead of spilling)
 template <int PARTS, bool AGG>
-__global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
+__global__ void __launch_bounds__(256, AGG ? (PARTS >= 6 ? 1 : PPQ_IP_AGG_MINB) : (PARTS <= 3 ? PPQ_IP_MINB : PARTS <= 5 ? 3 : 2)) k_ip_tma(KCtx c, IpArgs A, int n_g, int g_per_cta) {
     extern __shared__ __align__(128) unsigned char ip_smem[];
     u64* keys = reinterpret_cast<u64*>(ip_smem);              // [PARTS][2][IPT]
     u64* bar = keys + (size_t)PARTS * 2 * IPT;
@@ -971,7 +869,7 @@ __global__ void __launch_bounds__(256, AGG ? PPQ_IP_AGG_MINB : PPQ_IP_MINB) k_ip
 #define PPQ_IP_AGG_NB_MINB 2
 #endif
 template <int PARTS, int NB>
-__global__ void __launch_bounds__(256, PPQ_IP_AGG_NB_MINB) k_ip_agg(KCtx c, IpArgs A, IpMulti X, int n_g, int g_per_cta) {
+__global__ void __launch_bounds__(256, PARTS >= 7 ? 1 : PPQ_IP_AGG_NB_MINB) k_ip_agg(KCtx c, IpArgs A, IpMulti X, int n_g, int g_per_cta) {
     static_assert(IPC == 1, "k_ip_agg walks one 512-point step per (slot, client)");
     extern __shared__ __align__(128) unsigned char ip_smem[];
     u64* keys = reinterpret_cast<u64*>(ip_smem);  // [NB][PARTS][2][IPT]
@@ -1110,7 +1008,7 @@ __global__ void __launch_bounds__(256, PPQ_IP_AGG_NB_MINB) k_ip_agg(KCtx c, IpAr
 
 // Forward ROW pass + ModDown combine: out = (x - conv) * P^-1 (+ c0 on poly 0) (+ running sum).
 template <int S>
-__global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_moddown(KCtx c, MdArgs A, int n_g) {
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 7 ? 7 : PPQ_ROW_MINB) k_fwd_row_moddown(KCtx c, MdArgs A, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
@@ -1265,6 +1163,122 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_ROW_MINB) k_fwd_row_r
     }
     st8(A.out + g * A.out_gs + (size_t)y * N + roff + 8 * u, a);
 }
+
+#ifndef PPQ_NTT_TILE
+#define PPQ_NTT_TILE 0  // EXPERIMENT, not compiled by default.  Measured on B200 (profiles/r10_notes.md): bit-exact, but
+                        // 8-20 % SLOWER than the two-kernel form at N = 2^12..2^14 (1.22-1.28 vs 1.33-1.58 TB/s of
+                        // algorithmic bytes): the transform is bound by integer issue, not by HBM, so halving the
+                        // traffic buys nothing, and one 512-thread CTA per SM (128 KiB tile) has fewer warps in flight.
+#endif
+#if PPQ_NTT_TILE
+// =========================================================================================================
+// Single-CTA transforms for N <= 2^14 (plain batched NTT API: ppq_ntt_forward / ppq_ntt_inverse, and through it the
+// client path and key generation).  The limb (<= 128 KiB) lives in shared memory as an [n1][n2] tile between the COL
+// and the ROW pass, so a transform crosses HBM once (16 N bytes) instead of twice; the passes are the same register
+// radix-8 groups as the two-kernel form, exchanging IN PLACE in the tile (a thread always writes the words it read).
+// Tile layout: row pitch n2 + n2/8 words, column c at c + c/8: conflict free for the COL pass (a warp = 32 adjacent
+// columns of one row set) and for the ROW pass (RowPos' padding).
+// =========================================================================================================
+template <int S2>
+struct TileColPos {
+    static constexpr bool WARP_LOCAL = false;
+    static constexpr u32 RP = (1u << S2) + (1u << (S2 - 3));
+    u32 cp;  // padded column
+    __device__ __forceinline__ u32 operator()(u32 p) const { return p * RP + cp; }
+};
+template <int S2>
+struct TileRowPos {
+    static constexpr bool WARP_LOCAL = (S2 - 3) <= 5;
+    static constexpr u32 RP = (1u << S2) + (1u << (S2 - 3));
+    u32 base;  // row * RP
+    __device__ __forceinline__ u32 operator()(u32 p) const { return base + p + (p >> 3); }
+};
+constexpr int TILE_THREADS = 512;
+
+template <int S1, int S2>
+__global__ void __launch_bounds__(TILE_THREADS, 1) k_ntt_fwd_tile(KCtx c, u64* __restrict__ data, const int* __restrict__ limb_ids) {
+    extern __shared__ __align__(16) u64 tile[];
+    constexpr u32 n1 = 1u << S1, n2 = 1u << S2, N = n1 * n2;
+    constexpr u32 TPC = 1u << (S1 - 3), W = TILE_THREADS / TPC;  // threads per column, columns per step
+    constexpr u32 TPR = 1u << (S2 - 3), R = TILE_THREADS / TPR;  // threads per row, rows per step
+    static_assert(W <= n2 && R <= n1, "tile kernel geometry");
+    const int limb = limb_ids[blockIdx.x];
+    if (limb < 0) return;
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    u64* p = data + (size_t)blockIdx.x * N;
+    {   // COL pass: n2 / W steps of W columns
+        const u32 w = threadIdx.x % W, u = threadIdx.x / W;
+        for (u32 c0 = 0; c0 < n2; c0 += W) {
+            const u32 col = c0 + w;
+            u64 a[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = ld_stream(p + (size_t)point_of<S1 - 3>(u, k) * n2 + col);
+            TileColPos<S2> pos{col + (col >> 3)};
+            fwd_pass<S1, TileColPos<S2>, FWD_COL_IN>(a, tile, pos, u, tw, 1u, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
+#pragma unroll
+            for (int k = 0; k < 8; ++k) tile[pos(8 * u + k)] = a[k];  // lazy (< 16q), read back by the ROW pass
+        }
+    }
+    __syncthreads();
+    {   // ROW pass: n1 / R steps of R rows
+        const u32 wr = threadIdx.x / TPR, u = threadIdx.x % TPR;
+        for (u32 r0 = 0; r0 < n1; r0 += R) {
+            const u32 row = r0 + wr;
+            TileRowPos<S2> pos{row * TileRowPos<S2>::RP};
+            u64 a[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = tile[pos(point_of<S2 - 3>(u, k))];
+            fwd_pass<S2, TileRowPos<S2>, FWD_ROW_IN>(a, tile, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = canon_any16(a[k], lc);
+            st8(p + (size_t)row * n2 + 8 * u, a);
+        }
+    }
+}
+
+template <int S1, int S2>
+__global__ void __launch_bounds__(TILE_THREADS, 1) k_ntt_inv_tile(KCtx c, u64* __restrict__ data, const int* __restrict__ limb_ids,
+                                                                   const u64* __restrict__ scale) {
+    extern __shared__ __align__(16) u64 tile[];
+    constexpr u32 n1 = 1u << S1, n2 = 1u << S2, N = n1 * n2;
+    constexpr u32 TPC = 1u << (S1 - 3), W = TILE_THREADS / TPC;
+    constexpr u32 TPR = 1u << (S2 - 3), R = TILE_THREADS / TPR;
+    const int limb = limb_ids[blockIdx.x];
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twi + (size_t)limb * N;
+    u64* p = data + (size_t)blockIdx.x * N;
+    {   // ROW pass (canonical input, < 8q out)
+        const u32 wr = threadIdx.x / TPR, u = threadIdx.x % TPR;
+        for (u32 r0 = 0; r0 < n1; r0 += R) {
+            const u32 row = r0 + wr;
+            TileRowPos<S2> pos{row * TileRowPos<S2>::RP};
+            u64 a[8];
+            ld8(a, p + (size_t)row * n2 + 8 * u);
+            inv_pass<S2, TileRowPos<S2>, INV_ROW_IN>(a, tile, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) tile[pos(point_of<S2 - 3>(u, k))] = a[k];
+        }
+    }
+    __syncthreads();
+    {   // COL pass; the output factor (N^-1) rides on its last stage
+        const u32 w = threadIdx.x % W, u = threadIdx.x / W;
+        const ulonglong2 fs = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * blockIdx.x);
+        const ulonglong2 fw = __ldg(reinterpret_cast<const ulonglong2*>(scale) + 2 * blockIdx.x + 1);
+        for (u32 c0 = 0; c0 < n2; c0 += W) {
+            const u32 col = c0 + w;
+            TileColPos<S2> pos{col + (col >> 3)};
+            u64 a[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = tile[pos(8 * u + k)];
+            inv_pass<S1, TileColPos<S2>, INV_COL_IN, true>(a, tile, pos, u, tw, 1u, lc.q, lc.q2 << 1, false, fs, fw);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) p[(size_t)point_of<S1 - 3>(u, k) * n2 + col] = canon4(a[k], lc);
+        }
+    }
+}
+
+#endif  // PPQ_NTT_TILE
 
 // =========================================================================================================
 // pointwise kernels: grid.x covers N/2 (two residues per thread), grid.y = flattened (ct, poly, limb)
@@ -1477,7 +1491,37 @@ static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* ds
         k_fwd_col<S, W, MODE, false><<<grid, block, 0, st>>>(c, src, src_gs, dst, dst_gs, jobs, chat, limb_ids, q_src);
 }
 
+#if PPQ_NTT_TILE
+template <int S1, int S2>
+static void ntt_tile_launch(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale4, int n_polys, bool inverse,
+                            cudaStream_t st) {
+    const size_t smem = (size_t)(1u << S1) * TileRowPos<S2>::RP * sizeof(u64);
+    count_launch();
+    if (inverse) {
+        cudaFuncSetAttribute(k_ntt_inv_tile<S1, S2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_ntt_inv_tile<S1, S2><<<n_polys, TILE_THREADS, smem, st>>>(c, data, d_limb_ids, d_scale4);
+    } else {
+        cudaFuncSetAttribute(k_ntt_fwd_tile<S1, S2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_ntt_fwd_tile<S1, S2><<<n_polys, TILE_THREADS, smem, st>>>(c, data, d_limb_ids);
+    }
+}
+static bool ntt_tile(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale4, int n_polys, bool inverse,
+                     cudaStream_t st) {
+    static const bool off = [] { const char* e = std::getenv("PPQ_NTT_TILE"); return e && e[0] == '0'; }();
+    if (off) return false;
+    switch (c.logN) {
+        case 12: ntt_tile_launch<6, 6>(c, data, d_limb_ids, d_scale4, n_polys, inverse, st); return true;
+        case 13: ntt_tile_launch<7, 6>(c, data, d_limb_ids, d_scale4, n_polys, inverse, st); return true;
+        case 14: ntt_tile_launch<7, 7>(c, data, d_limb_ids, d_scale4, n_polys, inverse, st); return true;
+        default: return false;
+    }
+}
+#else
+static bool ntt_tile(const KCtx&, u64*, const int*, const u64*, int, bool, cudaStream_t) { return false; }
+#endif
+
 void launch_ntt_forward(const KCtx& c, u64* data, const int* d_limb_ids, int n_polys, cudaStream_t st) {
+    if (ntt_tile(c, data, d_limb_ids, nullptr, n_polys, false, st)) return;
     count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
@@ -1527,15 +1571,6 @@ void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, 
     count_launch();
     const Split sp = split_of(c.logN);
     const int n2 = 1 << sp.S2;
-#if PPQ_COL2_INV
-    if (sp.S1 == 8) {
-        constexpr int W2 = PPQ_COL2_W;
-        dim3 grid2(n2 / (2 * W2), n_slots, n_g), block2(W2 << 5);
-        if (sp.S2 == 8) k_inv_col2<8, W2, true><<<grid2, block2, 0, st>>>(c, data, gs, d_limb_map, d_scale4);
-        else k_inv_col2<8, W2, false><<<grid2, block2, 0, st>>>(c, data, gs, d_limb_map, d_scale4);
-        return;
-    }
-#endif
     if (sp.S1 == sp.S2) {
         PPQ_COL_DISPATCH(sp.S1, (k_inv_col<S, ColW<S>::W, true><<<dim3(n2 / ColW<S>::W, n_slots, n_g), ColW<S>::W << (S - 3), 0, st>>>(
                                     c, data, gs, d_limb_map, d_scale4)));
@@ -1546,6 +1581,7 @@ void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, 
 }
 void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u64* d_scale4,
                         int n_polys, cudaStream_t st) {
+    if (ntt_tile(c, data, d_limb_ids, d_scale4, n_polys, true, st)) return;
     launch_inv_row(c, data, 0, data, 0, d_limb_ids, n_polys, 1, st);
     launch_inv_col(c, data, 0, d_limb_ids, d_scale4, n_polys, 1, st);
 }
@@ -1650,12 +1686,6 @@ bool launch_bconv_wide(const KCtx& c, const u64* src, size_t src_gs, size_t in_s
 #undef PPQ_BW
 }
 
-void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
-    count_launch();
-    const Split sp = split_of(c.logN);
-    const int n1 = 1 << sp.S1;
-    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_ip<S><<<dim3(n1 / RowGeom<S>::R, n_g, a.ell + a.K), RowGeom<S>::THREADS, 0, st>>>(c, a)));
-}
 bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
     const int N = 1 << c.logN;
     if (N % IPT) return false;
@@ -1680,7 +1710,7 @@ bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st) {
         return true;                                                                                       \
     }
     switch (a.parts) {
-        PPQ_IP(1) PPQ_IP(2) PPQ_IP(3) PPQ_IP(4) PPQ_IP(5) PPQ_IP(6)
+        PPQ_IP(1) PPQ_IP(2) PPQ_IP(3) PPQ_IP(4) PPQ_IP(5) PPQ_IP(6) PPQ_IP(7) PPQ_IP(8)
         default: return false;
     }
 #undef PPQ_IP
@@ -1708,7 +1738,7 @@ bool launch_ip_agg(const KCtx& c, const IpArgs& a, const IpMulti& m, int n_g, cu
         if (m.nb == 2) PPQ_IPA(P, 2)       \
         PPQ_IPA(P, 4)
     switch (a.parts) {
-        PPQ_IPA_P(1) PPQ_IPA_P(2) PPQ_IPA_P(3) PPQ_IPA_P(4) PPQ_IPA_P(5) PPQ_IPA_P(6)
+        PPQ_IPA_P(1) PPQ_IPA_P(2) PPQ_IPA_P(3) PPQ_IPA_P(4) PPQ_IPA_P(5) PPQ_IPA_P(6) PPQ_IPA_P(7) PPQ_IPA_P(8)
         default: return false;
     }
 #undef PPQ_IPA_P

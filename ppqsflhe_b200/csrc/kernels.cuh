@@ -70,7 +70,7 @@ void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
 void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
                        int n_jobs, int n_g, u64 q_src, cudaStream_t st);
 
-// ---- forward ROW pass fused with the key inner product (hybrid key switch, EvalFastKeySwitchCoreExt).
+// ---- key inner product (hybrid key switch, EvalFastKeySwitchCoreExt) on digits that are already in EVAL form.
 struct IpArgs {
     const u64* c1;       // EVAL c1 limbs of the batch: c1 + g*c1_gs + r*N (own-digit limbs are used as they are)
     size_t c1_gs;
@@ -94,7 +94,6 @@ struct IpArgs {
     const u64* c0 = nullptr;  // c0 + g*c0_gs + r*N
     size_t c0_gs = 0;
 };
-void launch_fwd_row_ip(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
 // ---- several clients per inner-product launch (ppq_agg_add_many): client cl < nb has its own input ciphertexts, key
 // and P-limb output block; digits of client cl, slot g sit at a.digits + (cl*n_g + g)*a.dig_gs.  A CTA sums the Q-limb
 // results of the nb clients of a slot in registers, so the slot's running sum is read and written once per nb clients.
@@ -111,7 +110,7 @@ struct IpMulti {
 bool launch_ip_agg(const KCtx& c, const IpArgs& a, const IpMulti& m, int n_g, cudaStream_t st);
 // ---- split form: digits already in EVAL (k_fwd_row_plain on a.digits); pointwise inner product with the key tile
 // staged in shared memory by TMA bulk copies and reused across the wave.  extp receives EVAL P limbs (run
-// launch_inv_row on it afterwards).  Returns false if the shape is unsupported (parts > 6 or N < 2048).
+// launch_inv_row on it afterwards).  Returns false if the shape is unsupported (parts > 8 or N < 512).
 bool launch_ip_tma(const KCtx& c, const IpArgs& a, int n_g, cudaStream_t st);
 
 // ---- forward ROW pass fused with the ModDown combine (+ c0, + optional accumulate = EvalAdd).

@@ -446,32 +446,4 @@ __device__ __forceinline__ void inv_pass_x2(u64 (&a)[8], u64 (&b)[8], u64* sm, u
     }
 }
 
-// Inverse COL pass over two adjacent columns per thread (see fwd_pass_col2); FIN as in inv_pass.
-template <int S, int W2, int BIN>
-__device__ __forceinline__ void inv_pass_col2(u64 (&a)[8], u64 (&b)[8], u64* sm, u32 w, u32 u,
-                                              const ulonglong2* __restrict__ tw, u64 q, u64 q4, ulonglong2 fin_s,
-                                              ulonglong2 fin_w) {
-    static_assert(S > 6, "two-column COL passes are built for S >= 7");
-    constexpr int LOL = S - 3;
-    constexpr int LO1 = 3;
-    constexpr int B1 = inv_plan(BIN, 0).out;
-    constexpr int B2 = inv_plan(B1, 3 - LO1).out;
-    ulonglong2 t[7];
-    inv_group_tw<S, 0, 0>(t, tw, 1u, u);
-    inv_group<S, 0, 0, BIN>(a, t, q, q4);
-    inv_group<S, 0, 0, BIN>(b, t, q, q4);
-    sm_store2<0, W2, S>(a, b, sm, w, u);
-    __syncthreads();
-    sm_load2<LO1, W2, S>(a, b, sm, w, u);
-    inv_group_tw<S, LO1, 3>(t, tw, 1u, u);
-    inv_group<S, LO1, 3, B1, false>(a, t, q, q4);
-    inv_group<S, LO1, 3, B1, false>(b, t, q, q4);
-    sm_store2<LO1, W2, S>(a, b, sm, w, u);
-    __syncthreads();
-    sm_load2<LOL, W2, S>(a, b, sm, w, u);
-    inv_group_tw<S, LOL, 6>(t, tw, 1u, u);
-    inv_group<S, LOL, 6, B2, true>(a, t, q, q4, fin_s, fin_w);
-    inv_group<S, LOL, 6, B2, true>(b, t, q, q4, fin_s, fin_w);
-}
-
 }  // namespace ppq

@@ -101,3 +101,18 @@ def test_python_mirror_defaults_to_os_entropy():
     assert context._seed32(None) is None and len(context._seed32(5)) == 32
     src = open(os.path.join(ROOT, "ppqsflhe_b200", "csrc", "capi.cu")).read()
     assert "getrandom(" in src and "splitmix" not in open(os.path.join(ROOT, "ppqsflhe_b200", "csrc", "sampler.cu")).read()
+
+
+def test_no_kernel_spills_registers():
+    """ptxas -v logs of the in-tree build: every launched kernel must be spill-free (round-1 review: the S = 6 ROW kernels
+    and the fused inner product spilled up to 704 bytes)."""
+    import ppqsflhe_b200
+    ppqsflhe_b200.build()
+    bdir = os.path.join(ROOT, "ppqsflhe_b200", "csrc", "build")
+    logs = [f for f in os.listdir(bdir) if f.endswith(".ptxas.log")]
+    assert {"kernels.ptxas.log", "ckks.ptxas.log", "sampler.ptxas.log"} <= set(logs)
+    for f in logs:
+        text = open(os.path.join(bdir, f)).read()
+        bad = re.findall(r"(\d+) bytes spill stores", text)
+        assert all(int(b) == 0 for b in bad), f
+        assert bad or f == "capi.ptxas.log", f  # capi.cu holds no kernels

@@ -121,7 +121,8 @@ def test_modup_bit_exact(kind, ell):
         assert np.array_equal(got[g], o.modup(ell, c1[g])), f"ModUp differs (ct {g})"
 
 
-@pytest.mark.parametrize("kind,ell,n", [("c1", 4, 5), ("c1", 3, 2), ("c1", 1, 1), ((12, 5, 3, 45), 7, 3),
+@pytest.mark.parametrize("kind,ell,n", [("c1", 4, 5), ("c1", 3, 2), ("c1", 1, 1), ((12, 5, 3, 45), 7, 3), ((12, 12, 7, 45), 14, 2),
+                                        ((13, 14, 8, 45), 16, 2),
                                         ((12, 5, 3, 45), 5, 2), ((13, 4, 2, 50), 6, 2), ((15, 2, 2, 40), 4, 2),
                                         ((16, 6, 3, 59), 8, 2), ((17, 2, 2, 40), 4, 1),
                                         # BASELINE.json full sizes: C3 (N=2^16, 20 limbs, K=7, digits 7/7/6), its fan-out
@@ -162,23 +163,6 @@ def test_rekey_upload_and_borrowed_key_agree():
     out_upload = cc.ReEncrypt(batch, up).numpy()
     assert np.array_equal(out_upload, out_borrowed)
     assert np.array_equal(out_upload[0], o.reencrypt(o.L, ct[0], kb, ka))
-
-
-def test_fused_and_split_inner_product_agree(monkeypatch):
-    """The two forms of the key inner product (one fused ROW-pass kernel / forward ROW pass + TMA-staged pointwise
-    kernel + inverse ROW pass) must give identical ciphertexts."""
-    from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
-    outs = []
-    for fused in ("0", "1"):
-        monkeypatch.setenv("PPQ_IP_FUSED", fused)
-        o, cc = _cc_pair((14, 5, 3, 50))
-        rng = np.random.default_rng(21)
-        ct = _rand_ct(rng, o, o.L, 3)
-        kb, ka = _rand_key(rng, o)
-        outs.append(cc.ReEncrypt(CiphertextBatch(to_device_u64(ct, cc.device), CtMeta()), EvalKey(cc, kb, ka)).numpy())
-        cc.close()
-    assert np.array_equal(outs[0], outs[1])
-    assert np.array_equal(outs[0][0], o.reencrypt(o.L, ct[0], kb, ka))
 
 
 def test_full_size_round_trip_c3():
@@ -238,7 +222,7 @@ def test_reencrypt_accumulate_matches_oracle_batch():
 
 @pytest.mark.parametrize("kind,ell,n_clients,n_slots", [("c1", 4, 2, 3), ("c1", 3, 9, 2), ("c1", 1, 3, 1),
                                                         ((12, 5, 3, 45), 7, 17, 2), ((13, 4, 2, 50), 5, 8, 3),
-                                                        ((13, 38, 3, 59), 40, 9, 1), ((15, 6, 3, 50), 8, 3, 5),
+                                                        ((13, 38, 3, 59), 40, 9, 1), ((15, 6, 3, 50), 8, 3, 5), ((12, 12, 7, 45), 14, 5, 2),
                                                         ((16, 18, 3, 59), 20, 9, 2), ((16, 18, 3, 59), 19, 2, 3)])
 def test_aggregator_bit_exact(kind, ell, n_clients, n_slots):
     """ppq_agg_* (deferred ModDown: the linear tail of ApproxModDown applied to sums over clients) against the oracle's
@@ -618,8 +602,7 @@ def test_reencrypt_fanout_bit_exact(kind, ell, n, n_keys, monkeypatch):
     """ppq_reencrypt_fanout (shared ModUp, per-key inner product + ModDown) against the oracle's ReEncrypt per key and
     against separate ppq_reencrypt calls; C1 at ell = 3 is the reference's own fan-out level (uneven digits {q0,q1},{q2})."""
     from ppqsflhe_b200 import CiphertextBatch, CtMeta, EvalKey, to_device_u64
-    for fused in ("0", "1"):
-        monkeypatch.setenv("PPQ_IP_FUSED", fused)
+    for _ in range(1):
         o, cc = _cc_pair(kind)
         rng = np.random.default_rng(41)
         ct = _rand_ct(rng, o, ell, n)

@@ -106,7 +106,7 @@ def traffic(path, n_cts=54, tag=""):
     end = next(i for i in range(len(seq)) if seq[i][0].startswith("k_fwd_row_moddown"))
     seq = seq[: end + 1]  # exactly one wave
     stages = ["k_inv_row(c1)", "k_inv_col(c1,scale)", "k_bconv(modup)", "k_fwd_col(modup)", "k_fwd_row(modup)",
-              "k_ip_tma|k_fwd_row_ip", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
+              "k_ip_tma|k_ip_agg", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
               "k_fwd_row_moddown"]
     per = dict.fromkeys(stages, 0.0)
     n_cts = int(n_cts)
@@ -133,7 +133,7 @@ def traffic_agg(path, n_slots=54, cap_clients=8, job_clients=64, group=8, nb=4, 
     mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     n_slots, cap_clients, job_clients, group, nb = int(n_slots), int(cap_clients), int(job_clients), int(group), int(nb)
     stages = ["k_inv_row(c1)", "k_inv_col(c1,scale)", "k_bconv(modup)", "k_fwd_col(modup)", "k_fwd_row(modup)",
-              "k_ip_tma|k_fwd_row_ip", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
+              "k_ip_tma|k_ip_agg", "k_inv_row(P)", "k_inv_col(P,scale)", "k_bconv(moddown)", "k_fwd_col(moddown)",
               "k_fwd_row_moddown"]
     per_launch = dict.fromkeys(stages, 0.0)
     fma = {}
