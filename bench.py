@@ -232,9 +232,10 @@ def cpu_run(cfg, steps, warmup, sample_slots=None):
             times.append(dt)
     t = float(np.median(times))
     return {"value": sample_slots / t, "unit": UNIT, "cores": T, "kind": "port",
-            "note": "unoptimised restatement: unsigned __int128 products reduced with % (__umodti3) in the NTT and base "
-                    "conversion loops; a Barrett/Shoup CPU implementation such as OpenFHE's would be several times "
-                    "faster, so GPU/CPU ratios over this arm are upper bounds",
+            "note": "scalar C restatement of the OpenFHE algorithms: Shoup butterflies, 128-bit accumulators reduced by Barrett "
+                    "(no 128-bit division in the inner loops since round 2: 1.7-2x the round-1 port), branch-free modular "
+                    "add/sub, OpenMP over ciphertext slots; no SIMD -- an AVX-512 NTT such as OpenFHE+HEXL would be faster "
+                    "still, so GPU/CPU ratios over this arm remain upper bounds",
             "sample": f"{sample_slots} ciphertexts of 1 client (ell={ell}, N=2^{o.logN}, K={o.K}, dnum={o.dnum}) per step, "
                       f"{steps} steps after {warmup} warm-up, median; OpenFHE-algorithm CPU restatement (oracle/), "
                       f"OpenMP over ciphertexts",

@@ -120,10 +120,29 @@ static inline u64 shoup_of(u64 w, u64 q) { return (u64)(((u128)w << 64) / q); }
 static inline u64 mulmod_sh(u64 x, u64 w, u64 wsh, u64 q) {
     u64 hi = (u64)(((u128)x * wsh) >> 64);
     u64 r = x * w - hi * q;
-    return r >= q ? r - q : r;
+    return r - (q & (0 - (u64)(r >= q))); /* branch-free: the comparison is a coin flip on random residues */
 }
-static inline u64 addmod(u64 a, u64 b, u64 q) { u64 s = a + b; return s >= q ? s - q : s; }
-static inline u64 submod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }
+/* 128-bit value mod q by Barrett reduction, as OpenFHE reduces the 128-bit accumulators of ApproxSwitchCRTBasis
+ * (BarrettUint128ModUint64) -- same residues as `%`, without the libgcc division (__umodti3) that made the first
+ * version of this port spend most of its time dividing.  mu = floor(2^(64+sh) / q), sh = bitlen(q) - 1; valid for
+ * x < 2^(63 + bitlen(q)), e.g. a sum of 8 products of a 60-bit value and a residue. */
+typedef struct { u64 q, mu; int sh; } bar_t;
+static inline bar_t bar_of(u64 q) {
+    bar_t b;
+    b.q = q;
+    b.sh = 63 - __builtin_clzll(q);
+    b.mu = (u64)((((u128)1) << (64 + b.sh)) / q);
+    return b;
+}
+static inline u64 bar_red(u128 x, bar_t b) {
+    u64 x1 = (u64)(x >> b.sh);
+    u64 qh = (u64)(((u128)x1 * b.mu) >> 64);
+    u64 r = (u64)x - qh * b.q;
+    while (r >= b.q) r -= b.q;
+    return r;
+}
+static inline u64 addmod(u64 a, u64 b, u64 q) { u64 s = a + b; return s - (q & (0 - (u64)(s >= q))); }
+static inline u64 submod(u64 a, u64 b, u64 q) { return a - b + (q & (0 - (u64)(a < b))); }
 static inline size_t brev(size_t x, int bits) {
     size_t r = 0;
     for (int i = 0; i < bits; i++) { r = (r << 1) | (x & 1); x >>= 1; }
@@ -437,13 +456,22 @@ static void approx_switch(size_t N, int ns, const u64* sm, u64* const* y /* alre
             if (k != i) p = ppqo_mulmod(p, sm[k] % t, t);
         chat[i] = p;
     }
+    const bar_t bt = bar_of(t);
+    if (ns <= 8) { /* the common case: one reduction per output, no test inside the product loop */
+        for (size_t n = 0; n < N; n++) {
+            u128 acc = 0;
+            for (int i = 0; i < ns; i++) acc += (u128)y[i][n] * chat[i];
+            out[n] = bar_red(acc, bt);
+        }
+        return;
+    }
     for (size_t n = 0; n < N; n++) {
         u128 acc = 0;
         for (int i = 0; i < ns; i++) {
             acc += (u128)y[i][n] * chat[i];
-            if ((i & 7) == 7) acc %= t; /* keep below 2^128 for very wide digits */
+            if ((i & 7) == 7 && i + 1 < ns) acc = bar_red(acc, bt); /* at most 8 products (+ one residue) per reduction */
         }
-        out[n] = (u64)(acc % t);
+        out[n] = bar_red(acc, bt);
     }
 }
 static void scale_by_hat_inv(size_t N, int ns, const u64* sm, u64** x) {
@@ -491,17 +519,17 @@ void ppqo_inner_product(const ppqo_ctx* c, int ell, const u64* digits, const u64
     int M = ell + c->K, MK = c->L + c->K, parts = ppqo_num_parts(c, ell);
     for (int r = 0; r < M; r++) {
         int g = ext_limb(c, ell, r); /* key limb index: r for Q limbs, L + k for P limbs */
-        u64 q = c->mod[g];
+        const bar_t bq = bar_of(c->mod[g]);
         u64 *o0 = ct0 + (size_t)r * N, *o1 = ct1 + (size_t)r * N;
-        for (size_t n = 0; n < N; n++) {
-            u64 a0 = 0, a1 = 0;
+        for (size_t n = 0; n < N; n++) { /* sum of <= 8 products of residues, reduced once (same residue as term by term) */
+            u128 a0 = 0, a1 = 0;
             for (int j = 0; j < parts; j++) {
                 u64 d = digits[((size_t)j * M + r) * N + n];
-                a0 = addmod(a0, ppqo_mulmod(d, kb[((size_t)j * MK + g) * N + n], q), q);
-                a1 = addmod(a1, ppqo_mulmod(d, ka[((size_t)j * MK + g) * N + n], q), q);
+                a0 += (u128)d * kb[((size_t)j * MK + g) * N + n];
+                a1 += (u128)d * ka[((size_t)j * MK + g) * N + n];
             }
-            o0[n] = a0;
-            o1[n] = a1;
+            o0[n] = bar_red(a0, bq);
+            o1[n] = bar_red(a1, bq);
         }
     }
 }
@@ -877,9 +905,28 @@ void ppqo_reencrypt_accumulate_batch(const ppqo_ctx* c, int ell, int n_clients, 
     size_t N = c->N, CT = 2 * (size_t)ell * N;
     memset(acc, 0, sizeof(u64) * CT * n_slots);
     (void)nthreads;
+    int nt = 1;
+#ifdef _OPENMP
+    nt = nthreads > 0 ? nthreads : omp_get_max_threads();
+#endif
+    if (n_slots >= nt) {
+        /* enough slots for every thread: a thread owns whole slots and adds its clients in order -- no lock */
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic) num_threads(nt)
+#endif
+        for (int s = 0; s < n_slots; s++) {
+            u64* tmp = malloc(sizeof(u64) * CT);
+            for (int cl = 0; cl < n_clients; cl++) {
+                ppqo_reencrypt(c, ell, cts + ((size_t)cl * n_slots + s) * CT, kb[cl], ka[cl], tmp);
+                ppqo_eval_add(c, ell, acc + (size_t)s * CT, tmp, acc + (size_t)s * CT);
+            }
+            free(tmp);
+        }
+        return;
+    }
     int total = n_clients * n_slots;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic) num_threads(nthreads > 0 ? nthreads : omp_get_max_threads())
+#pragma omp parallel for schedule(dynamic) num_threads(nt)
 #endif
     for (int w = 0; w < total; w++) {
         int cl = w / n_slots, s = w % n_slots;
