@@ -12,8 +12,13 @@
  *     thread-local message.  There is NO CPU fallback: without a usable sm_100a device every compute entry
  *     point fails with PPQ_ECUDA.
  *   - pointers named d_* are DEVICE pointers (cudaMalloc / torch CUDA storage); h_* are HOST pointers.
- *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are asynchronous on
- *     that stream; a context owns scratch memory, so use one stream at a time per context.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are ASYNCHRONOUS on that
+ *     stream (they return once the work is enqueued; ppq_sync waits) -- with these stated exceptions, which return
+ *     after their work is complete: ppq_ntt_forward / ppq_ntt_inverse (the caller's host limb-id list is staged),
+ *     ppq_rekey_upload / ppq_rekey_from_device, the ppq_ks_* stage views (test-facing), and the ppq_*_host calls.
+ *     The first use of a limb count builds small device tables once (a blocking copy); later calls do not block.
+ *     A context owns scratch memory, so use one stream at a time per context.
+ *   - batch sizes are limited only by memory: calls walk large batches in chunks internally.
  *   - residues are uint64 little-endian, canonical in [0, q_i); polynomials are limb-major ([limb][N]) in
  *     EVALUATION format in OpenFHE's bit-reversed order unless stated otherwise, which is exactly the payload
  *     of a serialized OpenFHE DCRTPoly.

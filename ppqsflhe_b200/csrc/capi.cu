@@ -98,7 +98,10 @@ struct ppq_ctx {
     DevBuf<int> ids;       // limb ids of the plain NTT API
     DevBuf<u64> ids_scale; // [n][4] output factor N^-1 per poly (host::scale4)
     std::vector<u64> ntt_scale4;  // [L+K][4], built on first use
-    DevBuf<u64> fac;       // [2][L] EvalMult factors
+    std::map<int, std::unique_ptr<DevBuf<int>>> cyc;    // limb ids 0..ell-1 repeated (65536 entries) per ell
+    std::map<int, std::unique_ptr<DevBuf<u64>>> cyc_scale;  // [65536][4] inverse-NTT output factors in the same order
+    std::map<int, std::unique_ptr<DevBuf<u64>>> garner;  // per ell: [ell] Garner inverses then [ell] partial products as doubles
+    DevBuf<u64> pmod;      // [L] P mod q_r (ReKeyGen)
     DevBuf<int> kinds3;    // {ternary, gauss, gauss}: the polynomial kinds of one (v, e0, e1) / (u, e0, e1) triple
     ckks::Tables fft;
     int wave = 0;
@@ -253,7 +256,11 @@ extern "C" int ppq_ctx_set_wave(ppq_ctx* c, int n) {
 static int ntt_common(ppq_ctx* c, u64* d, const int32_t* ids, size_t n, void* stream, bool inverse) {
     if (!c || !d || !ids) return fail(PPQ_EINVAL, "ppq_ntt: null argument");
     if (n == 0) return PPQ_OK;
-    if (n > 65535) return fail(PPQ_EINVAL, "ppq_ntt: at most 65535 polynomials per call");
+    if (n > 65535) {  // walked in chunks: the grid limit is not the caller's problem
+        for (size_t s0 = 0; s0 < n; s0 += 32768)
+            if (int rc = ntt_common(c, d + s0 * c->hp.N, ids + s0, std::min<size_t>(32768, n - s0), stream, inverse)) return rc;
+        return PPQ_OK;
+    }
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const int M = c->hp.M();
@@ -393,6 +400,22 @@ static int get_ks_plan(ppq_ctx* c, int ell, KsPlanDev** out) {
         it = c->ks.emplace(ell, std::move(p)).first;
     }
     *out = it->second.get();
+    return PPQ_OK;
+}
+
+// limb ids (0, 1, .., ell-1) repeated: the id table of every batched transform whose polynomials cycle through the first
+// `ell` limbs.  Built once per ell (the only synchronising step), then every call that needs it is asynchronous.
+static const int CYC_LEN = 65536;
+static int cyc_ids(ppq_ctx* c, int ell, const int** out) {
+    auto it = c->cyc.find(ell);
+    if (it == c->cyc.end()) {
+        std::unique_ptr<DevBuf<int>> b(new DevBuf<int>);
+        std::vector<int> h(CYC_LEN);
+        for (int i = 0; i < CYC_LEN; ++i) h[i] = i % ell;
+        CU(b->upload(h));
+        it = c->cyc.emplace(ell, std::move(b)).first;
+    }
+    *out = it->second->p;
     return PPQ_OK;
 }
 
@@ -874,14 +897,19 @@ extern "C" int ppq_params_dump(int logN, int L, const uint64_t* q, int dnum, int
 }
 
 // ------------------------------------------------------------------------------------------- EvalAdd / EvalMult
+// Batches larger than one launch's grid are walked in chunks inside the library: no "batch too large" at the ABI.
+static size_t rows_chunk(int rows_per_ct) { return std::max<size_t>(1, 65535 / (size_t)rows_per_ct); }
+
 extern "C" int ppq_eval_add(ppq_ctx* c, int ell, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t n,
                             void* stream) {
     if (!c || !a || !b || !o) return fail(PPQ_EINVAL, "ppq_eval_add: null argument");
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_eval_add: bad limb count");
     if (n == 0) return PPQ_OK;
-    if (n * 2 * ell > 65535) return fail(PPQ_EINVAL, "ppq_eval_add: batch too large for one call");
     CU(cudaSetDevice(c->device));
-    launch_eval_add(c->k, (const u64*)a, (const u64*)b, (u64*)o, ell, n, (cudaStream_t)stream);
+    const size_t ct = (size_t)2 * ell * c->hp.N, step = rows_chunk(2 * ell);
+    for (size_t s0 = 0; s0 < n; s0 += step)
+        launch_eval_add(c->k, (const u64*)a + s0 * ct, (const u64*)b + s0 * ct, (u64*)o + s0 * ct, ell, std::min(step, n - s0),
+                        (cudaStream_t)stream);
     CU(cudaGetLastError());
     return PPQ_OK;
 }
@@ -889,9 +917,10 @@ extern "C" int ppq_finalize_sum(ppq_ctx* c, int ell, uint64_t* x, size_t n, void
     if (!c || !x) return fail(PPQ_EINVAL, "ppq_finalize_sum: null argument");
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_finalize_sum: bad limb count");
     if (n == 0) return PPQ_OK;
-    if (n * 2 * ell > 65535) return fail(PPQ_EINVAL, "ppq_finalize_sum: batch too large for one call");
     CU(cudaSetDevice(c->device));
-    launch_finalize_mod(c->k, (u64*)x, ell, n, (cudaStream_t)stream);
+    const size_t ct = (size_t)2 * ell * c->hp.N, step = rows_chunk(2 * ell);
+    for (size_t s0 = 0; s0 < n; s0 += step)
+        launch_finalize_mod(c->k, (u64*)x + s0 * ct, ell, std::min(step, n - s0), (cudaStream_t)stream);
     CU(cudaGetLastError());
     return PPQ_OK;
 }
@@ -900,8 +929,8 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
                                    double sf, int rescale, void* stream) {
     if (!c || !in || !out) return fail(PPQ_EINVAL, "ppq_eval_mult_const: null argument");
     if (ell < (rescale ? 2 : 1) || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_eval_mult_const: bad limb count");
+    if (ell > 64) return fail(PPQ_EINVAL, "ppq_eval_mult_const: more than 64 limbs");
     if (n == 0) return PPQ_OK;
-    if (n > 16383) return fail(PPQ_EINVAL, "ppq_eval_mult_const: batch too large for one call");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = c->hp.N;
@@ -909,12 +938,15 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
     std::vector<u64> f(2 * (size_t)lo);
     host::mult_const_factors(c->hp, lo, sf, cst, f.data());
     if (!rescale) {
-        for (int i = 0; i < lo; ++i) f[lo + i] = host::shoup(f[i], c->hp.mod[i]);
-        CU(c->fac.ensure(2 * (size_t)c->hp.L));
-        CU(cudaMemcpyAsync(c->fac.p, f.data(), f.size() * sizeof(u64), cudaMemcpyHostToDevice, st));
-        launch_mult_scalar(c->k, (const u64*)in, (u64*)out, c->fac.p, c->fac.p + lo, ell, n, st);
+        FacPack pk{};
+        for (int i = 0; i < lo; ++i) {
+            pk.f[i] = f[i];
+            pk.fs[i] = host::shoup(f[i], c->hp.mod[i]);
+        }
+        const size_t ct = (size_t)2 * ell * N, step = rows_chunk(2 * ell);
+        for (size_t s0 = 0; s0 < n; s0 += step)
+            launch_mult_scalar_pack(c->k, (const u64*)in + s0 * ct, (u64*)out + s0 * ct, pk, ell, std::min(step, n - s0) * 2 * ell, st);
         CU(cudaGetLastError());
-        CU(cudaStreamSynchronize(st));
         return PPQ_OK;
     }
     auto it = c->rs.find(ell);
@@ -924,41 +956,38 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
         CU(p->last_limb.upload(p->h.last_limb));
         CU(p->last_scale.upload(host::scale4(c->hp, p->h.last_limb, p->h.last_scale)));
         CU(p->jobs.upload(to_dev_jobs(p->h.jobs)));
-        CU(p->cst.ensure(lo));
-        CU(p->cst_sh.ensure(lo));
         it = c->rs.emplace(ell, std::move(p)).first;
     }
     RsPlanDev* p = it->second.get();
+    RsArgs ra{};
     for (int i = 0; i < lo; ++i) {  // (x - t) * q_last^-1 * f  ==  (x - t) * (q_last^-1 f mod q)
-        f[i] = host::mulmod(f[i], p->h.qlinv[i], c->hp.mod[i]);
-        f[lo + i] = host::shoup(f[i], c->hp.mod[i]);
+        ra.cst[i] = host::mulmod(f[i], p->h.qlinv[i], c->hp.mod[i]);
+        ra.cst_sh[i] = host::shoup(ra.cst[i], c->hp.mod[i]);
     }
-    CU(cudaMemcpyAsync(p->cst.p, f.data(), lo * sizeof(u64), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(p->cst_sh.p, f.data() + lo, lo * sizeof(u64), cudaMemcpyHostToDevice, st));
     // scratch: last limbs in COEFF [n][2][N] + converted limbs [n][2][ell-1][N]
     const size_t rs_ = (size_t)2 * N, cs_ = (size_t)2 * lo * N, ct = (size_t)2 * ell * N;
-    CU(c->scratch2.ensure((rs_ + cs_) * n));
-    u64* r = c->scratch2.p;
-    u64* conv = r + rs_ * n;
-    // gather the two last limbs of every ciphertext (poly stride ell*N) via the strided inverse ROW pass
-    for (int poly = 0; poly < 2; ++poly)
-        launch_inv_row(c->k, (const u64*)in + ((size_t)poly * ell + lo) * N, ct, r + (size_t)poly * N, rs_,
-                       p->last_limb.p, 1, (int)n, st);
-    launch_inv_col(c->k, r, rs_, p->last_limb.p, p->last_scale.p, 2, (int)n, st);
-    launch_sw_fwd_col(c->k, r, rs_, conv, cs_, p->jobs.p, (int)p->h.jobs.size(), (int)n, c->hp.mod[lo], st);
-    RsArgs ra;
-    ra.conv = conv;
-    ra.conv_gs = cs_;
-    ra.ct_in = (const u64*)in;
-    ra.in_gs = ct;
-    ra.out = (u64*)out;
-    ra.out_gs = cs_;
-    ra.cst = p->cst.p;
-    ra.cst_sh = p->cst_sh.p;
-    ra.ell = ell;
-    launch_fwd_row_rescale(c->k, ra, (int)n, st);
+    const size_t step = 8192;
+    CU(c->scratch2.ensure((rs_ + cs_) * std::min(n, step)));
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t m = std::min(step, n - s0);
+        const u64* in_c = (const u64*)in + s0 * ct;
+        u64* r = c->scratch2.p;
+        u64* conv = r + rs_ * m;
+        // gather the two last limbs of every ciphertext (poly stride ell*N) via the strided inverse ROW pass
+        for (int poly = 0; poly < 2; ++poly)
+            launch_inv_row(c->k, in_c + ((size_t)poly * ell + lo) * N, ct, r + (size_t)poly * N, rs_, p->last_limb.p, 1, (int)m, st);
+        launch_inv_col(c->k, r, rs_, p->last_limb.p, p->last_scale.p, 2, (int)m, st);
+        launch_sw_fwd_col(c->k, r, rs_, conv, cs_, p->jobs.p, (int)p->h.jobs.size(), (int)m, c->hp.mod[lo], st);
+        ra.conv = conv;
+        ra.conv_gs = cs_;
+        ra.ct_in = in_c;
+        ra.in_gs = ct;
+        ra.out = (u64*)out + s0 * cs_;
+        ra.out_gs = cs_;
+        ra.ell = ell;
+        launch_fwd_row_rescale(c->k, ra, (int)m, st);
+    }
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 
@@ -966,17 +995,14 @@ extern "C" int ppq_eval_mult_const(ppq_ctx* c, int ell, const uint64_t* in, uint
 extern "C" int ppq_encode(ppq_ctx* c, int ell, const double* d_vals, size_t n_vals, double sf, uint64_t* d_pt, size_t n,
                           void* stream) {
     if (!c || !d_vals || !d_pt) return fail(PPQ_EINVAL, "ppq_encode: null argument");
-    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_encode: bad limb count");
+    if (ell < 1 || ell > c->hp.L || ell > 64) return fail(PPQ_EINVAL, "ppq_encode: bad limb count");
     if (n_vals > c->hp.N / 2) return fail(PPQ_EINVAL, "ppq_encode: more values than slots");
     if (n == 0) return PPQ_OK;
-    if (n * ell > 65535) return fail(PPQ_EINVAL, "ppq_encode: batch too large for one call");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = c->hp.N;
-    // scratch2: complex work [n][N/2] double2  (= n*N u64)  +  int64 coefficients [n][N]
-    CU(c->scratch2.ensure(2 * n * N));
-    double2* z = reinterpret_cast<double2*>(c->scratch2.p);
-    int64_t* co = reinterpret_cast<int64_t*>(c->scratch2.p + n * N);
+    const int* ids;
+    if (int rc = cyc_ids(c, ell, &ids)) return rc;
     // Scaling factors beyond what an int64 coefficient can hold (FLEXIBLEAUTOEXT at level 0 with 59-bit scaling
     // primes: sfBig = 2^79) are applied in two steps, as OpenFHE's CKKSPackedEncoding::Encode does with its
     // approxFactor: round at sf / 2^a, then multiply the residues by 2^a mod q_i.  a keeps |coefficient| < 2^62 for
@@ -984,30 +1010,30 @@ extern "C" int ppq_encode(ppq_ctx* c, int ell, const double* d_vals, size_t n_va
     int sf_exp = 0;
     std::frexp(sf, &sf_exp);
     const int approx = sf_exp > 58 ? sf_exp - 58 : 0;
-    ckks::launch_encode_fft(c->fft, d_vals, n_vals, std::ldexp(sf, -approx), z, co, n, st);
-    launch_small_to_res(c->k, co, (u64*)d_pt, 1, ell, n, st);
-    if (approx > 0) {
-        std::vector<u64> f(2 * (size_t)ell);
+    FacPack pk{};
+    if (approx > 0)
         for (int i = 0; i < ell; ++i) {
             const u64 q = c->hp.mod[i];
             u64 t = 1, b = 2 % q;
             for (int e = approx; e; e >>= 1, b = host::mulmod(b, b, q))
                 if (e & 1) t = host::mulmod(t, b, q);
-            f[i] = t;
-            f[ell + i] = host::shoup(t, q);
+            pk.f[i] = t;
+            pk.fs[i] = host::shoup(t, q);
         }
-        CU(c->fac.ensure(2 * (size_t)c->hp.L));
-        CU(cudaMemcpyAsync(c->fac.p, f.data(), f.size() * sizeof(u64), cudaMemcpyHostToDevice, st));
-        CU(cudaStreamSynchronize(st));  // f is stack-owned staging
-        launch_mult_scalar_polys(c->k, (const u64*)d_pt, (u64*)d_pt, c->fac.p, c->fac.p + ell, ell, n * ell, st);
+    const size_t step = rows_chunk(ell);
+    // scratch2: complex work [m][N/2] double2  (= m*N u64)  +  int64 coefficients [m][N]
+    CU(c->scratch2.ensure(2 * std::min(n, step) * N));
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t m = std::min(step, n - s0);
+        double2* z = reinterpret_cast<double2*>(c->scratch2.p);
+        int64_t* co = reinterpret_cast<int64_t*>(c->scratch2.p + m * N);
+        u64* pt = (u64*)d_pt + s0 * ell * N;
+        ckks::launch_encode_fft(c->fft, d_vals + s0 * n_vals, n_vals, std::ldexp(sf, -approx), z, co, m, st);
+        launch_small_to_res(c->k, co, pt, 1, ell, m, st);
+        if (approx > 0) launch_mult_scalar_pack(c->k, pt, pt, pk, ell, m * ell, st);
+        launch_ntt_forward(c->k, pt, ids, (int)(m * ell), st);
     }
-    std::vector<int> ids(n * ell);
-    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % ell);
-    CU(c->ids.ensure(ids.size()));
-    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    launch_ntt_forward(c->k, (u64*)d_pt, c->ids.p, (int)ids.size(), st);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 
@@ -1016,21 +1042,21 @@ extern "C" int ppq_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint6
     if (!c || !pkb || !pka || !pt || !small || !ct) return fail(PPQ_EINVAL, "ppq_encrypt: null argument");
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_encrypt: bad limb count");
     if (n == 0) return PPQ_OK;
-    if (n * 3 * ell > 65535) return fail(PPQ_EINVAL, "ppq_encrypt: batch too large for one call");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = c->hp.N;
-    CU(c->scratch2.ensure(n * 3 * ell * N));
-    u64* vee = c->scratch2.p;  // [n][3][ell][N]
-    launch_small_to_res(c->k, small, vee, 3, ell, n, st);
-    std::vector<int> ids(n * 3 * ell);
-    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % ell);
-    CU(c->ids.ensure(ids.size()));
-    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    launch_ntt_forward(c->k, vee, c->ids.p, (int)ids.size(), st);
-    launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, (const u64*)pt, (u64*)ct, ell, n, st);
+    const int* ids;
+    if (int rc = cyc_ids(c, ell, &ids)) return rc;
+    const size_t step = rows_chunk(3 * ell);
+    CU(c->scratch2.ensure(std::min(n, step) * 3 * ell * N));
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t m = std::min(step, n - s0);
+        u64* vee = c->scratch2.p;  // [m][3][ell][N]
+        launch_small_to_res(c->k, small + s0 * 3 * N, vee, 3, ell, m, st);
+        launch_ntt_forward(c->k, vee, ids, (int)(m * 3 * ell), st);
+        launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, (const u64*)pt + s0 * ell * N, (u64*)ct + s0 * 2 * ell * N, ell, m, st);
+    }
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 
@@ -1071,12 +1097,10 @@ extern "C" int ppq_sample_encrypt_noise(ppq_ctx* c, const uint8_t* seed32, int64
 // against the oracle; ppq_sample_keygen / ppq_sample_encrypt_noise draw them on the device.
 static int small_to_eval(ppq_ctx* c, const int64_t* small, u64* out, int n_small, size_t n_groups, cudaStream_t st) {
     const int M = c->hp.M();
+    const int* ids;
+    if (int rc = cyc_ids(c, M, &ids)) return rc;
     launch_small_to_res(c->k, small, out, n_small, M, n_groups, st);
-    std::vector<int> ids(n_groups * n_small * M);
-    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)(i % M);
-    CU(c->ids.ensure(ids.size()));
-    CU(cudaMemcpyAsync(c->ids.p, ids.data(), ids.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    launch_ntt_forward(c->k, out, c->ids.p, (int)ids.size(), st);
+    launch_ntt_forward(c->k, out, ids, (int)(n_groups * n_small * M), st);
     return PPQ_OK;
 }
 
@@ -1095,7 +1119,6 @@ extern "C" int ppq_keygen(ppq_ctx* c, const int64_t* d_s, const int64_t* d_e, co
     if (int rc = small_to_eval(c, small, se, 2, 1, st)) return rc;
     launch_keygen_pw(c->k, se, (const u64*)d_a, (u64*)d_sk, (u64*)d_pkb, c->hp.L, M, st);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 
@@ -1133,18 +1156,18 @@ extern "C" int ppq_rekeygen(ppq_ctx* c, const uint64_t* d_sk_old, const uint64_t
     CU(c->scratch2.ensure((size_t)dnum * 3 * M * N));
     u64* uee = c->scratch2.p;  // [dnum][3][M][N]
     if (int rc = small_to_eval(c, d_small, uee, 3, (size_t)dnum, st)) return rc;
-    std::vector<u64> pm(L);  // P mod q_r
-    for (int r = 0; r < L; ++r) {
-        u64 v = 1;
-        for (int k = 0; k < c->hp.K; ++k) v = host::mulmod(v, c->hp.mod[L + k] % c->hp.mod[r], c->hp.mod[r]);
-        pm[r] = v;
+    if (!c->pmod.p) {  // P mod q_r, once per context
+        std::vector<u64> pm(L);
+        for (int r = 0; r < L; ++r) {
+            u64 v = 1;
+            for (int k = 0; k < c->hp.K; ++k) v = host::mulmod(v, c->hp.mod[L + k] % c->hp.mod[r], c->hp.mod[r]);
+            pm[r] = v;
+        }
+        CU(c->pmod.upload(pm));
     }
-    CU(c->fac.ensure(2 * (size_t)L));
-    CU(cudaMemcpyAsync(c->fac.p, pm.data(), L * sizeof(u64), cudaMemcpyHostToDevice, st));
-    launch_rekeygen_pw(c->k, (const u64*)d_pkb, (const u64*)d_pka, uee, (const u64*)d_sk_old, c->fac.p, (u64*)d_kb,
+    launch_rekeygen_pw(c->k, (const u64*)d_pkb, (const u64*)d_pka, uee, (const u64*)d_sk_old, c->pmod.p, (u64*)d_kb,
                        (u64*)d_ka, L, M, c->hp.alpha, dnum, st);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 
@@ -1153,13 +1176,34 @@ extern "C" int ppq_decrypt_core(ppq_ctx* c, int ell, const uint64_t* sk, const u
     if (!c || !sk || !ct || !coeff) return fail(PPQ_EINVAL, "ppq_decrypt_core: null argument");
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_decrypt_core: bad limb count");
     if (n == 0) return PPQ_OK;
-    if (n * ell > 65535) return fail(PPQ_EINVAL, "ppq_decrypt_core: batch too large for one call");
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
-    launch_decrypt_pw(c->k, (const u64*)ct, (const u64*)sk, (u64*)coeff, ell, n, st);
-    std::vector<int32_t> ids(n * ell);
-    for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int32_t)(i % ell);
-    return ntt_common(c, (u64*)coeff, ids.data(), ids.size(), stream, true);
+    const size_t N = c->hp.N;
+    const int* ids;
+    if (int rc = cyc_ids(c, ell, &ids)) return rc;
+    if (c->ntt_scale4.empty()) {  // per limb, once: (N^-1, shoup, N^-1 psi^-brev(1), shoup)
+        std::vector<int> all(c->hp.M());
+        for (int r = 0; r < c->hp.M(); ++r) all[r] = r;
+        c->ntt_scale4 = host::scale4(c->hp, all, c->hp.ninv);
+    }
+    auto it = c->cyc_scale.find(ell);
+    if (it == c->cyc_scale.end()) {  // the output factors of the inverse transform in the same cyclic order as the ids
+        std::unique_ptr<DevBuf<u64>> b(new DevBuf<u64>);
+        std::vector<u64> h((size_t)4 * CYC_LEN);
+        for (int i = 0; i < CYC_LEN; ++i)
+            for (int k = 0; k < 4; ++k) h[4 * (size_t)i + k] = c->ntt_scale4[4 * (size_t)(i % ell) + k];
+        CU(b->upload(h));
+        it = c->cyc_scale.emplace(ell, std::move(b)).first;
+    }
+    const size_t step = rows_chunk(ell);
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t m = std::min(step, n - s0);
+        u64* co = (u64*)coeff + s0 * ell * N;
+        launch_decrypt_pw(c->k, (const u64*)ct + s0 * 2 * ell * N, (const u64*)sk, co, ell, m, st);
+        launch_ntt_inverse(c->k, co, ids, it->second->p, (int)(m * ell), st);
+    }
+    CU(cudaGetLastError());
+    return PPQ_OK;
 }
 
 extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf, double* d_vals, size_t n,
@@ -1170,24 +1214,32 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = c->hp.N;
-    // Garner constants: ginv[i] = (q_0..q_{i-1})^-1 mod q_i ; wdbl[i] = double(q_0..q_{i-1})
-    std::vector<u64> gin(ell, 0);
-    std::vector<double> wd(ell, 1.0);
-    for (int i = 1; i < ell; ++i) {
-        u64 pr = 1;
-        for (int k = 0; k < i; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
-        gin[i] = host::invmod(pr, c->hp.mod[i]);
-        wd[i] = wd[i - 1] * (double)c->hp.mod[i - 1];
+    auto it = c->garner.find(ell);
+    if (it == c->garner.end()) {
+        // Garner constants, once per ell: ginv[i] = (q_0..q_{i-1})^-1 mod q_i ; wdbl[i] = double(q_0..q_{i-1})
+        std::vector<u64> g(2 * (size_t)ell, 0);
+        std::vector<double> wd(ell, 1.0);
+        for (int i = 1; i < ell; ++i) {
+            u64 pr = 1;
+            for (int k = 0; k < i; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
+            g[i] = host::invmod(pr, c->hp.mod[i]);
+            wd[i] = wd[i - 1] * (double)c->hp.mod[i - 1];
+        }
+        std::memcpy(g.data() + ell, wd.data(), ell * sizeof(double));
+        std::unique_ptr<DevBuf<u64>> b(new DevBuf<u64>);
+        CU(b->upload(g));
+        it = c->garner.emplace(ell, std::move(b)).first;
     }
-    CU(c->fac.ensure(2 * (size_t)c->hp.L));
-    CU(cudaMemcpyAsync(c->fac.p, gin.data(), ell * sizeof(u64), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(c->fac.p + c->hp.L, wd.data(), ell * sizeof(double), cudaMemcpyHostToDevice, st));
-    CU(c->scratch2.ensure(n * N));
-    double2* z = reinterpret_cast<double2*>(c->scratch2.p);
-    ckks::launch_decode(c->fft, c->k, (const u64*)coeff, ell, c->fac.p, reinterpret_cast<const double*>(c->fac.p + c->hp.L),
-                        sf, z, d_vals, n, st);
+    const u64* gin = it->second->p;
+    const size_t step = 8192;
+    CU(c->scratch2.ensure(std::min(n, step) * N));
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t m = std::min(step, n - s0);
+        double2* z = reinterpret_cast<double2*>(c->scratch2.p);
+        ckks::launch_decode(c->fft, c->k, (const u64*)coeff + s0 * ell * N, ell, gin, reinterpret_cast<const double*>(gin + ell), sf, z,
+                            d_vals + s0 * (N / 2), m, st);
+    }
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
     return PPQ_OK;
 }
 

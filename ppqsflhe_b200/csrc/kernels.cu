@@ -1318,6 +1318,17 @@ __global__ void k_mult_scalar(KCtx c, const u64* __restrict__ in, u64* __restric
             make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
     }
 }
+__global__ void k_mult_scalar_pack(KCtx c, const u64* __restrict__ in, u64* __restrict__ out, const __grid_constant__ FacPack P, int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const u64 q = c.limbs[i].q, w = P.f[i], ws = P.fs[i];
+    const size_t base = (size_t)blockIdx.y * N;
+    for (u32 n = (blockIdx.x * blockDim.x + threadIdx.x) * 2; n < N; n += gridDim.x * blockDim.x * 2) {
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(in + base + n);
+        *reinterpret_cast<ulonglong2*>(out + base + n) =
+            make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
+    }
+}
 // out[(j*out_stride + i)*N + n] = in[(j*in_stride + i)*N + n] * f[i] mod q_i ; grid (N/512, L, dnum)
 __global__ void k_scale_key(KCtx c, const u64* in, int in_stride, u64* out, int out_stride,  // in may alias out
                             const u64* __restrict__ f, const u64* __restrict__ fs) {
@@ -1783,6 +1794,10 @@ void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, 
                         size_t n_ct, cudaStream_t st) {
     count_launch();
     k_mult_scalar<<<pw_grid(c, n_ct * 2 * ell, 2), 256, 0, st>>>(c, in, out, d_f, d_f_sh, ell);
+}
+void launch_mult_scalar_pack(const KCtx& c, const u64* in, u64* out, const FacPack& p, int ell, size_t n_rows, cudaStream_t st) {
+    count_launch();
+    k_mult_scalar_pack<<<pw_grid(c, n_rows, 2), 256, 0, st>>>(c, in, out, p, ell);
 }
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st) {

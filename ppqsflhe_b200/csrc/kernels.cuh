@@ -140,8 +140,8 @@ struct RsArgs {
     size_t in_gs;
     u64* out;          // [g][2][ell-1][N]
     size_t out_gs;
-    const u64* cst;    // [ell-1]
-    const u64* cst_sh;
+    u64 cst[64];       // [ell-1] per-limb factor q_last^-1 * EvalMult constant, BY VALUE: the call stays asynchronous
+    u64 cst_sh[64];
     int ell;
 };
 void launch_fwd_row_rescale(const KCtx& c, const RsArgs& a, int n_g, cudaStream_t st);
@@ -154,6 +154,11 @@ void launch_finalize_mod(const KCtx& c, u64* x, int ell, size_t n_ct, cudaStream
 // out = in * f[i] mod q_i
 void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                         size_t n_ct, cudaStream_t st);
+// per-limb factors passed by value (kernel parameter): nothing to stage, nothing to wait for
+struct FacPack {
+    u64 f[64], fs[64];
+};
+void launch_mult_scalar_pack(const KCtx& c, const u64* in, u64* out, const FacPack& p, int ell, size_t n_rows, cudaStream_t st);
 // same over a flat list of n_polys polynomials whose limb index is (poly index % ell)
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st);
