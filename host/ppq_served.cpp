@@ -20,10 +20,26 @@
 //     STATS                                                       -> OK rounds=.. rekeys=.. key_parses=..
 //     QUIT                                                        -> OK bye
 // Errors: "ERR <message>"; the process stays up.
+//
+// --http <sConfig.json>: the same process is ALSO the file drop-box of the reference (server/src/runMserver.cpp:237-285,
+// same endpoints, same sConfig.json keys; HTTP/1.1, multipart uploads with the part name "file", `Expect: 100-continue`
+// answered), generalised from the hard-coded C1/C2 to CLIENT_<i>_* keys for i = 1..C:
+//     GET  /getCC, /sendPbKeyC<i>, /download/<rel>             POST /uploadPubKeyC<i>, /uploadReKeyC<i>, /uploadEncWeightsC<i>,
+//                                                                   /uploadDomainChange, /uploadAggregated, /uploadDomainChangeAgg
+// and it CALLS THE GPU PATH: an uploaded re-encryption key is loaded onto the device at once, and when the encrypted
+// weights of all C clients of a round have arrived the round runs in-process (target domain = client C, as in the
+// reference's flow for C = 2) and writes AGGREGATED_ENCRYPTED_WEIGHTS_PATH and OUTPUT_AGGREGATED_DOMAIN_CHANGED_PATH[_<i>],
+// which the clients then GET exactly as before (orchestration/comm_fns.sh:134-145).  The orchestrator's three server
+// steps per round (server_fns.sh:62-80) become no-ops.  Re-encryption keys: CLIENT_<i>_REKEY is client i -> client C for
+// i < C, and CLIENT_<C>_REKEY (C = 2) or CLIENT_<C>_REKEY_TO_<i> is client C -> client i.
+#include <arpa/inet.h>
+#include <netinet/in.h>
 #include <sys/socket.h>
 #include <sys/un.h>
 #include <unistd.h>
 
+#include <cctype>
+#include <fstream>
 #include <sstream>
 
 #include "ppq_ops.hpp"
@@ -239,12 +255,275 @@ static int serve_socket(Server& sv, const std::string& path) {
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ HTTP drop-box
+struct HttpCfg {
+    std::string ip = "0.0.0.0", cc_path;
+    int port = 8000, C = 0;
+    std::map<std::string, std::string> clients;  // the "CLIENTS" object of sConfig.json, verbatim
+    const std::string* get(const std::string& k) const {
+        auto it = clients.find(k);
+        return it == clients.end() ? nullptr : &it->second;
+    }
+};
+static HttpCfg load_http_cfg(const std::string& path) {
+    jmin::Ptr j = jmin::parse(wire::slurp(path));
+    HttpCfg c;
+    if (const jmin::Value* m = j->find("mSConfig")) {
+        if (const jmin::Value* v = m->find("SERVER_IP")) c.ip = v->as_string();
+        if (const jmin::Value* v = m->find("SERVER_PORT")) c.port = (int)v->as_i64();
+    }
+    c.cc_path = j->at("CC").at("path").as_string();
+    for (const auto& kv : j->at("CLIENTS").obj) c.clients[kv.first] = kv.second->as_string();
+    while (c.get("CLIENT_" + std::to_string(c.C + 1) + "_ENCRYPTED_WEIGHTS_PATH")) ++c.C;
+    if (c.C < 1) throw std::runtime_error("sConfig.json: no CLIENT_<i>_ENCRYPTED_WEIGHTS_PATH");
+    return c;
+}
+static bool read_n(int fd, std::string& buf, size_t want) {
+    char tmp[65536];
+    while (buf.size() < want) {
+        const ssize_t r = read(fd, tmp, std::min(sizeof tmp, want - buf.size()));
+        if (r <= 0) return false;
+        buf.append(tmp, (size_t)r);
+    }
+    return true;
+}
+static void http_reply(int fd, int code, const std::string& ctype, const std::string& body) {
+    const char* txt = code == 200 ? "OK" : code == 404 ? "Not Found" : code == 405 ? "Method Not Allowed" : "Internal Server Error";
+    std::ostringstream h;
+    h << "HTTP/1.1 " << code << " " << txt << "\r\n";
+    if (!ctype.empty()) h << "Content-Type: " << ctype << "\r\n";
+    h << "Content-Length: " << body.size() << "\r\nConnection: close\r\n\r\n";
+    const std::string head = h.str();
+    (void)!write(fd, head.data(), head.size());
+    size_t off = 0;
+    while (off < body.size()) {
+        const ssize_t w = write(fd, body.data() + off, body.size() - off);
+        if (w <= 0) break;
+        off += (size_t)w;
+    }
+}
+// body of the multipart part called "file" (the reference's handle_upload takes exactly that part, :152-160)
+static bool multipart_file(const std::string& ctype, const std::string& body, std::string& out) {
+    const size_t b = ctype.find("boundary=");
+    if (b == std::string::npos) return false;
+    std::string boundary = ctype.substr(b + 9);
+    if (!boundary.empty() && boundary[0] == '"') boundary = boundary.substr(1, boundary.find('"', 1) - 1);
+    const std::string delim = "--" + boundary;
+    size_t pos = body.find(delim);
+    while (pos != std::string::npos) {
+        pos += delim.size();
+        if (body.compare(pos, 2, "--") == 0) break;
+        const size_t hend = body.find("\r\n\r\n", pos);
+        if (hend == std::string::npos) break;
+        const std::string headers = body.substr(pos, hend - pos);
+        const size_t next = body.find("\r\n" + delim, hend + 4);
+        if (next == std::string::npos) break;
+        if (headers.find("name=\"file\"") != std::string::npos) {
+            out = body.substr(hend + 4, next - (hend + 4));
+            return true;
+        }
+        pos = next + 2;
+    }
+    return false;
+}
+
+struct HttpServer {
+    Server& sv;
+    HttpCfg cfg;
+    std::vector<bool> have;  // encrypted weights of client i received this round
+    size_t rounds_run = 0;
+    HttpServer(Server& s, const HttpCfg& c) : sv(s), cfg(c), have((size_t)c.C, false) {}
+
+    std::string rekey_name_up(int i) const { return "up" + std::to_string(i); }
+    std::string rekey_name_down(int i) const { return "down" + std::to_string(i); }
+    // which resident key a just-uploaded CLIENT_<i>_REKEY[_TO_<k>] file is
+    void maybe_load_rekey(const std::string& key, const std::string& path) {
+        const int C = cfg.C;
+        for (int i = 1; i <= C; ++i) {
+            if (i < C && key == "CLIENT_" + std::to_string(i) + "_REKEY") {
+                bool q = false;
+                std::cout << "[served] " << sv.handle("LOAD_REKEY " + rekey_name_up(i) + " " + path, q) << std::endl;
+            }
+            if (key == "CLIENT_" + std::to_string(C) + "_REKEY_TO_" + std::to_string(i) || (C == 2 && i == 1 && key == "CLIENT_2_REKEY")) {
+                bool q = false;
+                std::cout << "[served] " << sv.handle("LOAD_REKEY " + rekey_name_down(i) + " " + path, q) << std::endl;
+            }
+        }
+    }
+    void maybe_run_round() {
+        for (bool h : have)
+            if (!h) return;
+        const int C = cfg.C;
+        std::ostringstream cmd;
+        cmd << "ROUND target=" << *cfg.get("CLIENT_" + std::to_string(C) + "_ENCRYPTED_WEIGHTS_PATH")
+            << " out=" << *cfg.get("AGGREGATED_ENCRYPTED_WEIGHTS_PATH");
+        for (int i = 1; i < C; ++i) {
+            cmd << " up=" << rekey_name_up(i) << ":" << *cfg.get("CLIENT_" + std::to_string(i) + "_ENCRYPTED_WEIGHTS_PATH");
+            const std::string* o = cfg.get(i == 1 ? "OUTPUT_AGGREGATED_DOMAIN_CHANGED_PATH" : "OUTPUT_AGGREGATED_DOMAIN_CHANGED_PATH_" + std::to_string(i));
+            if (o && sv.rekeys.count(rekey_name_down(i))) cmd << " down=" << rekey_name_down(i) << ":" << *o;
+        }
+        bool q = false;
+        const std::string r = sv.handle(cmd.str(), q);
+        std::cout << "[served] round " << ++rounds_run << ": " << r << std::endl;
+        std::fill(have.begin(), have.end(), false);
+    }
+
+    void serve_file(int fd, const std::string& path) {
+        std::string data;
+        try {
+            data = wire::slurp(path);
+        } catch (const std::exception&) {
+            http_reply(fd, 404, "", "Not found\n");
+            return;
+        }
+        std::cout << "[SERVER] Serving file " << path << " (" << data.size() << " bytes)" << std::endl;
+        http_reply(fd, 200, "application/octet-stream", data);
+    }
+    void upload(int fd, const std::string& method, const std::string& ctype, const std::string& body, const std::string& key) {
+        if (method != "POST") return http_reply(fd, 405, "", "Method not allowed\n");
+        const std::string* dest = cfg.get(key);
+        std::string file;
+        if (!dest || !multipart_file(ctype, body, file)) return http_reply(fd, 500, "", "Error: cannot open file for writing\n");
+        try {
+            const size_t slash = dest->rfind('/');
+            if (slash != std::string::npos) (void)!system(("mkdir -p '" + dest->substr(0, slash) + "'").c_str());
+            wire::spit(*dest, file);
+        } catch (const std::exception&) {
+            return http_reply(fd, 500, "", "Error: cannot open file for writing\n");
+        }
+        std::cout << "[SERVER] Received " << file.size() << " bytes, saved to " << *dest << std::endl;
+        http_reply(fd, 200, "application/json", "{\"status\":\"received\"}");
+        if (key.find("_REKEY") != std::string::npos) maybe_load_rekey(key, *dest);
+        for (int i = 1; i <= cfg.C; ++i)
+            if (key == "CLIENT_" + std::to_string(i) + "_ENCRYPTED_WEIGHTS_PATH") {
+                have[(size_t)i - 1] = true;
+                maybe_run_round();
+            }
+    }
+    void handle(int fd) {
+        std::string buf;
+        char tmp[8192];
+        size_t hend;
+        while ((hend = buf.find("\r\n\r\n")) == std::string::npos) {
+            const ssize_t r = read(fd, tmp, sizeof tmp);
+            if (r <= 0) return;
+            buf.append(tmp, (size_t)r);
+            if (buf.size() > (1u << 20)) return;
+        }
+        std::istringstream rl(buf.substr(0, buf.find("\r\n")));
+        std::string method, uri;
+        rl >> method >> uri;
+        std::string headers = buf.substr(0, hend + 4), lower = headers;
+        for (auto& ch : lower) ch = (char)std::tolower((unsigned char)ch);
+        auto header = [&](const std::string& name) {
+            const size_t p = lower.find("\r\n" + name + ":");
+            if (p == std::string::npos) return std::string();
+            const size_t s0 = p + name.size() + 3, e0 = headers.find("\r\n", s0);
+            std::string v = headers.substr(s0, e0 - s0);
+            while (!v.empty() && v[0] == ' ') v.erase(0, 1);
+            return v;
+        };
+        const size_t clen = (size_t)std::strtoull(header("content-length").c_str(), nullptr, 10);
+        if (lower.find("expect: 100-continue") != std::string::npos) (void)!write(fd, "HTTP/1.1 100 Continue\r\n\r\n", 25);
+        std::string body = buf.substr(hend + 4);
+        if (clen > ((size_t)1 << 32) || !read_n(fd, body, clen)) return;
+        const std::string ctype = header("content-type");
+        auto client_of = [&](const std::string& prefix) -> int {  // "/uploadReKeyC7" -> 7
+            if (uri.compare(0, prefix.size(), prefix) != 0) return 0;
+            const int i = std::atoi(uri.c_str() + prefix.size());
+            return (i >= 1 && i <= cfg.C && uri == prefix + std::to_string(i)) ? i : 0;
+        };
+        int i;
+        if (uri == "/getCC" && method == "GET") {
+            std::cout << "[SERVER] Serving " << cfg.cc_path << std::endl;
+            serve_file(fd, cfg.cc_path);
+        } else if ((i = client_of("/sendPbKeyC")) && method == "GET") {
+            const std::string* p = cfg.get("CLIENT_" + std::to_string(i) + "_PUBLIC");
+            if (p) serve_file(fd, *p);
+            else http_reply(fd, 500, "", "Error: cannot open pubkey file\n");
+        } else if (uri.size() > 10 && uri.compare(0, 10, "/download/") == 0) {
+            const std::string rel = uri.substr(10);
+            const size_t slash = cfg.cc_path.rfind('/');
+            const std::string base = slash == std::string::npos ? "." : cfg.cc_path.substr(0, slash);
+            if (rel.find("..") != std::string::npos) http_reply(fd, 404, "", "Not found\n");
+            else serve_file(fd, base + "/" + rel);
+        } else if ((i = client_of("/uploadPubKeyC"))) {
+            upload(fd, method, ctype, body, "CLIENT_" + std::to_string(i) + "_PUBLIC");
+        } else if ((i = client_of("/uploadReKeyC"))) {
+            upload(fd, method, ctype, body, "CLIENT_" + std::to_string(i) + "_REKEY");
+        } else if (uri.compare(0, 13, "/uploadReKeyC") == 0 && uri.find("To") != std::string::npos) {  // /uploadReKeyC<C>To<i>
+            const int to = std::atoi(uri.c_str() + uri.find("To") + 2);
+            upload(fd, method, ctype, body, "CLIENT_" + std::to_string(cfg.C) + "_REKEY_TO_" + std::to_string(to));
+        } else if ((i = client_of("/uploadEncWeightsC"))) {
+            upload(fd, method, ctype, body, "CLIENT_" + std::to_string(i) + "_ENCRYPTED_WEIGHTS_PATH");
+        } else if (uri == "/uploadDomainChange") {
+            upload(fd, method, ctype, body, "OUTPUT_DOMAIN_CHANGED_PATH");
+        } else if (uri == "/uploadAggregated") {
+            upload(fd, method, ctype, body, "AGGREGATED_ENCRYPTED_WEIGHTS_PATH");
+        } else if (uri == "/uploadDomainChangeAgg") {
+            upload(fd, method, ctype, body, "OUTPUT_AGGREGATED_DOMAIN_CHANGED_PATH");
+        } else if (uri == "/shutdown" && method == "POST") {  // not in the reference: lets a test stop the listener
+            http_reply(fd, 200, "application/json", "{\"status\":\"bye\"}");
+            stop = true;
+        } else {
+            http_reply(fd, 404, "", "Not found\n");
+        }
+    }
+    bool stop = false;
+    int run() {
+        const int fd = socket(AF_INET, SOCK_STREAM, 0);
+        if (fd < 0) return 1;
+        int one = 1;
+        setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+        sockaddr_in a{};
+        a.sin_family = AF_INET;
+        a.sin_port = htons((uint16_t)cfg.port);
+        if (inet_pton(AF_INET, cfg.ip.c_str(), &a.sin_addr) != 1) a.sin_addr.s_addr = INADDR_ANY;
+        if (bind(fd, reinterpret_cast<sockaddr*>(&a), sizeof a) != 0 || listen(fd, 16) != 0) {
+            std::cerr << "[SERVER] Failed to start server on http://" << cfg.ip << ":" << cfg.port << std::endl;
+            return 1;
+        }
+        std::cout << "[SERVER] ppq_served HTTP server running on http://" << cfg.ip << ":" << cfg.port << " (" << cfg.C << " clients)" << std::endl;
+        while (!stop) {
+            const int c = accept(fd, nullptr, nullptr);
+            if (c < 0) break;
+            try {
+                handle(c);
+            } catch (const std::exception& e) {
+                http_reply(c, 500, "", std::string("Error: ") + e.what() + "\n");
+            }
+            close(c);
+        }
+        close(fd);
+        return 0;
+    }
+};
+
 int main(int argc, char* argv[]) {
     if (argc < 2) {
-        std::cerr << "Usage: " << argv[0] << " <cc_path> [--socket PATH] [--rekey NAME=PATH]..." << std::endl;
+        std::cerr << "Usage: " << argv[0] << " <cc_path> [--socket PATH] [--rekey NAME=PATH]...\n       " << argv[0]
+                  << " --http <sConfig.json>" << std::endl;
         return 1;
     }
     Server sv;
+    if (std::string(argv[1]) == "--http") {
+        if (argc != 3) {
+            std::cerr << "Usage: " << argv[0] << " --http <sConfig.json>" << std::endl;
+            return 1;
+        }
+        try {
+            const HttpCfg cfg = load_http_cfg(argv[2]);
+            sv.s.reset(new Session(cfg.cc_path));
+            std::cout << "[served] CryptoContext loaded" << std::endl;
+            HttpServer hs(sv, cfg);
+            for (const auto& kv : cfg.clients)  // keys already on disk from an earlier run stay usable
+                if (kv.first.find("_REKEY") != std::string::npos && std::ifstream(kv.second).good()) hs.maybe_load_rekey(kv.first, kv.second);
+            return hs.run();
+        } catch (const std::exception& e) {
+            std::cerr << "[SERVER] ERROR: " << e.what() << std::endl;
+            return 1;
+        }
+    }
     try {
         sv.s.reset(new Session(argv[1]));
     } catch (const std::exception& e) {

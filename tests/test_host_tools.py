@@ -388,3 +388,76 @@ def test_resident_server_three_clients_two_rounds(tools, tmp_path, ccjson_text):
         ok(0, T("decryptModelWeights"), str(cc_path), str(tmp_path / f"c{who}/private.key"), str(tmp_path / b), str(tmp_path / "db.json"))
         assert open(tmp_path / "da.json", "rb").read() == open(tmp_path / "db.json", "rb").read()
     print("ppq_served rounds:", rounds)
+
+    # ---- the same process as the reference's HTTP drop-box (runMserver.cpp:237-285) that calls the GPU path itself:
+    # keys and encrypted weights arrive as multipart uploads, the round runs when the last client's file lands, the
+    # clients download the results from the reference's URLs
+    import http.client
+    import socket
+    store = tmp_path / "server" / "storage"
+    (store / "client_1").mkdir(parents=True)
+    (store / "client_2").mkdir(parents=True)
+    (store / "CC.json").write_text(ccjson_text)
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    scfg = {"mSConfig": {"SERVER_IP": "127.0.0.1", "SERVER_PORT": port}, "CC": {"path": str(store / "CC.json")},
+            "CLIENTS": {"CLIENT_1_PUBLIC": str(store / "client_1/client_1-public.key"),
+                        "CLIENT_2_PUBLIC": str(store / "client_2/client_2-public.key"),
+                        "CLIENT_1_REKEY": str(store / "client_1/client_1-ReKey.key"),
+                        "CLIENT_2_REKEY": str(store / "client_2/client_2-ReKey.key"),
+                        "CLIENT_1_ENCRYPTED_WEIGHTS_PATH": str(store / "client_1/encrypted_weights_c1.json"),
+                        "CLIENT_2_ENCRYPTED_WEIGHTS_PATH": str(store / "client_2/encrypted_weights_c2.json"),
+                        "OUTPUT_DOMAIN_CHANGED_PATH": str(store / "client_2/c1_domainChange_c2.json"),
+                        "AGGREGATED_ENCRYPTED_WEIGHTS_PATH": str(store / "client_2/aggregated_weights.json"),
+                        "OUTPUT_AGGREGATED_DOMAIN_CHANGED_PATH": str(store / "client_1/c2_domainChange_c1.json")}}
+    (tmp_path / "sConfig.json").write_text(json.dumps(scfg))
+    hp = subprocess.Popen([T("ppq_served"), "--http", str(tmp_path / "sConfig.json")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                          text=True, env=dict(os.environ, PPQ_QUIET="1"))
+    try:
+        while True:
+            line = hp.stdout.readline()
+            assert line, "ppq_served --http died"
+            if "HTTP server running" in line:
+                assert "(2 clients)" in line
+                break
+
+        def req(method, url, body=None, ctype=None):
+            c = http.client.HTTPConnection("127.0.0.1", port, timeout=120)
+            c.request(method, url, body=body, headers={"Content-Type": ctype} if ctype else {})
+            r = c.getresponse()
+            data = r.read()
+            c.close()
+            return r.status, data
+
+        def upload(url, path):
+            bnd = "----ppqtestboundary7MA4YWxk"
+            body = (f"--{bnd}\r\nContent-Disposition: form-data; name=\"client_id\"\r\n\r\nclient\r\n"
+                    f"--{bnd}\r\nContent-Disposition: form-data; name=\"file\"; filename=\"f\"\r\n"
+                    f"Content-Type: application/octet-stream\r\n\r\n").encode() + open(path, "rb").read() + f"\r\n--{bnd}--\r\n".encode()
+            st, data = req("POST", url, body, f"multipart/form-data; boundary={bnd}")
+            assert st == 200 and data == b'{"status":"received"}', (url, st, data)
+
+        st, data = req("GET", "/getCC")
+        assert st == 200 and data == ccjson_text.encode()
+        assert req("GET", "/nothing")[0] == 404 and req("GET", "/download/../../etc/passwd")[0] == 404
+        upload("/uploadPubKeyC1", tmp_path / "c1/public.key")
+        assert req("GET", "/sendPbKeyC1")[1] == open(tmp_path / "c1/public.key", "rb").read()
+        upload("/uploadReKeyC1", tmp_path / "rk_1_2.key")    # 27 MB of JSON each: parsed once, resident from here on
+        upload("/uploadReKeyC2", tmp_path / "rk_2_1.key")
+        for rnd in (1, 2):
+            upload("/uploadEncWeightsC1", tmp_path / "enc_c1.json")
+            assert req("GET", "/download/client_2/aggregated_weights.json")[0] == (404 if rnd == 1 else 200)  # nothing runs early
+            upload("/uploadEncWeightsC2", tmp_path / "enc_c2.json")                                           # -> the round
+            st, agg2 = req("GET", "/download/client_2/aggregated_weights.json")
+            st1, agg1 = req("GET", "/download/client_1/c2_domainChange_c1.json")
+            assert st == 200 and st1 == 200 and len(agg2) == 28368755 and len(agg1) == 28368755
+            # identical to what the stdin server / the three tools produce for the same inputs
+            assert agg2 == open(tmp_path / "sv_agg.json", "rb").read()
+            assert agg1 == open(tmp_path / "sv_agg_to_c1.json", "rb").read()
+        assert req("POST", "/shutdown")[0] == 200
+        out = hp.stdout.read()
+        assert "round 2: OK clients=2 cts=27" in out, out[-2000:]
+        assert out.count("LOAD_REKEY") == 0 and out.count("OK rekey") == 2  # two keys, parsed once each
+    finally:
+        hp.kill()
