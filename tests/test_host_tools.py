@@ -461,3 +461,16 @@ def test_resident_server_three_clients_two_rounds(tools, tmp_path, ccjson_text):
         assert out.count("LOAD_REKEY") == 0 and out.count("OK rekey") == 2  # two keys, parsed once each
     finally:
         hp.kill()
+
+
+@pytest.mark.gpu
+def test_cpp_host_aggregates_over_all_gpus_through_the_c_abi(tools):
+    """host/multi_gpu_selftest: a plain C++ process (no Python, no torch), one thread per GPU, clients sharded round-robin,
+    ppq_reencrypt_aggregate_host_ranks on every rank (local ppq_agg_* + ONE ncclReduce + mod q on the root) -- the root's
+    aggregate must equal the single-GPU aggregate of all clients bit for bit.  Uses every GPU the box has (one rank on a
+    single-GPU box: the communicator and the reduce entry point still run)."""
+    r = run(os.path.join(tools, "multi_gpu_selftest"))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "IDENTICAL to the single-GPU aggregate" in r.stdout
+    import torch
+    assert f"{torch.cuda.device_count()} GPUs" in r.stdout
