@@ -1423,11 +1423,17 @@ static int agg_add_batch(ppq_agg* a, const ppq_rekey* const* rks, const uint64_t
         if (!launch_bconv(c->k, y, ys, dig, ds, p->up_jobs.data() + d.job_first, d.n_jobs, p->h.up_chat.data(), c->h_limbs.data(), d.ns, (int)ng, st))
             return fail(PPQ_EINVAL, "digit wider than 32 limbs");
     prof_mark(c, st, 2);
-    launch_fwd_col_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st);
-    prof_mark(c, st, 3);
     // digits canonical here: k_ip_agg puts the products of two clients into one Barrett operand (2 parts terms)
-    launch_fwd_row_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st, false);
-    prof_mark(c, st, 4);
+    static const bool use_cluster = [] { const char* e = std::getenv("PPQ_FWD_CLUSTER"); return e && e[0] == '1'; }();
+    if (use_cluster && launch_fwd_ntt_cluster(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st, false)) {
+        prof_mark(c, st, 3);  // experiment: both passes in one cluster kernel, booked under stage 3
+        prof_mark(c, st, 4);
+    } else {
+        launch_fwd_col_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st);
+        prof_mark(c, st, 3);
+        launch_fwd_row_plain(c->k, dig, ds, p->dig_ids.p, parts * M, (int)ng, st, false);
+        prof_mark(c, st, 4);
+    }
     IpArgs ia;
     ia.c1 = nullptr;
     ia.c1_gs = ct;

@@ -1281,6 +1281,106 @@ __global__ void __launch_bounds__(TILE_THREADS, 1) k_ntt_inv_tile(KCtx c, u64* _
 
 #endif  // PPQ_NTT_TILE
 
+#ifndef PPQ_FWD_CLUSTER
+#define PPQ_FWD_CLUSTER 0
+#endif
+#if PPQ_FWD_CLUSTER
+// =========================================================================================================
+// EXPERIMENT (build with -DPPQ_FWD_CLUSTER=1, run with PPQ_FWD_CLUSTER=1): forward NTT of one N = 2^16 limb in ONE kernel by an 8-CTA thread-block
+// cluster.  CTA r runs the COL pass of columns [32r, 32r+32) (two steps of k_fwd_col2's 16 columns), writes every
+// result straight into the shared memory of the CTA that owns its row (rows [32r', 32r'+32) live in CTA r':
+// st.shared::cluster through DSMEM), the cluster synchronises, and each CTA runs the ROW pass of its 32 rows out of its
+// own tile.  The limb crosses HBM once (16 N bytes) instead of twice.
+// MEASURED on B200 (profiles/r10_notes.md, profiles/r12_cluster_ncu.md): bit-exact, DRAM traffic halved (14.5 vs 27.6 GB
+// per 216 ciphertexts), but 65.8 us/ct against 37.8 for the two kernels -- 23 % warps active at 122 registers and 106 KiB
+// per CTA, barrier + long_scoreboard 37 % of the stall samples, 2x the shared-memory bank conflicts, fmaheavy 45 %.
+// Not compiled by default.
+// =========================================================================================================
+__device__ __forceinline__ u32 cluster_ctarank() {
+    u32 r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ u32 mapa_shared(u32 saddr, u32 rank) {
+    u32 r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_u64(u32 addr, u64 v) {
+    asm volatile("st.shared::cluster.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+struct ClusterRowPos {  // one 256-point row of the tile, RowPos' padding
+    static constexpr bool WARP_LOCAL = true;
+    static constexpr u32 RP = 288;
+    u32 base;
+    __device__ __forceinline__ u32 operator()(u32 p) const { return base + p + (p >> 3); }
+};
+constexpr int CL_TILE_WORDS = 32 * 288, CL_XCH_WORDS = 2 * (8 << 8);
+template <bool LAZY2>
+__global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(256, 2)
+    k_fwd_ntt_cluster(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids) {
+    extern __shared__ __align__(16) u64 cl_smem[];
+    u64* tile = cl_smem;
+    u64* sm = cl_smem + CL_TILE_WORDS;
+    constexpr int S = 8;
+    constexpr u32 n2 = 256, N = 65536, W2 = 8;
+    const u32 rank = cluster_ctarank();
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const int limb = limb_ids[y];
+    if (limb < 0) return;  // the same for all CTAs of the cluster
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    u64* p = data + g * gs + (size_t)y * N;
+    {   // COL pass of my 32 columns, results scattered to the row owners
+        const u32 w = threadIdx.x % W2, u = threadIdx.x / W2;
+        const u32 remote = mapa_shared(smem_u32(tile), u >> 2);  // rows 8u .. 8u+7 belong to CTA u / 4
+        for (u32 it = 0; it < 2; ++it) {
+            const u32 col = (rank * 16 + it * 8 + w) * 2;
+            u64 a[8], b[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const ulonglong2 v = __ldcs(reinterpret_cast<const ulonglong2*>(p + (size_t)point_of<S - 3>(u, k) * n2 + col));
+                a[k] = v.x;
+                b[k] = v.y;
+            }
+            fwd_pass_col2<S, W2, FWD_COL_IN>(a, b, sm, w, u, tw, lc.q, lc.q2 << 1, PPQ_Z(lc));
+            const u32 cpad = col + (col >> 3);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const u32 off = (8 * (u & 3) + (u32)k) * ClusterRowPos::RP + cpad;
+                st_cluster_u64(remote + off * 8u, a[k]);
+                st_cluster_u64(remote + (off + 1u) * 8u, b[k]);
+            }
+            __syncthreads();  // the exchange buffer is reused by the next step
+        }
+    }
+    cluster_sync_all();
+    {   // ROW pass of my 32 rows, one row per warp and step
+        const u32 wr = threadIdx.x / 32, u = threadIdx.x % 32;
+        for (u32 it = 0; it < 4; ++it) {
+            const u32 rl = it * 8 + wr, row = rank * 32 + rl;
+            ClusterRowPos pos{rl * ClusterRowPos::RP};
+            u64 a[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = tile[pos(point_of<S - 3>(u, k))];
+            fwd_pass<S, ClusterRowPos, FWD_ROW_IN>(a, tile, pos, u, tw, 256u + row, lc.q, lc.q2 << 1, false, PPQ_Z(lc));
+            if (lc.sh >= 28u) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a[k] = LAZY2 ? canon16_q_lazy2(a[k], lc) : canon16_q(a[k], lc);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a[k] = canon_b<16>(a[k], lc);
+            }
+            st8(p + (size_t)row * n2 + 8 * u, a);
+        }
+    }
+}
+
+#endif  // PPQ_FWD_CLUSTER
+
 // =========================================================================================================
 // pointwise kernels: grid.x covers N/2 (two residues per thread), grid.y = flattened (ct, poly, limb)
 // =========================================================================================================
@@ -1756,6 +1856,25 @@ bool launch_ip_agg(const KCtx& c, const IpArgs& a, const IpMulti& m, int n_g, cu
 #undef PPQ_IPA_P
 #undef PPQ_IPA
 }
+#if PPQ_FWD_CLUSTER
+bool launch_fwd_ntt_cluster(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g, cudaStream_t st,
+                            bool lazy2) {
+    if (c.logN != 16) return false;
+    const size_t smem = (size_t)(CL_TILE_WORDS + CL_XCH_WORDS) * sizeof(u64);
+    dim3 grid(8, n_slots, n_g);
+    count_launch();
+    if (lazy2) {
+        cudaFuncSetAttribute(k_fwd_ntt_cluster<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_fwd_ntt_cluster<true><<<grid, 256, smem, st>>>(c, data, gs, d_limb_ids);
+    } else {
+        cudaFuncSetAttribute(k_fwd_ntt_cluster<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_fwd_ntt_cluster<false><<<grid, 256, smem, st>>>(c, data, gs, d_limb_ids);
+    }
+    return true;
+}
+#else
+bool launch_fwd_ntt_cluster(const KCtx&, u64*, size_t, const int*, int, int, cudaStream_t, bool) { return false; }
+#endif
 void launch_fwd_row_moddown(const KCtx& c, const MdArgs& a, int n_g, cudaStream_t st) {
     count_launch();
     const Split sp = split_of(c.logN);

@@ -65,6 +65,10 @@ inline uint4 chat_split(u64 c) {
 // output is lazy [0,8q) and must be consumed by a forward ROW pass.
 void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g,
                           cudaStream_t st);
+// ---- EXPERIMENT: COL + ROW of an N = 2^16 limb in one kernel (8-CTA cluster, transpose through DSMEM); same result as
+// launch_fwd_col_plain followed by launch_fwd_row_plain.  Returns false for other ring sizes.
+bool launch_fwd_ntt_cluster(const KCtx& c, u64* data, size_t gs, const int* d_limb_ids, int n_slots, int n_g, cudaStream_t st,
+                            bool lazy2);
 // ---- centred SwitchModulus of ONE source limb with modulus q_src (rescale, DropLastElementAndScale) fused
 // into the forward COL pass.
 void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
