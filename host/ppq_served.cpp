@@ -39,6 +39,7 @@
 #include <unistd.h>
 
 #include <cctype>
+#include <filesystem>
 #include <fstream>
 #include <sstream>
 
@@ -385,8 +386,8 @@ struct HttpServer {
         std::string file;
         if (!dest || !multipart_file(ctype, body, file)) return http_reply(fd, 500, "", "Error: cannot open file for writing\n");
         try {
-            const size_t slash = dest->rfind('/');
-            if (slash != std::string::npos) (void)!system(("mkdir -p '" + dest->substr(0, slash) + "'").c_str());
+            const std::filesystem::path dp(*dest);
+            if (dp.has_parent_path()) std::filesystem::create_directories(dp.parent_path());
             wire::spit(*dest, file);
         } catch (const std::exception&) {
             return http_reply(fd, 500, "", "Error: cannot open file for writing\n");
