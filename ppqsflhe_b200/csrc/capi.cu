@@ -1029,9 +1029,8 @@ extern "C" int ppq_encode(ppq_ctx* c, int ell, const double* d_vals, size_t n_va
         int64_t* co = reinterpret_cast<int64_t*>(c->scratch2.p + m * N);
         u64* pt = (u64*)d_pt + s0 * ell * N;
         ckks::launch_encode_fft(c->fft, d_vals + s0 * n_vals, n_vals, std::ldexp(sf, -approx), z, co, m, st);
-        launch_small_to_res(c->k, co, pt, 1, ell, m, st);
-        if (approx > 0) launch_mult_scalar_pack(c->k, pt, pt, pk, ell, m * ell, st);
-        launch_ntt_forward(c->k, pt, ids, (int)(m * ell), st);
+        launch_small_fwd_ntt(c->k, co, pt, 1, ell, m, ids, st);
+        if (approx > 0) launch_mult_scalar_pack(c->k, pt, pt, pk, ell, m * ell, st);  // the NTT is linear: 2^a applied after it
     }
     CU(cudaGetLastError());
     return PPQ_OK;
@@ -1052,8 +1051,7 @@ extern "C" int ppq_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint6
     for (size_t s0 = 0; s0 < n; s0 += step) {
         const size_t m = std::min(step, n - s0);
         u64* vee = c->scratch2.p;  // [m][3][ell][N]
-        launch_small_to_res(c->k, small + s0 * 3 * N, vee, 3, ell, m, st);
-        launch_ntt_forward(c->k, vee, ids, (int)(m * 3 * ell), st);
+        launch_small_fwd_ntt(c->k, small + s0 * 3 * N, vee, 3, ell, m, ids, st);
         launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, (const u64*)pt + s0 * ell * N, (u64*)ct + s0 * 2 * ell * N, ell, m, st);
     }
     CU(cudaGetLastError());
@@ -1099,8 +1097,7 @@ static int small_to_eval(ppq_ctx* c, const int64_t* small, u64* out, int n_small
     const int M = c->hp.M();
     const int* ids;
     if (int rc = cyc_ids(c, M, &ids)) return rc;
-    launch_small_to_res(c->k, small, out, n_small, M, n_groups, st);
-    launch_ntt_forward(c->k, out, ids, (int)(n_groups * n_small * M), st);
+    launch_small_fwd_ntt(c->k, small, out, n_small, M, n_groups, ids, st);
     return PPQ_OK;
 }
 
@@ -1216,16 +1213,15 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     const size_t N = c->hp.N;
     auto it = c->garner.find(ell);
     if (it == c->garner.end()) {
-        // Garner constants, once per ell: ginv[i] = (q_0..q_{i-1})^-1 mod q_i ; wdbl[i] = double(q_0..q_{i-1})
-        std::vector<u64> g(2 * (size_t)ell, 0);
-        std::vector<double> wd(ell, 1.0);
+        // Garner constants, once per ell: ginv[i] = (q_0..q_{i-1})^-1 mod q_i, then the table q_k mod q_i
+        std::vector<u64> g((size_t)ell + (size_t)ell * ell, 0);
         for (int i = 1; i < ell; ++i) {
             u64 pr = 1;
             for (int k = 0; k < i; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
             g[i] = host::invmod(pr, c->hp.mod[i]);
-            wd[i] = wd[i - 1] * (double)c->hp.mod[i - 1];
         }
-        std::memcpy(g.data() + ell, wd.data(), ell * sizeof(double));
+        for (int i = 0; i < ell; ++i)
+            for (int k = 0; k < ell; ++k) g[(size_t)ell + (size_t)i * ell + k] = c->hp.mod[k] % c->hp.mod[i];
         std::unique_ptr<DevBuf<u64>> b(new DevBuf<u64>);
         CU(b->upload(g));
         it = c->garner.emplace(ell, std::move(b)).first;
@@ -1236,8 +1232,7 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     for (size_t s0 = 0; s0 < n; s0 += step) {
         const size_t m = std::min(step, n - s0);
         double2* z = reinterpret_cast<double2*>(c->scratch2.p);
-        ckks::launch_decode(c->fft, c->k, (const u64*)coeff + s0 * ell * N, ell, gin, reinterpret_cast<const double*>(gin + ell), sf, z,
-                            d_vals + s0 * (N / 2), m, st);
+        ckks::launch_decode(c->fft, c->k, (const u64*)coeff + s0 * ell * N, ell, gin, gin + ell, sf, z, d_vals + s0 * (N / 2), m, st);
     }
     CU(cudaGetLastError());
     return PPQ_OK;

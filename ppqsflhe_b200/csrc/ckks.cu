@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(FB_THREADS)
 // X > (Q-1)/2  <=>  digits compare above ((q_i-1)/2)_i from the top; then Q - X has digits q_i-1-v_i, plus 1.
 #define PPQ_MAX_DECODE_LIMBS 64
 __global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell, const u64* __restrict__ ginv,
-                                 double sf, double2* __restrict__ z) {
+                                 const u64* __restrict__ qmod, double sf, double2* __restrict__ z) {
     const u32 N = 1u << c.logN, Nh = N / 2;
     const size_t g = blockIdx.y;
     const u64* x = coeff + g * (size_t)ell * N;
@@ -191,10 +191,13 @@ __global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell,
         v[0] = x[n];
         for (int i = 1; i < ell; ++i) {
             const LimbC li = c.limbs[i];
+            const u64* qm = qmod + (size_t)i * ell;  // q_k mod q_i, k < i (host table: no reduction of constants here)
+            // Horner in mixed radix: acc = v_0 + q_0 (v_1 + q_1 (...)) mod q_i, one 128-bit multiply-add and ONE Barrett
+            // reduction per step (acc < q_i, q_k mod q_i < q_i, v_k < 2^60: the operand stays below 2^121)
             u64 acc = 0;
             for (int k = i - 1; k >= 0; --k) {
-                const u64 qk = reduce64(c.limbs[k].q, li);
-                acc = addmod(mulmod_barrett(acc, qk, li), reduce64(v[k], li), li.q);
+                unsigned __int128 t = (unsigned __int128)acc * qm[k] + v[k];
+                acc = barrett128((u64)(t >> 64), (u64)t, li);
             }
             v[i] = mulmod_barrett(submod(x[(size_t)i * N + n], acc, li.q), ginv[i], li);
         }
@@ -225,13 +228,13 @@ __global__ void k_take_real(const double2* __restrict__ z, double* __restrict__ 
         out[g * Nh + i] = z[g * Nh + i].x;
 }
 
-void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const double*,
+void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const u64* d_qmod,
                    double sf, double2* z, double* d_vals, size_t n, cudaStream_t st) {
     const unsigned N = 1u << t.logN, Nh = N / 2, m = 2 * N;
     const int bits = t.logN - 1;
     const unsigned logB = bits < FB_LOG ? (unsigned)bits : (unsigned)FB_LOG, B = 1u << logB;
     const size_t smem = (size_t)B * sizeof(double2);
-    k_crt_to_complex<<<grid_for(N, n), 256, 0, st>>>(k, coeff, ell, d_ginv, sf, z);
+    k_crt_to_complex<<<grid_for(N, n), 256, 0, st>>>(k, coeff, ell, d_ginv, d_qmod, sf, z);
     dim3 grid(Nh / B, (unsigned)n, 1);
     if (Nh <= B) {
         cudaFuncSetAttribute(k_fft_fwd_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

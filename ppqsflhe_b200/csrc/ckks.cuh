@@ -25,7 +25,8 @@ bool build_tables(int logN, Tables& t, std::string& err);
 void launch_encode_fft(const Tables& t, const double* d_vals, size_t n_vals, double sf, double2* z, int64_t* co,
                        size_t n, cudaStream_t st);
 // coeff [n][ell][N] canonical COEFF residues -> vals [n][N/2]
-void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const double* d_unused,
+// d_ginv [ell]: (q_0..q_{i-1})^-1 mod q_i; d_qmod [ell][ell]: q_k mod q_i (Garner's mixed-radix constants)
+void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const u64* d_qmod,
                    double sf, double2* z, double* d_vals, size_t n, cudaStream_t st);
 }  // namespace ckks
 

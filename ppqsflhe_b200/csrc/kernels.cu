@@ -73,6 +73,8 @@ __device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
 // =========================================================================================================
 // MODE 0: plain (src poly = blockIdx.y, limb from limb_ids; a negative limb id skips the slot)
 // MODE 2: centred SwitchModulus prologue (DropLastElementAndScale)
+// MODE 3: small signed coefficients -> residues prologue (secret / noise / encoded plaintext polynomials): the int64
+//         polynomial is read once per limb by the pass itself instead of being expanded to n_small * ell limbs first
 // SAME: the ROW size equals the COL size (n2 = 2^S), else n2 = 2^(S-1) (split_of): with n2 known at compile time the
 // eight strided accesses of a thread share one base register and use immediate offsets.
 template <int S, int W, int MODE, bool SAME>
@@ -94,6 +96,11 @@ __global__ void __launch_bounds__(W << (S - 3), S == 9 ? 1 : (MODE == 2 && S == 
         if (limb < 0) return;  // block-uniform
         in = src + g * src_gs + (size_t)y * N;
         out = dst + g * dst_gs + (size_t)y * N;
+    } else if (MODE == 3) {  // source: small signed coefficients [g][src_gs][N] (int64); slot y = s * ell + i, ell = q_src
+        const u32 ell = (u32)q_src;
+        limb = (int)(y % ell);
+        in = src + (g * src_gs + y / ell) * N;
+        out = dst + g * dst_gs + (size_t)y * N;
     } else {
         const BcJob jb = jobs[y];
         limb = jb.limb;
@@ -109,6 +116,13 @@ __global__ void __launch_bounds__(W << (S - 3), S == 9 ? 1 : (MODE == 2 && S == 
     if (MODE == 0) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] = ld_stream(in + (size_t)point_of<S - 3>(u, k) * n2 + col);
+    } else if (MODE == 3) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const long long v = reinterpret_cast<const long long*>(in)[(size_t)point_of<S - 3>(u, k) * n2 + col];
+            const u64 m = reduce64(v < 0 ? (u64)(-v) : (u64)v, lc);
+            a[k] = (v < 0 && m != 0) ? lc.q - m : m;
+        }
     } else {
         const u64 half = q_src >> 1;
         const u64 qs_mod = reduce64(q_src, lc);
@@ -1441,22 +1455,6 @@ __global__ void k_scale_key(KCtx c, const u64* in, int in_stride, u64* out, int 
     *reinterpret_cast<ulonglong2*>(out + ((size_t)j * out_stride + i) * N + n) =
         make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
 }
-// out[g][s][i][n] = small[g][s][n] mod q_i ; grid.y = g * n_small * ell + s * ell + i
-__global__ void k_small_to_res(KCtx c, const long long* __restrict__ small, u64* __restrict__ out, int n_small,
-                               int ell) {
-    const u32 N = 1u << c.logN;
-    const int i = blockIdx.y % ell;
-    const size_t sidx = blockIdx.y / ell;  // g * n_small + s
-    const LimbC lc = c.limbs[i];
-    const long long* sp = small + sidx * N;
-    u64* op = out + (size_t)blockIdx.y * N;
-    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
-        const long long v = sp[n];
-        const u64 m = reduce64(v < 0 ? (u64)(-v) : (u64)v, lc);
-        op[n] = (v < 0 && m != 0) ? lc.q - m : m;
-    }
-    (void)n_small;
-}
 // grid.y = g * ell + i
 __global__ void k_encrypt_pw(KCtx c, const u64* __restrict__ pkb, const u64* __restrict__ pka,
                              const u64* __restrict__ vee, const u64* __restrict__ pt, u64* __restrict__ ct, int ell) {
@@ -1704,6 +1702,18 @@ void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
     PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 0>(c, data, gs, data, gs, nullptr, nullptr, d_limb_ids, 0, n_slots, n_g, st)));
 }
 
+void launch_small_fwd_ntt(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_groups,
+                          const int* d_cyc_ids, cudaStream_t st) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1, ny = n_small * ell;
+    const size_t gs = (size_t)ny << c.logN;
+    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 3>(c, reinterpret_cast<const u64*>(small), (size_t)n_small, out, gs, nullptr, nullptr,
+                                                  nullptr, (u64)ell, ny, (int)n_groups, st)));
+    count_launch();
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, 1, (unsigned)(n_groups * ny)), RowGeom<S>::THREADS, 0, st>>>(
+                                c, out, 0, d_cyc_ids, 1)));
+}
+
 void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,
                        int n_jobs, int n_g, u64 q_src, cudaStream_t st) {
     const Split sp = split_of(c.logN);
@@ -1928,11 +1938,6 @@ void launch_scale_key(const KCtx& c, const u64* in, int in_stride, u64* out, int
     count_launch();
     const u32 N = 1u << c.logN;
     k_scale_key<<<dim3((N / 2 + 255) / 256, L, dnum), 256, 0, st>>>(c, in, in_stride, out, out_stride, d_pinv, d_pinv_sh);
-}
-void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
-                         cudaStream_t st) {
-    count_launch();
-    k_small_to_res<<<pw_grid(c, n_ct * n_small * ell, 1), 256, 0, st>>>(c, (const long long*)small, out, n_small, ell);
 }
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee, const u64* pt, u64* ct, int ell,
                        size_t n_ct, cudaStream_t st) {

@@ -166,9 +166,10 @@ void launch_mult_scalar_pack(const KCtx& c, const u64* in, u64* out, const FacPa
 // same over a flat list of n_polys polynomials whose limb index is (poly index % ell)
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st);
-// small signed coefficients -> residues of limb i:  out[g][y][n] = small[g][y / ell][n] mod q_{y % ell}
-void launch_small_to_res(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_ct,
-                         cudaStream_t st);
+// forward NTT of small signed polynomials on the first `ell` limbs: out[g][s][i] = NTT_i(small[g][s]), g < n_groups,
+// s < n_small (the residues are formed inside the COL pass); d_cyc_ids: limb ids 0..ell-1 repeated (>= n_groups*n_small*ell)
+void launch_small_fwd_ntt(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_groups,
+                          const int* d_cyc_ids, cudaStream_t st);
 // encrypt combine: ct[g][0][i] = pkb[i]*v + e0 + m ; ct[g][1][i] = pka[i]*v + e1   (all EVAL)
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee /*[g][3][ell][N]*/,
                        const u64* pt /*[g][ell][N]*/, u64* ct, int ell, size_t n_ct, cudaStream_t st);
