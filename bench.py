@@ -606,52 +606,77 @@ def main():
     e2e = None
     if not args.no_e2e:
         blk = n_slots * 2 * ell * N
+        pblk = n_slots * int(lib().ppq_packed_words(cc.h, ell))
         old_aff, near_cpus = bind_near_gpu(local)
         pool_n = max(1, min(len(my_clients), 4))
-        pool = [torch.empty(blk, dtype=torch.int64).pin_memory() for _ in range(pool_n)]
-        for i, p in enumerate(pool):
-            if i < len(cts):
-                p.copy_(cts[i].data.view(-1))
-        h_acc = torch.empty(blk, dtype=torch.int64).pin_memory()
-        h2d = len(my_clients) * blk * 8
-        d2h = blk * 8 if rank == 0 else 0
         nk = len(keys)
         rks = (vp * max(1, nk))(*[k.h for k in keys])
-        ptrs = (vp * max(1, nk))(*[pool[i % pool_n].data_ptr() for i in range(nk)])
-        if world == 1:
-            def e2e_step():
-                check(lib().ppq_reencrypt_aggregate_host(cc.h, rks, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
-        else:
-            def e2e_step():
-                check(lib().ppq_reencrypt_aggregate_host_ranks(cc.h, comm.h, 0, rks, ell, ptrs, nk, n_slots,
-                                                               vp(h_acc.data_ptr())))
 
-        def copy_step():
-            check(lib().ppq_copy_ceiling_host(cc.h, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
+        def e2e_leg(packed):
+            """one format of the host buffers: [n_slots][2][ell][N] u64, or packed residues (bitlen(q_i) bits each)"""
+            words = pblk if packed else blk
+            pool = [torch.empty(words, dtype=torch.int64).pin_memory() for _ in range(pool_n)]
+            for i, p in enumerate(pool):
+                if i < len(cts):
+                    if packed:  # the deserialiser's output format; made here by the device packer
+                        d_pk = torch.empty(words, dtype=torch.int64, device=dev)
+                        check(lib().ppq_pack(cc.h, ell, vp(cts[i].data.data_ptr()), vp(d_pk.data_ptr()), n_slots, None))
+                        torch.cuda.synchronize()
+                        p.copy_(d_pk)
+                        del d_pk
+                    else:
+                        p.copy_(cts[i].data.view(-1))
+            h_acc = torch.empty(words, dtype=torch.int64).pin_memory()
+            h2d = len(my_clients) * words * 8
+            d2h = words * 8 if rank == 0 else 0
+            ptrs = (vp * max(1, nk))(*[pool[i % pool_n].data_ptr() for i in range(nk)])
+            sfx = "_packed" if packed else ""
+            f_one = getattr(lib(), "ppq_reencrypt_aggregate_host" + sfx)
+            f_ranks = getattr(lib(), "ppq_reencrypt_aggregate_host" + sfx + "_ranks")
+            f_copy = getattr(lib(), "ppq_copy_ceiling_host" + sfx)
+            if world == 1:
+                def e2e_step():
+                    check(f_one(cc.h, rks, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
+            else:
+                def e2e_step():
+                    check(f_ranks(cc.h, comm.h, 0, rks, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
 
-        for _ in range(args.warmup):
-            e2e_step()
-        copy_step()
-        c_ms = timed(copy_step, args.steps)           # the copy-only leg runs before AND after the e2e leg; the faster
-        e_ms = timed(e2e_step, args.steps)            # of the two is the ceiling (host-side contention varies run to run)
-        c_ms = min(c_ms, timed(copy_step, args.steps))
-        tot = torch.tensor([float(h2d), float(d2h)], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(tot)
-        bytes_step = float(tot[0].item() + tot[1].item())
-        e_val = n_ct_step / (e_ms / args.steps * 1e-3)
-        c_val = n_ct_step / (c_ms / args.steps * 1e-3)
-        e2e = {"value": e_val, "unit": UNIT, "h2d_bytes_per_step": int(tot[0].item()),
-               "d2h_bytes_per_step": int(tot[1].item()), "ms_per_step": e_ms / args.steps,
-               "api": "ppq_reencrypt_aggregate_host (C ABI, pinned host buffers)" if world == 1 else
-                      "ppq_reencrypt_aggregate_host_ranks (C ABI, pinned host buffers, ends in ppq_reduce_across_ranks)",
-               "note": f"every client's {blk * 8 >> 20} MiB upload is copied each step from a pool of {pool_n} pinned buffers",
-               "host_cpus_near_gpu": near_cpus,
-               "copy_gbs": bytes_step / (e_ms / args.steps * 1e-3) / 1e9,
-               "h2d_ceiling_gbs": bytes_step / (c_ms / args.steps * 1e-3) / 1e9,
-               "ceiling_value": c_val, "frac_of_copy_ceiling": e_val / c_val,
-               "ceiling_note": "ppq_copy_ceiling_host: the same pinned pools, streams and copies with no kernel launched"}
-        del pool, h_acc
+            def copy_step():
+                check(f_copy(cc.h, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
+
+            for _ in range(args.warmup):
+                e2e_step()
+            copy_step()
+            c_ms = timed(copy_step, args.steps)       # the copy-only leg runs before AND after the e2e leg; the faster
+            e_ms = timed(e2e_step, args.steps)        # of the two is the ceiling (host-side contention varies run to run)
+            c_ms = min(c_ms, timed(copy_step, args.steps))
+            tot = torch.tensor([float(h2d), float(d2h)], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(tot)
+            bytes_step = float(tot[0].item() + tot[1].item())
+            e_val = n_ct_step / (e_ms / args.steps * 1e-3)
+            c_val = n_ct_step / (c_ms / args.steps * 1e-3)
+            name = "ppq_reencrypt_aggregate_host" + sfx
+            return {"value": e_val, "unit": UNIT, "h2d_bytes_per_step": int(tot[0].item()),
+                    "d2h_bytes_per_step": int(tot[1].item()), "ms_per_step": e_ms / args.steps,
+                    "api": f"{name} (C ABI, pinned host buffers)" if world == 1 else
+                           f"{name}_ranks (C ABI, pinned host buffers, ends in ppq_reduce_across_ranks)",
+                    "host_format": ("packed residues: bitlen(q_i) bits per residue of limb i, unpacked on the device "
+                                    "(include/ppq_b200.h)") if packed else "[n_slots][2][ell][N] u64",
+                    "note": f"every client's {words * 8 >> 20} MiB upload is copied each step from a pool of {pool_n} "
+                            "pinned buffers",
+                    "host_cpus_near_gpu": near_cpus,
+                    "copy_gbs": bytes_step / (e_ms / args.steps * 1e-3) / 1e9,
+                    "h2d_ceiling_gbs": bytes_step / (c_ms / args.steps * 1e-3) / 1e9,
+                    "ceiling_value": c_val, "frac_of_copy_ceiling": e_val / c_val,
+                    "ceiling_note": "ppq_copy_ceiling_host" + sfx + ": the same pinned pools, streams and copies with no "
+                                    "kernel launched"}
+
+        # headline: packed host buffers (the path is bound by the host->device copy, and a residue of limb i carries
+        # bitlen(q_i) bits); the u64 form of the same call is reported beside it
+        e2e_u64 = e2e_leg(False)
+        e2e = e2e_leg(True)
+        e2e["u64_host_buffers"] = e2e_u64
         if old_aff is not None:
             os.sched_setaffinity(0, old_aff)  # the CPU baseline below uses every host core again
 

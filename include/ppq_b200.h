@@ -229,6 +229,30 @@ int ppq_reencrypt_aggregate_host_ranks(ppq_ctx*, ppq_comm*, int root, const ppq_
 int ppq_copy_ceiling_host(ppq_ctx*, int ell, const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
                           uint64_t* h_acc);
 
+/* ---- packed residues: the wire format of the *_host_packed calls.  A residue of limb i needs bitlen(q_i) bits, not 64
+ *      (C3: 1142 of 1280 bits per coefficient), and the host->device copy is what bounds the end-to-end path.  A packed
+ *      ciphertext is [2][ell] limbs; limb i = N residues of bitlen(q_i) bits each as a little-endian bit stream
+ *      (N * bitlen(q_i) / 64 words).  ppq_packed_words = u64 words of one packed ciphertext (0 on a bad argument).
+ *      The deserialiser of a cereal blob (8-byte residues, changeCipherDomain.cpp:68-72, aggregateEncryptedWeights.cpp:
+ *      18-30) writes this layout instead of [2][ell][N] u64: ppq_pack_host / ppq_unpack_host are that conversion on the
+ *      host (format only, no arithmetic); ppq_pack / ppq_unpack are the device kernels, asynchronous on `stream`. */
+size_t ppq_packed_words(const ppq_ctx*, int ell);
+int ppq_pack_host(const ppq_ctx*, int ell, const uint64_t* h_in, uint64_t* h_packed, size_t n);
+int ppq_unpack_host(const ppq_ctx*, int ell, const uint64_t* h_packed, uint64_t* h_out, size_t n);
+int ppq_pack(ppq_ctx*, int ell, const uint64_t* d_in, uint64_t* d_packed, size_t n, void* stream);
+int ppq_unpack(ppq_ctx*, int ell, const uint64_t* d_packed, uint64_t* d_out, size_t n, void* stream);
+/* the host-buffer calls above with packed host buffers on both sides: h_cts[client] -> [n_slots] packed ciphertexts,
+ * h_acc -> [n_slots] packed ciphertexts.  The upload is unpacked on the device (one HBM-bound kernel per client, hidden
+ * under the next client's copy), the aggregate packed before its download; the arithmetic and the result are those of
+ * ppq_reencrypt_aggregate_host.  Residues must be canonical, as everywhere. */
+int ppq_reencrypt_aggregate_host_packed(ppq_ctx*, const ppq_rekey* const* rekeys, int ell, const uint64_t* const* h_cts,
+                                        size_t n_clients, size_t n_slots, uint64_t* h_acc);
+int ppq_reencrypt_aggregate_host_packed_ranks(ppq_ctx*, ppq_comm*, int root, const ppq_rekey* const* rekeys, int ell,
+                                              const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                              uint64_t* h_acc);
+int ppq_copy_ceiling_host_packed(ppq_ctx*, int ell, const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                 uint64_t* h_acc);
+
 /* ---- per-stage device timing of the key-switch pipeline (CUDA events on the caller's stream).
  *      stage s < PPQ_PROFILE_STAGES: see ppq_profile_stage_name.  ms / launches: arrays of that length. */
 #define PPQ_PROFILE_STAGES 11

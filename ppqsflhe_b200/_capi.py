@@ -91,6 +91,16 @@ _SIGS = {
     "ppq_reencrypt_aggregate_host_ranks": (C.c_int, [vp, vp, C.c_int, C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_size_t,
                                                      C.c_size_t, vp]),
     "ppq_copy_ceiling_host": (C.c_int, [vp, C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
+    "ppq_packed_words": (C.c_size_t, [vp, C.c_int]),
+    "ppq_pack_host": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t]),
+    "ppq_unpack_host": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t]),
+    "ppq_pack": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, vp]),
+    "ppq_unpack": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, vp]),
+    "ppq_reencrypt_aggregate_host_packed": (C.c_int, [vp, C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t,
+                                                      vp]),
+    "ppq_reencrypt_aggregate_host_packed_ranks": (C.c_int, [vp, vp, C.c_int, C.POINTER(vp), C.c_int, C.POINTER(vp),
+                                                            C.c_size_t, C.c_size_t, vp]),
+    "ppq_copy_ceiling_host_packed": (C.c_int, [vp, C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
     "ppq_launch_count": (C.c_uint64, []),
     "ppq_profile_enable": (C.c_int, [vp, C.c_int]),
     "ppq_profile_read": (C.c_int, [vp, f64p, u64p, C.c_int]),

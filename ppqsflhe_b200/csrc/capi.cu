@@ -1655,12 +1655,105 @@ extern "C" int ppq_reduce_across_ranks(ppq_ctx* c, ppq_comm* m, int ell, uint64_
     return PPQ_OK;
 }
 
+// ------------------------------------------------------------------------------------------- packed residues
+// Wire format of the *_host_packed calls: a residue of limb i needs bitlen(q_i) bits, not 64 (C3: 1142 of 1280 bits per
+// coefficient), and the host->device copy is what bounds the end-to-end path.  Packed ciphertext = [2][ell] limbs, limb
+// i = N residues as a little-endian bit stream of bitlen(q_i) bits each (N * bitlen / 64 words, N is a multiple of 64).
+static bool pack_layout(const ppq_ctx* c, int ell, PackLay& lay) {
+    if (!c || ell < 1 || ell > c->hp.L || ell > 64) return false;
+    u32 off = 0;
+    for (int i = 0; i < ell; ++i) {
+        lay.off[i] = off;
+        off += (u32)(c->hp.N / 64) * (c->h_limbs[i].sh + 1u);
+    }
+    for (int i = ell; i < 64; ++i) lay.off[i] = 0;
+    lay.words = off;
+    return true;
+}
+extern "C" size_t ppq_packed_words(const ppq_ctx* c, int ell) {
+    PackLay lay;
+    return pack_layout(c, ell, lay) ? (size_t)2 * lay.words : 0;
+}
+extern "C" int ppq_pack_host(const ppq_ctx* c, int ell, const uint64_t* h_in, uint64_t* h_packed, size_t n) {
+    PackLay lay;
+    if (!h_in || !h_packed || !pack_layout(c, ell, lay)) return fail(PPQ_EINVAL, "ppq_pack_host: bad argument");
+    const size_t N = c->hp.N;
+    const long rows = (long)(n * 2 * (size_t)ell);
+#pragma omp parallel for schedule(static)
+    for (long y = 0; y < rows; ++y) {
+        const int i = (int)(y % ell);
+        const unsigned w = c->h_limbs[i].sh + 1u;
+        const uint64_t* src = h_in + (size_t)y * N;
+        uint64_t* dst = h_packed + (size_t)(y / ell) * lay.words + lay.off[i];
+        unsigned __int128 acc = 0;  // bits not yet written, low end first
+        unsigned have = 0;
+        for (size_t k = 0; k < N; ++k) {
+            acc |= (unsigned __int128)src[k] << have;
+            have += w;
+            if (have >= 64) {
+                *dst++ = (u64)acc;
+                acc >>= 64;
+                have -= 64;
+            }
+        }
+    }
+    return PPQ_OK;
+}
+extern "C" int ppq_unpack_host(const ppq_ctx* c, int ell, const uint64_t* h_packed, uint64_t* h_out, size_t n) {
+    PackLay lay;
+    if (!h_packed || !h_out || !pack_layout(c, ell, lay)) return fail(PPQ_EINVAL, "ppq_unpack_host: bad argument");
+    const size_t N = c->hp.N;
+    const long rows = (long)(n * 2 * (size_t)ell);
+#pragma omp parallel for schedule(static)
+    for (long y = 0; y < rows; ++y) {
+        const int i = (int)(y % ell);
+        const unsigned w = c->h_limbs[i].sh + 1u;
+        const u64 mask = w == 64 ? ~0ull : ((1ull << w) - 1ull);
+        const uint64_t* src = h_packed + (size_t)(y / ell) * lay.words + lay.off[i];
+        uint64_t* dst = h_out + (size_t)y * N;
+        unsigned __int128 acc = 0;
+        unsigned have = 0;
+        for (size_t k = 0; k < N; ++k) {
+            if (have < w) {
+                acc |= (unsigned __int128)(*src++) << have;
+                have += 64;
+            }
+            dst[k] = (u64)acc & mask;
+            acc >>= w;
+            have -= w;
+        }
+    }
+    return PPQ_OK;
+}
+static int pack_dev(ppq_ctx* c, int ell, const uint64_t* in, uint64_t* out, size_t n, void* stream, bool unpack,
+                    const char* who) {
+    PackLay lay;
+    if (!in || !out || !pack_layout(c, ell, lay)) return fail(PPQ_EINVAL, std::string(who) + ": bad argument");
+    if (n == 0) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    const size_t ct = (size_t)2 * ell * c->hp.N, pk = (size_t)2 * lay.words, step = rows_chunk(2 * ell);
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t rows = std::min(step, n - s0) * 2 * ell;
+        if (unpack) launch_unpack(c->k, (const u64*)in + s0 * pk, (u64*)out + s0 * ct, lay, ell, rows, (cudaStream_t)stream);
+        else launch_pack(c->k, (const u64*)in + s0 * ct, (u64*)out + s0 * pk, lay, ell, rows, (cudaStream_t)stream);
+    }
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+extern "C" int ppq_unpack(ppq_ctx* c, int ell, const uint64_t* d_packed, uint64_t* d_out, size_t n, void* stream) {
+    return pack_dev(c, ell, d_packed, d_out, n, stream, true, "ppq_unpack");
+}
+extern "C" int ppq_pack(ppq_ctx* c, int ell, const uint64_t* d_in, uint64_t* d_packed, size_t n, void* stream) {
+    return pack_dev(c, ell, d_in, d_packed, n, stream, false, "ppq_pack");
+}
+
 // ------------------------------------------------------------------------------------------- host-buffer path
 // Persistent per-context resources of the host-buffer calls: two device upload buffers, the device aggregate, two
 // streams and the hand-over events.  Created on first use, reused while the shape fits, freed with the context:
 // nothing is allocated inside a steady-state call and no early return can leak.
 struct ppq_ctx::HostPath {
     DevBuf<u64> in[2], out;
+    DevBuf<u64> pk_in[2], pk_out;  // packed staging of the *_host_packed calls
     cudaStream_t sc = nullptr, sx = nullptr;
     cudaEvent_t up[2] = {}, done[2] = {};
     bool made = false;
@@ -1682,7 +1775,7 @@ ppq_ctx::~ppq_ctx() {
     for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
 }
 
-static int hostpath_get(ppq_ctx* c, int ell, size_t n_slots, ppq_ctx::HostPath** out) {
+static int hostpath_get(ppq_ctx* c, int ell, size_t n_slots, size_t packed_blk, ppq_ctx::HostPath** out) {
     if (!c->hostpath) c->hostpath = new ppq_ctx::HostPath;
     ppq_ctx::HostPath* h = c->hostpath;
     if (!h->made) {
@@ -1698,6 +1791,11 @@ static int hostpath_get(ppq_ctx* c, int ell, size_t n_slots, ppq_ctx::HostPath**
     CU(h->in[0].ensure(blk));
     CU(h->in[1].ensure(blk));
     CU(h->out.ensure(blk));
+    if (packed_blk) {
+        CU(h->pk_in[0].ensure(packed_blk));
+        CU(h->pk_in[1].ensure(packed_blk));
+        CU(h->pk_out.ensure(packed_blk));
+    }
     if (h->agg && (h->agg->ell != ell || h->agg->n_slots != n_slots || h->agg->count != 0)) {
         ppq_agg_destroy(h->agg);
         h->agg = nullptr;
@@ -1709,9 +1807,10 @@ static int hostpath_get(ppq_ctx* c, int ell, size_t n_slots, ppq_ctx::HostPath**
 }
 
 // copy_only: the same uploads/downloads on the same streams without any kernel (the box's copy ceiling for e2e)
+// packed: h_cts / h_acc hold packed residues (ppq_packed_words per ciphertext); the upload is unpacked on the device
 static int aggregate_host_impl(ppq_ctx* c, ppq_comm* comm, int root, const ppq_rekey* const* rekeys, int ell,
                                const uint64_t* const* h_cts, size_t n_clients, size_t n_slots, uint64_t* h_acc,
-                               bool copy_only) {
+                               bool copy_only, bool packed = false) {
     if (!c || !h_cts || (!rekeys && !copy_only)) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null argument");
     if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: bad limb count");
     if (!n_slots) return PPQ_OK;
@@ -1722,7 +1821,10 @@ static int aggregate_host_impl(ppq_ctx* c, ppq_comm* comm, int root, const ppq_r
     if (is_root && !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host: null output");
     CU(cudaSetDevice(c->device));
     ppq_ctx::HostPath* h;
-    if (int rc = hostpath_get(c, ell, n_slots, &h)) return rc;
+    PackLay lay;
+    if (packed && !pack_layout(c, ell, lay)) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host_packed: more than 64 limbs");
+    const size_t pblk = packed ? (size_t)2 * lay.words * n_slots : 0;
+    if (int rc = hostpath_get(c, ell, n_slots, pblk, &h)) return rc;
     const size_t blk = (size_t)2 * ell * c->hp.N * n_slots;
     int rc = PPQ_OK;
     cudaError_t ce = cudaSuccess;
@@ -1731,9 +1833,12 @@ static int aggregate_host_impl(ppq_ctx* c, ppq_comm* comm, int root, const ppq_r
     for (size_t cl = 0; cl < n_clients && rc == PPQ_OK && ce == cudaSuccess; ++cl) {
         const int b = (int)(cl & 1);
         if (cl >= 2) HP(cudaStreamWaitEvent(h->sc, h->done[b], 0));
-        HP(cudaMemcpyAsync(h->in[b].p, h_cts[cl], blk * sizeof(u64), cudaMemcpyHostToDevice, h->sc));
+        if (packed) HP(cudaMemcpyAsync(h->pk_in[b].p, h_cts[cl], pblk * sizeof(u64), cudaMemcpyHostToDevice, h->sc));
+        else HP(cudaMemcpyAsync(h->in[b].p, h_cts[cl], blk * sizeof(u64), cudaMemcpyHostToDevice, h->sc));
         HP(cudaEventRecord(h->up[b], h->sc));
         HP(cudaStreamWaitEvent(h->sx, h->up[b], 0));
+        if (packed && !copy_only && rc == PPQ_OK && ce == cudaSuccess)
+            rc = ppq_unpack(c, ell, (const uint64_t*)h->pk_in[b].p, (uint64_t*)h->in[b].p, n_slots, h->sx);
         if (!copy_only && rc == PPQ_OK && ce == cudaSuccess) rc = ppq_agg_add(h->agg, rekeys[cl], (const uint64_t*)h->in[b].p, h->sx);
         HP(cudaEventRecord(h->done[b], h->sx));
     }
@@ -1742,7 +1847,13 @@ static int aggregate_host_impl(ppq_ctx* c, ppq_comm* comm, int root, const ppq_r
         else HP(cudaMemsetAsync(h->out.p, 0, blk * sizeof(u64), h->sx));  // a rank without clients contributes zero
         if (rc == PPQ_OK && comm) rc = ppq_reduce_across_ranks(c, comm, ell, (uint64_t*)h->out.p, n_slots, root, h->sx);
     }
-    if (is_root) HP(cudaMemcpyAsync(h_acc, h->out.p, blk * sizeof(u64), cudaMemcpyDeviceToHost, h->sx));
+    if (is_root && packed) {
+        if (!copy_only && rc == PPQ_OK && ce == cudaSuccess)
+            rc = ppq_pack(c, ell, (const uint64_t*)h->out.p, (uint64_t*)h->pk_out.p, n_slots, h->sx);
+        HP(cudaMemcpyAsync(h_acc, h->pk_out.p, pblk * sizeof(u64), cudaMemcpyDeviceToHost, h->sx));
+    } else if (is_root) {
+        HP(cudaMemcpyAsync(h_acc, h->out.p, blk * sizeof(u64), cudaMemcpyDeviceToHost, h->sx));
+    }
 #undef HP
     // always drain both streams: the caller's host buffers must not be in flight when this returns, error or not
     const cudaError_t e1 = cudaStreamSynchronize(h->sc), e2 = cudaStreamSynchronize(h->sx);
@@ -1773,4 +1884,21 @@ extern "C" int ppq_reencrypt_aggregate_host_ranks(ppq_ctx* c, ppq_comm* comm, in
 extern "C" int ppq_copy_ceiling_host(ppq_ctx* c, int ell, const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
                                      uint64_t* h_acc) {
     return aggregate_host_impl(c, nullptr, 0, nullptr, ell, h_cts, n_clients, n_slots, h_acc, true);
+}
+extern "C" int ppq_reencrypt_aggregate_host_packed(ppq_ctx* c, const ppq_rekey* const* rekeys, int ell,
+                                                   const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                                   uint64_t* h_acc) {
+    if (!rekeys || !h_acc) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host_packed: null argument");
+    return aggregate_host_impl(c, nullptr, 0, rekeys, ell, h_cts, n_clients, n_slots, h_acc, false, true);
+}
+extern "C" int ppq_reencrypt_aggregate_host_packed_ranks(ppq_ctx* c, ppq_comm* comm, int root,
+                                                         const ppq_rekey* const* rekeys, int ell,
+                                                         const uint64_t* const* h_cts, size_t n_clients, size_t n_slots,
+                                                         uint64_t* h_acc) {
+    if (!comm) return fail(PPQ_EINVAL, "ppq_reencrypt_aggregate_host_packed_ranks: null communicator");
+    return aggregate_host_impl(c, comm, root, rekeys, ell, h_cts, n_clients, n_slots, h_acc, false, true);
+}
+extern "C" int ppq_copy_ceiling_host_packed(ppq_ctx* c, int ell, const uint64_t* const* h_cts, size_t n_clients,
+                                            size_t n_slots, uint64_t* h_acc) {
+    return aggregate_host_impl(c, nullptr, 0, nullptr, ell, h_cts, n_clients, n_slots, h_acc, true, true);
 }

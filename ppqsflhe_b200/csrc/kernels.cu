@@ -1443,6 +1443,48 @@ __global__ void k_mult_scalar_pack(KCtx c, const u64* __restrict__ in, u64* __re
             make_ulonglong2(mul_shoup(x.x, w, ws, q), mul_shoup(x.y, w, ws, q));
     }
 }
+// ---- packed residues (the host<->device wire format of the ppq_*_host_packed calls): limb i of a polynomial is a
+// little-endian bit stream of N residues of bitlen(q_i) bits each, N*bitlen(q_i)/64 words; polynomial row y of the
+// batch starts at word y/ell * lay.words + lay.off[y % ell].  grid (N/512, rows)
+__global__ void k_unpack(KCtx c, const u64* __restrict__ in, u64* __restrict__ out, const __grid_constant__ PackLay lay, int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const u32 w = c.limbs[i].sh + 1u;
+    const u64 mask = w == 64u ? ~0ull : ((1ull << w) - 1ull);
+    const u64* src = in + (size_t)(blockIdx.y / ell) * lay.words + lay.off[i];
+    u64* dst = out + (size_t)blockIdx.y * N;
+    const u32 last = (N >> 6) * w - 1u;  // last word of the limb
+    for (u32 n = (blockIdx.x * blockDim.x + threadIdx.x) * 2; n < N; n += gridDim.x * blockDim.x * 2) {
+        u64 r[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const u32 bit = (n + k) * w, wi = bit >> 6, sh = bit & 63u;
+            const u64 lo = src[wi];
+            const u64 hi = src[wi < last ? wi + 1u : wi];
+            r[k] = (sh ? (lo >> sh) | (hi << (64u - sh)) : lo) & mask;
+        }
+        *reinterpret_cast<ulonglong2*>(dst + n) = make_ulonglong2(r[0], r[1]);
+    }
+}
+// one thread per packed word: the residues that overlap bits [64m, 64m + 64) of the limb's stream.  grid (ceil, rows)
+__global__ void k_pack(KCtx c, const u64* __restrict__ in, u64* __restrict__ out, const __grid_constant__ PackLay lay, int ell) {
+    const u32 N = 1u << c.logN;
+    const int i = blockIdx.y % ell;
+    const u32 w = c.limbs[i].sh + 1u;
+    const u32 nw = (N >> 6) * w;
+    const u64* src = in + (size_t)blockIdx.y * N;
+    u64* dst = out + (size_t)(blockIdx.y / ell) * lay.words + lay.off[i];
+    for (u32 m = blockIdx.x * blockDim.x + threadIdx.x; m < nw; m += gridDim.x * blockDim.x) {
+        const u64 b0 = (u64)m << 6;
+        u32 k = (u32)(b0 / w);
+        u64 acc = 0;
+        for (u64 bit = (u64)k * w; bit < b0 + 64u && k < N; bit += w, ++k) {
+            const u64 v = src[k];
+            acc |= bit >= b0 ? v << (bit - b0) : v >> (b0 - bit);
+        }
+        dst[m] = acc;
+    }
+}
 // out[(j*out_stride + i)*N + n] = in[(j*in_stride + i)*N + n] * f[i] mod q_i ; grid (N/512, L, dnum)
 __global__ void k_scale_key(KCtx c, const u64* in, int in_stride, u64* out, int out_stride,  // in may alias out
                             const u64* __restrict__ f, const u64* __restrict__ fs) {
@@ -1927,6 +1969,14 @@ void launch_mult_scalar(const KCtx& c, const u64* in, u64* out, const u64* d_f, 
 void launch_mult_scalar_pack(const KCtx& c, const u64* in, u64* out, const FacPack& p, int ell, size_t n_rows, cudaStream_t st) {
     count_launch();
     k_mult_scalar_pack<<<pw_grid(c, n_rows, 2), 256, 0, st>>>(c, in, out, p, ell);
+}
+void launch_unpack(const KCtx& c, const u64* in, u64* out, const PackLay& lay, int ell, size_t n_rows, cudaStream_t st) {
+    count_launch();
+    k_unpack<<<pw_grid(c, n_rows, 2), 256, 0, st>>>(c, in, out, lay, ell);
+}
+void launch_pack(const KCtx& c, const u64* in, u64* out, const PackLay& lay, int ell, size_t n_rows, cudaStream_t st) {
+    count_launch();
+    k_pack<<<pw_grid(c, n_rows, 1), 256, 0, st>>>(c, in, out, lay, ell);
 }
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st) {

@@ -163,6 +163,14 @@ struct FacPack {
     u64 f[64], fs[64];
 };
 void launch_mult_scalar_pack(const KCtx& c, const u64* in, u64* out, const FacPack& p, int ell, size_t n_rows, cudaStream_t st);
+// packed residues: limb i of a polynomial = N residues of bitlen(q_i) bits as a little-endian bit stream; row y
+// ([ct][poly][limb] flattened) of a batch starts at word (y / ell) * words + off[y % ell]
+struct PackLay {
+    u32 off[64];  // word offset of limb i inside a packed polynomial
+    u32 words;    // words of one packed polynomial (ell limbs)
+};
+void launch_unpack(const KCtx& c, const u64* in, u64* out, const PackLay& lay, int ell, size_t n_rows, cudaStream_t st);
+void launch_pack(const KCtx& c, const u64* in, u64* out, const PackLay& lay, int ell, size_t n_rows, cudaStream_t st);
 // same over a flat list of n_polys polynomials whose limb index is (poly index % ell)
 void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64* d_f, const u64* d_f_sh, int ell,
                               size_t n_polys, cudaStream_t st);

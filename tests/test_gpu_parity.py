@@ -370,6 +370,83 @@ def test_host_buffer_aggregate_entry_point():
     assert np.array_equal(out, want)
 
 
+def _pack_ref(ct, widths):
+    """packed residues in Python integers: limb i = little-endian bit stream of N residues of widths[i] bits"""
+    words = []
+    for poly in ct:
+        for i, limb in enumerate(poly):
+            w = widths[i]
+            big = 0
+            for k, r in enumerate(limb.tolist()):
+                big |= int(r) << (k * w)
+            nw = len(limb) * w // 64
+            words += [(big >> (64 * m)) & (2**64 - 1) for m in range(nw)]
+    return np.array(words, dtype=np.uint64)
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 3), ((12, 5, 3, 45), 7), ((13, 3, 2, 30), 4)])
+def test_packed_residues_round_trip(kind, ell):
+    # the wire format of the *_host_packed calls (include/ppq_b200.h): device and host packers against a Python-integer
+    # restatement, and both unpackers back to the input; extreme residues (0 and q-1) included
+    import torch
+    from ppqsflhe_b200._capi import check, lib, vp
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(101)
+    n = 3
+    ct = _rand_ct(rng, o, ell, n)
+    for i in range(ell):
+        ct[0, 0, i, :] = int(o.moduli[i]) - 1
+        ct[0, 1, i, ::2] = 0
+        ct[1, 0, i, -1] = int(o.moduli[i]) - 1
+    widths = [int(o.moduli[i]).bit_length() for i in range(ell)]
+    pw = lib().ppq_packed_words(cc.h, ell)
+    assert pw == 2 * sum(o.N * w // 64 for w in widths)
+    want = np.stack([_pack_ref(ct[g], widths) for g in range(n)])
+    hp = np.zeros((n, pw), dtype=np.uint64)
+    check(lib().ppq_pack_host(cc.h, ell, ct.ctypes.data_as(vp), hp.ctypes.data_as(vp), n))
+    assert np.array_equal(hp, want)
+    d_ct = torch.from_numpy(ct.view(np.int64)).to("cuda:0")
+    d_pk = torch.zeros((n, pw), dtype=torch.int64, device="cuda:0")
+    check(lib().ppq_pack(cc.h, ell, vp(d_ct.data_ptr()), vp(d_pk.data_ptr()), n, None))
+    torch.cuda.synchronize()
+    assert np.array_equal(d_pk.cpu().numpy().view(np.uint64), want)
+    back = np.zeros_like(ct)
+    check(lib().ppq_unpack_host(cc.h, ell, hp.ctypes.data_as(vp), back.ctypes.data_as(vp), n))
+    assert np.array_equal(back, ct)
+    d_back = torch.zeros_like(d_ct)
+    check(lib().ppq_unpack(cc.h, ell, vp(d_pk.data_ptr()), vp(d_back.data_ptr()), n, None))
+    torch.cuda.synchronize()
+    assert np.array_equal(d_back.cpu().numpy().view(np.uint64), ct)
+
+
+def test_host_buffer_aggregate_packed_entry_point():
+    from ppqsflhe_b200 import EvalKey
+    from ppqsflhe_b200._capi import check, lib, vp
+    o, cc = _cc_pair("c1")
+    rng = np.random.default_rng(18)
+    ell, n_clients, n_slots = 3, 5, 2
+    cts = np.ascontiguousarray(np.stack([_rand_ct(rng, o, ell, n_slots) for _ in range(n_clients)]))
+    keys = [_rand_key(rng, o) for _ in range(n_clients)]
+    rks = [EvalKey(cc, *k) for k in keys]
+    pw = lib().ppq_packed_words(cc.h, ell)
+    packed = np.zeros((n_clients, n_slots, pw), dtype=np.uint64)
+    for c in range(n_clients):
+        check(lib().ppq_pack_host(cc.h, ell, cts[c].ctypes.data_as(vp), packed[c].ctypes.data_as(vp), n_slots))
+    arr = (vp * n_clients)(*[r.h for r in rks])
+    ptrs = (vp * n_clients)(*[packed[c].ctypes.data for c in range(n_clients)])
+    out_p = np.zeros((n_slots, pw), dtype=np.uint64)
+    check(lib().ppq_reencrypt_aggregate_host_packed(cc.h, arr, ell, ptrs, n_clients, n_slots, out_p.ctypes.data_as(vp)))
+    out = np.zeros((n_slots, 2, ell, o.N), dtype=np.uint64)
+    check(lib().ppq_unpack_host(cc.h, ell, out_p.ctypes.data_as(vp), out.ctypes.data_as(vp), n_slots))
+    want = o.reencrypt_accumulate_batch(ell, cts, [k[0] for k in keys], [k[1] for k in keys])
+    assert np.array_equal(out, want)
+    # the copy-only leg moves the same bytes and must leave the library usable
+    check(lib().ppq_copy_ceiling_host_packed(cc.h, ell, ptrs, n_clients, n_slots, out_p.ctypes.data_as(vp)))
+    check(lib().ppq_reencrypt_aggregate_host_packed(cc.h, arr, ell, ptrs, n_clients, n_slots, out_p.ctypes.data_as(vp)))
+    check(lib().ppq_unpack_host(cc.h, ell, out_p.ctypes.data_as(vp), out.ctypes.data_as(vp), n_slots))
+    assert np.array_equal(out, want)
+
+
 def test_eval_add_and_finalize_bit_exact():
     from ppqsflhe_b200 import CiphertextBatch, CtMeta, to_device_u64
     o, cc = _cc_pair("c1")
