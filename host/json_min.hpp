@@ -148,7 +148,12 @@ class Parser {
         std::string out;
         // fast path: base64 payloads are megabytes without escapes
         const char* s = p_;
-        while (p_ < e_ && *p_ != '"' && *p_ != '\\') ++p_;
+        {
+            const char* q = static_cast<const char*>(std::memchr(p_, '"', (size_t)(e_ - p_)));
+            if (!q) fail("unterminated string");
+            const char* b = static_cast<const char*>(std::memchr(p_, '\\', (size_t)(q - p_)));
+            p_ = b ? b : q;
+        }
         out.assign(s, p_);
         while (p_ < e_ && *p_ != '"') {
             if (*p_ == '\\') {
@@ -219,6 +224,27 @@ inline Ptr parse(const std::string& text) { return Parser(text.data(), text.size
 
 inline void escape_to(std::string& out, const std::string& s) {
     out += '"';
+    {   // fast path: nothing to escape (base64 payloads are megabytes of plain characters)
+        // eight bytes per step: a byte is < 0x20, '"' or '\\' iff the matching "has zero byte" test fires
+        const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+        auto has_zero = [&](uint64_t v) { return ((v - ones) & ~v & highs) != 0; };
+        bool plain = true;
+        size_t i = 0;
+        for (; plain && i + 8 <= s.size(); i += 8) {
+            uint64_t w;
+            std::memcpy(&w, s.data() + i, 8);
+            plain = !(has_zero(w & 0xe0e0e0e0e0e0e0e0ull) || has_zero(w ^ (ones * 0x22)) || has_zero(w ^ (ones * 0x5c)));
+        }
+        for (; plain && i < s.size(); ++i) {
+            const unsigned char c = (unsigned char)s[i];
+            plain = c >= 0x20 && c != '"' && c != '\\';
+        }
+        if (plain) {
+            out += s;
+            out += '"';
+            return;
+        }
+    }
     for (unsigned char c : s) {
         switch (c) {
             case '"': out += "\\\""; break;

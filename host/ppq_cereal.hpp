@@ -182,9 +182,18 @@ inline void mark_context_versions(Versions& vs) {  // types whose version the em
         vs.seen.insert(t);
 }
 
-inline std::string encode(const Context& cx, const Meta& m, uint32_t ell, const uint64_t* data) {
+// the archive is written into `out` (cleared first; its capacity is reused, which matters when blobs are coded from
+// many threads: fresh megabyte allocations fault their pages in under one lock)
+inline void encode_to(std::string& out, const Context& cx, const Meta& m, uint32_t ell, const uint64_t* data) {
     if (ell == 0 || ell > cx.moduli.size()) throw std::runtime_error("cereal encode: bad limb count");
     W w;
+    w.o.swap(out);
+    w.o.clear();
+    struct Back {  // hand the buffer back on every exit
+        std::string& a;
+        std::string& b;
+        ~Back() { a.swap(b); }
+    } back{out, w.o};
     const uint32_t N = cx.N;
     w.o.reserve(2048 + (size_t)2 * ell * ((size_t)N * 8 + 96));
     Versions vs;
@@ -262,7 +271,11 @@ inline std::string encode(const Context& cx, const Meta& m, uint32_t ell, const 
     w.put<uint32_t>(m.slots);
     w.put<uint32_t>(MSB | next_id++);       // "m": shared_ptr<map<string, shared_ptr<Metadata>>>, empty
     w.put<uint64_t>(0);
-    return w.o;
+}
+inline std::string encode(const Context& cx, const Meta& m, uint32_t ell, const uint64_t* data) {
+    std::string out;
+    encode_to(out, cx, m, ell, data);
+    return out;
 }
 
 inline bool looks_like_cereal(const unsigned char* p, size_t n) {
@@ -273,7 +286,8 @@ inline bool looks_like_cereal(const unsigned char* p, size_t n) {
     return a == MSB2 && b == (MSB | 1u);
 }
 
-inline Ct decode(const Context& cx, const unsigned char* raw, size_t n) {
+// dst != nullptr: the residues go to dst ([2][ell][N], at most dst_cap words; more is an error) and Ct::data stays empty
+inline Ct decode(const Context& cx, const unsigned char* raw, size_t n, uint64_t* dst = nullptr, size_t dst_cap = 0) {
     R r{raw, raw + n};
     if (r.get<uint8_t>() != 1) throw std::runtime_error("cereal blob: big-endian archives are not supported");
     if (r.get<uint32_t>() != MSB2 || r.get<uint32_t>() != (MSB | 1u)) throw std::runtime_error("cereal blob: not a Ciphertext archive");
@@ -297,7 +311,12 @@ inline Ct decode(const Context& cx, const unsigned char* raw, size_t n) {
         if (poly == 0) {
             c.ell = (uint32_t)ell;
             c.moduli.resize(ell);
-            c.data.resize((size_t)2 * ell * c.N);
+            if (dst) {
+                if ((size_t)2 * ell * c.N > dst_cap) throw std::runtime_error("cereal blob: more limbs than the batch it belongs to");
+            } else {
+                c.data.resize((size_t)2 * ell * c.N);
+                dst = c.data.data();
+            }
         } else if (ell != c.ell) {
             throw std::runtime_error("cereal blob: polynomials differ in limb count");
         }
@@ -326,7 +345,7 @@ inline Ct decode(const Context& cx, const unsigned char* raw, size_t n) {
             const uint64_t len = r.get<uint64_t>();
             if (len != c.N) throw std::runtime_error("cereal blob: limb length is not the ring dimension");
             if ((uint64_t)(r.e - r.p) < len * 8) throw std::runtime_error("cereal blob truncated");
-            std::memcpy(c.data.data() + ((size_t)poly * c.ell + i) * c.N, r.p, (size_t)len * 8);
+            std::memcpy(dst + ((size_t)poly * c.ell + i) * c.N, r.p, (size_t)len * 8);
             r.p += len * 8;
             const uint64_t q = r.get<uint64_t>();
             if (q != cx.moduli[i]) throw std::runtime_error("cereal blob: limb modulus does not match CC.json's basis");

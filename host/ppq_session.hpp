@@ -120,7 +120,58 @@ struct Batch {
 };
 // decode all blobs, grouped by limb count (one group in every file the reference flow produces)
 inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<BlobRef>& refs) {
-    // base64 + blob decoding is the host-side cost of a file (a 38 MB container holds 27 blobs): one blob per thread
+    // base64 + blob decoding is the host-side cost of a file (a 38 MB container holds 27 blobs): one blob per thread,
+    // residues written straight into the batch.  Blobs of equal text length have equal limb counts, so the first blob of
+    // each length is decoded alone to learn the shape, the batches are allocated (and touched) once by this thread, and
+    // the parallel loop allocates nothing; a blob that turns out to have another shape sends the file down the
+    // general path below.
+    std::map<size_t, uint32_t> ell_of_len;
+    std::vector<wire::CtMeta> metas(refs.size());
+    std::vector<uint32_t> ells(refs.size(), 0);
+    std::map<uint32_t, Batch> groups;
+    bool fast = true;
+    try {
+        for (size_t i = 0; i < refs.size(); ++i) {
+            const size_t len = refs[i].slot->size();
+            if (!ell_of_len.count(len)) {
+                uint64_t probe_cap = (size_t)2 * s.L * s.N;
+                std::vector<uint64_t> probe(probe_cap);
+                ell_of_len[len] = s.codec.decode(*refs[i].slot, probe.data(), probe_cap).ell;
+            }
+            ells[i] = ell_of_len[len];
+            Batch& b = groups[ells[i]];
+            b.ell = ells[i];
+            b.index.push_back(i);
+        }
+    } catch (const std::exception&) {
+        fast = false;  // the general path reports the error with its own message
+    }
+    if (fast) {
+        std::vector<size_t> pos(refs.size());
+        for (auto& kv : groups) {
+            Batch& b = kv.second;
+            b.data.resize(b.n() * (size_t)2 * b.ell * s.N);
+            b.meta.resize(b.n());
+            for (size_t k = 0; k < b.n(); ++k) pos[b.index[k]] = k;
+        }
+        int bad = 0;
+#pragma omp parallel for schedule(dynamic) reduction(+ : bad)
+        for (size_t i = 0; i < refs.size(); ++i) {
+            try {
+                Batch& b = groups[ells[i]];
+                const size_t ct = (size_t)2 * b.ell * s.N;
+                wire::Ct c = s.codec.decode(*refs[i].slot, b.data.data() + pos[i] * ct, ct);
+                bool ok = c.ell == b.ell && c.N == s.N;
+                for (uint32_t k = 0; ok && k < c.ell; ++k) ok = c.moduli[k] == s.moduli[k];
+                if (!ok) ++bad;
+                b.meta[pos[i]] = std::move(c.meta);
+            } catch (const std::exception&) {
+                ++bad;
+            }
+        }
+        if (!bad) return groups;
+    }
+    groups.clear();
     std::vector<wire::Ct> cts(refs.size());
     std::vector<std::string> errs(refs.size());
 #pragma omp parallel for schedule(dynamic)
@@ -131,7 +182,6 @@ inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<
             errs[i] = e.what()[0] ? e.what() : "decode error";
         }
     }
-    std::map<uint32_t, Batch> groups;
     for (size_t i = 0; i < refs.size(); ++i) {
         if (!errs[i].empty()) throw std::runtime_error(errs[i]);
         wire::Ct& c = cts[i];
@@ -157,8 +207,9 @@ inline void encode_back(const Session& s, const Batch& b, uint32_t ell_out, cons
                         const std::vector<uint64_t>& data, const std::vector<BlobRef>& refs) {
     const size_t ct = (size_t)2 * ell_out * s.N;
     s.codec.warn_once();
+    // each new blob overwrites the text of the blob it replaces (same or shorter), so nothing is allocated in the loop
 #pragma omp parallel for schedule(dynamic)
-    for (size_t k = 0; k < b.n(); ++k) *refs[b.index[k]].slot = s.codec.encode(meta[k], ell_out, data.data() + k * ct);
+    for (size_t k = 0; k < b.n(); ++k) s.codec.encode_to(*refs[b.index[k]].slot, meta[k], ell_out, data.data() + k * ct);
 }
 
 // CryptoObject::keyTag of a new key pair: 32 hex digits (OpenFHE's GenerateUniqueKeyID writes 128 random bits this way)

@@ -24,6 +24,9 @@
 #include <stdexcept>
 #include <string>
 #include <vector>
+#if defined(__x86_64__) && defined(__GNUC__)
+#include <immintrin.h>
+#endif
 
 #include "json_min.hpp"
 #include "ppq_cereal.hpp"
@@ -31,70 +34,201 @@
 namespace wire {
 
 // ------------------------------------------------------------------------------------------------ files
+// whole-file reads and writes with one read()/write() loop: a container is tens of megabytes and an iostream copy of it
+// costs as much as decoding it
 inline std::string slurp(const std::string& path) {
-    std::ifstream f(path, std::ios::binary);
-    if (!f.is_open()) throw std::runtime_error("cannot open " + path);
-    std::ostringstream ss;
-    ss << f.rdbuf();
-    return ss.str();
+    std::FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("cannot open " + path);
+    std::string out;
+    if (std::fseek(f, 0, SEEK_END) == 0) {
+        const long n = std::ftell(f);
+        if (n > 0) out.resize((size_t)n);
+        std::rewind(f);
+    }
+    size_t got = 0;
+    if (!out.empty()) got = std::fread(&out[0], 1, out.size(), f);
+    out.resize(got);
+    char buf[65536];  // not seekable (a pipe) or still growing: take the rest
+    for (size_t n; (n = std::fread(buf, 1, sizeof buf, f)) > 0;) out.append(buf, n);
+    const bool bad = std::ferror(f) != 0;
+    std::fclose(f);
+    if (bad) throw std::runtime_error("read error on " + path);
+    return out;
 }
 inline void spit(const std::string& path, const std::string& data) {
-    std::ofstream f(path, std::ios::binary);
-    if (!f.is_open()) throw std::runtime_error("cannot write " + path);
-    f.write(data.data(), (std::streamsize)data.size());
-    if (!f.good()) throw std::runtime_error("short write to " + path);
+    std::FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    const size_t put = std::fwrite(data.data(), 1, data.size(), f);
+    const bool bad = put != data.size() || std::fclose(f) != 0;
+    if (bad) throw std::runtime_error("short write to " + path);
 }
 
 // ------------------------------------------------------------------------------------------------ base64
-inline std::string base64_encode(const unsigned char* p, size_t n) {
-    static const char T[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
-    std::string out;
+// standard alphabet, '=' padding, no line breaks on output (lib/base64_utils.h:10-49: BIO_FLAGS_BASE64_NO_NL); line
+// breaks are tolerated on input.  Three bytes per step through a 4096-entry pair table / four characters per step
+// through a 256-entry table: a blob is ~1.4 MB of text and a round decodes and encodes hundreds of them.
+namespace b64detail {
+struct Tables {
+    char pair[4096][2];  // 12 bits -> two characters
+    int8_t dec[256];     // character -> 6 bits, -1 invalid
+    Tables() {
+        static const char T[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+        for (int i = 0; i < 4096; ++i) {
+            pair[i][0] = T[i >> 6];
+            pair[i][1] = T[i & 63];
+        }
+        std::memset(dec, -1, sizeof dec);
+        for (int i = 0; i < 64; ++i) dec[(unsigned char)T[i]] = (int8_t)i;
+    }
+};
+inline const Tables& tables() {
+    static const Tables t;  // initialised once, thread-safe (blobs are coded from OpenMP loops)
+    return t;
+}
+#if defined(__x86_64__) && defined(__GNUC__)
+#define PPQ_B64_AVX2 1
+// 32 characters -> 24 bytes / 24 bytes -> 32 characters per step with byte shuffles (the published vector algorithm of
+// Mula & Lemire, "Faster Base64 Encoding and Decoding Using AVX2 Instructions"): classify each character by its two
+// nibbles (invalid ones stop the loop and are left to the scalar code), add the per-range offset, then pack 4 x 6 bits
+// into 3 bytes with two multiply-adds.  Returns the number of characters / bytes consumed.
+__attribute__((target("avx2"))) inline size_t decode_avx2(const unsigned char* p, size_t n, unsigned char* o) {
+    const __m256i lut_lo = _mm256_setr_epi8(0x15, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x13, 0x1A, 0x1B, 0x1B,
+                                            0x1B, 0x1A, 0x15, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x11, 0x13, 0x1A,
+                                            0x1B, 0x1B, 0x1B, 0x1A);
+    const __m256i lut_hi = _mm256_setr_epi8(0x10, 0x10, 0x01, 0x02, 0x04, 0x08, 0x04, 0x08, 0x10, 0x10, 0x10, 0x10, 0x10, 0x10,
+                                            0x10, 0x10, 0x10, 0x10, 0x01, 0x02, 0x04, 0x08, 0x04, 0x08, 0x10, 0x10, 0x10, 0x10,
+                                            0x10, 0x10, 0x10, 0x10);
+    const __m256i lut_roll = _mm256_setr_epi8(0, 16, 19, 4, -65, -65, -71, -71, 0, 0, 0, 0, 0, 0, 0, 0, 0, 16, 19, 4, -65, -65,
+                                              -71, -71, 0, 0, 0, 0, 0, 0, 0, 0);
+    const __m256i mask_2f = _mm256_set1_epi8(0x2f);
+    const __m256i pack = _mm256_setr_epi8(2, 1, 0, 6, 5, 4, 10, 9, 8, 14, 13, 12, -1, -1, -1, -1, 2, 1, 0, 6, 5, 4, 10, 9, 8, 14,
+                                          13, 12, -1, -1, -1, -1);
+    const __m256i lanes = _mm256_setr_epi32(0, 1, 2, 4, 5, 6, -1, -1);
+    size_t i = 0;
+    // the 32-byte store writes 8 bytes past the 24 it produces: stop while 45 characters (>= 33 output bytes) remain
+    for (; i + 45 <= n; i += 32, o += 24) {
+        __m256i str = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(p + i));
+        const __m256i hi_nib = _mm256_and_si256(_mm256_srli_epi32(str, 4), mask_2f);
+        const __m256i lo_nib = _mm256_and_si256(str, mask_2f);
+        const __m256i hi = _mm256_shuffle_epi8(lut_hi, hi_nib);
+        const __m256i lo = _mm256_shuffle_epi8(lut_lo, lo_nib);
+        if (!_mm256_testz_si256(lo, hi)) break;
+        const __m256i eq_2f = _mm256_cmpeq_epi8(str, mask_2f);
+        const __m256i roll = _mm256_shuffle_epi8(lut_roll, _mm256_add_epi8(eq_2f, hi_nib));
+        str = _mm256_add_epi8(str, roll);
+        const __m256i ab_bc = _mm256_maddubs_epi16(str, _mm256_set1_epi32(0x01400140));
+        __m256i out = _mm256_madd_epi16(ab_bc, _mm256_set1_epi32(0x00011000));
+        out = _mm256_shuffle_epi8(out, pack);
+        out = _mm256_permutevar8x32_epi32(out, lanes);
+        _mm256_storeu_si256(reinterpret_cast<__m256i*>(o), out);
+    }
+    return i;
+}
+__attribute__((target("avx2"))) inline size_t encode_avx2(const unsigned char* p, size_t n, char* o) {
+    const __m256i spread = _mm256_setr_epi8(1, 0, 2, 1, 4, 3, 5, 4, 7, 6, 8, 7, 10, 9, 11, 10, 1, 0, 2, 1, 4, 3, 5, 4, 7, 6, 8, 7,
+                                            10, 9, 11, 10);
+    const __m256i lut = _mm256_setr_epi8(65, 71, -4, -4, -4, -4, -4, -4, -4, -4, -4, -4, -19, -16, 0, 0, 65, 71, -4, -4, -4, -4,
+                                         -4, -4, -4, -4, -4, -4, -19, -16, 0, 0);
+    size_t i = 0;
+    for (; i + 28 <= n; i += 24, o += 32) {  // the second 16-byte load reads bytes 12..27
+        const __m128i lo = _mm_loadu_si128(reinterpret_cast<const __m128i*>(p + i));
+        const __m128i hi = _mm_loadu_si128(reinterpret_cast<const __m128i*>(p + i + 12));
+        __m256i in = _mm256_shuffle_epi8(_mm256_set_m128i(hi, lo), spread);
+        const __m256i t0 = _mm256_and_si256(in, _mm256_set1_epi32(0x0fc0fc00));
+        const __m256i t1 = _mm256_mulhi_epu16(t0, _mm256_set1_epi32(0x04000040));
+        const __m256i t2 = _mm256_and_si256(in, _mm256_set1_epi32(0x003f03f0));
+        const __m256i t3 = _mm256_mullo_epi16(t2, _mm256_set1_epi32(0x01000010));
+        in = _mm256_or_si256(t1, t3);  // one 6-bit value per byte
+        __m256i idx = _mm256_subs_epu8(in, _mm256_set1_epi8(51));
+        idx = _mm256_sub_epi8(idx, _mm256_cmpgt_epi8(in, _mm256_set1_epi8(25)));
+        _mm256_storeu_si256(reinterpret_cast<__m256i*>(o), _mm256_add_epi8(in, _mm256_shuffle_epi8(lut, idx)));
+    }
+    return i;
+}
+inline bool have_avx2() {
+    static const bool yes = __builtin_cpu_supports("avx2");
+    return yes;
+}
+#endif
+}  // namespace b64detail
+// `out` is resized (its capacity reused) and overwritten
+inline void base64_encode_to(std::string& out, const unsigned char* p, size_t n) {
+    const b64detail::Tables& t = b64detail::tables();
     out.resize((n + 2) / 3 * 4);
-    size_t o = 0, i = 0;
-    for (; i + 2 < n; i += 3) {
+    char* o = &out[0];
+    size_t i = 0;
+#ifdef PPQ_B64_AVX2
+    if (b64detail::have_avx2()) {
+        i = b64detail::encode_avx2(p, n, o);
+        o += i / 3 * 4;
+    }
+#endif
+    for (; i + 2 < n; i += 3, o += 4) {
         const uint32_t v = ((uint32_t)p[i] << 16) | ((uint32_t)p[i + 1] << 8) | p[i + 2];
-        out[o++] = T[v >> 18];
-        out[o++] = T[(v >> 12) & 63];
-        out[o++] = T[(v >> 6) & 63];
-        out[o++] = T[v & 63];
+        std::memcpy(o, t.pair[v >> 12], 2);
+        std::memcpy(o + 2, t.pair[v & 4095], 2);
     }
     if (i < n) {
         uint32_t v = (uint32_t)p[i] << 16;
         if (i + 1 < n) v |= (uint32_t)p[i + 1] << 8;
-        out[o++] = T[v >> 18];
-        out[o++] = T[(v >> 12) & 63];
-        out[o++] = (i + 1 < n) ? T[(v >> 6) & 63] : '=';
-        out[o++] = '=';
+        std::memcpy(o, t.pair[v >> 12], 2);
+        o[2] = (i + 1 < n) ? t.pair[v & 4095][0] : '=';
+        o[3] = '=';
     }
+}
+inline std::string base64_encode(const unsigned char* p, size_t n) {
+    std::string out;
+    base64_encode_to(out, p, n);
     return out;
 }
-inline std::vector<unsigned char> base64_decode(const std::string& s) {
-    static int8_t D[256];
-    static bool init = false;
-    if (!init) {
-        std::memset(D, -1, sizeof D);
-        const char* T = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
-        for (int i = 0; i < 64; ++i) D[(unsigned char)T[i]] = (int8_t)i;
-        init = true;
-    }
-    std::vector<unsigned char> out;
-    out.reserve(s.size() / 4 * 3);
+inline void base64_decode_to(std::vector<unsigned char>& out, const std::string& s) {
+    const b64detail::Tables& t = b64detail::tables();
+    out.resize(s.size() / 4 * 3 + 3);
+    unsigned char* o = out.data();
+    const unsigned char* p = reinterpret_cast<const unsigned char*>(s.data());
+    const unsigned char* e = p + s.size();
     uint32_t acc = 0;
     int bits = 0;
-    for (unsigned char c : s) {
-        if (c == '=') break;
-        const int8_t d = D[c];
+    while (p < e) {
+#ifdef PPQ_B64_AVX2
+        if (bits == 0 && b64detail::have_avx2()) {
+            const size_t used = b64detail::decode_avx2(p, (size_t)(e - p), o);
+            p += used;
+            o += used / 4 * 3;
+        }
+#endif
+        if (bits == 0) {  // aligned: whole quads of valid characters, three bytes per step
+            while (e - p >= 4) {
+                const int a = t.dec[p[0]], b = t.dec[p[1]], c = t.dec[p[2]], d = t.dec[p[3]];
+                if ((a | b | c | d) < 0) break;  // padding, a line break or an invalid character: one careful step
+                const uint32_t v = ((uint32_t)a << 18) | ((uint32_t)b << 12) | ((uint32_t)c << 6) | (uint32_t)d;
+                o[0] = (unsigned char)(v >> 16);
+                o[1] = (unsigned char)(v >> 8);
+                o[2] = (unsigned char)v;
+                o += 3;
+                p += 4;
+            }
+            if (p >= e) break;
+        }
+        const unsigned char ch = *p++;
+        if (ch == '=') break;
+        const int8_t d = t.dec[ch];
         if (d < 0) {
-            if (c == '\n' || c == '\r') continue;
+            if (ch == '\n' || ch == '\r') continue;
             throw std::runtime_error("base64: invalid character");
         }
         acc = (acc << 6) | (uint32_t)d;
         bits += 6;
         if (bits >= 8) {
             bits -= 8;
-            out.push_back((unsigned char)(acc >> bits));
+            *o++ = (unsigned char)(acc >> bits);
         }
     }
+    out.resize((size_t)(o - out.data()));
+}
+inline std::vector<unsigned char> base64_decode(const std::string& s) {
+    std::vector<unsigned char> out;
+    base64_decode_to(out, s);
     return out;
 }
 
@@ -219,7 +353,17 @@ struct Codec {
                                  "reference's own cereal-JSON files and file sizes; byte identity is unverified against OpenFHE\n");
     }
     std::string encode(const CtMeta& m, uint32_t ell, const uint64_t* data) const {
-        if (!write_cereal) return encode_ct(m, ell, cx.N, cx.moduli.data(), data);
+        std::string out;
+        encode_to(out, m, ell, data);
+        return out;
+    }
+    // the blob replaces the contents of `out`, reusing its capacity (a re-encoded blob is never longer than the one it
+    // replaces) and a per-thread scratch archive: no megabyte allocation per blob inside the callers' OpenMP loops
+    void encode_to(std::string& out, const CtMeta& m, uint32_t ell, const uint64_t* data) const {
+        if (!write_cereal) {
+            out = encode_ct(m, ell, cx.N, cx.moduli.data(), data);
+            return;
+        }
         warn_once();
         cerealpb::Meta cm;
         cm.noise_scale_deg = m.noise_scale_deg;
@@ -230,16 +374,27 @@ struct Codec {
         cm.scaling_factor = m.scaling_factor;
         cm.scaling_factor_int = m.scaling_factor_int;
         cm.key_tag = m.key_tag.empty() ? std::string(32, '0') : m.key_tag;
-        const std::string raw = cerealpb::encode(cx, cm, ell, data);
-        return base64_encode(reinterpret_cast<const unsigned char*>(raw.data()), raw.size());
+        static thread_local std::string raw;
+        cerealpb::encode_to(raw, cx, cm, ell, data);
+        base64_encode_to(out, reinterpret_cast<const unsigned char*>(raw.data()), raw.size());
     }
-    Ct decode(const std::string& b64) const {
-        if (b64.compare(0, 8, "UFBRQ1Qx") == 0) return decode_ct(b64);  // base64 of "PPQCT1"
-        const std::vector<unsigned char> raw = base64_decode(b64);
+    // dst != nullptr: residues straight into the caller's batch ([2][ell][N], at most dst_cap words), Ct::data left empty
+    Ct decode(const std::string& b64, uint64_t* dst = nullptr, size_t dst_cap = 0) const {
+        if (b64.compare(0, 8, "UFBRQ1Qx") == 0) {  // base64 of "PPQCT1"
+            Ct o = decode_ct(b64);
+            if (dst) {
+                if (o.data.size() > dst_cap) throw std::runtime_error("ciphertext blob: more limbs than the batch it belongs to");
+                std::memcpy(dst, o.data.data(), o.data.size() * sizeof(uint64_t));
+                o.data.clear();
+            }
+            return o;
+        }
+        static thread_local std::vector<unsigned char> raw;
+        base64_decode_to(raw, b64);
         if (!cerealpb::looks_like_cereal(raw.data(), raw.size()))
             throw std::runtime_error("ciphertext blob is neither a cereal PortableBinary Ciphertext archive nor PPQCT1");
         warn_once();
-        cerealpb::Ct c = cerealpb::decode(cx, raw.data(), raw.size());
+        cerealpb::Ct c = cerealpb::decode(cx, raw.data(), raw.size(), dst, dst_cap);
         Ct o;
         o.meta.noise_scale_deg = c.meta.noise_scale_deg;
         o.meta.level = c.meta.level;
@@ -456,29 +611,59 @@ inline std::vector<Layer> read_container(const std::string& path) {
             else if (kv.first == "shape") l.shape = kv.second;
         }
         if (!l.layer || !l.shape) throw std::runtime_error(path + ": entry without layer/shape");
-        l.mean = e->at("mean").as_string();
-        l.std_dev = e->at("std_dev").as_string();
-        for (const auto& v : e->at("values").arr) l.values.push_back(v->as_string());
+        // the blobs are megabytes each: move them out of the parsed tree (it is dropped right after) instead of copying
+        auto take = [&](const jmin::Value& v) {
+            v.as_string();  // type check
+            return std::move(const_cast<jmin::Value&>(v).s);
+        };
+        l.mean = take(e->at("mean"));
+        l.std_dev = take(e->at("std_dev"));
+        for (const auto& v : e->at("values").arr) l.values.push_back(take(*v));
         out.push_back(std::move(l));
     }
     return out;
 }
 inline void write_container(const std::string& path, const std::vector<Layer>& layers) {
-    jmin::Ptr root = jmin::make(jmin::Value::Object);
-    jmin::Ptr arr = jmin::make(jmin::Value::Array);
+    // same text as dump(root, 2) of {"weights_summary": [{layer, mean, shape, std_dev, values}]} with sorted keys (the
+    // reference prints with `std::setw(2) << nlohmann::json`), written straight into one buffer: the blobs are not copied
+    // into a tree first
+    size_t need = 64;
     for (const Layer& l : layers) {
-        jmin::Ptr o = jmin::make(jmin::Value::Object);
-        jmin::set(o, "layer", l.layer);
-        jmin::set(o, "shape", l.shape);
-        jmin::set(o, "mean", jmin::make_string(l.mean));
-        jmin::set(o, "std_dev", jmin::make_string(l.std_dev));
-        jmin::Ptr vals = jmin::make(jmin::Value::Array);
-        for (const std::string& v : l.values) vals->arr.push_back(jmin::make_string(v));
-        jmin::set(o, "values", vals);
-        arr->arr.push_back(o);
+        need += 256 + l.mean.size() + l.std_dev.size();
+        for (const std::string& v : l.values) need += v.size() + 16;
     }
-    jmin::set(root, "weights_summary", arr);
-    spit(path, jmin::dump(*root, 2) + "\n");
+    std::string out;
+    out.reserve(need + need / 64);
+    out += "{\n  \"weights_summary\": [";
+    if (layers.empty()) out += "]";
+    for (size_t k = 0; k < layers.size(); ++k) {
+        const Layer& l = layers[k];
+        out += k ? ",\n    {\n" : "\n    {\n";
+        out += "      \"layer\": ";
+        jmin::dump_to(out, *l.layer, 2, 6, true);
+        out += ",\n      \"mean\": ";
+        jmin::escape_to(out, l.mean);
+        out += ",\n      \"shape\": ";
+        jmin::dump_to(out, *l.shape, 2, 6, true);
+        out += ",\n      \"std_dev\": ";
+        jmin::escape_to(out, l.std_dev);
+        out += ",\n      \"values\": ";
+        if (l.values.empty()) {
+            out += "[]";
+        } else {
+            out += "[\n";
+            for (size_t i = 0; i < l.values.size(); ++i) {
+                out += "        ";
+                jmin::escape_to(out, l.values[i]);
+                out += i + 1 < l.values.size() ? ",\n" : "\n";
+            }
+            out += "      ]";
+        }
+        out += "\n    }";
+        if (k + 1 == layers.size()) out += "\n  ]";
+    }
+    out += "\n}\n";
+    spit(path, out);
 }
 inline bool same_json(const jmin::Value& a, const jmin::Value& b) { return jmin::dump(a, 0) == jmin::dump(b, 0); }
 

@@ -4,6 +4,10 @@
 //   wire_selftest json                   parser / printer round trip, nlohmann-style key ordering and indent
 //   wire_selftest privkey <file>         parse a cereal-JSON PrivateKey: prints limb count, N, moduli, FNV-1a of limbs
 //   wire_selftest mkkeys <in.json> <dir> fabricate key files in OpenFHE's cereal JSON element layout from residues
+#include <omp.h>
+#include <time.h>
+
+#include <cstdio>
 #include <iostream>
 #include <random>
 
@@ -47,6 +51,36 @@ static int t_base64() {
     bool threw = false;
     try { wire::base64_decode("ab$d"); } catch (const std::exception&) { threw = true; }
     CHECK(threw);
+    {   // the vector paths against a one-character-at-a-time restatement; line breaks and bad characters deep inside
+        static const char T[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+        for (int n : {24, 27, 28, 29, 44, 45, 46, 95, 96, 97, 4099, 100003}) {
+            std::vector<unsigned char> v(n);
+            for (auto& c : v) c = (unsigned char)rng();
+            if (n > 64) for (int k = 0; k < 64; ++k) v[k] = (unsigned char)(k * 4 + (k >> 4));  // every 6-bit value
+            std::string want;
+            for (int i = 0; i < n; i += 3) {
+                const uint32_t b0 = v[i], b1 = i + 1 < n ? v[i + 1] : 0, b2 = i + 2 < n ? v[i + 2] : 0, x = (b0 << 16) | (b1 << 8) | b2;
+                want += T[x >> 18];
+                want += T[(x >> 12) & 63];
+                want += i + 1 < n ? T[(x >> 6) & 63] : '=';
+                want += i + 2 < n ? T[x & 63] : '=';
+            }
+            CHECK(wire::base64_encode(v.data(), v.size()) == want);
+            CHECK(wire::base64_decode(want) == v);
+            std::string broken = want;
+            for (size_t at = 76; at < broken.size(); at += 77) broken.insert(at, "\n");
+            CHECK(wire::base64_decode(broken) == v);
+            if (n > 50) {
+                for (char bad : {'$', '-', '_', '\0', '\x80', '\xff', '@', '[', '`', '{'}) {
+                    std::string evil = want;
+                    evil[want.size() / 2 + 1] = bad;
+                    bool t2 = false;
+                    try { wire::base64_decode(evil); } catch (const std::exception&) { t2 = true; }
+                    CHECK(t2);
+                }
+            }
+        }
+    }
     return fails;
 }
 
@@ -141,6 +175,84 @@ static int t_cereal(const char* ccjson_path) {
     return fails;
 }
 
+// host-side cost of one encrypted container (the part of a round that is not on the GPU): write, parse, decode every
+// blob, re-encode, print.  27 blobs of 4 limbs at N = 2^14 is the reference's own upload (37.8 MB).
+static double now_ms() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+static int t_hostbench(const char* ccjson_path, int n_blobs) {
+    const std::string text = wire::slurp(ccjson_path);
+    jmin::Ptr root = jmin::parse(text);
+    const jmin::Value& top = wire::find_member_any(*root, "elp")->at("ptr_wrapper").at("data");
+    const uint32_t N = (uint32_t)top.at("value0").at("rd").as_u64();
+    std::vector<uint64_t> mod, ru;
+    for (const auto& np : top.at("p").arr) {
+        const jmin::Value& v = np->at("ptr_wrapper").at("data").at("value0");
+        mod.push_back(v.at("cm").at("v").as_u64());
+        ru.push_back(v.at("ru").at("v").as_u64());
+    }
+    const uint32_t L = (uint32_t)mod.size();
+    setenv("PPQ_QUIET", "1", 1);
+    wire::Codec codec;
+    codec.init(text, N, mod.data(), ru.data(), L);
+    std::mt19937_64 rng(5);
+    const size_t ct = (size_t)2 * L * N;
+    std::vector<uint64_t> data((size_t)n_blobs * ct);
+    for (size_t i = 0; i < data.size(); ++i) data[i] = rng() % mod[(i / N) % L];
+    wire::CtMeta m;
+    m.noise_scale_deg = 2; m.slots = N / 2; m.scaling_factor = 6.124908131173663e17; m.scaling_factor_int = 1;
+    m.key_tag = "8857ae2821d966b1c2d1cc2bde17d2f1";
+    std::vector<std::string> blobs(n_blobs);
+    double t0 = now_ms();
+#pragma omp parallel for schedule(dynamic)
+    for (int k = 0; k < n_blobs; ++k) blobs[k] = codec.encode(m, L, data.data() + (size_t)k * ct);
+    const double t_enc = now_ms() - t0;
+    wire::Layer l;
+    l.layer = jmin::make_string("gru/kernel");
+    l.shape = jmin::make(jmin::Value::Array);
+    l.mean = blobs[0];
+    l.std_dev = blobs[n_blobs > 1 ? 1 : 0];
+    for (int k = 2; k < n_blobs; ++k) l.values.push_back(blobs[k]);
+    const std::string path = "/tmp/ppq_hostbench.json";
+    t0 = now_ms();
+    wire::write_container(path, {l});
+    const double t_write = now_ms() - t0;
+    t0 = now_ms();
+    std::vector<wire::Layer> back = wire::read_container(path);
+    const double t_read = now_ms() - t0;
+    std::vector<const std::string*> refs = {&back[0].mean, &back[0].std_dev};
+    for (const auto& v : back[0].values) refs.push_back(&v);
+    // as decode_all / encode_back do it: residues straight into one batch, new blobs over the old ones' text
+    t0 = now_ms();
+    std::vector<uint64_t> batch(refs.size() * ct);
+#pragma omp parallel for schedule(dynamic)
+    for (size_t k = 0; k < refs.size(); ++k) codec.decode(*refs[k], batch.data() + k * ct, ct);
+    double t_dec = now_ms() - t0;
+    CHECK(batch == data);
+    for (int rep = 0; rep < 2; ++rep) {  // steady state of a resident server: the batch and the per-thread scratch exist
+        t0 = now_ms();
+#pragma omp parallel for schedule(dynamic)
+        for (size_t k = 0; k < refs.size(); ++k) codec.decode(*refs[k], batch.data() + k * ct, ct);
+        std::printf("hostbench: decode again %.1f ms\n", now_ms() - t0);
+    }
+    std::vector<std::string*> slots = {&back[0].mean, &back[0].std_dev};
+    for (auto& v : back[0].values) slots.push_back(&v);
+    t0 = now_ms();
+#pragma omp parallel for schedule(dynamic)
+    for (size_t k = 0; k < slots.size(); ++k) codec.encode_to(*slots[k], m, L, batch.data() + k * ct);
+    const double t_enc2 = now_ms() - t0;
+    for (size_t k = 0; k < slots.size(); ++k) CHECK(*slots[k] == blobs[k]);
+    std::printf("hostbench: decode into one batch %.1f ms, re-encode in place %.1f ms\n", t_dec, t_enc2);
+    const double mb = (double)wire::slurp(path).size() / 1e6;
+    std::printf("hostbench: %d blobs, file %.1f MB, threads %d: encode %.1f ms, write %.1f ms, read+parse %.1f ms, decode %.1f ms "
+                "(read+decode %.0f MB/s, encode+write %.0f MB/s)\n", n_blobs, mb, omp_get_max_threads(), t_enc, t_write, t_read, t_dec,
+                mb / (t_read + t_dec) * 1e3, mb / (t_enc + t_write) * 1e3);
+    std::remove(path.c_str());
+    return fails;
+}
+
 static int t_json() {
     const std::string src = "{\"weights_summary\":[{\"values\":[\"QQ==\"],\"shape\":[2,3],\"layer\":\"gru/kernel\",\"mean\":\"TQ==\",\"std_dev\":\"Uw==\"}],\"x\":18446744073709551615,\"y\":-1.5e-3,\"z\":\"a\\\"b\\n\"}";
     jmin::Ptr v = jmin::parse(src);
@@ -157,6 +269,39 @@ static int t_json() {
     bool threw = false;
     try { jmin::parse("{\"a\": [1, 2}"); } catch (const std::exception&) { threw = true; }
     CHECK(threw);
+    {   // write_container prints without building a tree: same bytes as the tree printer, and it reads back
+        std::vector<wire::Layer> layers(3);
+        for (size_t k = 0; k < layers.size(); ++k) {
+            layers[k].layer = jmin::make_string(k == 1 ? "dense \"q\"\n" : "gru/kernel");
+            layers[k].shape = jmin::parse(k == 2 ? "[]" : "[2, 3]");
+            layers[k].mean = "TQ==";
+            layers[k].std_dev = std::string(37 + k, 'A') + "\\";
+            for (size_t i = 0; i < k; ++i) layers[k].values.push_back(std::string(100 + i, 'Q'));
+        }
+        jmin::Ptr root = jmin::make(jmin::Value::Object), arr = jmin::make(jmin::Value::Array);
+        for (const wire::Layer& l : layers) {
+            jmin::Ptr o = jmin::make(jmin::Value::Object), vals = jmin::make(jmin::Value::Array);
+            jmin::set(o, "layer", l.layer);
+            jmin::set(o, "shape", l.shape);
+            jmin::set(o, "mean", jmin::make_string(l.mean));
+            jmin::set(o, "std_dev", jmin::make_string(l.std_dev));
+            for (const std::string& v : l.values) vals->arr.push_back(jmin::make_string(v));
+            jmin::set(o, "values", vals);
+            arr->arr.push_back(o);
+        }
+        jmin::set(root, "weights_summary", arr);
+        const std::string path = "/tmp/ppq_wire_selftest_container.json";
+        wire::write_container(path, layers);
+        CHECK(wire::slurp(path) == jmin::dump(*root, 2) + "\n");
+        std::vector<wire::Layer> back = wire::read_container(path);
+        CHECK(back.size() == 3 && back[2].values == layers[2].values && back[1].std_dev == layers[1].std_dev);
+        CHECK(back[1].layer->as_string() == "dense \"q\"\n");
+        wire::write_container(path, {});
+        jmin::Ptr empty = jmin::make(jmin::Value::Object);
+        jmin::set(empty, "weights_summary", jmin::make(jmin::Value::Array));
+        CHECK(wire::slurp(path) == jmin::dump(*empty, 2) + "\n");
+        std::remove(path.c_str());
+    }
     // DCRTPoly element layout round trip
     wire::Poly p;
     p.moduli = {97, 193};
@@ -208,6 +353,7 @@ int main(int argc, char** argv) {
         if (mode == "blob") return t_blob() ? 1 : 0;
         if (mode == "json") return t_json() ? 1 : 0;
         if (mode == "cereal" && argc == 3) return t_cereal(argv[2]) ? 1 : 0;
+        if (mode == "hostbench" && argc >= 3) return t_hostbench(argv[2], argc > 3 ? std::atoi(argv[3]) : 27) ? 1 : 0;
         if (mode == "privkey" && argc == 3) return t_privkey(argv[2]);
         if (mode == "mkkeys" && argc == 4) return t_mkkeys(argv[2], argv[3]);
         std::cerr << "usage: wire_selftest base64|blob|json|cereal <CC.json>|privkey <file>|mkkeys <in.json> <dir>\n";
