@@ -84,19 +84,16 @@ int main(int argc, char* argv[]) {
         if (n) {
             const double sf = ppq_ctx_scaling_factor_big(s->cc, 0);
             Dev<double> d_vals(vals.size());
-            Dev<uint64_t> d_pt(n * ell * s->N), d_ct(n * ct), d_b(pkb.size()), d_a(pka.size());
+            Dev<uint64_t> d_ct(n * ct), d_b(pkb.size()), d_a(pka.size());
             Dev<int64_t> d_small(n * 3 * s->N);
             d_vals.upload(vals.data(), vals.size());
             d_b.upload(pkb.data(), pkb.size());
             d_a.upload(pka.data(), pka.size());
             const ppqhost::SamplerSeed seed;  // NULL (fresh OS entropy per call) unless the test-only PPQ_SEED is set
             ck(ppq_sample_encrypt_noise(s->cc, seed.ptr(), d_small.p, n, nullptr), "ppq_sample_encrypt_noise");
-            const size_t step = std::max<size_t>(1, 65535 / (3 * ell));
-            for (size_t k0 = 0; k0 < n; k0 += step) {
-                const size_t k1 = std::min(n, k0 + step);
-                ck(ppq_encode(s->cc, (int)ell, d_vals.p + k0 * batchSize, batchSize, sf, d_pt.p + k0 * ell * s->N, k1 - k0, nullptr), "ppq_encode");
-                ck(ppq_encrypt(s->cc, (int)ell, d_b.p, d_a.p, d_pt.p + k0 * ell * s->N, d_small.p + k0 * 3 * s->N, d_ct.p + k0 * ct, k1 - k0, nullptr), "ppq_encrypt");
-            }
+            // MakeCKKSPackedPlaintext + Encrypt of every chunk of the file in one call (3*ell limb transforms per ciphertext)
+            ck(ppq_encode_encrypt(s->cc, (int)ell, d_b.p, d_a.p, d_vals.p, batchSize, sf, d_small.p, d_ct.p, n, nullptr),
+               "ppq_encode_encrypt");
             ck(ppq_sync(s->cc, nullptr), "ppq_sync");
             std::vector<uint64_t> h_ct(n * ct);
             d_ct.download(h_ct.data(), h_ct.size());
@@ -106,8 +103,8 @@ int main(int argc, char* argv[]) {
             m.scaling_factor = sf;
             m.slots = (uint32_t)batchSize;
             m.key_tag = key_tag;
-            for (size_t k = 0; k < n; ++k)
-                *dst[k] = s->codec.encode(m, (uint32_t)ell, h_ct.data() + k * ct);
+#pragma omp parallel for schedule(dynamic)
+            for (size_t k = 0; k < n; ++k) s->codec.encode_to(*dst[k], m, (uint32_t)ell, h_ct.data() + k * ct);
         }
         try {
             wire::write_container(output_encfile, out);

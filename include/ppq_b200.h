@@ -147,6 +147,11 @@ int ppq_encode(ppq_ctx*, int ell, const double* d_vals, size_t n_vals, double sf
  *      d_pkb / d_pka: [>=ell][N] EVAL (first ell limbs of the QP public key). */
 int ppq_encrypt(ppq_ctx*, int ell, const uint64_t* d_pkb, const uint64_t* d_pka, const uint64_t* d_pt,
                 const int64_t* d_small, uint64_t* d_ct, size_t n, void* stream);
+/* ---- the two calls above as one (client/src/encryptModelWeights.cpp:109-110, MakeCKKSPackedPlaintext then Encrypt per
+ *      chunk): the encoded coefficients are added to e0 before the transform (the NTT is linear), so a fresh ciphertext
+ *      costs 3*ell forward limb transforms instead of 4*ell.  d_ct is bit-identical to ppq_encode + ppq_encrypt. */
+int ppq_encode_encrypt(ppq_ctx*, int ell, const uint64_t* d_pkb, const uint64_t* d_pka, const double* d_vals,
+                       size_t n_vals, double sf, const int64_t* d_small, uint64_t* d_ct, size_t n, void* stream);
 /* fills d_small [n][3][N] with (ternary, discrete Gaussian sigma 3.19, Gaussian) polynomials: ChaCha20 streams keyed
  * by seed32 (32 bytes), one stream per polynomial; ternary by rejection on 2-bit draws, Gaussian by inversion of a
  * 64-bit cumulative table (csrc/sampler.cu).  seed32 == NULL draws a fresh 256-bit key from getrandom(2) for this

@@ -404,6 +404,30 @@ class CryptoContext:
                                     e - s, _stream()))
         return CiphertextBatch(ct, replace(pt.meta))
 
+    def EncodeEncrypt(self, pk, values, ell=None, small=None, seed=None):
+        """MakeCKKSPackedPlaintext + Encrypt in one call (client/src/encryptModelWeights.cpp:109-110 per chunk): the
+        encoded coefficients join e0 before the transform, 3*ell instead of 4*ell limb transforms per ciphertext; the
+        result is bit-identical to Encrypt(pk, MakeCKKSPackedPlaintext(values), small)."""
+        b, a = pk
+        ell = self.L if ell is None else ell
+        v = values if torch.is_tensor(values) else torch.from_numpy(np.ascontiguousarray(values, dtype=np.float64))
+        v = v.to(self.device, dtype=torch.float64).contiguous()
+        if v.dim() == 1:
+            v = v[None, :]
+        n, nv = v.shape
+        sf = self.sf_big(0)
+        if small is None:
+            small = torch.empty((n, 3, self.N), dtype=torch.int64, device=self.device)
+            for s0 in range(0, n, 16384):
+                e0 = min(n, s0 + 16384)
+                sd = _seed32(seed)
+                if sd is not None and s0:
+                    sd = _seed32((int.from_bytes(sd, "little") + s0) % (1 << 256))
+                check(lib().ppq_sample_encrypt_noise(self.h, sd, _ptr(small[s0:e0]), e0 - s0, _stream()))
+        ct = self.empty_cts(n, ell)
+        check(lib().ppq_encode_encrypt(self.h, ell, _ptr(b), _ptr(a), _ptr(v), nv, sf, _ptr(small), _ptr(ct), n, _stream()))
+        return CiphertextBatch(ct, CtMeta(noise_scale_deg=2, level=0, scaling_factor=sf, slots=self.N // 2))
+
     def KeyGen(self, seed=None, samples=None):
         """cc->KeyGen() (client/src/keyGen.cpp:33).  Returns (sk [L][N], (pk_b, pk_a) [L+K][N] each), CUDA int64, EVAL.
         samples: optional (s [N] int64, e [N] int64, a [L+K][N]) CUDA tensors injected for parity tests; drawn on

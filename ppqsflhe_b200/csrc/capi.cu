@@ -1036,6 +1036,41 @@ extern "C" int ppq_encode(ppq_ctx* c, int ell, const double* d_vals, size_t n_va
     return PPQ_OK;
 }
 
+// MakeCKKSPackedPlaintext + Encrypt in one call: the encoded coefficients join e0 BEFORE the transform (the NTT is
+// linear), so a fresh ciphertext costs 3*ell forward limb transforms instead of 4*ell; output identical to ppq_encode
+// followed by ppq_encrypt.
+extern "C" int ppq_encode_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint64_t* pka, const double* d_vals,
+                                  size_t n_vals, double sf, const int64_t* small, uint64_t* ct, size_t n, void* stream) {
+    if (!c || !pkb || !pka || !d_vals || !small || !ct) return fail(PPQ_EINVAL, "ppq_encode_encrypt: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_encode_encrypt: bad limb count");
+    if (n_vals > c->hp.N / 2) return fail(PPQ_EINVAL, "ppq_encode_encrypt: more values than slots");
+    if (n == 0) return PPQ_OK;
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = c->hp.N;
+    const int* ids;
+    if (int rc = cyc_ids(c, ell, &ids)) return rc;
+    int sf_exp = 0;
+    std::frexp(sf, &sf_exp);
+    const int approx = sf_exp > 58 ? sf_exp - 58 : 0;  // as ppq_encode: round at sf / 2^approx, then times 2^approx
+    if (approx > 62) return fail(PPQ_EINVAL, "ppq_encode_encrypt: scaling factor out of range");
+    const size_t step = rows_chunk(3 * ell);
+    const size_t m_max = std::min(n, step);
+    // scratch2: (v, m + e0, e1) in EVAL [m][3][ell][N], then the FFT work [m][N/2] double2 and the coefficients [m][N]
+    CU(c->scratch2.ensure(m_max * (3 * (size_t)ell + 2) * N));
+    for (size_t s0 = 0; s0 < n; s0 += step) {
+        const size_t m = std::min(step, n - s0);
+        u64* vee = c->scratch2.p;
+        double2* z = reinterpret_cast<double2*>(vee + m * 3 * ell * N);
+        int64_t* co = reinterpret_cast<int64_t*>(vee + m * (3 * (size_t)ell + 1) * N);
+        ckks::launch_encode_fft(c->fft, d_vals + s0 * n_vals, n_vals, std::ldexp(sf, -approx), z, co, m, st);
+        launch_small_fwd_ntt(c->k, small + s0 * 3 * N, vee, 3, ell, m, ids, st, co, approx);
+        launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, nullptr, (u64*)ct + s0 * 2 * ell * N, ell, m, st);
+    }
+    CU(cudaGetLastError());
+    return PPQ_OK;
+}
+
 extern "C" int ppq_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint64_t* pka, const uint64_t* pt,
                            const int64_t* small, uint64_t* ct, size_t n, void* stream) {
     if (!c || !pkb || !pka || !pt || !small || !ct) return fail(PPQ_EINVAL, "ppq_encrypt: null argument");

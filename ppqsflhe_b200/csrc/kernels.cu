@@ -123,6 +123,20 @@ __global__ void __launch_bounds__(W << (S - 3), S == 9 ? 1 : (MODE == 2 && S == 
             const u64 m = reduce64(v < 0 ? (u64)(-v) : (u64)v, lc);
             a[k] = (v < 0 && m != 0) ? lc.q - m : m;
         }
+        // fused encode + encrypt (ppq_encode_encrypt): slot 1 (e0) also receives the encoded plaintext coefficients
+        // `chat` [g][N] (int64) times 2^approx, so that m + e0 costs ONE transform per limb (the NTT is linear)
+        if (chat != nullptr && y / (u32)q_src == 1u) {  // block-uniform
+            const long long* co = reinterpret_cast<const long long*>(chat) + (size_t)g * N;
+            const u32 approx = (u32)(q_src >> 32);
+            const u64 f = reduce64(1ull << approx, lc);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const long long v = co[(size_t)point_of<S - 3>(u, k) * n2 + col];
+                u64 m = reduce64(v < 0 ? (u64)(-v) : (u64)v, lc);
+                if (approx) m = mulmod_barrett(m, f, lc);
+                a[k] = addmod(a[k], (v < 0 && m != 0) ? lc.q - m : m, lc.q);
+            }
+        }
     } else {
         const u64 half = q_src >> 1;
         const u64 qs_mod = reduce64(q_src, lc);
@@ -1507,14 +1521,15 @@ __global__ void k_encrypt_pw(KCtx c, const u64* __restrict__ pkb, const u64* __r
     const u64* v = vee + ((g * 3 + 0) * ell + i) * N;
     const u64* e0 = vee + ((g * 3 + 1) * ell + i) * N;
     const u64* e1 = vee + ((g * 3 + 2) * ell + i) * N;
-    const u64* m = pt + (g * ell + i) * N;
+    const u64* m = pt ? pt + (g * ell + i) * N : nullptr;  // nullptr: the plaintext is already inside the e0 slot
     const u64* b = pkb + (size_t)i * N;
     const u64* a = pka + (size_t)i * N;
     u64* c0 = ct + ((g * 2 + 0) * ell + i) * N;
     u64* c1 = ct + ((g * 2 + 1) * ell + i) * N;
     for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
         const u64 vv = v[n];
-        c0[n] = addmod(addmod(mulmod_barrett(vv, __ldg(b + n), lc), e0[n], lc.q), m[n], lc.q);
+        const u64 t = addmod(mulmod_barrett(vv, __ldg(b + n), lc), e0[n], lc.q);
+        c0[n] = m ? addmod(t, m[n], lc.q) : t;
         c1[n] = addmod(mulmod_barrett(vv, __ldg(a + n), lc), e1[n], lc.q);
     }
 }
@@ -1745,12 +1760,13 @@ void launch_fwd_col_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
 }
 
 void launch_small_fwd_ntt(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_groups,
-                          const int* d_cyc_ids, cudaStream_t st) {
+                          const int* d_cyc_ids, cudaStream_t st, const int64_t* pt_coeff, int pt_approx) {
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1, ny = n_small * ell;
     const size_t gs = (size_t)ny << c.logN;
-    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 3>(c, reinterpret_cast<const u64*>(small), (size_t)n_small, out, gs, nullptr, nullptr,
-                                                  nullptr, (u64)ell, ny, (int)n_groups, st)));
+    const u64 mode_arg = (u64)ell | ((u64)(pt_coeff ? pt_approx : 0) << 32);
+    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 3>(c, reinterpret_cast<const u64*>(small), (size_t)n_small, out, gs, nullptr,
+                                                  reinterpret_cast<const u64*>(pt_coeff), nullptr, mode_arg, ny, (int)n_groups, st)));
     count_launch();
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, 1, (unsigned)(n_groups * ny)), RowGeom<S>::THREADS, 0, st>>>(
                                 c, out, 0, d_cyc_ids, 1)));

@@ -176,9 +176,10 @@ void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64*
                               size_t n_polys, cudaStream_t st);
 // forward NTT of small signed polynomials on the first `ell` limbs: out[g][s][i] = NTT_i(small[g][s]), g < n_groups,
 // s < n_small (the residues are formed inside the COL pass); d_cyc_ids: limb ids 0..ell-1 repeated (>= n_groups*n_small*ell)
+// pt_coeff != nullptr ([n_groups][N] int64, needs n_small >= 2): slot 1 becomes NTT(small[g][1] + pt_coeff[g] * 2^pt_approx)
 void launch_small_fwd_ntt(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_groups,
-                          const int* d_cyc_ids, cudaStream_t st);
-// encrypt combine: ct[g][0][i] = pkb[i]*v + e0 + m ; ct[g][1][i] = pka[i]*v + e1   (all EVAL)
+                          const int* d_cyc_ids, cudaStream_t st, const int64_t* pt_coeff = nullptr, int pt_approx = 0);
+// encrypt combine: ct[g][0][i] = pkb[i]*v + e0 + m ; ct[g][1][i] = pka[i]*v + e1   (all EVAL); pt may be nullptr (m = 0)
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee /*[g][3][ell][N]*/,
                        const u64* pt /*[g][ell][N]*/, u64* ct, int ell, size_t n_ct, cudaStream_t st);
 // decrypt combine: out[g][i] = c0 + c1 * s   (EVAL)

@@ -517,6 +517,28 @@ def test_encrypt_bit_exact_with_injected_samples_and_decrypt_core():
         assert np.array_equal(co[g], o.decrypt_core(ell, sk, got[g]))
 
 
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ("c1", 2), ((13, 3, 2, 40), 4), ((16, 18, 3, 59), 20)])
+def test_encode_encrypt_fused_equals_the_two_calls(kind, ell):
+    # ppq_encode_encrypt adds the encoded coefficients to e0 before the transform (3*ell limb transforms instead of
+    # 4*ell): bit-identical to MakeCKKSPackedPlaintext followed by Encrypt with the same samples, which is the pair the
+    # oracle pins (test_encrypt_bit_exact_with_injected_samples_and_decrypt_core, test_encode_decode_tolerance)
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(41)
+    n = 3
+    vals = np.clip(rng.normal(0, 0.5, (n, o.N // 2)), -3.0, 3.0)
+    vals[1, 7:] = 0.0
+    small = np.stack([np.stack([oracle.sample_ternary(100 + g, o.N), oracle.sample_gauss(200 + g, o.N),
+                                oracle.sample_gauss(300 + g, o.N)]) for g in range(n)])
+    d_small = torch.from_numpy(small).to(cc.device)
+    qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(cc.device)
+    pk = tuple(torch.randint(0, 1 << 62, (cc.M, cc.N), dtype=torch.int64, device=cc.device).remainder_(qv.view(-1, 1))
+               for _ in range(2))
+    two = cc.Encrypt(pk, cc.MakeCKKSPackedPlaintext(vals, ell=ell), small=d_small)
+    one = cc.EncodeEncrypt(pk, vals, ell=ell, small=d_small)
+    assert torch.equal(one.data, two.data)
+    assert one.meta.scaling_factor == two.meta.scaling_factor and one.meta.noise_scale_deg == 2
+
+
 def test_encode_decode_tolerance():
     """CKKS encode is not bit-reproducible (SURVEY 3.4): compare through decode.  Tolerance 2^-20 (north_star);
     observed ~1e-9."""

@@ -40,9 +40,12 @@ def main():
     us_enc, pt = t(lambda: cc.MakeCKKSPackedPlaintext(vals))
     us_smp, _ = t(lambda: check(lib().ppq_sample_encrypt_noise(cc.h, None, vp(small.data_ptr()), n, None)))
     us_ect, ct = t(lambda: cc.Encrypt(pk, pt, small=small))
+    us_fus, ct2 = t(lambda: cc.EncodeEncrypt(pk, vals, small=small))
+    assert torch.equal(ct2.data, ct.data)
+    us_fus2, _ = t(lambda: cc.EncodeEncrypt(pk, vals))
     us_dec, co = t(lambda: cc.DecryptCore(sk, ct))
     us_dcd, _ = t(lambda: cc.Decrypt(sk, ct))
-    print(f"[{a.config}] per ct (us): encode {us_enc:.1f}  sample {us_smp:.1f}  encrypt {us_ect:.1f}  decrypt_core {us_dec:.1f}  "
+    print(f"[{a.config}] per ct (us): encode {us_enc:.1f}  sample {us_smp:.1f}  encrypt {us_ect:.1f}  encode+encrypt fused {us_fus:.1f} (with sampling {us_fus2:.1f})  decrypt_core {us_dec:.1f}  "
           f"decrypt+decode {us_dcd:.1f}   ({cc.L} limbs, N=2^{cc.logN}, {n} cts)")
 
 
