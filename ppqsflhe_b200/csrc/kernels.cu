@@ -28,6 +28,11 @@
 #ifndef PPQ_COL_MINB
 #define PPQ_COL_MINB 5  // 51 registers: 8.4 -> 7.7 us/ct on the inverse COL passes, forward unchanged (profiles/r03_notes.md)
 #endif
+#ifndef PPQ_COL9_MINB
+// 512-thread COL CTAs (n1 = 512, N = 2^17) at 2 CTAs/SM: 64 registers, no spills; C4 601 -> 528 us/ct against 1 CTA/SM
+// (92 registers); 3 CTAs/SM spills 8-44 bytes for 521, 4 CTAs/SM 523 (tools/stage_times.py --config c4)
+#define PPQ_COL9_MINB 2
+#endif
 namespace ppq {
 
 #ifndef PPQ_NO_ZADD
@@ -78,7 +83,7 @@ __device__ __forceinline__ void st8(u64* p, const u64 (&a)[8]) {
 // SAME: the ROW size equals the COL size (n2 = 2^S), else n2 = 2^(S-1) (split_of): with n2 known at compile time the
 // eight strided accesses of a thread share one base register and use immediate offsets.
 template <int S, int W, int MODE, bool SAME>
-__global__ void __launch_bounds__(W << (S - 3), S == 9 ? 1 : (MODE == 2 && S == 6) ? 4 : PPQ_COL_MINB)
+__global__ void __launch_bounds__(W << (S - 3), S == 9 ? PPQ_COL9_MINB : (MODE == 2 && S == 6) ? 4 : PPQ_COL_MINB)
     k_fwd_col(KCtx c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs,
               const BcJob* __restrict__ jobs, const u64* __restrict__ chat, const int* __restrict__ limb_ids,
               u64 q_src) {
@@ -199,7 +204,7 @@ __global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
 }
 
 template <int S, int W, bool SAME>
-__global__ void __launch_bounds__(W << (S - 3), S == 9 ? 1 : PPQ_COL_MINB)
+__global__ void __launch_bounds__(W << (S - 3), S == 9 ? PPQ_COL9_MINB : PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
               const u64* __restrict__ scale) {
     __shared__ u64 sm[W << S];
