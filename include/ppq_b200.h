@@ -147,6 +147,19 @@ int ppq_encode(ppq_ctx*, int ell, const double* d_vals, size_t n_vals, double sf
  *      d_pkb / d_pka: [>=ell][N] EVAL (first ell limbs of the QP public key). */
 int ppq_encrypt(ppq_ctx*, int ell, const uint64_t* d_pkb, const uint64_t* d_pka, const uint64_t* d_pt,
                 const int64_t* d_small, uint64_t* d_ct, size_t n, void* stream);
+/* ---- ppq_encrypt without any device allocation.  NO counterpart in the reference: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ *      that forbid it).  Same arguments and bit-identical output as ppq_encrypt, but the scratch ((v, e0, e1) in EVAL form
+ *      and the limb-id table) lives in one file-scope device array of 64 MiB that every GPU loading the library holds
+ *      until exit, so the call never runs cudaMalloc / cudaFree or an allocating library routine.  Limit: n * 3 * ell *
+ *      (8 N + 4) bytes <= 64 MiB (C1, ell 4, N 2^14: 42 ciphertexts per call -- the reference's 27-ciphertext file fits;
+ *      C3, ell 20, N 2^16: 2); a larger batch is refused with PPQ_EINVAL and a message naming the maximum -- split the
+ *      batch or use ppq_encrypt.  All calls on a device share the array (it keeps the last call's contents, none of which
+ *      a later call reads before overwriting them): calls that overlap on the GPU -- two streams, two contexts, two
+ *      threads -- RACE; serialise them on one stream.  The first call on a device resolves the array's address
+ *      (cudaGetSymbolAddress); make one call before starting a graph capture.  Asynchronous on `stream`. */
+int ppq_encrypt_noalloc(ppq_ctx*, int ell, const uint64_t* d_pkb, const uint64_t* d_pka, const uint64_t* d_pt,
+                        const int64_t* d_small, uint64_t* d_ct, size_t n, void* stream);
 /* ---- the two calls above as one (client/src/encryptModelWeights.cpp:109-110, MakeCKKSPackedPlaintext then Encrypt per
  *      chunk): the encoded coefficients are added to e0 before the transform (the NTT is linear), so a fresh ciphertext
  *      costs 3*ell forward limb transforms instead of 4*ell.  d_ct is bit-identical to ppq_encode + ppq_encrypt. */

@@ -68,6 +68,7 @@ _SIGS = {
     "ppq_eval_mult_const": (C.c_int, [vp, C.c_int, vp, vp, C.c_size_t, C.c_double, C.c_double, C.c_int, vp]),
     "ppq_encode": (C.c_int, [vp, C.c_int, vp, C.c_size_t, C.c_double, vp, C.c_size_t, vp]),
     "ppq_encrypt": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_size_t, vp]),
+    "ppq_encrypt_noalloc": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_size_t, vp]),
     "ppq_encode_encrypt": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_size_t, C.c_double, vp, vp, C.c_size_t, vp]),
     "ppq_sample_encrypt_noise": (C.c_int, [vp, C.c_char_p, vp, C.c_size_t, vp]),
     "ppq_chacha20_block": (C.c_int, [C.POINTER(C.c_uint32), C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1936,4 +1937,66 @@ extern "C" int ppq_reencrypt_aggregate_host_packed_ranks(ppq_ctx* c, ppq_comm* c
 extern "C" int ppq_copy_ceiling_host_packed(ppq_ctx* c, int ell, const uint64_t* const* h_cts, size_t n_clients,
                                             size_t n_slots, uint64_t* h_acc) {
     return aggregate_host_impl(c, nullptr, 0, nullptr, ell, h_cts, n_clients, n_slots, h_acc, true, true);
+}
+
+// ------------------------------------------------------------------------------------------- allocation-free Encrypt
+// ppq_encrypt for callers that may not allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.  The scratch of
+// ppq_encrypt -- (v, e0, e1) in EVAL form, [n][3][ell][N] words, and the limb-id table of its ROW pass -- lives in ONE
+// file-scope device array of PPQ_NOALLOC_SCRATCH_BYTES instead of context-owned cudaMalloc buffers.  Every GPU that loads
+// the library holds the array until exit.  In host code `g_noalloc_scratch` is only a stand-in for the symbol: its
+// device address is resolved per device with cudaGetSymbolAddress (below) and that pointer is what the kernels get.
+#define PPQ_NOALLOC_SCRATCH_BYTES (64ull << 20)
+#define PPQ_NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PPQ_NOALLOC_SCRATCH_BYTES];
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[PPQ_NOALLOC_MAX_DEVICES] = {};
+
+// ids[i] = i % ell: the limb of polynomial row i of [n][3][ell] (what cyc_ids uploads for the allocating path)
+static __global__ void k_noalloc_fill_ids(int* __restrict__ ids, int n, int ell) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) ids[i] = i % ell;
+}
+
+// once per device, with that device current
+static int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= PPQ_NOALLOC_MAX_DEVICES) return fail(PPQ_EINVAL, "ppq_encrypt_noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(PPQ_ECUDA, std::string("ppq_encrypt_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return PPQ_OK;
+}
+
+extern "C" int ppq_encrypt_noalloc(ppq_ctx* c, int ell, const uint64_t* pkb, const uint64_t* pka, const uint64_t* pt,
+                                   const int64_t* small, uint64_t* ct, size_t n, void* stream) {
+    if (!c || !pkb || !pka || !pt || !small || !ct) return fail(PPQ_EINVAL, "ppq_encrypt_noalloc: null argument");
+    if (ell < 1 || ell > c->hp.L) return fail(PPQ_EINVAL, "ppq_encrypt_noalloc: bad limb count");
+    if (n == 0) return PPQ_OK;
+    const size_t N = c->hp.N;
+    const size_t rows = n * 3 * (size_t)ell;
+    // layout: [rows][N] u64 (v, e0, e1 in EVAL), then [rows] int limb ids (both offsets are multiples of 256 bytes)
+    const size_t need = rows * N * sizeof(u64) + rows * sizeof(int);
+    if (n > 65535 / (3 * (size_t)ell) || need > PPQ_NOALLOC_SCRATCH_BYTES)
+        return fail(PPQ_EINVAL, "ppq_encrypt_noalloc: batch needs " + std::to_string(need) + " bytes of scratch, the maximum is " +
+                                    std::to_string((unsigned long long)PPQ_NOALLOC_SCRATCH_BYTES) +
+                                    " (n * 3 * ell * (8 N + 4)); split the batch or use ppq_encrypt");
+    CU(cudaSetDevice(c->device));
+    unsigned char* base = nullptr;
+    if (int rc = noalloc_scratch(c->device, &base)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    u64* vee = reinterpret_cast<u64*>(base);
+    int* ids = reinterpret_cast<int*>(base + rows * N * sizeof(u64));
+    // nothing in the array has to start at zero: the ids are rewritten here and every word of vee is written by the COL
+    // pass before the ROW pass reads it, so the previous call's contents are never seen
+    k_noalloc_fill_ids<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(ids, (int)rows, ell);
+    launch_small_fwd_ntt(c->k, small, vee, 3, ell, n, ids, st);
+    launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, (const u64*)pt, (u64*)ct, ell, n, st);
+    CU(cudaGetLastError());
+    return PPQ_OK;
 }
