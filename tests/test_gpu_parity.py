@@ -950,3 +950,63 @@ def test_rescale_is_exact_centred_division_big_integers(kind, ell):
     for i in range(ell - 1):
         q = mods[i]
         assert all(int(a) == int(b) % q for a, b in zip(res[i], Y)), f"limb {i}"
+
+
+def test_empty_batches_and_bad_arguments_through_the_c_abi():
+    # the reference's loops simply do not run on an empty file (server/src/changeCipherDomain.cpp:57-124 over an empty
+    # weights_summary); here n = 0 is PPQ_OK and writes nothing, and a bad limb count / null pointer / empty aggregate is
+    # PPQ_EINVAL with a message, never a launch
+    import ctypes as C
+    from ppqsflhe_b200 import EvalKey
+    from ppqsflhe_b200._capi import lib, vp
+    o, cc = _cc_pair("c1")
+    L = lib()
+    rng = np.random.default_rng(5)
+    rk = EvalKey(cc, *_rand_key(rng, o))
+    ell = 4
+    buf = torch.full((2, 2, ell, cc.N), 7, dtype=torch.int64, device=cc.device)
+    out = torch.full_like(buf, 9)
+    p, q = vp(buf.data_ptr()), vp(out.data_ptr())
+    assert L.ppq_reencrypt(cc.h, rk.h, ell, p, q, 0, None) == 0
+    assert L.ppq_reencrypt_accumulate(cc.h, rk.h, ell, p, q, 0, None) == 0
+    assert L.ppq_eval_add(cc.h, ell, p, p, q, 0, None) == 0
+    assert L.ppq_finalize_sum(cc.h, ell, q, 0, None) == 0
+    assert L.ppq_eval_mult_const(cc.h, ell, p, q, 0, 0.5, cc.sf(1), 1, None) == 0
+    assert L.ppq_decrypt_core(cc.h, ell, p, p, q, 0, None) == 0
+    assert L.ppq_encrypt(cc.h, ell, p, p, p, p, q, 0, None) == 0
+    assert L.ppq_encode_encrypt(cc.h, ell, p, p, p, 0, 1.0, p, q, 0, None) == 0
+    assert L.ppq_pack(cc.h, ell, p, q, 0, None) == 0 and L.ppq_unpack(cc.h, ell, p, q, 0, None) == 0
+    assert L.ppq_ntt_forward(cc.h, q, None, 0, None) in (0, -1)  # a null id list may be refused; nothing is launched
+    torch.cuda.synchronize()
+    assert int((out != 9).sum().item()) == 0 and int((buf != 7).sum().item()) == 0
+    for bad_ell in (0, -1, cc.L + 1):
+        assert L.ppq_reencrypt(cc.h, rk.h, bad_ell, p, q, 1, None) == -1
+        assert L.ppq_eval_add(cc.h, bad_ell, p, p, q, 1, None) == -1
+        assert L.ppq_encrypt(cc.h, bad_ell, p, p, p, p, q, 1, None) == -1
+        assert L.ppq_packed_words(cc.h, bad_ell) == 0
+        assert b"limb" in L.ppq_last_error() or b"bad" in L.ppq_last_error()
+    assert L.ppq_eval_mult_const(cc.h, 1, p, q, 1, 0.5, 1.0, 1, None) == -1  # nothing to rescale into
+    assert L.ppq_reencrypt(cc.h, None, ell, p, q, 1, None) == -1
+    assert L.ppq_reencrypt(cc.h, rk.h, ell, None, q, 1, None) == -1
+    agg = C.c_void_p()
+    assert L.ppq_agg_create(cc.h, ell, 2, C.byref(agg)) == 0
+    assert L.ppq_agg_count(agg) == 0
+    assert L.ppq_agg_finish(agg, q, None) == -1  # nothing was added
+    assert L.ppq_agg_add_many(agg, None, None, 0, None) in (0, -1)
+    L.ppq_agg_destroy(agg)
+    torch.cuda.synchronize()
+    assert int((out != 9).sum().item()) == 0
+
+
+def test_short_value_vectors_are_zero_padded():
+    # `mean` / `std_dev` are one-value plaintexts and the last chunk of a layer is ragged
+    # (client/src/encryptModelWeights.cpp:82,90,100-109): n_vals < N/2 must equal the zero-padded full vector, bit for bit
+    o, cc = _cc_pair("c1")
+    rng = np.random.default_rng(6)
+    for nv in (1, 5, 1000, cc.N // 2 - 1):
+        vals = rng.normal(0, 0.1, (2, nv))
+        full = np.zeros((2, cc.N // 2))
+        full[:, :nv] = vals
+        a = cc.MakeCKKSPackedPlaintext(vals)
+        b = cc.MakeCKKSPackedPlaintext(full)
+        assert torch.equal(a.data, b.data)
