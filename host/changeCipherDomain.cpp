@@ -54,7 +54,7 @@ int main(int argc, char* argv[]) {
             d_out.download(b.data.data(), b.data.size());
             if (!rekey_tag.empty())
                 for (auto& m : b.meta) m.key_tag = rekey_tag;
-            encode_back(*s, b, b.ell, b.meta, b.data, refs);  // level / scale / slots unchanged by a key switch
+            encode_back(*s, b, b.ell, b.meta, b.data.data(), refs);  // level / scale / slots unchanged by a key switch
         }
         ppq_rekey_destroy(rk);
 

@@ -38,6 +38,8 @@
 #include <sys/un.h>
 #include <unistd.h>
 
+#include <omp.h>
+
 #include <cctype>
 #include <filesystem>
 #include <fstream>
@@ -52,6 +54,9 @@ struct Server {
     std::map<std::string, ppq_rekey*> rekeys;
     std::map<std::string, std::string> rekey_tag;
     size_t rounds = 0, key_parses = 0;
+    // device buffers of a round, kept from round to round (grow-only): no cudaMalloc / cudaFree in the steady state
+    DevGrow<uint64_t> dv_sum, dv_t, dv_agg;
+    std::vector<std::unique_ptr<DevGrow<uint64_t>>> dv_out;
 
     ~Server() {
         for (auto& kv : rekeys) ppq_rekey_destroy(kv.second);
@@ -82,12 +87,26 @@ struct Server {
         const double t0 = now_ms();
         // ---- decode every upload (host): one batch per client
         EncFile tf;
-        read_enc_file(*s, target, tf);
         std::vector<EncFile> uf(up.size());
-        for (size_t i = 0; i < up.size(); ++i) {
-            read_enc_file(*s, up[i].second, uf[i]);
-            if (!same_structure(uf[i], tf)) throw std::runtime_error(up[i].second + ": tensors differ from the target client's file");
+        {   // the files are independent: one reader per file, each decoding its blobs with its own inner team
+            std::vector<std::string> errs(up.size() + 1);
+            omp_set_max_active_levels(2);
+            const int inner = std::max(1, omp_get_num_procs() / (int)(up.size() + 1));
+#pragma omp parallel for schedule(static, 1) num_threads((int)up.size() + 1)
+            for (size_t i = 0; i <= up.size(); ++i) {
+                omp_set_num_threads(inner);
+                try {
+                    if (i == 0) read_enc_file(*s, target, tf);
+                    else read_enc_file(*s, up[i - 1].second, uf[i - 1]);
+                } catch (const std::exception& e) {
+                    errs[i] = e.what()[0] ? e.what() : "read error";
+                }
+            }
+            for (const std::string& e : errs)
+                if (!e.empty()) throw std::runtime_error(e);
         }
+        for (size_t i = 0; i < up.size(); ++i)
+            if (!same_structure(uf[i], tf)) throw std::runtime_error(up[i].second + ": tensors differ from the target client's file");
         const uint32_t ell = tf.batch.ell;
         const size_t n = tf.batch.n(), N = s->N, ct = (size_t)2 * ell * N;
         const wire::CtMeta m0 = tf.batch.meta[0];
@@ -98,7 +117,12 @@ struct Server {
         const double t1 = now_ms();
         // ---- device: re-encrypt + sum the uploads, add the target client's own ciphertexts, scale by 1/C
         const size_t C = up.size() + 1;
-        Dev<uint64_t> d_sum(n * ct), d_t(n * ct);
+        struct View {  // the round's device buffers live in the server
+            uint64_t* p;
+            void upload(const uint64_t* h, size_t count) { cu(cudaMemcpy(p, h, count * sizeof(uint64_t), cudaMemcpyHostToDevice), "H2D copy"); }
+            void download(uint64_t* h, size_t count) const { cu(cudaMemcpy(h, p, count * sizeof(uint64_t), cudaMemcpyDeviceToHost), "D2H copy"); }
+        };
+        View d_sum{dv_sum.ensure(n * ct)}, d_t{dv_t.ensure(n * ct)};
         d_t.upload(tf.batch.data.data(), n * ct);
         if (!up.empty()) {
             std::vector<const ppq_rekey*> rks;
@@ -107,7 +131,7 @@ struct Server {
                 rks.push_back(key(up[i].first));
                 ptrs.push_back(uf[i].batch.data.data());
             }
-            std::vector<uint64_t> h_acc(n * ct);
+            HVec h_acc(n * ct);
             ck(ppq_reencrypt_aggregate_host(s->cc, rks.data(), (int)ell, ptrs.data(), up.size(), n, h_acc.data()), "ppq_reencrypt_aggregate_host");
             d_sum.upload(h_acc.data(), n * ct);
             const size_t step = std::max<size_t>(1, 65535 / (2 * ell));
@@ -124,7 +148,7 @@ struct Server {
         const uint32_t lo = rescale ? ell - 1 : ell;
         const size_t ct_out = (size_t)2 * lo * N;
         const double sf = ppq_ctx_scaling_factor(s->cc, (int)(m0.level + (rescale ? 1 : 0)));
-        Dev<uint64_t> d_agg(n * ct_out);
+        View d_agg{dv_agg.ensure(n * ct_out)};
         for (size_t k0 = 0; k0 < n; k0 += 8192) {
             const size_t k1 = std::min(n, k0 + 8192);
             ck(ppq_eval_mult_const(s->cc, (int)ell, d_sum.p + k0 * ct, d_agg.p + k0 * ct_out, k1 - k0, 1.0 / (double)C, sf, rescale ? 1 : 0, nullptr),
@@ -139,34 +163,74 @@ struct Server {
         mo.noise_scale_deg += 1;
         mo.scaling_factor *= sf;
         // ---- fan-out of the aggregate to the other key domains (second changeCipherDomain pass, server_fns.sh:76-80)
-        std::vector<Dev<uint64_t>> d_out(down.size());
+        std::vector<View> d_out(down.size());
         if (!down.empty()) {
             std::vector<const ppq_rekey*> rks;
             std::vector<uint64_t*> outs;
+            while (dv_out.size() < down.size()) dv_out.emplace_back(new DevGrow<uint64_t>);
             for (size_t i = 0; i < down.size(); ++i) {
                 rks.push_back(key(down[i].first));
-                d_out[i].alloc(n * ct_out);
+                d_out[i].p = dv_out[i]->ensure(n * ct_out);
                 outs.push_back(d_out[i].p);
             }
             ck(ppq_reencrypt_fanout(s->cc, rks.data(), (int)down.size(), (int)lo, d_agg.p, outs.data(), n, nullptr), "ppq_reencrypt_fanout");
         }
         ck(ppq_sync(s->cc, nullptr), "ppq_sync");
-        std::vector<uint64_t> h(n * ct_out);
+        HVec h(n * ct_out);
         d_agg.download(h.data(), h.size());
         const double t2 = now_ms();
-        // ---- encode: same containers, new blobs
+        // ---- encode: same containers, new blobs; the outputs are independent, one writer per file (the aggregate re-uses
+        // the target file's container in place, every fan-out file gets its own copy of it)
         std::vector<wire::CtMeta> metas(n, mo);
         for (size_t k = 0; k < n; ++k) metas[k].slots = tf.batch.meta[k].slots;
-        encode_back(*s, tf.batch, lo, metas, h, tf.refs);
-        wire::write_container(out, tf.layers);
-        for (size_t i = 0; i < down.size(); ++i) {
-            d_out[i].download(h.data(), h.size());
-            std::vector<wire::CtMeta> md = metas;
-            const std::string& tag = rekey_tag[down[i].first];
-            if (!tag.empty())
-                for (auto& m : md) m.key_tag = tag;
-            encode_back(*s, tf.batch, lo, md, h, tf.refs);
-            wire::write_container(down[i].second, tf.layers);
+        {
+            const size_t n_out = down.size() + 1;
+            std::vector<std::string> errs(n_out), tags(n_out);
+            for (size_t i = 1; i < n_out; ++i) {
+                auto it = rekey_tag.find(down[i - 1].first);
+                if (it != rekey_tag.end()) tags[i] = it->second;
+            }
+            std::vector<std::vector<wire::Layer>> copies(n_out);
+            omp_set_max_active_levels(2);
+            const int inner = std::max(1, omp_get_num_procs() / (int)n_out);
+#pragma omp parallel num_threads((int)n_out)
+            {
+                const size_t tid = (size_t)omp_get_thread_num(), nth = (size_t)omp_get_num_threads();
+                omp_set_num_threads(inner);
+                // first every fan-out writer copies the container (blob texts of the right size to overwrite) ...
+                for (size_t i = tid; i < n_out; i += nth)
+                    if (i > 0) {
+                        try {
+                            copies[i] = tf.layers;
+                        } catch (const std::exception& e) {
+                            errs[i] = "out of memory";
+                        }
+                    }
+#pragma omp barrier
+                // ... then the aggregate overwrites the original in place
+                for (size_t i = tid; i < n_out; i += nth) {
+                    if (!errs[i].empty()) continue;
+                    try {
+                        if (i == 0) {
+                            encode_back(*s, tf.batch, lo, metas, h.data(), tf.refs);
+                            wire::write_container(out, tf.layers);
+                        } else {
+                            HVec hi(n * ct_out);
+                            d_out[i - 1].download(hi.data(), hi.size());
+                            std::vector<wire::CtMeta> md = metas;
+                            if (!tags[i].empty())
+                                for (auto& m : md) m.key_tag = tags[i];
+                            const std::vector<BlobRef> refs = blob_refs(copies[i]);
+                            encode_back(*s, tf.batch, lo, md, hi.data(), refs);
+                            wire::write_container(down[i - 1].second, copies[i]);
+                        }
+                    } catch (const std::exception& e) {
+                        errs[i] = e.what()[0] ? e.what() : "write error";
+                    }
+                }
+            }
+            for (const std::string& e : errs)
+                if (!e.empty()) throw std::runtime_error(e);
         }
         const double t3 = now_ms();
         ++rounds;
@@ -515,6 +579,7 @@ int main(int argc, char* argv[]) {
         try {
             const HttpCfg cfg = load_http_cfg(argv[2]);
             sv.s.reset(new Session(cfg.cc_path));
+            HostPool::get().pinned = true;  // resident process: ciphertext batches in pooled pinned memory
             std::cout << "[served] CryptoContext loaded" << std::endl;
             HttpServer hs(sv, cfg);
             for (const auto& kv : cfg.clients)  // keys already on disk from an earlier run stay usable
@@ -527,6 +592,7 @@ int main(int argc, char* argv[]) {
     }
     try {
         sv.s.reset(new Session(argv[1]));
+        HostPool::get().pinned = true;  // resident process: ciphertext batches in pooled pinned memory
     } catch (const std::exception& e) {
         std::cerr << "[served] ERROR: Failed to load CryptoContext from " << argv[1] << " (" << e.what() << ")" << std::endl;
         return 1;

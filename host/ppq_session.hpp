@@ -9,6 +9,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
+#include <new>
+#include <utility>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -42,6 +45,93 @@ struct Dev {
     }
     void upload(const T* h, size_t count) { cu(cudaMemcpy(p, h, count * sizeof(T), cudaMemcpyHostToDevice), "H2D copy"); }
     void download(T* h, size_t count) const { cu(cudaMemcpy(h, p, count * sizeof(T), cudaMemcpyDeviceToHost), "D2H copy"); }
+};
+
+// Host memory of the ciphertext batches.  In the one-shot tools it is plain malloc.  A resident process
+// (ppq_served) turns the pool on: blocks come from cudaHostAlloc (pinned: host<->device copies run at the PCIe rate, not
+// through the driver's pageable staging) and go back to a free list instead of being released, so a steady-state round
+// allocates nothing.
+struct HostPool {
+    bool pinned = false;
+    std::mutex mu;
+    std::multimap<size_t, void*> free_blocks;  // by capacity
+    std::map<void*, size_t> live;              // pinned blocks handed out -> capacity
+    static HostPool& get() {
+        static HostPool p;
+        return p;
+    }
+    void* take(size_t bytes) {
+        if (!pinned) {
+            void* q = std::malloc(bytes ? bytes : 1);
+            if (!q) throw std::bad_alloc();
+            return q;
+        }
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = free_blocks.lower_bound(bytes);
+        if (it != free_blocks.end() && it->first <= 2 * bytes + (1u << 20)) {
+            void* q = it->second;
+            live[q] = it->first;
+            free_blocks.erase(it);
+            return q;
+        }
+        void* q = nullptr;
+        const size_t cap = bytes ? bytes : 1;
+        if (cudaHostAlloc(&q, cap, cudaHostAllocDefault) != cudaSuccess) throw std::bad_alloc();
+        live[q] = cap;
+        return q;
+    }
+    void give(void* q) {
+        if (!q) return;
+        std::unique_lock<std::mutex> lk(mu);
+        auto it = live.find(q);
+        if (it == live.end()) {  // a malloc block (the pool was off when it was taken)
+            lk.unlock();
+            std::free(q);
+            return;
+        }
+        free_blocks.emplace(it->second, q);
+        live.erase(it);
+    }
+};
+template <class T>
+struct PoolAlloc {
+    typedef T value_type;
+    PoolAlloc() {}
+    template <class U>
+    PoolAlloc(const PoolAlloc<U>&) {}
+    T* allocate(size_t n) { return static_cast<T*>(HostPool::get().take(n * sizeof(T))); }
+    void deallocate(T* p, size_t) { HostPool::get().give(p); }
+    // resize() leaves new residues uninitialised (every word is written by the decoder or a device->host copy)
+    template <class U>
+    void construct(U* p) { ::new (static_cast<void*>(p)) U; }
+    template <class U, class... A>
+    void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
+    template <class U>
+    bool operator==(const PoolAlloc<U>&) const { return true; }
+    template <class U>
+    bool operator!=(const PoolAlloc<U>&) const { return false; }
+};
+typedef std::vector<uint64_t, PoolAlloc<uint64_t>> HVec;
+
+// grow-only device buffer for a resident process (Dev<T> allocates and frees per use)
+template <class T>
+struct DevGrow {
+    T* p = nullptr;
+    size_t cap = 0;
+    DevGrow() {}
+    DevGrow(const DevGrow&) = delete;
+    DevGrow& operator=(const DevGrow&) = delete;
+    ~DevGrow() { if (p) cudaFree(p); }
+    T* ensure(size_t count) {
+        if (count > cap) {
+            if (p) cudaFree(p);
+            p = nullptr;
+            cap = 0;
+            cu(cudaMalloc(&p, count * sizeof(T)), "cudaMalloc");
+            cap = count;
+        }
+        return p;
+    }
 };
 
 struct Session {
@@ -115,7 +205,7 @@ struct Batch {
     uint32_t ell = 0;
     std::vector<size_t> index;         // position in the file-order blob list
     std::vector<wire::CtMeta> meta;
-    std::vector<uint64_t> data;
+    HVec data;
     size_t n() const { return index.size(); }
 };
 // decode all blobs, grouped by limb count (one group in every file the reference flow produces)
@@ -204,12 +294,12 @@ inline std::map<uint32_t, Batch> decode_all(const Session& s, const std::vector<
     return groups;
 }
 inline void encode_back(const Session& s, const Batch& b, uint32_t ell_out, const std::vector<wire::CtMeta>& meta,
-                        const std::vector<uint64_t>& data, const std::vector<BlobRef>& refs) {
+                        const uint64_t* data, const std::vector<BlobRef>& refs) {
     const size_t ct = (size_t)2 * ell_out * s.N;
     s.codec.warn_once();
     // each new blob overwrites the text of the blob it replaces (same or shorter), so nothing is allocated in the loop
 #pragma omp parallel for schedule(dynamic)
-    for (size_t k = 0; k < b.n(); ++k) s.codec.encode_to(*refs[b.index[k]].slot, meta[k], ell_out, data.data() + k * ct);
+    for (size_t k = 0; k < b.n(); ++k) s.codec.encode_to(*refs[b.index[k]].slot, meta[k], ell_out, data + k * ct);
 }
 
 // CryptoObject::keyTag of a new key pair: 32 hex digits (OpenFHE's GenerateUniqueKeyID writes 128 random bits this way)
