@@ -486,9 +486,9 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from ppqsflhe_b200 import Communicator, CryptoContext
+    from ppqsflhe_b200 import Communicator, CryptoContext, EvalKey
     from ppqsflhe_b200._capi import check, lib, vp
-    from ppqsflhe_b200.aggregate import clients_of_rank
+    from ppqsflhe_b200.aggregate import clients_of_rank, plan_shards
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -615,7 +615,7 @@ def main():
         old_aff, near_cpus = bind_near_gpu(local)
         pool_n = max(1, min(len(my_clients), 4))
         nk = len(keys)
-        rks = (vp * max(1, nk))(*[k.h for k in keys])
+        qv_all = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
 
         def e2e_leg(packed):
             """one format of the host buffers: [n_slots][2][ell][N] u64, or packed residues (bitlen(q_i) bits each)"""
@@ -632,22 +632,51 @@ def main():
                     else:
                         p.copy_(cts[i].data.view(-1))
             h_acc = torch.empty(words, dtype=torch.int64).pin_memory()
-            h2d = len(my_clients) * words * 8
             d2h = words * 8 if rank == 0 else 0
-            ptrs = (vp * max(1, nk))(*[pool[i % pool_n].data_ptr() for i in range(nk)])
             sfx = "_packed" if packed else ""
             f_one = getattr(lib(), "ppq_reencrypt_aggregate_host" + sfx)
             f_ranks = getattr(lib(), "ppq_reencrypt_aggregate_host" + sfx + "_ranks")
             f_copy = getattr(lib(), "ppq_copy_ceiling_host" + sfx)
+            # Shards for the host-buffer path.  The ranks of one box do not all copy at the same rate (8-GPU B200 box, all
+            # ranks copying: 23 GB/s on GPUs 0-3, 35 GB/s on GPUs 4-7, tools/copy_rates.py), and the step ends with the
+            # slowest rank: every rank times one copy-only pass of an equal shard while all ranks copy, the per-client
+            # costs are gathered and ppq_plan_shards gives each rank the clients it can move in the same time.
+            nk_e, shards, costs = nk, None, None
+            if world > 1:
+                ptrs0 = (vp * max(1, nk))(*[pool[i % pool_n].data_ptr() for i in range(nk)])
+                mine_ms = []
+                for _ in range(2):  # the second pass is the measurement
+                    dist.barrier()
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    check(f_copy(cc.h, ell, ptrs0, nk, n_slots, vp(h_acc.data_ptr())))  # synchronous
+                    mine_ms.append((time.perf_counter() - t0) * 1e3)
+                ct = torch.tensor([mine_ms[-1] / max(1, nk) if nk else 1e9], device=dev, dtype=torch.float64)
+                allc = [torch.zeros_like(ct) for _ in range(world)]
+                dist.all_gather(allc, ct)
+                costs = [float(c.item()) for c in allc]
+                shards = plan_shards(cfg["clients"], costs)
+                nk_e = shards[rank]
+            while len(keys) < nk_e:  # a rank that takes more clients holds their re-encryption keys too
+                keys.append(EvalKey(cc, _rand_res(torch, dev, (cc.dnum, M, N), qv_all.view(1, M, 1)),
+                                    _rand_res(torch, dev, (cc.dnum, M, N), qv_all.view(1, M, 1))))
+            rks_e = (vp * max(1, nk_e))(*[k.h for k in keys[:nk_e]])
+            ptrs = (vp * max(1, nk_e))(*[pool[i % pool_n].data_ptr() for i in range(nk_e)])
+            h2d = nk_e * words * 8
             if world == 1:
                 def e2e_step():
-                    check(f_one(cc.h, rks, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
+                    check(f_one(cc.h, rks_e, ell, ptrs, nk_e, n_slots, vp(h_acc.data_ptr())))
             else:
                 def e2e_step():
-                    check(f_ranks(cc.h, comm.h, 0, rks, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
+                    check(f_ranks(cc.h, comm.h, 0, rks_e, ell, ptrs, nk_e, n_slots, vp(h_acc.data_ptr())))
 
             def copy_step():
-                check(f_copy(cc.h, ell, ptrs, nk, n_slots, vp(h_acc.data_ptr())))
+                check(f_copy(cc.h, ell, ptrs, nk_e, n_slots, vp(h_acc.data_ptr())))
+                if world > 1:
+                    # the real step ends in a collective, so no rank starts its next uploads while another still copies;
+                    # without the same rendezvous here the early ranks take bandwidth from the late ones and the
+                    # "ceiling" comes out BELOW the real leg (171 vs 198 GB/s on the 8-GPU box)
+                    dist.barrier()
 
             for _ in range(args.warmup):
                 e2e_step()
@@ -671,6 +700,10 @@ def main():
                     "note": f"every client's {words * 8 >> 20} MiB upload is copied each step from a pool of {pool_n} "
                             "pinned buffers",
                     "host_cpus_near_gpu": near_cpus,
+                    "shards": shards, "shard_cost_ms_per_client": costs,
+                    "shard_note": None if shards is None else
+                    "clients per rank from ppq_plan_shards over each rank's measured copy-only time per client (all ranks "
+                    "copying at once); the device-resident `value` keeps equal shards",
                     "copy_gbs": bytes_step / (e_ms / args.steps * 1e-3) / 1e9,
                     "h2d_ceiling_gbs": bytes_step / (c_ms / args.steps * 1e-3) / 1e9,
                     "ceiling_value": c_val, "frac_of_copy_ceiling": e_val / c_val,

@@ -230,6 +230,13 @@ void ppq_comm_destroy(ppq_comm*);
 /* d_acc [n][2][ell][N] in place: the sum lands on `root` (root < 0: on every rank), canonical */
 int ppq_reduce_across_ranks(ppq_ctx*, ppq_comm*, int ell, uint64_t* d_acc, size_t n, int root, void* stream);
 
+/* ---- shard planning for ranks that do not all move data at the same rate (host only, no device is touched): cost[r] =
+ *      seconds rank r needs per client (e.g. one timed ppq_copy_ceiling_host_packed of an equal shard / its clients);
+ *      counts[r] = clients for rank r, minimising max_r counts[r] * cost[r] with sum counts = n_clients.  Deterministic:
+ *      every rank holding the same cost vector computes the same plan.  The reference aggregates on one host
+ *      (server/src/aggregateEncryptedWeights.cpp:68-110); this belongs to SURVEY.md 8 row e. */
+int ppq_plan_shards(size_t n_clients, int world, const double* cost, size_t* counts);
+
 /* ---- host-buffer convenience (the call a drop-in server makes once every client's upload has arrived):
  *      h_cts[client] -> [n_slots][2][ell][N] in host memory (pinned for full PCIe rate); rekeys[n_clients];
  *      h_acc [n_slots][2][ell][N] = sum over clients of ReEncrypt(ct, rekey[client]) (ppq_agg_* inside).  Uploads

@@ -103,6 +103,7 @@ _SIGS = {
     "ppq_reencrypt_aggregate_host_packed_ranks": (C.c_int, [vp, vp, C.c_int, C.POINTER(vp), C.c_int, C.POINTER(vp),
                                                             C.c_size_t, C.c_size_t, vp]),
     "ppq_copy_ceiling_host_packed": (C.c_int, [vp, C.c_int, C.POINTER(vp), C.c_size_t, C.c_size_t, vp]),
+    "ppq_plan_shards": (C.c_int, [C.c_size_t, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_size_t)]),
     "ppq_launch_count": (C.c_uint64, []),
     "ppq_profile_enable": (C.c_int, [vp, C.c_int]),
     "ppq_profile_read": (C.c_int, [vp, f64p, u64p, C.c_int]),

@@ -12,11 +12,29 @@ the uint64 sum.
 MAX_WORLD = 15
 
 
-def clients_of_rank(n_clients, world, rank):
-    """Round-robin client partition: rank r owns clients {c : c mod world == r} (its rekeys live only there)."""
+def clients_of_rank(n_clients, world, rank, counts=None):
+    """Client partition: rank r owns its clients' rekeys and nobody else's.  Without `counts`: round-robin,
+    {c : c mod world == r}.  With `counts` (plan_shards): contiguous blocks of counts[r] clients."""
     if not (0 <= rank < world):
         raise ValueError("rank out of range")
-    return [c for c in range(n_clients) if c % world == rank]
+    if counts is None:
+        return [c for c in range(n_clients) if c % world == rank]
+    if len(counts) != world or sum(counts) != n_clients or min(counts) < 0:
+        raise ValueError("counts must be one non-negative entry per rank summing to n_clients")
+    first = sum(counts[:rank])
+    return list(range(first, first + counts[rank]))
+
+
+def plan_shards(n_clients, cost):
+    """Clients per rank when the ranks do not move data at the same rate (ppq_plan_shards, include/ppq_b200.h): cost[r] =
+    seconds per client on rank r; minimises max_r counts[r] * cost[r].  Host only."""
+    import ctypes as C
+    from ._capi import check, lib
+    world = len(cost)
+    c = (C.c_double * world)(*[float(x) for x in cost])
+    out = (C.c_size_t * world)()
+    check(lib().ppq_plan_shards(n_clients, world, c, out))
+    return [int(x) for x in out]
 
 
 def reduce_partial_sums(acc, world, dst=0, group=None):

@@ -1691,6 +1691,26 @@ extern "C" int ppq_reduce_across_ranks(ppq_ctx* c, ppq_comm* m, int ell, uint64_
     return PPQ_OK;
 }
 
+// ------------------------------------------------------------------------------------------- shard planning
+// Clients per rank for a job whose ranks do not all move data at the same rate (measured on the 8-GPU B200 box with all
+// ranks copying: 23 GB/s host->device on GPUs 0-3, 35 GB/s on GPUs 4-7, profiles/r16_notes.md): cost[r] is the time rank r
+// needs per client (e.g. one timed ppq_copy_ceiling_host_packed of an equal shard, divided by its clients); counts[r]
+// minimises max_r counts[r] * cost[r] with sum counts = n_clients (greedy on the next finishing time, exact for this
+// objective; ties go to the lower rank, so every rank that holds the same cost vector computes the same plan).
+extern "C" int ppq_plan_shards(size_t n_clients, int world, const double* cost, size_t* counts) {
+    if (world < 1 || !cost || !counts) return fail(PPQ_EINVAL, "ppq_plan_shards: bad argument");
+    for (int r = 0; r < world; ++r)
+        if (!(cost[r] > 0.0) || !std::isfinite(cost[r])) return fail(PPQ_EINVAL, "ppq_plan_shards: costs must be positive and finite");
+    for (int r = 0; r < world; ++r) counts[r] = 0;
+    for (size_t c = 0; c < n_clients; ++c) {
+        int best = 0;
+        for (int r = 1; r < world; ++r)
+            if ((double)(counts[r] + 1) * cost[r] < (double)(counts[best] + 1) * cost[best]) best = r;
+        ++counts[best];
+    }
+    return PPQ_OK;
+}
+
 // ------------------------------------------------------------------------------------------- packed residues
 // Wire format of the *_host_packed calls: a residue of limb i needs bitlen(q_i) bits, not 64 (C3: 1142 of 1280 bits per
 // coefficient), and the host->device copy is what bounds the end-to-end path.  Packed ciphertext = [2][ell] limbs, limb

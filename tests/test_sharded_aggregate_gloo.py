@@ -24,7 +24,7 @@ def _worker(rank, world, port, q):
     import torch
     import torch.distributed as dist
     import oracle
-    from ppqsflhe_b200.aggregate import clients_of_rank, reduce_partial_sums
+    from ppqsflhe_b200.aggregate import clients_of_rank, plan_shards, reduce_partial_sums
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     o = oracle.Oracle.synthetic(12, 2, 60, 40, 20, 2)
     ell, n_clients, n_slots = o.L, 5, 2
@@ -34,7 +34,10 @@ def _worker(rank, world, port, q):
     keys = [(rng.integers(0, 1 << 62, (o.dnum, o.M, o.N), dtype=np.uint64) % mods.reshape(1, o.M, 1),
              rng.integers(0, 1 << 62, (o.dnum, o.M, o.N), dtype=np.uint64) % mods.reshape(1, o.M, 1))
             for _ in range(n_clients)]
-    mine = clients_of_rank(n_clients, world, rank)
+    # ranks that move data at different rates get unequal shards (ppq_plan_shards); the sum must not care
+    counts = plan_shards(n_clients, [1.0, 2.5, 1.7][:world])
+    assert sum(counts) == n_clients and counts[0] > counts[1]
+    mine = clients_of_rank(n_clients, world, rank, counts)
     part = o.reencrypt_accumulate_batch(ell, cts[mine], [keys[c][0] for c in mine], [keys[c][1] for c in mine])
     t = torch.from_numpy(part.view(np.int64).copy())
     reduce_partial_sums(t, world, dst=0)
@@ -74,3 +77,28 @@ def test_partition_and_overflow_guard():
         reduce_partial_sums(None, 16)
     with pytest.raises(ValueError):
         clients_of_rank(4, 2, 2)
+
+
+def test_shard_plan_minimises_the_slowest_rank():
+    import itertools
+    from ppqsflhe_b200.aggregate import clients_of_rank, plan_shards
+    # equal costs: balanced; the 8-GPU box's measured copy rates (23.1 GB/s on four ranks, 35.1 GB/s on the others)
+    assert sorted(plan_shards(64, [1.0] * 8)) == [8] * 8
+    c = plan_shards(64, [1 / 23.1] * 4 + [1 / 35.1] * 4)
+    assert c == [6, 6, 6, 6, 10, 10, 10, 10]
+    # optimal against brute force on small cases, and deterministic
+    for cost in ([1.0, 2.0], [3.0, 1.0, 2.0], [1.0, 1.0, 5.0], [0.5, 0.7, 0.9, 1.1]):
+        for n in (0, 1, 5, 9):
+            got = plan_shards(n, cost)
+            assert sum(got) == n and got == plan_shards(n, cost)
+            best = min(max(k * w for k, w in zip(ks, cost))
+                       for ks in itertools.product(range(n + 1), repeat=len(cost)) if sum(ks) == n)
+            assert max(k * w for k, w in zip(got, cost)) == pytest.approx(best)
+            seen = sorted(x for r in range(len(cost)) for x in clients_of_rank(n, len(cost), r, got))
+            assert seen == list(range(n))
+    from ppqsflhe_b200._capi import PPQError
+    for bad in ([1.0, 0.0], [1.0, -2.0], [float("nan")], [float("inf"), 1.0]):
+        with pytest.raises(PPQError):
+            plan_shards(4, bad)
+    with pytest.raises(ValueError):
+        clients_of_rank(4, 2, 0, [3, 2])
