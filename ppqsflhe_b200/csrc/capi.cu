@@ -1049,8 +1049,6 @@ extern "C" int ppq_encode_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, cons
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = c->hp.N;
-    const int* ids;
-    if (int rc = cyc_ids(c, ell, &ids)) return rc;
     int sf_exp = 0;
     std::frexp(sf, &sf_exp);
     const int approx = sf_exp > 58 ? sf_exp - 58 : 0;  // as ppq_encode: round at sf / 2^approx, then times 2^approx
@@ -1065,8 +1063,8 @@ extern "C" int ppq_encode_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, cons
         double2* z = reinterpret_cast<double2*>(vee + m * 3 * ell * N);
         int64_t* co = reinterpret_cast<int64_t*>(vee + m * (3 * (size_t)ell + 1) * N);
         ckks::launch_encode_fft(c->fft, d_vals + s0 * n_vals, n_vals, std::ldexp(sf, -approx), z, co, m, st);
-        launch_small_fwd_ntt(c->k, small + s0 * 3 * N, vee, 3, ell, m, ids, st, co, approx);
-        launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, nullptr, (u64*)ct + s0 * 2 * ell * N, ell, m, st);
+        launch_small_fwd_encrypt(c->k, small + s0 * 3 * N, vee, ell, m, (const u64*)pkb, (const u64*)pka, nullptr,
+                                 (u64*)ct + s0 * 2 * ell * N, st, co, approx);
     }
     CU(cudaGetLastError());
     return PPQ_OK;
@@ -1080,15 +1078,13 @@ extern "C" int ppq_encrypt(ppq_ctx* c, int ell, const uint64_t* pkb, const uint6
     CU(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = c->hp.N;
-    const int* ids;
-    if (int rc = cyc_ids(c, ell, &ids)) return rc;
     const size_t step = rows_chunk(3 * ell);
     CU(c->scratch2.ensure(std::min(n, step) * 3 * ell * N));
     for (size_t s0 = 0; s0 < n; s0 += step) {
         const size_t m = std::min(step, n - s0);
         u64* vee = c->scratch2.p;  // [m][3][ell][N]
-        launch_small_fwd_ntt(c->k, small + s0 * 3 * N, vee, 3, ell, m, ids, st);
-        launch_encrypt_pw(c->k, (const u64*)pkb, (const u64*)pka, vee, (const u64*)pt + s0 * ell * N, (u64*)ct + s0 * 2 * ell * N, ell, m, st);
+        launch_small_fwd_encrypt(c->k, small + s0 * 3 * N, vee, ell, m, (const u64*)pkb, (const u64*)pka,
+                                 (const u64*)pt + s0 * ell * N, (u64*)ct + s0 * 2 * ell * N, st);
     }
     CU(cudaGetLastError());
     return PPQ_OK;

@@ -621,6 +621,60 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 6 : PPQ_ROW_MINB
     }
 }
 
+// Forward ROW pass of the three small polynomials of a fresh ciphertext (v, e0 [+ m], e1: vee [g][3][ell][N], COL-pass
+// output) with the Encrypt combine as its epilogue: c0 = pkb * v + e0 (+ pt), c1 = pka * v + e1, written straight into the
+// ciphertext.  The three transforms of a (ciphertext, limb, row) run in one thread group with the same twiddles; v stays
+// in registers.  Same canonical values as k_fwd_row_plain followed by k_encrypt_pw, without the [3][ell][N] round trip
+// through HBM (C3: 63 MB per ciphertext).  grid (n1 / R, 1, n_ct * ell)
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB)
+    k_fwd_row_encrypt(KCtx c, const u64* __restrict__ vee, const u64* __restrict__ pkb, const u64* __restrict__ pka,
+                      const u64* __restrict__ pt, u64* __restrict__ ct, int ell) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const int i = blockIdx.z % ell;
+    const size_t g = blockIdx.z / ell;
+    const LimbC lc = c.limbs[i];
+    const ulonglong2* tw = c.twf + (size_t)i * N;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    const size_t roff = (size_t)row * n2;
+    u64 v[8];
+#pragma unroll 1
+    for (int s3 = 0; s3 < 3; ++s3) {
+        const u64* p = vee + ((g * 3 + s3) * ell + i) * N + roff;
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = p[point_of<S - 3>(u, k)];
+        fwd_pass<S, RowPos<S>, FWD_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true, PPQ_Z(lc));
+        if (FwdOut<S, FWD_ROW_IN>::B > 8 && lc.sh >= 28u) {  // block-uniform
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = canon16_q(a[k], lc);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = canon_b<FwdOut<S, FWD_ROW_IN>::B>(a[k], lc);
+        }
+        if (s3 == 0) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = a[k];
+        } else {
+            u64 key[8];
+            ld8_ro(key, (s3 == 1 ? pkb : pka) + (size_t)i * N + roff + 8 * u);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = addmod(mulmod_barrett(v[k], key[k], lc), a[k], lc.q);
+            if (s3 == 1 && pt != nullptr) {
+                u64 m[8];
+                ld8_ro(m, pt + (g * ell + i) * N + roff + 8 * u);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], m[k], lc.q);
+            }
+            st8(ct + ((g * 2 + (s3 - 1)) * ell + i) * N + roff + 8 * u, a);
+        }
+    }
+}
+
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB)
     k_inv_row(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs,
@@ -1775,6 +1829,20 @@ void launch_small_fwd_ntt(const KCtx& c, const int64_t* small, u64* out, int n_s
     count_launch();
     PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_plain<S><<<dim3(n1 / RowGeom<S>::R, 1, (unsigned)(n_groups * ny)), RowGeom<S>::THREADS, 0, st>>>(
                                 c, out, 0, d_cyc_ids, 1)));
+}
+
+void launch_small_fwd_encrypt(const KCtx& c, const int64_t* small, u64* vee, int ell, size_t n_ct, const u64* pkb,
+                              const u64* pka, const u64* pt, u64* ct, cudaStream_t st, const int64_t* pt_coeff,
+                              int pt_approx) {
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1, ny = 3 * ell;
+    const size_t gs = (size_t)ny << c.logN;
+    const u64 mode_arg = (u64)ell | ((u64)(pt_coeff ? pt_approx : 0) << 32);
+    PPQ_COL_DISPATCH(sp.S1, (fwd_col_launch<S, 3>(c, reinterpret_cast<const u64*>(small), (size_t)3, vee, gs, nullptr,
+                                                  reinterpret_cast<const u64*>(pt_coeff), nullptr, mode_arg, ny, (int)n_ct, st)));
+    count_launch();
+    PPQ_ROW_DISPATCH(sp.S2, (k_fwd_row_encrypt<S><<<dim3(n1 / RowGeom<S>::R, 1, (unsigned)(n_ct * ell)), RowGeom<S>::THREADS, 0, st>>>(
+                                c, vee, pkb, pka, pt, ct, ell)));
 }
 
 void launch_sw_fwd_col(const KCtx& c, const u64* src, size_t src_gs, u64* dst, size_t dst_gs, const BcJob* d_jobs,

@@ -179,6 +179,13 @@ void launch_mult_scalar_polys(const KCtx& c, const u64* in, u64* out, const u64*
 // pt_coeff != nullptr ([n_groups][N] int64, needs n_small >= 2): slot 1 becomes NTT(small[g][1] + pt_coeff[g] * 2^pt_approx)
 void launch_small_fwd_ntt(const KCtx& c, const int64_t* small, u64* out, int n_small, int ell, size_t n_groups,
                           const int* d_cyc_ids, cudaStream_t st, const int64_t* pt_coeff = nullptr, int pt_approx = 0);
+// Encrypt from the sampled polynomials in one pair of launches: COL pass of small [n_ct][3][N] (v, e0, e1; the encoded
+// plaintext coefficients pt_coeff * 2^pt_approx join e0 when given) into vee [n_ct][3][ell][N], then the ROW pass with the
+// combine ct[g][0] = pkb*v + e0 (+ pt), ct[g][1] = pka*v + e1 as its epilogue (vee is never read back as EVAL data).
+// pt: optional EVAL plaintext [n_ct][ell][N]
+void launch_small_fwd_encrypt(const KCtx& c, const int64_t* small, u64* vee, int ell, size_t n_ct, const u64* pkb,
+                              const u64* pka, const u64* pt, u64* ct, cudaStream_t st, const int64_t* pt_coeff = nullptr,
+                              int pt_approx = 0);
 // encrypt combine: ct[g][0][i] = pkb[i]*v + e0 + m ; ct[g][1][i] = pka[i]*v + e1   (all EVAL); pt may be nullptr (m = 0)
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee /*[g][3][ell][N]*/,
                        const u64* pt /*[g][ell][N]*/, u64* ct, int ell, size_t n_ct, cudaStream_t st);
