@@ -1246,7 +1246,8 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     auto it = c->garner.find(ell);
     if (it == c->garner.end()) {
         // Garner constants, once per ell: ginv[i] = (q_0..q_{i-1})^-1 mod q_i, then the table q_k mod q_i
-        std::vector<u64> g((size_t)ell + (size_t)ell * ell, 0);
+        // ... and q_0 q_1 q_2 mod q_i for the short interpolation's check
+        std::vector<u64> g((size_t)ell + (size_t)ell * ell + (size_t)ell, 0);
         for (int i = 1; i < ell; ++i) {
             u64 pr = 1;
             for (int k = 0; k < i; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
@@ -1254,6 +1255,11 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
         }
         for (int i = 0; i < ell; ++i)
             for (int k = 0; k < ell; ++k) g[(size_t)ell + (size_t)i * ell + k] = c->hp.mod[k] % c->hp.mod[i];
+        for (int i = 3; i < ell; ++i) {
+            u64 pr = 1;
+            for (int k = 0; k < 3; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
+            g[(size_t)ell + (size_t)ell * ell + i] = pr;
+        }
         std::unique_ptr<DevBuf<u64>> b(new DevBuf<u64>);
         CU(b->upload(g));
         it = c->garner.emplace(ell, std::move(b)).first;
@@ -1264,7 +1270,7 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     for (size_t s0 = 0; s0 < n; s0 += step) {
         const size_t m = std::min(step, n - s0);
         double2* z = reinterpret_cast<double2*>(c->scratch2.p);
-        ckks::launch_decode(c->fft, c->k, (const u64*)coeff + s0 * ell * N, ell, gin, gin + ell, sf, z, d_vals + s0 * (N / 2), m, st);
+        ckks::launch_decode(c->fft, c->k, (const u64*)coeff + s0 * ell * N, ell, gin, gin + ell, gin + ell + (size_t)ell * ell, sf, z, d_vals + s0 * (N / 2), m, st);
     }
     CU(cudaGetLastError());
     return PPQ_OK;

@@ -181,41 +181,88 @@ __global__ void __launch_bounds__(FB_THREADS)
 // double conversion of CKKSPackedEncoding::Decode).  Digits v_i: X = sum v_i * prod_{k<i} q_k.
 // X > (Q-1)/2  <=>  digits compare above ((q_i-1)/2)_i from the top; then Q - X has digits q_i-1-v_i, plus 1.
 #define PPQ_MAX_DECODE_LIMBS 64
+// digits v_0..v_{n_lim-1} of the residues x_i = x[i * N] (stride N), generic limb count: O(n_lim^2) Barrett steps
+__device__ __forceinline__ void garner_digits(const KCtx& c, const u64* __restrict__ x, u32 N, int n_lim, int ell,
+                                              const u64* __restrict__ ginv, const u64* __restrict__ qmod, u64* v) {
+    v[0] = x[0];
+    for (int i = 1; i < n_lim; ++i) {
+        const LimbC li = c.limbs[i];
+        const u64* qm = qmod + (size_t)i * ell;  // q_k mod q_i, k < i (host table: no reduction of constants here)
+        // Horner in mixed radix: acc = v_0 + q_0 (v_1 + q_1 (...)) mod q_i, one 128-bit multiply-add and ONE Barrett
+        // reduction per step (acc < q_i, q_k mod q_i < q_i, v_k < 2^60: the operand stays below 2^121)
+        u64 acc = 0;
+        for (int k = i - 1; k >= 0; --k) {
+            unsigned __int128 t = (unsigned __int128)acc * qm[k] + v[k];
+            acc = barrett128((u64)(t >> 64), (u64)t, li);
+        }
+        v[i] = mulmod_barrett(submod(x[(size_t)i * N], acc, li.q), ginv[i], li);
+    }
+}
+// centred value of the mixed-radix number (v_i) over the first n_lim moduli, as a double
+__device__ __forceinline__ double centred_double(const KCtx& c, const u64* v, int n_lim, bool* neg_out) {
+    bool neg = false;
+    for (int i = n_lim - 1; i >= 0; --i) {
+        const u64 h = (c.limbs[i].q - 1) >> 1;
+        if (v[i] != h) {
+            neg = v[i] > h;
+            break;
+        }
+    }
+    double d = 0.0;
+    for (int i = n_lim - 1; i >= 0; --i) {
+        const u64 q = c.limbs[i].q;
+        const u64 dig = neg ? q - 1 - v[i] : v[i];
+        d = d * (double)q + (double)dig;
+    }
+    *neg_out = neg;
+    return neg ? -(d + 1.0) : d;
+}
+// all ell limbs (the definition); kept out of line so that its 64-word digit array costs the short path nothing
+__device__ __noinline__ double crt_full(const KCtx& c, const u64* __restrict__ x, u32 N, int ell,
+                                        const u64* __restrict__ ginv, const u64* __restrict__ qmod) {
+    u64 v[PPQ_MAX_DECODE_LIMBS];
+    garner_digits(c, x, N, ell, ell, ginv, qmod, v);
+    bool neg;
+    return centred_double(c, v, ell, &neg);
+}
+// A decrypted CKKS coefficient is small against Q (|m + noise| ~ 2^60..2^120 against Q ~ 2^(60 ell)).  If y, the centred
+// value of the residues modulo P3 = q_0 q_1 q_2 alone, ALSO reproduces every other residue, then y is congruent to X
+// modulo Q and |y| <= P3 / 2 < Q / 2, i.e. y IS the centred representative the full interpolation returns -- with the
+// same three low digits, so the double comes out bit for bit the same (the 17 leading digits contribute exact zeros).
+// 3 + 2 (ell - 3) Barrett steps per coefficient instead of ell (ell - 1) / 2; a coefficient that fails the check (it
+// never does for a decryption of a valid ciphertext) takes the full path.
+constexpr int CRT_FAST = 3;
 __global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell, const u64* __restrict__ ginv,
-                                 const u64* __restrict__ qmod, double sf, double2* __restrict__ z) {
+                                 const u64* __restrict__ qmod, const u64* __restrict__ p3mod, double sf,
+                                 double2* __restrict__ z) {
     const u32 N = 1u << c.logN, Nh = N / 2;
     const size_t g = blockIdx.y;
-    const u64* x = coeff + g * (size_t)ell * N;
+    const u64* xg = coeff + g * (size_t)ell * N;
     for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
-        u64 v[PPQ_MAX_DECODE_LIMBS];
-        v[0] = x[n];
-        for (int i = 1; i < ell; ++i) {
-            const LimbC li = c.limbs[i];
-            const u64* qm = qmod + (size_t)i * ell;  // q_k mod q_i, k < i (host table: no reduction of constants here)
-            // Horner in mixed radix: acc = v_0 + q_0 (v_1 + q_1 (...)) mod q_i, one 128-bit multiply-add and ONE Barrett
-            // reduction per step (acc < q_i, q_k mod q_i < q_i, v_k < 2^60: the operand stays below 2^121)
-            u64 acc = 0;
-            for (int k = i - 1; k >= 0; --k) {
-                unsigned __int128 t = (unsigned __int128)acc * qm[k] + v[k];
-                acc = barrett128((u64)(t >> 64), (u64)t, li);
+        const u64* x = xg + n;
+        double d;
+        if (ell <= CRT_FAST) {
+            d = crt_full(c, x, N, ell, ginv, qmod);
+        } else {
+            u64 v[CRT_FAST];
+            garner_digits(c, x, N, CRT_FAST, ell, ginv, qmod, v);
+            bool neg;
+            d = centred_double(c, v, CRT_FAST, &neg);
+            bool ok = true;
+            for (int i = CRT_FAST; i < ell; ++i) {
+                const LimbC li = c.limbs[i];
+                const u64* qm = qmod + (size_t)i * ell;
+                u64 acc = 0;
+#pragma unroll
+                for (int k = CRT_FAST - 1; k >= 0; --k) {
+                    unsigned __int128 t = (unsigned __int128)acc * qm[k] + v[k];
+                    acc = barrett128((u64)(t >> 64), (u64)t, li);
+                }
+                if (neg) acc = submod(acc, p3mod[i], li.q);  // y = Y' - P3
+                ok &= acc == x[(size_t)i * N];
             }
-            v[i] = mulmod_barrett(submod(x[(size_t)i * N + n], acc, li.q), ginv[i], li);
+            if (!ok) d = crt_full(c, x, N, ell, ginv, qmod);
         }
-        bool neg = false;
-        for (int i = ell - 1; i >= 0; --i) {
-            const u64 h = (c.limbs[i].q - 1) >> 1;
-            if (v[i] != h) {
-                neg = v[i] > h;
-                break;
-            }
-        }
-        double d = 0.0;
-        for (int i = ell - 1; i >= 0; --i) {
-            const u64 q = c.limbs[i].q;
-            const u64 dig = neg ? q - 1 - v[i] : v[i];
-            d = d * (double)q + (double)dig;
-        }
-        if (neg) d = -(d + 1.0);
         d /= sf;
         // stored at the bit-reversed position: FFTSpecial starts with that permutation (k_fft_fwd_block reads contiguously)
         if (n < Nh) z[g * Nh + (__brev(n) >> (33 - c.logN))].x = d;
@@ -229,12 +276,12 @@ __global__ void k_take_real(const double2* __restrict__ z, double* __restrict__ 
 }
 
 void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const u64* d_qmod,
-                   double sf, double2* z, double* d_vals, size_t n, cudaStream_t st) {
+                   const u64* d_p3mod, double sf, double2* z, double* d_vals, size_t n, cudaStream_t st) {
     const unsigned N = 1u << t.logN, Nh = N / 2, m = 2 * N;
     const int bits = t.logN - 1;
     const unsigned logB = bits < FB_LOG ? (unsigned)bits : (unsigned)FB_LOG, B = 1u << logB;
     const size_t smem = (size_t)B * sizeof(double2);
-    k_crt_to_complex<<<grid_for(N, n), 256, 0, st>>>(k, coeff, ell, d_ginv, d_qmod, sf, z);
+    k_crt_to_complex<<<grid_for(N, n), 256, 0, st>>>(k, coeff, ell, d_ginv, d_qmod, d_p3mod, sf, z);
     dim3 grid(Nh / B, (unsigned)n, 1);
     if (Nh <= B) {
         cudaFuncSetAttribute(k_fft_fwd_block<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

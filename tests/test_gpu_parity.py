@@ -1010,3 +1010,40 @@ def test_short_value_vectors_are_zero_padded():
         a = cc.MakeCKKSPackedPlaintext(vals)
         b = cc.MakeCKKSPackedPlaintext(full)
         assert torch.equal(a.data, b.data)
+
+
+@pytest.mark.parametrize("kind,ell", [("c1", 4), ((12, 5, 3, 45), 7), ((13, 3, 2, 30), 3)])
+def test_decode_short_interpolation_and_its_fallback(kind, ell):
+    # ppq_decode interpolates from three limbs and checks the result against every other residue (ckks.cu); values too
+    # large for that (here: values anywhere in (-Q/2, Q/2]) must take the full Garner path.  Residues are made from
+    # Python integers; the checker is the oracle's decode, which always interpolates over all limbs.
+    from ppqsflhe_b200._capi import check, lib, vp
+    from ppqsflhe_b200 import to_device_u64
+    o, cc = _cc_pair(kind)
+    rng = np.random.default_rng(77)
+    n = 2
+    mods = [int(q) for q in o.moduli[:ell]]
+    Q = 1
+    for q in mods:
+        Q *= q
+    small = rng.integers(-(1 << 62), 1 << 62, (n, o.N), dtype=np.int64)
+    vals = [[int(v) for v in small[g]] for g in range(n)]
+    for k in range(0, o.N, 3):           # every third coefficient of ciphertext 1: anywhere in (-Q/2, Q/2]
+        vals[1][k] = int(rng.integers(0, 1 << 62)) * (Q >> 63) - Q // 2 + 1
+    vals[0][5] = -1
+    vals[0][6] = (mods[0] * mods[1] * mods[2]) // 2 if ell > 3 else 7   # the edge of the short path's range
+    vals[0][7] = -vals[0][6]
+    co = np.zeros((n, ell, o.N), dtype=np.uint64)
+    for g in range(n):
+        for i, q in enumerate(mods):
+            co[g, i] = np.array([v % q for v in vals[g]], dtype=np.uint64)
+    sf = float(2 ** 40)
+    out = torch.empty((n, o.N // 2), dtype=torch.float64, device=cc.device)
+    d = to_device_u64(co, cc.device)
+    check(lib().ppq_decode(cc.h, ell, vp(d.data_ptr()), sf, vp(out.data_ptr()), n, None))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    for g in range(n):
+        want = o.decode(ell, co[g], sf)
+        scale = max(1.0, float(np.max(np.abs(want))))
+        assert np.max(np.abs(got[g] - want)) / scale < 1e-9
