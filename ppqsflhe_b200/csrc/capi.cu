@@ -1228,8 +1228,7 @@ extern "C" int ppq_decrypt_core(ppq_ctx* c, int ell, const uint64_t* sk, const u
     for (size_t s0 = 0; s0 < n; s0 += step) {
         const size_t m = std::min(step, n - s0);
         u64* co = (u64*)coeff + s0 * ell * N;
-        launch_decrypt_pw(c->k, (const u64*)ct + s0 * 2 * ell * N, (const u64*)sk, co, ell, m, st);
-        launch_ntt_inverse(c->k, co, ids, it->second->p, (int)(m * ell), st);
+        launch_decrypt_inv_ntt(c->k, (const u64*)ct + s0 * 2 * ell * N, (const u64*)sk, co, ell, m, ids, it->second->p, st);
     }
     CU(cudaGetLastError());
     return PPQ_OK;

@@ -701,6 +701,34 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB
     }
 }
 
+// Inverse ROW pass with the Decrypt combine c0 + c1 * s as its prologue (a pointwise kernel followed by k_inv_row, without
+// the [ell][N] round trip through HBM).  out [n_ct][ell][N]; grid (n1 / R, 1, n_ct * ell)
+template <int S>
+__global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB)
+    k_inv_row_decrypt(KCtx c, const u64* __restrict__ ct, const u64* __restrict__ sk, u64* __restrict__ out, int ell) {
+    typedef RowGeom<S> G;
+    __shared__ u64 sm[G::SMEM];
+    const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
+    const u32 w = threadIdx.x / G::TPT, u = threadIdx.x % G::TPT;
+    const u32 row = blockIdx.x * G::R + w;
+    const int i = blockIdx.z % ell;
+    const size_t g = blockIdx.z / ell;
+    const LimbC lc = c.limbs[i];
+    const ulonglong2* tw = c.twi + (size_t)i * N;
+    const size_t roff = (size_t)row * n2;
+    RowPos<S> pos{w * (u32)RowPos<S>::PITCH};
+    u64 a[8], c1[8], s[8];
+    ld8(a, ct + ((g * 2 + 0) * ell + i) * N + roff + 8 * u);
+    ld8(c1, ct + ((g * 2 + 1) * ell + i) * N + roff + 8 * u);
+    ld8_ro(s, sk + (size_t)i * N + roff + 8 * u);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], mulmod_barrett(c1[k], s[k], lc), lc.q);
+    inv_pass<S, RowPos<S>, INV_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    u64* o = out + (g * ell + i) * N + roff;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy (< 8q): consumed by k_inv_col
+}
+
 // Inverse ROW pass over pairs of ciphertexts (see k_fwd_row_plain2).
 // Measured on B200, C3: 6.3 + 4.5 -> 6.0 + 4.3 us/ct.
 #ifndef PPQ_INV_X2
@@ -1636,19 +1664,6 @@ __global__ void k_rekeygen_pw(KCtx c, const u64* __restrict__ pkb, const u64* __
         oa[n] = addmod(mulmod_barrett(__ldg(a + n), uv, lc), e1[n], lc.q);
     }
 }
-__global__ void k_decrypt_pw(KCtx c, const u64* __restrict__ ct, const u64* __restrict__ sk, u64* __restrict__ out,
-                             int ell) {
-    const u32 N = 1u << c.logN;
-    const int i = blockIdx.y % ell;
-    const size_t g = blockIdx.y / ell;
-    const LimbC lc = c.limbs[i];
-    const u64* c0 = ct + ((g * 2 + 0) * ell + i) * N;
-    const u64* c1 = ct + ((g * 2 + 1) * ell + i) * N;
-    const u64* s = sk + (size_t)i * N;
-    u64* o = out + (g * ell + i) * N;
-    for (u32 n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x)
-        o[n] = addmod(c0[n], mulmod_barrett(c1[n], __ldg(s + n), lc), lc.q);
-}
 
 // =========================================================================================================
 // launchers
@@ -1791,6 +1806,15 @@ void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t
 #endif
     PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
                                 c, in, in_gs, out, out_gs, d_limb_map, n_g)));
+}
+void launch_decrypt_inv_ntt(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct,
+                            const int* d_cyc_ids, const u64* d_scale4, cudaStream_t st) {
+    count_launch();
+    const Split sp = split_of(c.logN);
+    const int n1 = 1 << sp.S1;
+    PPQ_ROW_DISPATCH(sp.S2, (k_inv_row_decrypt<S><<<dim3(n1 / RowGeom<S>::R, 1, (unsigned)(n_ct * ell)), RowGeom<S>::THREADS, 0, st>>>(
+                                c, ct, sk, out, ell)));
+    launch_inv_col(c, out, 0, d_cyc_ids, d_scale4, (int)(n_ct * ell), 1, st);
 }
 void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale4, int n_slots,
                     int n_g, cudaStream_t st) {
@@ -2091,10 +2115,6 @@ void launch_rekeygen_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64
                         const u64* d_pmod, u64* kb, u64* ka, int L, int M, int alpha, int dnum, cudaStream_t st) {
     count_launch();
     k_rekeygen_pw<<<pw_grid(c, (size_t)dnum * M, 1), 256, 0, st>>>(c, pkb, pka, uee, sk_old, d_pmod, kb, ka, L, M, alpha);
-}
-void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st) {
-    count_launch();
-    k_decrypt_pw<<<pw_grid(c, n_ct * ell, 1), 256, 0, st>>>(c, ct, sk, out, ell);
 }
 
 const char* kernels_build_info() { return "ppq_b200 kernels: sm_100a, radix-8 register groups, 2-pass (COL,ROW) NTT"; }

@@ -189,8 +189,10 @@ void launch_small_fwd_encrypt(const KCtx& c, const int64_t* small, u64* vee, int
 // encrypt combine: ct[g][0][i] = pkb[i]*v + e0 + m ; ct[g][1][i] = pka[i]*v + e1   (all EVAL); pt may be nullptr (m = 0)
 void launch_encrypt_pw(const KCtx& c, const u64* pkb, const u64* pka, const u64* vee /*[g][3][ell][N]*/,
                        const u64* pt /*[g][ell][N]*/, u64* ct, int ell, size_t n_ct, cudaStream_t st);
-// decrypt combine: out[g][i] = c0 + c1 * s   (EVAL)
-void launch_decrypt_pw(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct, cudaStream_t st);
+// Decrypt core in two launches: out[g][i] = iNTT_i(c0 + c1 * s), canonical COEFF residues; the combine is the prologue
+// of the inverse ROW pass.  d_cyc_ids / d_scale4: limb ids 0..ell-1 repeated and the N^-1 factors in that order
+void launch_decrypt_inv_ntt(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct,
+                            const int* d_cyc_ids, const u64* d_scale4, cudaStream_t st);
 // key generation: se [2][M][N] EVAL (s, e), a [M][N] -> sk [L][N], pkb [M][N] = e - a*s
 void launch_keygen_pw(const KCtx& c, const u64* se, const u64* a, u64* sk, u64* pkb, int L, int M, cudaStream_t st);
 // uee [dnum][3][M][N] EVAL (u, e0, e1), sk_old [L][N], d_pmod [L] = P mod q_r -> kb, ka [dnum][M][N]
