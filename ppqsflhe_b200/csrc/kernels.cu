@@ -203,6 +203,64 @@ __global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
     }
 }
 
+// EXPERIMENT (-DPPQ_COL2_PF=<ciphertexts per CTA>): the same pass over PPQ_COL2_PF consecutive ciphertexts per CTA with
+// the NEXT ciphertext's tile on its way into a per-thread staging area of shared memory (cp.async, 16 bytes per copy,
+// no registers held) while the current one is transformed: k_fwd_col2 shows 16 % long_scoreboard stall samples, the
+// loads at the start of every CTA.
+#ifndef PPQ_COL2_PF
+#define PPQ_COL2_PF 0
+#endif
+#if PPQ_COL2_PF
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const u32 d = (u32)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+template <int S, int W2, bool SAME>
+__global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
+    k_fwd_col2p(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_ids, int n_g) {
+    extern __shared__ __align__(16) u64 dsm[];
+    constexpr u32 T = W2 << (S - 3);
+    u64* sm = dsm;                                                              // exchange tile, 2 * (W2 << S) words
+    ulonglong2* stage = reinterpret_cast<ulonglong2*>(dsm + 2 * (W2 << S));  // [8][T], private to each thread
+    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
+    const u32 w = threadIdx.x % W2, u = threadIdx.x / W2;
+    const u32 col = (blockIdx.x * W2 + w) * 2;
+    const u32 y = blockIdx.y;
+    const int limb = limb_ids[y];
+    if (limb < 0) return;  // block-uniform
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    const u32 g0 = blockIdx.z * PPQ_COL2_PF, g1 = min((u32)n_g, g0 + PPQ_COL2_PF);
+    u64* p = data + g0 * gs + (size_t)y * N + col;
+    ulonglong2* mine = stage + threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) cp_async16(mine + k * T, p + (size_t)point_of<S - 3>(u, k) * n2);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (u32 g = g0; g < g1; ++g, p += gs) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        u64 a[8], b[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const ulonglong2 v = mine[k * T];
+            a[k] = v.x;
+            b[k] = v.y;
+        }
+        if (g + 1 < g1) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) cp_async16(mine + k * T, p + gs + (size_t)point_of<S - 3>(u, k) * n2);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
+        fwd_pass_col2<S, W2, FWD_COL_IN>(a, b, sm, w, u, tw, lc.q, lc.q2 << 1, PPQ_Z(lc));
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // lazy (< 16q): consumed by a ROW pass
+            p[(size_t)(8 * u + k) * n2] = a[k];
+            p[(size_t)(8 * u + k) * n2 + 1] = b[k];
+        }
+        if (g + 1 < g1) __syncthreads();  // the exchange tile is reused
+    }
+}
+#endif
+
 template <int S, int W, bool SAME>
 __global__ void __launch_bounds__(W << (S - 3), S == 9 ? PPQ_COL9_MINB : PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
@@ -1718,6 +1776,21 @@ static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* ds
     if constexpr (MODE == 0 && S == 8) {
         if (src == dst && src_gs == dst_gs) {
             constexpr int W2 = PPQ_COL2_W;
+#if PPQ_COL2_PF
+            if (ng >= 2 * PPQ_COL2_PF) {
+                constexpr int SMEM = (2 * (W2 << S) + 16 * (W2 << (S - 3))) * (int)sizeof(u64);
+                dim3 gridp(n2 / (2 * W2), ny, (ng + PPQ_COL2_PF - 1) / PPQ_COL2_PF), blockp(W2 << (S - 3));
+                static bool attr = false;
+                if (!attr) {
+                    cudaFuncSetAttribute(k_fwd_col2p<S, W2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+                    cudaFuncSetAttribute(k_fwd_col2p<S, W2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+                    attr = true;
+                }
+                if (n2 == (1 << S)) k_fwd_col2p<S, W2, true><<<gridp, blockp, SMEM, st>>>(c, dst, dst_gs, limb_ids, ng);
+                else k_fwd_col2p<S, W2, false><<<gridp, blockp, SMEM, st>>>(c, dst, dst_gs, limb_ids, ng);
+                return;
+            }
+#endif
             dim3 grid2(n2 / (2 * W2), ny, ng), block2(W2 << (S - 3));
             if (n2 == (1 << S)) k_fwd_col2<S, W2, true><<<grid2, block2, 0, st>>>(c, dst, dst_gs, limb_ids);
             else k_fwd_col2<S, W2, false><<<grid2, block2, 0, st>>>(c, dst, dst_gs, limb_ids);
