@@ -1,7 +1,8 @@
 // multi_gpu_selftest -- a plain C++ host (no Python, no torch) aggregating over several GPUs through the C ABI alone:
 // one thread per device, clients sharded round-robin (SURVEY.md 8 row e), every rank calls
 // ppq_reencrypt_aggregate_host_ranks (local ppq_agg_* + ONE ncclReduce + mod q on the root), and the root's result is
-// compared bit for bit with the single-GPU aggregate of all clients.  NCCL comes from the system libnccl.so.2 (dlopen).
+// compared bit for bit with the single-GPU aggregate of all clients; a second pass does the same over PACKED host buffers
+// (ppq_reencrypt_aggregate_host_packed_ranks) with the shards ppq_plan_shards gives for unequal per-rank costs.  NCCL comes from the system libnccl.so.2 (dlopen).
 //
 //     multi_gpu_selftest [n_gpus] [n_clients] [n_slots] [logN] [depth]        exit 0 = identical
 #include <cuda_runtime.h>
@@ -69,38 +70,70 @@ int main(int argc, char** argv) {
         CK(ppq_reencrypt_aggregate_host(ctx[0], rk.data(), (int)ell, ptr.data(), (size_t)C, S, want.data()));
         for (auto* k : rk) ppq_rekey_destroy(k);
     }
-    // sharded: rank r owns clients {c : c % G == r}
-    uint8_t id[128];
-    CK(ppq_comm_unique_id(id));
-    std::vector<std::thread> th;
-    std::vector<int> rc(G, 0);
-    for (int r = 0; r < G; ++r)
-        th.emplace_back([&, r]() {
-            ppq_comm* comm = nullptr;
-            if (ppq_comm_init(ctx[r], G, r, id, &comm) != PPQ_OK) {
-                std::fprintf(stderr, "rank %d: ppq_comm_init: %s\n", r, ppq_last_error());
-                rc[r] = 1;
-                return;
-            }
-            std::vector<ppq_rekey*> rk;
-            std::vector<const uint64_t*> ptr;
-            for (int c = r; c < C; c += G) {
-                ppq_rekey* k = nullptr;
-                if (ppq_rekey_upload(ctx[r], kb[c].data(), ka[c].data(), &k) != PPQ_OK) rc[r] = 1;
-                rk.push_back(k);
-                ptr.push_back(cts[c].data());
-            }
-            if (ppq_reencrypt_aggregate_host_ranks(ctx[r], comm, 0, rk.data(), (int)ell, ptr.data(), rk.size(), S, r == 0 ? got.data() : nullptr) != PPQ_OK) {
-                std::fprintf(stderr, "rank %d: %s\n", r, ppq_last_error());
-                rc[r] = 1;
-            }
-            for (auto* k : rk) ppq_rekey_destroy(k);
-            ppq_comm_destroy(comm);
-        });
-    for (auto& t : th) t.join();
-    for (int r = 0; r < G; ++r)
-        if (rc[r]) return 1;
-    const bool same = std::memcmp(want.data(), got.data(), blk * sizeof(uint64_t)) == 0;
+    // pass 0: u64 host buffers, rank r owns clients {c : c % G == r}
+    // pass 1: PACKED host buffers (bitlen(q_i) bits per residue) and shards from ppq_plan_shards for ranks that copy at
+    //         different rates (contiguous blocks of counts[r] clients)
+    const size_t pw = ppq_packed_words(ctx[0], (int)ell);
+    std::vector<std::vector<uint64_t>> pk(C, std::vector<uint64_t>(pw * S));
+    for (int c = 0; c < C; ++c) CK(ppq_pack_host(ctx[0], (int)ell, cts[c].data(), pk[c].data(), S));
+    std::vector<double> cost(G);
+    for (int r = 0; r < G; ++r) cost[r] = 1.0 + 0.6 * (r % 2);
+    std::vector<size_t> counts(G);
+    CK(ppq_plan_shards((size_t)C, G, cost.data(), counts.data()));
+    bool all_same = true;
+    for (int pass = 0; pass < 2; ++pass) {
+        uint8_t id[128];
+        CK(ppq_comm_unique_id(id));
+        std::vector<std::thread> th;
+        std::vector<int> rc(G, 0);
+        std::vector<uint64_t> got_p(pw * S);
+        std::fill(got.begin(), got.end(), 0);
+        for (int r = 0; r < G; ++r)
+            th.emplace_back([&, r]() {
+                ppq_comm* comm = nullptr;
+                if (ppq_comm_init(ctx[r], G, r, id, &comm) != PPQ_OK) {
+                    std::fprintf(stderr, "rank %d: ppq_comm_init: %s\n", r, ppq_last_error());
+                    rc[r] = 1;
+                    return;
+                }
+                std::vector<int> mine;
+                if (pass == 0) {
+                    for (int c = r; c < C; c += G) mine.push_back(c);
+                } else {
+                    size_t first = 0;
+                    for (int q = 0; q < r; ++q) first += counts[q];
+                    for (size_t c = first; c < first + counts[r]; ++c) mine.push_back((int)c);
+                }
+                std::vector<ppq_rekey*> rk;
+                std::vector<const uint64_t*> ptr;
+                for (int c : mine) {
+                    ppq_rekey* k = nullptr;
+                    if (ppq_rekey_upload(ctx[r], kb[c].data(), ka[c].data(), &k) != PPQ_OK) rc[r] = 1;
+                    rk.push_back(k);
+                    ptr.push_back(pass == 0 ? cts[c].data() : pk[c].data());
+                }
+                const int e = pass == 0
+                                  ? ppq_reencrypt_aggregate_host_ranks(ctx[r], comm, 0, rk.data(), (int)ell, ptr.data(), rk.size(), S,
+                                                                       r == 0 ? got.data() : nullptr)
+                                  : ppq_reencrypt_aggregate_host_packed_ranks(ctx[r], comm, 0, rk.data(), (int)ell, ptr.data(),
+                                                                              rk.size(), S, r == 0 ? got_p.data() : nullptr);
+                if (e != PPQ_OK) {
+                    std::fprintf(stderr, "rank %d: %s\n", r, ppq_last_error());
+                    rc[r] = 1;
+                }
+                for (auto* k : rk) ppq_rekey_destroy(k);
+                ppq_comm_destroy(comm);
+            });
+        for (auto& t : th) t.join();
+        for (int r = 0; r < G; ++r)
+            if (rc[r]) return 1;
+        if (pass == 1) CK(ppq_unpack_host(ctx[0], (int)ell, got_p.data(), got.data(), S));
+        const bool ok = std::memcmp(want.data(), got.data(), blk * sizeof(uint64_t)) == 0;
+        std::printf("multi_gpu_selftest: pass %d (%s): %s\n", pass,
+                    pass == 0 ? "u64 buffers, round-robin shards" : "packed buffers, planned shards", ok ? "identical" : "MISMATCH");
+        all_same = all_same && ok;
+    }
+    const bool same = all_same;
     std::printf("multi_gpu_selftest: %d GPUs, %d clients x %zu cts, N=2^%d, %zu limbs: %s\n", G, C, S, info.logN, ell,
                 same ? "IDENTICAL to the single-GPU aggregate" : "MISMATCH");
     for (auto* c : ctx) ppq_ctx_destroy(c);
