@@ -1446,8 +1446,11 @@ static int agg_add_batch(ppq_agg* a, const ppq_rekey* const* rks, const uint64_t
     const size_t ext_gs = (size_t)2 * K * N, ring_stride = n * ext_gs;
     u64* extp = a->ring.p + (size_t)a->in_group * ring_stride;
     prof_mark(c, st, -1);
-    for (int cl = 0; cl < nb; ++cl)
-        launch_inv_row(c->k, (const u64*)ins[cl] + (size_t)ell * N, ct, y + (size_t)cl * n * ys, ys, p->c1_limb.p, ell, (int)n, st);
+    {   // c1 of the nb clients of this pass (separate input buffers) in one launch
+        const u64* c1s[4] = {nullptr, nullptr, nullptr, nullptr};
+        for (int cl = 0; cl < nb; ++cl) c1s[cl] = (const u64*)ins[cl] + (size_t)ell * N;
+        launch_inv_row_multi(c->k, c1s, nb, (int)n, ct, y, ys, p->c1_limb.p, ell, st);
+    }
     prof_mark(c, st, 0);
     launch_inv_col(c->k, y, ys, p->c1_limb.p, p->c1_scale.p, ell, (int)ng, st);
     prof_mark(c, st, 1);

@@ -733,9 +733,21 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB
     }
 }
 
+// Source of an inverse ROW pass: ciphertext g of the launch is ciphertext g % n_per of buffer g / n_per (the clients of an
+// aggregation pass live in separate buffers; one launch covers them all instead of one launch per client, which at
+// N = 2^14 were 20 us launches of 8 us of work)
+struct InvSrc {
+    const u64* in[4];
+    u32 n_per;
+    __device__ __forceinline__ const u64* at(u32 g, size_t gs) const {
+        const u32 b = g / n_per;
+        const u64* base = b == 0 ? in[0] : b == 1 ? in[1] : b == 2 ? in[2] : in[3];  // selects, not an indexed local copy
+        return base + (size_t)(g - b * n_per) * gs;
+    }
+};
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB)
-    k_inv_row(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs,
+    k_inv_row(KCtx c, const InvSrc src, size_t in_gs, u64* out, size_t out_gs,
               const int* __restrict__ limb_map, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[G::SMEM];
@@ -751,7 +763,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB
     const u32 gend = min((u32)n_g, (blockIdx.y + 1) * PPQ_ROW_GPC);
     for (u32 g = blockIdx.y * PPQ_ROW_GPC; g < gend; ++g) {
     u64 a[8];
-    ld8(a, in + g * in_gs + off + 8 * u);
+    ld8(a, src.at(g, in_gs) + off + 8 * u);
     inv_pass<S, RowPos<S>, INV_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, PPQ_ROW_GPC > 1);
     u64* o = out + g * out_gs + off;
 #pragma unroll
@@ -797,7 +809,7 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB
 #endif
 template <int S>
 __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_INV_X2_MINB)
-    k_inv_row2(KCtx c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* __restrict__ limb_map, int n_g) {
+    k_inv_row2(KCtx c, const InvSrc src, size_t in_gs, u64* out, size_t out_gs, const int* __restrict__ limb_map, int n_g) {
     typedef RowGeom<S> G;
     __shared__ u64 sm[2 * G::SMEM];
     const u32 N = 1u << c.logN, n2 = 1u << S, n1 = N >> S;
@@ -813,8 +825,8 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, PPQ_INV_X2_MINB)
     for (u32 g = blockIdx.y * (2 * PPQ_ROW_X2_PAIRS); g < gend; g += 2) {
         const u32 g1 = g + 1 < gend ? g + 1 : g;  // an odd tail is paired with itself (read twice, written twice)
         u64 a[8], b[8];
-        ld8(a, in + g * in_gs + off + 8 * u);
-        ld8(b, in + g1 * in_gs + off + 8 * u);
+        ld8(a, src.at(g, in_gs) + off + 8 * u);
+        ld8(b, src.at(g1, in_gs) + off + 8 * u);
         inv_pass_x2<S, RowPos<S>, INV_ROW_IN>(a, b, sm, (u32)G::SMEM, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, true);
         u64* o0 = out + g * out_gs + off;
         u64* o1 = out + g1 * out_gs + off;
@@ -1865,20 +1877,30 @@ void launch_fwd_row_plain(const KCtx& c, u64* data, size_t gs, const int* d_limb
                                 c, data, gs, d_limb_ids, n_g)));
 }
 
-void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
-                    int n_slots, int n_g, cudaStream_t st) {
+static void inv_row_launch(const KCtx& c, const InvSrc& src, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
+                           int n_slots, int n_g, cudaStream_t st) {
     count_launch();
     const Split sp = split_of(c.logN);
     const int n1 = 1 << sp.S1;
 #if PPQ_INV_X2
     if (n_g > 1 && c.logN >= PPQ_X2_MIN_LOGN) {
         const int by = (n_g + 2 * PPQ_ROW_X2_PAIRS - 1) / (2 * PPQ_ROW_X2_PAIRS);
-        PPQ_ROW_DISPATCH(sp.S2, (k_inv_row2<S><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, in, in_gs, out, out_gs, d_limb_map, n_g)));
+        PPQ_ROW_DISPATCH(sp.S2, (k_inv_row2<S><<<dim3(n1 / RowGeom<S>::R, by, n_slots), RowGeom<S>::THREADS, 0, st>>>(c, src, in_gs, out, out_gs, d_limb_map, n_g)));
         return;
     }
 #endif
     PPQ_ROW_DISPATCH(sp.S2, (k_inv_row<S><<<dim3(n1 / RowGeom<S>::R, gpc_blocks(n_g), n_slots), RowGeom<S>::THREADS, 0, st>>>(
-                                c, in, in_gs, out, out_gs, d_limb_map, n_g)));
+                                c, src, in_gs, out, out_gs, d_limb_map, n_g)));
+}
+void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
+                    int n_slots, int n_g, cudaStream_t st) {
+    InvSrc src{{in, in, in, in}, 0x7fffffffu};
+    inv_row_launch(c, src, in_gs, out, out_gs, d_limb_map, n_slots, n_g, st);
+}
+void launch_inv_row_multi(const KCtx& c, const u64* const* ins, int n_in, int n_per, size_t in_gs, u64* out, size_t out_gs,
+                          const int* d_limb_map, int n_slots, cudaStream_t st) {
+    InvSrc src{{ins[0], ins[n_in > 1 ? 1 : 0], ins[n_in > 2 ? 2 : 0], ins[n_in > 3 ? 3 : 0]}, (u32)n_per};
+    inv_row_launch(c, src, in_gs, out, out_gs, d_limb_map, n_slots, n_in * n_per, st);
 }
 void launch_decrypt_inv_ntt(const KCtx& c, const u64* ct, const u64* sk, u64* out, int ell, size_t n_ct,
                             const int* d_cyc_ids, const u64* d_scale4, cudaStream_t st) {

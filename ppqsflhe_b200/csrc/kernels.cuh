@@ -40,6 +40,10 @@ void launch_ntt_inverse(const KCtx& c, u64* data, const int* d_limb_ids, const u
 // row pass and column pass are separate launches; `tmp` may alias `out`.
 void launch_inv_row(const KCtx& c, const u64* in, size_t in_gs, u64* out, size_t out_gs, const int* d_limb_map,
                     int n_slots, int n_g, cudaStream_t st);
+// the same over n_in <= 4 source buffers of n_per ciphertexts each in ONE launch: ciphertext g of the launch is
+// ciphertext g % n_per of ins[g / n_per]; out is contiguous over all n_in * n_per ciphertexts
+void launch_inv_row_multi(const KCtx& c, const u64* const* ins, int n_in, int n_per, size_t in_gs, u64* out, size_t out_gs,
+                          const int* d_limb_map, int n_slots, cudaStream_t st);
 void launch_inv_col(const KCtx& c, u64* data, size_t gs, const int* d_limb_map, const u64* d_scale4, int n_slots,
                     int n_g, cudaStream_t st);
 
