@@ -1246,7 +1246,7 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
     if (it == c->garner.end()) {
         // Garner constants, once per ell: ginv[i] = (q_0..q_{i-1})^-1 mod q_i, then the table q_k mod q_i
         // ... and q_0 q_1 q_2 mod q_i for the short interpolation's check
-        std::vector<u64> g((size_t)ell + (size_t)ell * ell + (size_t)ell, 0);
+        std::vector<u64> g((size_t)ell + (size_t)ell * ell + 2 * (size_t)ell, 0);
         for (int i = 1; i < ell; ++i) {
             u64 pr = 1;
             for (int k = 0; k < i; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
@@ -1258,6 +1258,8 @@ extern "C" int ppq_decode(ppq_ctx* c, int ell, const uint64_t* coeff, double sf,
             u64 pr = 1;
             for (int k = 0; k < 3; ++k) pr = host::mulmod(pr, c->hp.mod[k] % c->hp.mod[i], c->hp.mod[i]);
             g[(size_t)ell + (size_t)ell * ell + i] = pr;
+            g[(size_t)ell + (size_t)ell * ell + ell + i] =
+                host::mulmod(c->hp.mod[0] % c->hp.mod[i], c->hp.mod[1] % c->hp.mod[i], c->hp.mod[i]);
         }
         std::unique_ptr<DevBuf<u64>> b(new DevBuf<u64>);
         CU(b->upload(g));

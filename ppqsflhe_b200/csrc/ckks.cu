@@ -232,6 +232,7 @@ __device__ __noinline__ double crt_full(const KCtx& c, const u64* __restrict__ x
 // 3 + 2 (ell - 3) Barrett steps per coefficient instead of ell (ell - 1) / 2; a coefficient that fails the check (it
 // never does for a decryption of a valid ciphertext) takes the full path.
 constexpr int CRT_FAST = 3;
+static_assert(CRT_FAST == 3, "the check below is written for three digits");
 __global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell, const u64* __restrict__ ginv,
                                  const u64* __restrict__ qmod, const u64* __restrict__ p3mod, double sf,
                                  double2* __restrict__ z) {
@@ -251,13 +252,10 @@ __global__ void k_crt_to_complex(KCtx c, const u64* __restrict__ coeff, int ell,
             bool ok = true;
             for (int i = CRT_FAST; i < ell; ++i) {
                 const LimbC li = c.limbs[i];
-                const u64* qm = qmod + (size_t)i * ell;
-                u64 acc = 0;
-#pragma unroll
-                for (int k = CRT_FAST - 1; k >= 0; --k) {
-                    unsigned __int128 t = (unsigned __int128)acc * qm[k] + v[k];
-                    acc = barrett128((u64)(t >> 64), (u64)t, li);
-                }
+                // Y' mod q_i = v_0 + v_1 (q_0 mod q_i) + v_2 (q_0 q_1 mod q_i): two 120-bit products and v_0 in one 128-bit
+                // sum (< 2^122), ONE Barrett reduction
+                const unsigned __int128 t = (unsigned __int128)v[1] * qmod[(size_t)i * ell] + (unsigned __int128)v[2] * p3mod[ell + i] + v[0];
+                u64 acc = barrett128((u64)(t >> 64), (u64)t, li);
                 if (neg) acc = submod(acc, p3mod[i], li.q);  // y = Y' - P3
                 ok &= acc == x[(size_t)i * N];
             }

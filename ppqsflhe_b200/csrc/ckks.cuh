@@ -26,7 +26,7 @@ void launch_encode_fft(const Tables& t, const double* d_vals, size_t n_vals, dou
                        size_t n, cudaStream_t st);
 // coeff [n][ell][N] canonical COEFF residues -> vals [n][N/2]
 // d_ginv [ell]: (q_0..q_{i-1})^-1 mod q_i; d_qmod [ell][ell]: q_k mod q_i (Garner's mixed-radix constants)
-// d_p3mod [ell]: q_0 q_1 q_2 mod q_i (the short interpolation's check, ckks.cu)
+// d_p3mod [2][ell]: q_0 q_1 q_2 mod q_i, then q_0 q_1 mod q_i (the short interpolation's check, ckks.cu)
 void launch_decode(const Tables& t, const KCtx& k, const u64* coeff, int ell, const u64* d_ginv, const u64* d_qmod,
                    const u64* d_p3mod, double sf, double2* z, double* d_vals, size_t n, cudaStream_t st);
 }  // namespace ckks
