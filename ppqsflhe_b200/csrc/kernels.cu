@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(W << (S - 3), S == 9 ? PPQ_COL9_MINB : (MODE =
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const long long v = reinterpret_cast<const long long*>(in)[(size_t)point_of<S - 3>(u, k) * n2 + col];
-            const u64 m = reduce64(v < 0 ? (u64)(-v) : (u64)v, lc);
+            const u64 av = v < 0 ? (u64)(-v) : (u64)v;
+            const u64 m = av < lc.q ? av : reduce64(av, lc);  // samples are a few bits wide: no reduction (warp-uniform)
             a[k] = (v < 0 && m != 0) ? lc.q - m : m;
         }
         // fused encode + encrypt (ppq_encode_encrypt): slot 1 (e0) also receives the encoded plaintext coefficients
