@@ -262,6 +262,57 @@ __global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
 }
 #endif
 
+// The two-column forward COL pass with the small-coefficient prologue of k_fwd_col<MODE 3> (signed samples -> residues,
+// the encoded plaintext joining slot 1): what Encrypt / KeyGen / ReKeyGen run on their sampled polynomials at n1 = 256.
+template <int S, int W2, bool SAME>
+__global__ void __launch_bounds__(W2 << (S - 3), PPQ_COL2_MINB)
+    k_fwd_col2_small(KCtx c, const long long* __restrict__ small, u32 n_small, u64* __restrict__ out, size_t gs, u32 ell,
+                     const long long* __restrict__ pt_coeff, u32 approx) {
+    __shared__ u64 sm[2 * (W2 << S)];
+    constexpr u32 n2 = 1u << (SAME ? S : S - 1), N = n2 << S;
+    const u32 w = threadIdx.x % W2, u = threadIdx.x / W2;
+    const u32 col = (blockIdx.x * W2 + w) * 2;
+    const u32 y = blockIdx.y, g = blockIdx.z;
+    const u32 limb = y % ell, slot = y / ell;
+    const LimbC lc = c.limbs[limb];
+    const ulonglong2* tw = c.twf + (size_t)limb * N;
+    const long long* in = small + ((size_t)g * n_small + slot) * N + col;
+    auto res = [&](long long v) {
+        const u64 av = v < 0 ? (u64)(-v) : (u64)v;
+        const u64 m = av < lc.q ? av : reduce64(av, lc);
+        return (v < 0 && m != 0) ? lc.q - m : m;
+    };
+    u64 a[8], b[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const longlong2 v = *reinterpret_cast<const longlong2*>(in + (size_t)point_of<S - 3>(u, k) * n2);
+        a[k] = res(v.x);
+        b[k] = res(v.y);
+    }
+    if (pt_coeff != nullptr && slot == 1u) {  // block-uniform: m * 2^approx joins e0 before the transform
+        const long long* co = pt_coeff + (size_t)g * N + col;
+        const u64 f = reduce64(1ull << approx, lc);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const longlong2 v = *reinterpret_cast<const longlong2*>(co + (size_t)point_of<S - 3>(u, k) * n2);
+            u64 mx = res(v.x), my = res(v.y);
+            if (approx) {
+                mx = mulmod_barrett(mx, f, lc);
+                my = mulmod_barrett(my, f, lc);
+            }
+            a[k] = addmod(a[k], mx, lc.q);
+            b[k] = addmod(b[k], my, lc.q);
+        }
+    }
+    fwd_pass_col2<S, W2, FWD_COL_IN>(a, b, sm, w, u, tw, lc.q, lc.q2 << 1, PPQ_Z(lc));
+    u64* p = out + (size_t)g * gs + (size_t)y * N + col;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {  // lazy (< 16q): consumed by a ROW pass
+        p[(size_t)(8 * u + k) * n2] = a[k];
+        p[(size_t)(8 * u + k) * n2 + 1] = b[k];
+    }
+}
+
 template <int S, int W, bool SAME>
 __global__ void __launch_bounds__(W << (S - 3), S == 9 ? PPQ_COL9_MINB : PPQ_COL_MINB)
     k_inv_col(KCtx c, u64* __restrict__ data, size_t gs, const int* __restrict__ limb_map,
@@ -1786,6 +1837,16 @@ static void fwd_col_launch(const KCtx& c, const u64* src, size_t src_gs, u64* ds
     constexpr int W = ColW<S>::W;
     const int n2 = (1 << c.logN) >> S;
 #if PPQ_COL2
+    if constexpr (MODE == 3 && S == 8) {
+        constexpr int W2 = PPQ_COL2_W;
+        dim3 grid2(n2 / (2 * W2), ny, ng), block2(W2 << (S - 3));
+        const u32 ell = (u32)q_src, approx = (u32)(q_src >> 32);
+        const long long* sm_in = reinterpret_cast<const long long*>(src);
+        const long long* co = reinterpret_cast<const long long*>(chat);
+        if (n2 == (1 << S)) k_fwd_col2_small<S, W2, true><<<grid2, block2, 0, st>>>(c, sm_in, (u32)src_gs, dst, dst_gs, ell, co, approx);
+        else k_fwd_col2_small<S, W2, false><<<grid2, block2, 0, st>>>(c, sm_in, (u32)src_gs, dst, dst_gs, ell, co, approx);
+        return;
+    }
     if constexpr (MODE == 0 && S == 8) {
         if (src == dst && src_gs == dst_gs) {
             constexpr int W2 = PPQ_COL2_W;
