@@ -745,7 +745,7 @@ def main():
     # ---- CPU baseline on rank 0, N = 1 only
     cpu = None
     if world == 1 and not args.no_cpu:
-        r = cpu_run(cfg, 1, 1)
+        r = cpu_run(cfg, 3, 1)  # >= 3 repetitions, median (about 1.3 s each at C3 on 16 threads)
         cpu = {k: v for k, v in r.items() if not k.startswith("_") and k != "ms_per_step"}
 
     if rank == 0:
