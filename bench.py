@@ -460,6 +460,45 @@ def client_leg(torch, name, n_ct):
         torch.cuda.empty_cache()
 
 
+def round_tail_leg(torch, name="c3", n_keys=8):
+    """What a round does with the aggregate: cc->EvalMult(sum, 1/C) with its rescale
+    (server/src/aggregateEncryptedWeights.cpp:83,92,107) and the fan-out of the result to the other key domains
+    (orchestration/server_fns.sh:76-80: ppq_reencrypt_fanout, ModUp shared over the keys), device-resident."""
+    from ppqsflhe_b200 import CiphertextBatch, CryptoContext, CtMeta, EvalKey
+    cfg = CONFIGS[name]
+    dev_i = torch.cuda.current_device()
+    cc = CryptoContext.synthetic(cfg["logN"], cfg["depth"], cfg["first"], cfg["scale"], cfg["extra"], cfg["dnum"], dev_i)
+    try:
+        dev, ell, M, N, n = cc.device, cc.L, cc.M, cc.N, cfg["slots"]
+        qv = torch.from_numpy(cc.moduli.astype(np.int64)).to(dev)
+        agg = CiphertextBatch(_rand_res(torch, dev, (n, 2, ell, N), qv[:ell].view(1, 1, ell, 1)),
+                              CtMeta(noise_scale_deg=2, level=0, scaling_factor=cc.sf_big(0)))
+        keys = [EvalKey(cc, _rand_res(torch, dev, (cc.dnum, M, N), qv.view(1, M, 1)),
+                        _rand_res(torch, dev, (cc.dnum, M, N), qv.view(1, M, 1))) for _ in range(n_keys)]
+
+        def t(fn, reps=3):
+            r = fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                r = fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / reps, r
+
+        ms_mul, scaled = t(lambda: cc.EvalMult(agg, 1.0 / cfg["clients"]))
+        ms_fan, outs = t(lambda: cc.ReEncryptFanOut(scaled, keys))
+        return {"workload": cfg["desc"], "cts": n, "limbs_in": ell, "limbs_out": scaled.ell, "keys": n_keys,
+                "eval_mult_rescale": {"us_per_ct": ms_mul * 1e3 / n, "cts_per_s": n / (ms_mul * 1e-3),
+                                      "api": "ppq_eval_mult_const (rescale + constant)"},
+                "fanout": {"us_per_ct_key": ms_fan * 1e3 / (n * n_keys), "ct_keys_per_s": n * n_keys / (ms_fan * 1e-3),
+                           "api": "ppq_reencrypt_fanout"}}
+    finally:
+        cc.close()
+        torch.cuda.empty_cache()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -741,6 +780,10 @@ def main():
             except Exception as e:
                 client[name] = {"error": repr(e)}
         extras["client"] = client
+        try:
+            extras["round_tail"] = round_tail_leg(torch)
+        except Exception as e:
+            extras["round_tail"] = {"error": repr(e)}
 
     # ---- CPU baseline on rank 0, N = 1 only
     cpu = None
@@ -764,6 +807,7 @@ def main():
             "roofline": roofline, "ntt": ntt, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks,
             "configs": {k: v for k, v in extras.items() if k in ("c1", "c2", "c3", "c4")},
             "c5_ntt_sweep": extras.get("c5_ntt_sweep"), "client": extras.get("client"),
+            "round_tail": extras.get("round_tail"),
         }
         print(json.dumps(line), flush=True)
     if comm is not None:
