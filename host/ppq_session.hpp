@@ -76,7 +76,12 @@ struct HostPool {
         }
         void* q = nullptr;
         const size_t cap = bytes ? bytes : 1;
-        if (cudaHostAlloc(&q, cap, cudaHostAllocDefault) != cudaSuccess) throw std::bad_alloc();
+        if (cudaHostAlloc(&q, cap, cudaHostAllocDefault) != cudaSuccess) {
+            (void)cudaGetLastError();  // no pinned memory left: a pageable block works too, only slower to copy
+            q = std::malloc(cap);
+            if (!q) throw std::bad_alloc();
+            return q;                  // not in `live`: give() frees it
+        }
         live[q] = cap;
         return q;
     }
