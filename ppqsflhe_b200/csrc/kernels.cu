@@ -844,8 +844,9 @@ __global__ void __launch_bounds__(RowGeom<S>::THREADS, S == 6 ? 5 : PPQ_ROW_MINB
     ld8(c1, ct + ((g * 2 + 1) * ell + i) * N + roff + 8 * u);
     ld8_ro(s, sk + (size_t)i * N + roff + 8 * u);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = addmod(a[k], mulmod_barrett(c1[k], s[k], lc), lc.q);
-    inv_pass<S, RowPos<S>, INV_ROW_IN>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
+    for (int k = 0; k < 8; ++k)  // c0 (< q) + the product left in [0, 3q): the pass is told its input is below 4q
+        a[k] += barrett128_lazy3(__umul64hi(c1[k], s[k]), c1[k] * s[k], lc);
+    inv_pass<S, RowPos<S>, 4>(a, sm, pos, u, tw, n1 + row, lc.q, lc.q2 << 1, false);
     u64* o = out + (g * ell + i) * N + roff;
 #pragma unroll
     for (int k = 0; k < 8; ++k) o[point_of<S - 3>(u, k)] = a[k];  // lazy (< 8q): consumed by k_inv_col
