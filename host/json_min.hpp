@@ -30,6 +30,12 @@ struct Value {
     std::string s;                                   // String payload or Number source text
     std::vector<Ptr> arr;
     std::vector<std::pair<std::string, Ptr>> obj;    // insertion order (cereal JSON relies on order)
+    // parse_lazy only: a long array of unsigned integers (the residues of a key file: 16384 numbers per limb, 27 MB per
+    // re-encryption key) is kept as its source text [raw_b, raw_e) instead of one node per number; the text must outlive
+    // the tree.  numbers_to() converts it; arr stays empty.
+    const char* raw_b = nullptr;
+    const char* raw_e = nullptr;
+    size_t raw_n = 0;
 
     bool is_object() const { return kind == Object; }
     bool is_array() const { return kind == Array; }
@@ -48,10 +54,31 @@ struct Value {
         return *v;
     }
     const Value& at(size_t i) const {
+        if (kind == Array && raw_b) throw std::runtime_error("JSON: element access into a lazily held numeric array");
         if (kind != Array || i >= arr.size()) throw std::runtime_error("JSON: array index out of range");
         return *arr[i];
     }
-    size_t size() const { return kind == Array ? arr.size() : kind == Object ? obj.size() : 0; }
+    size_t size() const { return kind == Array ? (raw_b ? raw_n : arr.size()) : kind == Object ? obj.size() : 0; }
+    // every element of an array of unsigned integers, whichever way it is held
+    void numbers_to(uint64_t* out) const {
+        if (kind != Array) throw std::runtime_error("JSON: not an array");
+        if (!raw_b) {
+            for (size_t i = 0; i < arr.size(); ++i) out[i] = arr[i]->as_u64();
+            return;
+        }
+        size_t n = 0;
+        for (const char* p = raw_b; p < raw_e;) {
+            const unsigned d = (unsigned char)*p - '0';
+            if (d > 9) {
+                ++p;
+                continue;
+            }
+            uint64_t v = 0;
+            for (; p < raw_e && (unsigned)((unsigned char)*p - '0') <= 9; ++p) v = v * 10 + ((unsigned char)*p - '0');
+            out[n++] = v;
+        }
+        if (n != raw_n) throw std::runtime_error("JSON: numeric array changed under the tree");
+    }
     uint64_t as_u64() const {
         if (kind == String || kind == Number) return std::strtoull(s.c_str(), nullptr, 10);
         throw std::runtime_error("JSON: not a number");
@@ -104,7 +131,7 @@ inline void set(Ptr& o, const std::string& key, Ptr v) {
 
 class Parser {
   public:
-    Parser(const char* p, size_t n) : p_(p), e_(p + n) {}
+    Parser(const char* p, size_t n, bool lazy = false) : p_(p), e_(p + n), lazy_(lazy) {}
     Ptr parse() {
         Ptr v = value();
         ws();
@@ -115,6 +142,7 @@ class Parser {
   private:
     const char* p_;
     const char* e_;
+    bool lazy_ = false;
     [[noreturn]] void fail(const char* m) { throw std::runtime_error(std::string("JSON parse error: ") + m); }
     void ws() {
         while (p_ < e_ && (*p_ == ' ' || *p_ == '\n' || *p_ == '\t' || *p_ == '\r')) ++p_;
@@ -189,6 +217,37 @@ class Parser {
         Ptr v = make(Value::Array);
         ws();
         if (p_ < e_ && *p_ == ']') { ++p_; return v; }
+        if (lazy_ && p_ < e_ && (unsigned)((unsigned char)*p_ - '0') <= 9) {
+            // digits, commas and white space up to the closing bracket: an array of unsigned integers.  One branch-free
+            // pass classifies the bytes and counts the commas; numbers_to() checks the element count again
+            const char* s = p_;
+            const char* q = static_cast<const char*>(std::memchr(s, ']', (size_t)(e_ - s)));
+            if (q) {
+                static const struct Cls {
+                    unsigned char t[256];
+                    Cls() {
+                        for (int i = 0; i < 256; ++i) t[i] = 2;  // anything else
+                        for (int i = '0'; i <= '9'; ++i) t[i] = 0;
+                        t[(unsigned char)' '] = t[(unsigned char)'\n'] = t[(unsigned char)'\t'] = t[(unsigned char)'\r'] = 0;
+                        t[(unsigned char)','] = 1;
+                    }
+                } cls;
+                size_t commas = 0;
+                unsigned bad = 0;
+                for (const char* r = s; r < q; ++r) {
+                    const unsigned char c = cls.t[(unsigned char)*r];
+                    commas += c & 1u;
+                    bad |= c & 2u;
+                }
+                if (!bad && commas + 1 >= 64) {
+                    v->raw_b = s;
+                    v->raw_e = q;
+                    v->raw_n = commas + 1;
+                    p_ = q + 1;
+                    return v;
+                }
+            }
+        }
         for (;;) {
             v->arr.push_back(value());
             ws();
@@ -221,6 +280,8 @@ class Parser {
 };
 
 inline Ptr parse(const std::string& text) { return Parser(text.data(), text.size()).parse(); }
+// the same with long arrays of unsigned integers held as text spans (Value::raw_b): `text` must outlive the tree
+inline Ptr parse_lazy(const std::string& text) { return Parser(text.data(), text.size(), true).parse(); }
 
 inline void escape_to(std::string& out, const std::string& s) {
     out += '"';
@@ -268,6 +329,12 @@ inline void dump_to(std::string& out, const Value& v, int indent, int cur, bool 
         case Value::Number: out += v.s; break;
         case Value::String: escape_to(out, v.s); break;
         case Value::Array: {
+            if (v.raw_b) {  // lazily held numbers: their source text, whatever its layout
+                out += '[';
+                out.append(v.raw_b, v.raw_e);
+                out += ']';
+                break;
+            }
             if (v.arr.empty()) { out += "[]"; break; }
             out += "[\n";
             for (size_t i = 0; i < v.arr.size(); ++i) {

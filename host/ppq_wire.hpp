@@ -433,7 +433,7 @@ inline Poly read_dcrtpoly(const jmin::Value& v) {
         const jmin::Value& d = np->at("v").at("ptr_wrapper").at("data");
         const jmin::Value& vals = d.at("v");
         std::vector<uint64_t> limb(vals.size());
-        for (size_t i = 0; i < limb.size(); ++i) limb[i] = vals.arr[i]->as_u64();
+        vals.numbers_to(limb.data());
         p.moduli.push_back(d.at("m").at("v").as_u64());
         p.limbs.push_back(std::move(limb));
     }
@@ -470,14 +470,14 @@ inline const jmin::Value* find_member_any(const jmin::Value& v, const std::strin
 }
 // PrivateKeyImpl: member "s" (client/src/keyGen.cpp:46 writes it; decryptModelWeights.cpp:49-54 reads it)
 inline Poly read_private_key(const std::string& text) {
-    jmin::Ptr root = jmin::parse(text);
+    jmin::Ptr root = jmin::parse_lazy(text);
     const jmin::Value* s = find_member(*root, "s");
     if (!s) throw std::runtime_error("private key file: no member \"s\"");
     return read_dcrtpoly(*s);
 }
 // PublicKeyImpl: member "h" = [b, a] (keyGen.cpp:41; encryptModelWeights.cpp:44-48)
 inline std::vector<Poly> read_public_key(const std::string& text) {
-    jmin::Ptr root = jmin::parse(text);
+    jmin::Ptr root = jmin::parse_lazy(text);
     const jmin::Value* h = find_member(*root, "h");
     if (!h || !h->is_array() || h->size() != 2) throw std::runtime_error("public key file: no member \"h\" with two elements");
     return {read_dcrtpoly(h->at(0)), read_dcrtpoly(h->at(1))};
@@ -488,7 +488,7 @@ struct EvalKeyPolys {
     std::vector<Poly> a, b;
 };
 inline EvalKeyPolys read_eval_key(const std::string& text) {
-    jmin::Ptr root = jmin::parse(text);
+    jmin::Ptr root = jmin::parse_lazy(text);
     const jmin::Value* k = find_member(*root, "k");
     if (!k || !k->is_array() || k->size() != 2) throw std::runtime_error("re-encryption key file: no member \"k\" with two vectors");
     EvalKeyPolys out;
@@ -531,7 +531,7 @@ inline jmin::Ptr dcrtpoly_to_json(const Poly& p) {
 
 // CryptoObject::keyTag of a key file ("kt" as a STRING; the "kt" inside the embedded context is the scheme object)
 inline std::string read_key_tag(const std::string& text) {
-    jmin::Ptr root = jmin::parse(text);
+    jmin::Ptr root = jmin::parse_lazy(text);
     std::string tag;
     std::vector<const jmin::Value*> stack{root.get()};
     while (!stack.empty() && tag.empty()) {

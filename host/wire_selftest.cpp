@@ -302,6 +302,33 @@ static int t_json() {
         CHECK(wire::slurp(path) == jmin::dump(*empty, 2) + "\n");
         std::remove(path.c_str());
     }
+    {   // parse_lazy: long arrays of unsigned integers are held as text spans, everything else as usual
+        std::string big = "{\"v\": [", mixed = "[", shortv = "[";
+        std::vector<uint64_t> want;
+        for (int i = 0; i < 300; ++i) {
+            const uint64_t x = 18446744073709551615ull - (uint64_t)i * 1234567891234567ull;
+            want.push_back(x);
+            big += (i ? ",\n      " : "") + std::to_string(x);
+            mixed += (i ? ", " : "") + std::to_string(i);
+        }
+        big += "], \"m\": 7}";
+        mixed += ", \"x\"]";
+        for (int i = 0; i < 10; ++i) shortv += (i ? "," : "") + std::to_string(i);
+        shortv += "]";
+        jmin::Ptr a = jmin::parse_lazy(big), g = jmin::parse(big);
+        CHECK(a->at("v").raw_b != nullptr && a->at("v").size() == 300 && g->at("v").raw_b == nullptr && g->at("v").size() == 300);
+        std::vector<uint64_t> got(300), got2(300);
+        a->at("v").numbers_to(got.data());
+        g->at("v").numbers_to(got2.data());
+        CHECK(got == want && got2 == want && a->at("m").as_u64() == 7);
+        CHECK(jmin::dump(*jmin::parse(jmin::dump(*a, 0)), 0) == jmin::dump(*g, 0));
+        jmin::Ptr mx = jmin::parse_lazy(mixed);
+        CHECK(mx->raw_b == nullptr && mx->size() == 301 && mx->at(300).as_string() == "x");
+        CHECK(jmin::parse_lazy(shortv)->raw_b == nullptr);
+        bool threw2 = false;
+        try { jmin::parse_lazy("[1,2,,3" + std::string(400, ',') + "4]")->numbers_to(got.data()); } catch (const std::exception&) { threw2 = true; }
+        CHECK(threw2);
+    }
     // DCRTPoly element layout round trip
     wire::Poly p;
     p.moduli = {97, 193};
